@@ -1,0 +1,125 @@
+"""ctypes loader of the CPU oracle (oracle/_build/liboracle.so).  TEST INFRASTRUCTURE ONLY.
+
+Allowed importers: tests/, __graft_entry__.smoke(), bench.py (cpu_baseline / --impl reference legs).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from ilqr_planner_b200 import cabi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_build", "liboracle.so")
+_lib = None
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "ilqr_oracle.cpp")
+    hdr = os.path.join(_HERE, "..", "include", "ilqrb.h")
+    if (not force and os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= max(os.path.getmtime(src), os.path.getmtime(hdr))):
+        return LIB_PATH
+    subprocess.check_call(["make", "-C", _HERE, "-B"], stdout=subprocess.DEVNULL)
+    return LIB_PATH
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    build()
+    lib = C.CDLL(LIB_PATH)
+    P = C.POINTER
+    lib.oracle_last_error.restype = C.c_char_p
+    lib.oracle_get_dims.argtypes = [P(cabi.ProblemDesc), P(cabi.Dims)]
+    lib.oracle_solve_recursive.argtypes = [P(cabi.ProblemDesc), cabi.c_double_p, P(cabi.SolveOpts), P(cabi.Result), C.c_int]
+    lib.oracle_solve_al.argtypes = [P(cabi.ProblemDesc), cabi.c_double_p, P(cabi.ALDesc), P(cabi.SolveOpts), P(cabi.Result), C.c_int]
+    lib.oracle_solve_batch.argtypes = [P(cabi.ProblemDesc), cabi.c_double_p, P(cabi.BatchDesc), P(cabi.SolveOpts), P(cabi.Result), C.c_int]
+    lib.oracle_rollout.argtypes = [P(cabi.ProblemDesc), cabi.c_double_p, cabi.c_double_p, cabi.c_double_p, cabi.c_double_p, cabi.c_double_p, C.c_int]
+    lib.oracle_kinematics.argtypes = [P(cabi.ProblemDesc), C.c_int, C.c_int] + [cabi.c_double_p] * 7
+    _lib = lib
+    return lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise RuntimeError("oracle error %d: %s" % (rc, load().oracle_last_error().decode()))
+
+
+def hardware_threads():
+    return int(load().oracle_hardware_threads())
+
+
+def solve_recursive(pb, U0, nb_iter, line_search=True, early_stop=False, threads=1):
+    from ilqr_planner_b200.problem import ResultBuffers
+    d = pb.to_desc()
+    out = ResultBuffers(pb, nb_iter, "recursive")
+    opts = cabi.SolveOpts(nb_iter, int(line_search), int(early_stop), 0)
+    U0 = None if U0 is None else np.ascontiguousarray(np.asarray(U0, dtype=np.float64).reshape(pb.batch, pb.horizon - 1, pb.m))
+    _check(load().oracle_solve_recursive(C.byref(d), cabi.dptr(U0), C.byref(opts), C.byref(out.res), threads))
+    return out
+
+
+def make_al_desc(pb, A, b, lambda0, lag_update_step, penalty, scaling_factor):
+    A = np.ascontiguousarray(np.asarray(A, dtype=np.float64))
+    b = np.ascontiguousarray(np.asarray(b, dtype=np.float64))
+    lam = np.ascontiguousarray(np.asarray(lambda0, dtype=np.float64))
+    per_step = 1 if A.ndim == 3 else 0
+    nc = A.shape[-2]
+    al = cabi.ALDesc(nc, per_step, cabi.dptr(A), cabi.dptr(b), cabi.dptr(lam), int(lag_update_step), 0, float(penalty), float(scaling_factor))
+    al._keep = (A, b, lam)
+    return al
+
+
+def solve_al(pb, U0, A, b, lambda0, nb_iter, lag_update_step, penalty, scaling_factor, line_search=True, early_stop=False, threads=1):
+    from ilqr_planner_b200.problem import ResultBuffers
+    d = pb.to_desc()
+    al = make_al_desc(pb, A, b, lambda0, lag_update_step, penalty, scaling_factor)
+    out = ResultBuffers(pb, nb_iter, "al", nc=al.nc)
+    opts = cabi.SolveOpts(nb_iter, int(line_search), int(early_stop), 0)
+    U0 = None if U0 is None else np.ascontiguousarray(np.asarray(U0, dtype=np.float64).reshape(pb.batch, pb.horizon - 1, pb.m))
+    _check(load().oracle_solve_al(C.byref(d), cabi.dptr(U0), C.byref(al), C.byref(opts), C.byref(out.res), threads))
+    return out
+
+
+def make_batch_desc(Q=None, psi=None):
+    Q = None if Q is None else np.ascontiguousarray(np.asarray(Q, dtype=np.float64))
+    psi = None if psi is None else np.ascontiguousarray(np.asarray(psi, dtype=np.float64))
+    bd = cabi.BatchDesc(cabi.dptr(Q), cabi.dptr(psi), 0 if psi is None else psi.shape[1], 0)
+    bd._keep = (Q, psi)
+    return bd
+
+
+def solve_batch(pb, u0, nb_iter, early_stop=False, Q=None, psi=None, threads=1):
+    from ilqr_planner_b200.problem import ResultBuffers
+    d = pb.to_desc()
+    bd = make_batch_desc(Q, psi)
+    out = ResultBuffers(pb, nb_iter, "batch")
+    opts = cabi.SolveOpts(nb_iter, 1, int(early_stop), 0)
+    u0 = None if u0 is None else np.ascontiguousarray(np.asarray(u0, dtype=np.float64).reshape(pb.batch, -1))
+    _check(load().oracle_solve_batch(C.byref(d), cabi.dptr(u0), C.byref(bd), C.byref(opts), C.byref(out.res), threads))
+    return out
+
+
+def rollout(pb, U, threads=1):
+    d = pb.to_desc()
+    B, H = pb.batch, pb.horizon
+    U = np.ascontiguousarray(np.asarray(U, dtype=np.float64).reshape(B, H - 1, pb.m))
+    X = np.empty((B, H, pb.n))
+    fX = np.empty((B, H, pb.nt))
+    J = np.empty((B, H, pb.r, pb.n))
+    cost = np.empty(B)
+    _check(load().oracle_rollout(C.byref(d), cabi.dptr(U), cabi.dptr(X), cabi.dptr(fX), cabi.dptr(J), cabi.dptr(cost), threads))
+    return X, fX, J, cost
+
+
+def kinematics(pb, robot, q, dq=None):
+    d = pb.to_desc()
+    dof = pb.robots[robot].dof
+    q = np.ascontiguousarray(np.asarray(q, dtype=np.float64).reshape(-1, dof))
+    nq = q.shape[0]
+    dq = np.zeros_like(q) if dq is None else np.ascontiguousarray(np.asarray(dq, dtype=np.float64).reshape(-1, dof))
+    x, quat, J, dx, w = np.zeros((nq, 3)), np.zeros((nq, 4)), np.zeros((nq, 6, dof)), np.zeros((nq, 3)), np.zeros((nq, 3))
+    _check(load().oracle_kinematics(C.byref(d), robot, nq, cabi.dptr(q), cabi.dptr(dq), cabi.dptr(x), cabi.dptr(quat), cabi.dptr(J), cabi.dptr(dx), cabi.dptr(w)))
+    return x, quat, J, dx, w
