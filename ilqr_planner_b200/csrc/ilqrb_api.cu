@@ -1,0 +1,809 @@
+// ilqrb_api.cu — C ABI of libilqrb.so (include/ilqrb.h): handle management, descriptor flattening, kernel
+// launch sequences of the four solvers, result download.  Host logic only orchestrates; all arithmetic of the
+// solve path runs in the CUDA kernels of recursive.cuh / batch.cuh.  There is no CPU fallback.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "batch.cuh"
+#include "recursive.cuh"
+
+using namespace ilqrb;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+
+#define CU(call)                                                                                              \
+    do {                                                                                                      \
+        cudaError_t e_ = (call);                                                                              \
+        if (e_ != cudaSuccess) return fail(ILQRB_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+enum ProfSlot { PS_ROLLOUT_INIT = 0, PS_KP_DERIVS, PS_BACKWARD, PS_LINESEARCH, PS_ACCEPT, PS_FINAL, PS_BATCH_FP, PS_BATCH_ASM, PS_BATCH_SYRK, PS_BATCH_CHOL, PS_BATCH_LS, PS_MISC };
+const char* kProfNames[ILQRB_PROF_SLOTS] = {"rollout_init", "kp_derivs",  "riccati_backward", "linesearch_rollout", "accept",     "final_fx",
+                                            "batch_fp",     "batch_assemble", "batch_syrk",    "batch_cholesky",     "batch_linesearch", "misc"};
+
+}  // namespace
+
+struct ilqrb_handle_s {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    DevProblem hp;          // host copy holding device pointers
+    DevProblem* dp = nullptr;
+    ilqrb_dims dims;
+    Work W;
+    std::vector<void*> allocs;
+    int cap_iter = 0;
+    int last_nb_iter = 0;
+    int last_solver = 0;  // 1 recursive, 2 al, 3 batch
+    double* d_fX = nullptr;
+    double* d_pack = nullptr;  // staging for packed downloads
+    size_t pack_elems = 0;
+    double* d_alA = nullptr;
+    double* d_alb = nullptr;
+    size_t alA_elems = 0, alb_elems = 0;
+    std::vector<double> h_lam0;
+    BatchWork BW;
+    // profiling
+    bool prof = false;
+    std::vector<cudaEvent_t> ev_pool;
+    struct Rec { int slot; cudaEvent_t a, b; };
+    std::vector<Rec> recs;
+    size_t ev_used = 0;
+    double prof_ms[ILQRB_PROF_SLOTS] = {0};
+    int64_t prof_n[ILQRB_PROF_SLOTS] = {0};
+    int64_t launches = 0;
+
+    template <class T>
+    int alloc(T** p, size_t count) {
+        void* q = nullptr;
+        cudaError_t e = cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T));
+        if (e != cudaSuccess) return fail(ILQRB_ENOMEM, std::string("cudaMalloc: ") + cudaGetErrorString(e));
+        allocs.push_back(q);
+        *p = (T*)q;
+        return 0;
+    }
+    cudaEvent_t ev() {
+        if (ev_used == ev_pool.size()) {
+            cudaEvent_t e;
+            cudaEventCreate(&e);
+            ev_pool.push_back(e);
+        }
+        return ev_pool[ev_used++];
+    }
+    void begin(int slot) {
+        launches++;
+        if (!prof) return;
+        Rec r{slot, ev(), ev()};
+        cudaEventRecord(r.a, stream);
+        recs.push_back(r);
+    }
+    void end() {
+        if (!prof) return;
+        cudaEventRecord(recs.back().b, stream);
+    }
+    void resolve() {
+        if (recs.empty()) return;
+        cudaStreamSynchronize(stream);
+        for (auto& r : recs) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, r.a, r.b);
+            prof_ms[r.slot] += ms;
+            prof_n[r.slot]++;
+        }
+        recs.clear();
+        ev_used = 0;
+    }
+};
+
+namespace {
+
+int derive_dims(const ilqrb_problem_desc* d, ilqrb_dims* o, int* task_nt, int* task_r) {
+    if (!d) return fail(ILQRB_EINVAL, "null descriptor");
+    if (d->abi_version != ILQRB_ABI_VERSION) return fail(ILQRB_EINVAL, "descriptor abi_version mismatch");
+    if (d->nb_deriv != 1 && d->nb_deriv != 2) return fail(ILQRB_EINVAL, "nb_deriv must be 1 or 2");
+    if (d->sys_kind < 0 || d->sys_kind > 2) return fail(ILQRB_EUNSUPPORTED, "unsupported System kind");
+    if (d->n_tasks < 1 || d->n_tasks > ILQRB_MAX_TASKS) return fail(ILQRB_EINVAL, "n_tasks out of range");
+    if (d->n_robots < 1 || d->n_robots > ILQRB_MAX_TASKS) return fail(ILQRB_EINVAL, "n_robots out of range");
+    if (d->horizon < 2) return fail(ILQRB_EINVAL, "horizon must be >= 2");
+    if (d->batch < 1) return fail(ILQRB_EINVAL, "batch must be >= 1");
+    const int time = d->sys_kind == ILQRB_SYS_POS_ORN_TIME ? 1 : 0;
+    o->n = d->nb_deriv * d->dof + time;
+    o->m = d->dof + time;
+    if (o->n > MAXN - 1 || o->m > MAXM) return fail(ILQRB_EUNSUPPORTED, "state/control size exceeds the compiled bounds (n <= 31, m <= 16)");
+    o->nt = 0;
+    o->r = 0;
+    o->n_kp_total = 0;
+    for (int t = 0; t < d->n_tasks; t++) {
+        const ilqrb_task& tk = d->tasks[t];
+        if (tk.robot < 0 || tk.robot >= d->n_robots) return fail(ILQRB_EINVAL, "task.robot out of range");
+        if (tk.n_keypoints < 1 || tk.n_keypoints > ILQRB_MAX_KEYPOINTS) return fail(ILQRB_EINVAL, "n_keypoints out of range (1..8)");
+        const ilqrb_robot& rb = d->robots[tk.robot];
+        if (rb.dof < 1 || rb.dof > ILQRB_MAX_ROBOT_DOF) return fail(ILQRB_EUNSUPPORTED, "robot dof must be 1..7 (KDLRobot.cpp:112 limit)");
+        if (tk.joint_offset < 0 || tk.joint_offset + rb.dof > d->dof) return fail(ILQRB_EINVAL, "task joint range outside the state");
+        int nt, r;
+        if (d->sys_kind == ILQRB_SYS_POSITION) {
+            if (tk.has_transform) return fail(ILQRB_EUNSUPPORTED, "POSITION tasks do not take a transform");
+            const int car = rb.kind == ILQRB_ROBOT_2D ? 2 : 3;
+            nt = car * d->nb_deriv;
+            r = nt;
+        } else {
+            if (rb.kind == ILQRB_ROBOT_2D) return fail(ILQRB_EUNSUPPORTED, "Robot2D only supports the POSITION system (SURVEY 8g C1)");
+            nt = 7 * d->nb_deriv + time;
+            r = 6 * d->nb_deriv + time;
+        }
+        if (task_nt) task_nt[t] = nt;
+        if (task_r) task_r[t] = r;
+        o->nt += nt;
+        o->r += r;
+        o->n_kp_total += tk.n_keypoints;
+        for (int i = 0; i < tk.n_keypoints; i++) {
+            if (tk.kp_timestep[i] < 0 || tk.kp_timestep[i] >= d->horizon) return fail(ILQRB_EINVAL, "keypoint timestep outside the horizon");
+            if (i > 0 && tk.kp_timestep[i] <= tk.kp_timestep[i - 1]) return fail(ILQRB_EINVAL, "keypoint timesteps must be strictly ascending");
+        }
+    }
+    o->H = d->horizon;
+    o->B = d->batch;
+    return 0;
+}
+
+template <class T>
+int upload(ilqrb_handle h, T** dst, const T* src, size_t count) {
+    int rc = h->alloc(dst, count);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(*dst, src, count * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+    return 0;
+}
+
+// ---- dispatch over the compiled size classes -------------------------------------------------------------
+int size_class(int n, int m) {  // thread kernels <N, M>
+    if (n <= 8 && m <= 8) return 0;
+    if (n <= 16 && m <= 8) return 1;
+    if (n <= 16 && m <= 16) return 2;
+    return 3;
+}
+#define DISPATCH_NM(cls, CALL)          \
+    switch (cls) {                      \
+        case 0: { CALL(8, 8); } break;  \
+        case 1: { CALL(16, 8); } break; \
+        case 2: { CALL(16, 16); } break;\
+        default: { CALL(32, 16); } break;\
+    }
+
+int tile_class(int n, int m) {  // backward kernel <NXT, NUT>: 8*NXT >= n+1, 8*NUT >= m
+    if (n + 1 <= 8 && m <= 8) return 0;
+    if (n + 1 <= 16 && m <= 8) return 1;
+    if (n + 1 <= 16 && m <= 16) return 2;
+    return 3;
+}
+
+template <int NXT, int NUT, bool TIME, bool AL, int WARPS, int MINB>
+int launch_backward_t(ilqrb_handle h, double penalty_frozen) {
+    using S = BwdSmem<NXT, NUT>;
+    const size_t smem = ((TIME ? WARPS : 1) * S::DYN + (size_t)WARPS * S::PER_WARP) * sizeof(double);
+    auto kern = k_backward<NXT, NUT, TIME, AL, WARPS, MINB>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    const int B = h->hp.B;
+    kern<<<(B + WARPS - 1) / WARPS, 32 * WARPS, smem, h->stream>>>(h->dp, h->W, penalty_frozen);
+    return 0;
+}
+template <bool TIME, bool AL>
+int launch_backward_ta(ilqrb_handle h, double pf) {
+    switch (tile_class(h->hp.n, h->hp.m)) {
+        case 0: return launch_backward_t<1, 1, TIME, AL, 4, 7>(h, pf);
+        case 1: return launch_backward_t<2, 1, TIME, AL, 4, 3>(h, pf);
+        case 2: return launch_backward_t<2, 2, TIME, AL, 4, 2>(h, pf);
+        default: return launch_backward_t<4, 2, TIME, AL, 2, 1>(h, pf);
+    }
+}
+int launch_backward(ilqrb_handle h, bool al, double pf) {
+    h->begin(PS_BACKWARD);
+    int rc;
+    if (h->hp.time) rc = al ? launch_backward_ta<true, true>(h, pf) : launch_backward_ta<true, false>(h, pf);
+    else rc = al ? launch_backward_ta<false, true>(h, pf) : launch_backward_ta<false, false>(h, pf);
+    h->end();
+    if (rc) return rc;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+int ensure_iter_capacity(ilqrb_handle h, int nb_iter) {
+    if (nb_iter <= h->cap_iter) return 0;
+    int rc;
+    if ((rc = h->alloc(&h->W.cost_hist, (size_t)h->hp.B * nb_iter))) return rc;
+    if ((rc = h->alloc(&h->W.alpha_hist, (size_t)h->hp.B * nb_iter))) return rc;
+    h->cap_iter = nb_iter;
+    return 0;
+}
+
+__global__ void k_fill(double* p, size_t n, double v) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+// strided pack: dst[row][0..w) = src[row*stride + 0..w) * (scale ? scale[row / rows_per_problem] : 1)
+__global__ void k_pack(double* __restrict__ dst, const double* __restrict__ src, size_t rows, int w, int stride, const double* __restrict__ scale, int rows_per_problem) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * w) return;
+    size_t row = i / w;
+    int c = (int)(i % w);
+    double v = src[row * stride + c];
+    if (scale) v *= scale[row / rows_per_problem];
+    dst[i] = v;
+}
+__global__ void k_unpack(double* __restrict__ dst, const double* __restrict__ src, size_t rows, int w, int stride) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * stride) return;
+    size_t row = i / stride;
+    int c = (int)(i % stride);
+    dst[i] = (c < w && src) ? src[row * w + c] : 0.0;
+}
+
+int ensure_pack(ilqrb_handle h, size_t elems) {
+    if (elems <= h->pack_elems) return 0;
+    int rc = h->alloc(&h->d_pack, elems);
+    if (rc) return rc;
+    h->pack_elems = elems;
+    return 0;
+}
+
+int download_packed(ilqrb_handle h, double* dst_host, const double* src_dev, size_t rows, int w, int stride, const double* scale, int rpp) {
+    if (!dst_host) return 0;
+    int rc = ensure_pack(h, rows * w);
+    if (rc) return rc;
+    const size_t tot = rows * w;
+    k_pack<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(h->d_pack, src_dev, rows, w, stride, scale, rpp);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(dst_host, h->d_pack, tot * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));  // staging buffer is reused
+    return 0;
+}
+
+// one thread per (problem, timestep): stacked task Jacobian (test hook)
+__global__ void k_rollout_jac(const DevProblem* __restrict__ Pp, Work W, double* __restrict__ Jout) {
+    const DevProblem& P = *Pp;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P.B * P.H) return;
+    const int b = idx / P.H, k = idx % P.H, n = P.n, dof = P.dof;
+    const double* x = W.X + ((size_t)b * P.H + k) * W.ns;
+    double xs[MAXN], dqs[MAXM];
+    for (int i = 0; i < n; i++) xs[i] = x[i];
+    for (int i = 0; i < dof; i++) dqs[i] = (P.nb_deriv == 2) ? xs[dof + i] : 0.0;
+    double* out = Jout + (size_t)idx * P.r * n;
+    for (int t = 0; t < P.n_tasks; t++) {
+        const DevTask& tk = P.tasks[t];
+        EEState e;
+        task_ee(P, tk, xs, dqs, e);
+        task_jacobian(P, tk, e, out + (size_t)tk.r_off * n, n);
+    }
+}
+__global__ void k_kinematics(const DevProblem* __restrict__ Pp, int robot, int nq, const double* __restrict__ q, const double* __restrict__ dq, double* x, double* quat,
+                             double* J, double* dx, double* w) {
+    const DevProblem& P = *Pp;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nq) return;
+    const DevRobot& rb = P.robots[robot];
+    double qs[RDOF], dqs[RDOF];
+    for (int c = 0; c < RDOF; c++) {
+        qs[c] = c < rb.dof ? q[(size_t)i * rb.dof + c] : 0.0;
+        dqs[c] = c < rb.dof ? dq[(size_t)i * rb.dof + c] : 0.0;
+    }
+    EEState e;
+    if (rb.kind == ILQRB_ROBOT_2D) robot2d_update_kinematics(rb.lengths, rb.dof, qs, dqs, e);
+    else kdl_update_kinematics(rb.segs, rb.n_segments, rb.dof, qs, dqs, e);
+    for (int a = 0; a < 3; a++) {
+        x[(size_t)i * 3 + a] = e.x[a];
+        dx[(size_t)i * 3 + a] = e.dx[a];
+        w[(size_t)i * 3 + a] = e.w[a];
+    }
+    for (int a = 0; a < 4; a++) quat[(size_t)i * 4 + a] = e.quat[a];
+    for (int a = 0; a < 6; a++)
+        for (int c = 0; c < rb.dof; c++) J[((size_t)i * 6 + a) * rb.dof + c] = a < 3 ? e.Jv[c][a] : e.Jw[c][a - 3];
+}
+
+int launch_init(ilqrb_handle h) {
+    const int B = h->hp.B;
+    h->begin(PS_ROLLOUT_INIT);
+#define CALL(N, M) k_rollout_init<N, M><<<(B + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W)
+    DISPATCH_NM(size_class(h->hp.n, h->hp.m), CALL)
+#undef CALL
+    h->end();
+    CU(cudaGetLastError());
+    return 0;
+}
+int launch_derivs(ilqrb_handle h) {
+    const int tot = h->hp.B * h->hp.n_kp_steps;
+    h->begin(PS_KP_DERIVS);
+    k_kp_derivs<<<(tot + 63) / 64, 64, 0, h->stream>>>(h->dp, h->W);
+    h->end();
+    CU(cudaGetLastError());
+    return 0;
+}
+int launch_linesearch(ilqrb_handle h, int line_search) {
+    const int tot = h->hp.B * CAND_LANES;
+    h->begin(PS_LINESEARCH);
+#define CALL(N, M) k_linesearch<N, M><<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, line_search)
+    DISPATCH_NM(size_class(h->hp.n, h->hp.m), CALL)
+#undef CALL
+    h->end();
+    CU(cudaGetLastError());
+    return 0;
+}
+int launch_accept(ilqrb_handle h, int it, int nb_iter, int line_search, int early_stop, int al, int lag, double pen_next) {
+    const int tot = h->hp.B * 32;
+    h->begin(PS_ACCEPT);
+#define CALL(N, M) k_accept<N, M><<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, it, nb_iter, line_search, early_stop, al, lag, pen_next)
+    DISPATCH_NM(size_class(h->hp.n, h->hp.m), CALL)
+#undef CALL
+    h->end();
+    CU(cudaGetLastError());
+    return 0;
+}
+
+int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solve_opts* opts) {
+    if (!opts) return fail(ILQRB_EINVAL, "null opts");
+    if (opts->nb_iter < 0) return fail(ILQRB_EINVAL, "nb_iter < 0");
+    CU(cudaSetDevice(h->device));
+    int rc;
+    const int B = h->hp.B, H = h->hp.H, n = h->hp.n, m = h->hp.m;
+    if ((rc = ensure_iter_capacity(h, std::max(opts->nb_iter, 1)))) return rc;
+    const size_t nh = (size_t)B * std::max(opts->nb_iter, 1);
+    k_fill<<<(unsigned)((nh + 255) / 256), 256, 0, h->stream>>>(h->W.cost_hist, nh, NAN);
+    k_fill<<<(unsigned)((nh + 255) / 256), 256, 0, h->stream>>>(h->W.alpha_hist, nh, NAN);
+    CU(cudaMemsetAsync(h->W.K, 0, (size_t)B * (H - 1) * m * h->W.ns * sizeof(double), h->stream));
+    CU(cudaMemsetAsync(h->W.d, 0, (size_t)B * (H - 1) * h->W.ms * sizeof(double), h->stream));
+    double pen = 0, pen_frozen = 0;
+    if (al) {
+        if (al->nc < 1 || al->nc > MAX_NC) return fail(ILQRB_EUNSUPPORTED, "AL: constraint rows per step must be 1..32");
+        if (al->lag_update_step < 1) return fail(ILQRB_EINVAL, "AL: lag_update_step must be >= 1");
+        const int nc = al->nc, steps = al->per_step ? H - 1 : 1;
+        const size_t ea = (size_t)steps * nc * (n + m), eb = (size_t)steps * nc;
+        if (ea > h->alA_elems) {
+            if ((rc = h->alloc(&h->d_alA, ea))) return rc;
+            h->alA_elems = ea;
+        }
+        if (eb > h->alb_elems) {
+            if ((rc = h->alloc(&h->d_alb, eb))) return rc;
+            h->alb_elems = eb;
+        }
+        CU(cudaMemcpyAsync(h->d_alA, al->A, ea * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        CU(cudaMemcpyAsync(h->d_alb, al->b, eb * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        if (h->W.nc != nc || !h->W.lam) {
+            if ((rc = h->alloc(&h->W.lam, (size_t)B * (H - 1) * nc))) return rc;
+            if ((rc = h->alloc(&h->W.Cs, (size_t)B * (H - 1) * nc))) return rc;
+            if (!h->W.mask && (rc = h->alloc(&h->W.mask, (size_t)B * (H - 1)))) return rc;
+        }
+        h->W.nc = nc;
+        h->W.al_per_step = al->per_step;
+        h->W.alA = h->d_alA;
+        h->W.alb = h->d_alb;
+        // initial multipliers replicated over the batch (and over steps when given once)
+        h->h_lam0.resize((size_t)B * (H - 1) * nc);
+        for (int b = 0; b < B; b++)
+            for (int k = 0; k < H - 1; k++)
+                std::memcpy(&h->h_lam0[((size_t)b * (H - 1) + k) * nc], al->lambda0 + (size_t)(al->per_step ? k : 0) * nc, nc * sizeof(double));
+        CU(cudaMemcpyAsync(h->W.lam, h->h_lam0.data(), h->h_lam0.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        pen = al->penalty;
+        pen_frozen = pen;
+    }
+    if ((rc = launch_init(h))) return rc;
+    if (al) {
+        h->begin(PS_MISC);
+        k_al_init<<<(B * 32 + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W);
+        h->end();
+        CU(cudaGetLastError());
+    }
+    for (int it = 0; it < opts->nb_iter; it++) {
+        if ((rc = launch_derivs(h))) return rc;
+        if ((rc = launch_backward(h, al != nullptr, pen_frozen))) return rc;
+        if ((rc = launch_linesearch(h, opts->line_search))) return rc;
+        double pen_next = pen;
+        bool upd = false;
+        if (al) {
+            upd = ((it + 1) % al->lag_update_step) == 0;
+            if (upd) pen_next = pen * al->scaling_factor;
+        }
+        if ((rc = launch_accept(h, it, std::max(opts->nb_iter, 1), opts->line_search, opts->early_stop, al != nullptr, al ? al->lag_update_step : 1, pen_next))) return rc;
+        pen_frozen = pen;  // Is[k] keeps the penalty of the rollout that produced it (AL-ILQR.cpp:190)
+        pen = pen_next;
+    }
+    h->last_nb_iter = opts->nb_iter;
+    h->last_solver = al ? 2 : 1;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ilqrb_abi_version(void) { return ILQRB_ABI_VERSION; }
+void ilqrb_set_error_(const char* msg) { g_err = msg ? msg : ""; }  // used by host_utils.cpp
+const char* ilqrb_last_error(void) { return g_err.c_str(); }
+
+int ilqrb_get_dims(const ilqrb_problem_desc* desc, ilqrb_dims* out) {
+    if (!out) return fail(ILQRB_EINVAL, "null out");
+    return derive_dims(desc, out, nullptr, nullptr);
+}
+
+int ilqrb_create(const ilqrb_problem_desc* d, int device, ilqrb_handle* out) {
+    if (!out) return fail(ILQRB_EINVAL, "null out");
+    ilqrb_dims dm;
+    int task_nt[ILQRB_MAX_TASKS], task_r[ILQRB_MAX_TASKS];
+    int rc = derive_dims(d, &dm, task_nt, task_r);
+    if (rc) return rc;
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0)
+        return fail(ILQRB_ECUDA, std::string("no CUDA device available (there is no CPU fallback): ") + (ce != cudaSuccess ? cudaGetErrorString(ce) : "device count 0"));
+    if (device < 0 || device >= ndev) return fail(ILQRB_EINVAL, "device index out of range");
+    CU(cudaSetDevice(device));
+    ilqrb_handle h = new ilqrb_handle_s();
+    h->device = device;
+    h->dims = dm;
+    std::memset(&h->W, 0, sizeof(Work));
+    std::memset(&h->BW, 0, sizeof(BatchWork));
+    cudaError_t se = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (se != cudaSuccess) {
+        delete h;
+        return fail(ILQRB_ECUDA, std::string("cudaStreamCreate: ") + cudaGetErrorString(se));
+    }
+    h->own_stream = true;
+    DevProblem& P = h->hp;
+    std::memset(&P, 0, sizeof(P));
+    P.sys_kind = d->sys_kind;
+    P.nb_deriv = d->nb_deriv;
+    P.H = d->horizon;
+    P.B = d->batch;
+    P.dof = d->dof;
+    P.n_robots = d->n_robots;
+    P.n_tasks = d->n_tasks;
+    P.time = d->sys_kind == ILQRB_SYS_POS_ORN_TIME ? 1 : 0;
+    P.n = dm.n;
+    P.m = dm.m;
+    P.nt = dm.nt;
+    P.r = dm.r;
+    P.dt = d->dt;
+    for (int i = 0; i < dm.m; i++) P.r_diag[i] = d->r_diag[i];
+    for (int i = 0; i < d->n_robots; i++) {
+        const ilqrb_robot& rb = d->robots[i];
+        DevRobot& o = P.robots[i];
+        o.kind = rb.kind;
+        o.dof = rb.dof;
+        o.n_segments = rb.n_segments;
+        if (rb.kind == ILQRB_ROBOT_KDL) {
+            if (rb.n_segments < 1 || rb.n_segments > ILQRB_MAX_SEGMENTS) {
+                ilqrb_destroy(h);
+                return fail(ILQRB_EINVAL, "n_segments out of range (1..24)");
+            }
+            int nj = 0;
+            for (int s = 0; s < rb.n_segments; s++) {
+                o.segs[s] = rb.segments[s];
+                if (rb.segments[s].joint_type != ILQRB_JOINT_FIXED) nj++;
+            }
+            if (nj != rb.dof) {
+                ilqrb_destroy(h);
+                return fail(ILQRB_EINVAL, "robot.dof does not match the chain's movable joints");
+            }
+        } else if (rb.kind == ILQRB_ROBOT_2D) {
+            for (int c = 0; c < rb.dof; c++) o.lengths[c] = rb.lengths[c];
+        } else {
+            ilqrb_destroy(h);
+            return fail(ILQRB_EUNSUPPORTED, "unsupported SimulationInterface kind");
+        }
+    }
+    const size_t B = d->batch;
+    int fx_off = 0, r_off = 0;
+    std::vector<int> steps;
+    for (int t = 0; t < d->n_tasks; t++) {
+        const ilqrb_task& tk = d->tasks[t];
+        DevTask& o = P.tasks[t];
+        o.robot = tk.robot;
+        o.joint_offset = tk.joint_offset;
+        o.has_transform = tk.has_transform;
+        o.n_keypoints = tk.n_keypoints;
+        std::memcpy(o.T, tk.T, sizeof(o.T));
+        for (int i = 0; i < tk.n_keypoints; i++) {
+            o.kp_timestep[i] = tk.kp_timestep[i];
+            bool seen = false;
+            for (int s : steps) seen = seen || s == tk.kp_timestep[i];
+            if (!seen) steps.push_back(tk.kp_timestep[i]);
+        }
+        o.precision_per_problem = tk.precision_per_problem;
+        o.limits_set = tk.limits_set;
+        o.nt_t = task_nt[t];
+        o.r_t = task_r[t];
+        o.fx_off = fx_off;
+        o.r_off = r_off;
+        fx_off += task_nt[t];
+        r_off += task_r[t];
+        for (int i = 0; i < dm.m; i++) o.r_diag[i] = tk.r_diag[i];
+        if (tk.limits_set) {
+            P.any_limits = 1;
+            for (int i = 0; i < dm.n; i++) {
+                o.state_max[i] = tk.state_max[i];
+                o.state_min[i] = tk.state_min[i];
+                o.limit_weight[i] = tk.limit_weight[i];
+            }
+        }
+        double* dtg = nullptr;
+        double* dpr = nullptr;
+        if ((rc = upload(h, &dtg, tk.kp_target, B * tk.n_keypoints * ILQRB_KP_STRIDE)) ||
+            (rc = upload(h, &dpr, tk.kp_precision, (size_t)(tk.precision_per_problem ? B : 1) * tk.n_keypoints * task_r[t] * task_r[t]))) {
+            ilqrb_destroy(h);
+            return rc;
+        }
+        o.kp_target = dtg;
+        o.kp_precision = dpr;
+    }
+    std::sort(steps.begin(), steps.end());
+    P.n_kp_steps = (int)steps.size();
+    for (size_t i = 0; i < steps.size(); i++) P.kp_steps[i] = steps[i];
+    double *dq0 = nullptr, *ddq0 = nullptr;
+    if ((rc = upload(h, &dq0, d->q0, B * d->dof)) || (rc = upload(h, &ddq0, d->dq0, B * d->dof))) {
+        ilqrb_destroy(h);
+        return rc;
+    }
+    P.q0 = dq0;
+    P.dq0 = ddq0;
+    if ((rc = upload(h, &h->dp, &P, 1))) {
+        ilqrb_destroy(h);
+        return rc;
+    }
+    // work buffers
+    Work& W = h->W;
+    const int H = d->horizon, n = dm.n, m = dm.m;
+    W.ns = (n + 1) & ~1;
+    W.ms = (m + 1) & ~1;
+    const size_t S = P.n_kp_steps;
+    if ((rc = h->alloc(&W.X, B * H * W.ns)) || (rc = h->alloc(&W.U, B * (H - 1) * W.ms)) || (rc = h->alloc(&W.K, B * (H - 1) * m * W.ns)) ||
+        (rc = h->alloc(&W.d, B * (H - 1) * W.ms)) || (rc = h->alloc(&W.Uc, B * (H - 1) * NCAND * W.ms)) || (rc = h->alloc(&W.cost_c, B * NCAND)) ||
+        (rc = h->alloc(&W.dun_c, B * NCAND)) || (rc = h->alloc(&W.cost0, B)) || (rc = h->alloc(&W.LX, B * S * n)) || (rc = h->alloc(&W.LXX, B * S * n * n)) ||
+        (rc = h->alloc(&W.alpha_last, B)) || (rc = h->alloc(&W.done, B)) || (rc = h->alloc(&W.iters, B)) || (rc = h->alloc(&W.status, B)) ||
+        (rc = h->alloc(&h->d_fX, B * H * dm.nt))) {
+        ilqrb_destroy(h);
+        return rc;
+    }
+    cudaMemsetAsync(W.U, 0, B * (H - 1) * W.ms * sizeof(double), h->stream);
+    cudaMemsetAsync(W.X, 0, B * H * W.ns * sizeof(double), h->stream);
+    cudaMemsetAsync(W.done, 0, B * sizeof(int), h->stream);
+    cudaMemsetAsync(W.iters, 0, B * sizeof(int), h->stream);
+    cudaMemsetAsync(W.status, 0, B * sizeof(int), h->stream);
+    cudaError_t e2 = cudaStreamSynchronize(h->stream);
+    if (e2 != cudaSuccess) {
+        ilqrb_destroy(h);
+        return fail(ILQRB_ECUDA, std::string("create: ") + cudaGetErrorString(e2));
+    }
+    *out = h;
+    return 0;
+}
+
+int ilqrb_destroy(ilqrb_handle h) {
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (void* p : h->allocs) cudaFree(p);
+    for (auto e : h->ev_pool) cudaEventDestroy(e);
+    if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return 0;
+}
+
+int ilqrb_set_stream(ilqrb_handle h, void* s) {
+    if (!h) return fail(ILQRB_EINVAL, "null handle");
+    cudaStreamSynchronize(h->stream);
+    if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+    h->stream = (cudaStream_t)s;
+    h->own_stream = false;
+    return 0;
+}
+
+int ilqrb_synchronize(ilqrb_handle h) {
+    if (!h) return fail(ILQRB_EINVAL, "null handle");
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+int ilqrb_update_problems(ilqrb_handle h, const double* q0, const double* dq0, int task, const double* kp_target) {
+    if (!h) return fail(ILQRB_EINVAL, "null handle");
+    CU(cudaSetDevice(h->device));
+    const size_t B = h->hp.B;
+    if (q0) CU(cudaMemcpyAsync((void*)h->hp.q0, q0, B * h->hp.dof * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    if (dq0) CU(cudaMemcpyAsync((void*)h->hp.dq0, dq0, B * h->hp.dof * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    if (kp_target) {
+        if (task < 0 || task >= h->hp.n_tasks) return fail(ILQRB_EINVAL, "task out of range");
+        const DevTask& tk = h->hp.tasks[task];
+        CU(cudaMemcpyAsync((void*)tk.kp_target, kp_target, B * tk.n_keypoints * ILQRB_KP_STRIDE * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    }
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+int ilqrb_upload_u0(ilqrb_handle h, const double* U0) {
+    if (!h) return fail(ILQRB_EINVAL, "null handle");
+    CU(cudaSetDevice(h->device));
+    const size_t rows = (size_t)h->hp.B * (h->hp.H - 1);
+    const int m = h->hp.m, ms = h->W.ms;
+    if (!U0) {
+        CU(cudaMemsetAsync(h->W.U, 0, rows * ms * sizeof(double), h->stream));
+        return 0;
+    }
+    int rc = ensure_pack(h, rows * m);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(h->d_pack, U0, rows * m * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    const size_t tot = rows * ms;
+    k_unpack<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(h->W.U, h->d_pack, rows, m, ms);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+int ilqrb_run_recursive(ilqrb_handle h, const ilqrb_solve_opts* opts) {
+    if (!h) return fail(ILQRB_EINVAL, "null handle");
+    return run_recursive_like(h, nullptr, opts);
+}
+int ilqrb_run_al(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solve_opts* opts) {
+    if (!h) return fail(ILQRB_EINVAL, "null handle");
+    if (!al || !al->A || !al->b || !al->lambda0) return fail(ILQRB_EINVAL, "AL descriptor incomplete");
+    return run_recursive_like(h, al, opts);
+}
+
+int ilqrb_download(ilqrb_handle h, ilqrb_result* out) {
+    if (!h || !out) return fail(ILQRB_EINVAL, "null argument");
+    CU(cudaSetDevice(h->device));
+    const DevProblem& P = h->hp;
+    const size_t B = P.B;
+    const int H = P.H, n = P.n, m = P.m, nit = std::max(h->last_nb_iter, 1);
+    int rc;
+    if (h->last_solver == 3) return batch_download(h->stream, P, h->BW, out, nit);
+    if ((rc = download_packed(h, out->X, h->W.X, B * H, n, h->W.ns, nullptr, 1))) return rc;
+    if ((rc = download_packed(h, out->U, h->W.U, B * (H - 1), m, h->W.ms, nullptr, 1))) return rc;
+    if (h->last_solver == 1) {
+        if ((rc = download_packed(h, out->K, h->W.K, B * (H - 1) * m, n, h->W.ns, nullptr, 1))) return rc;
+        // ds are returned multiplied by the accepted alpha (ILQRRecursive.cpp:128,144,162)
+        if ((rc = download_packed(h, out->d, h->W.d, B * (H - 1), m, h->W.ms, h->last_nb_iter > 0 ? h->W.alpha_last : nullptr, H - 1))) return rc;
+    }
+    if (out->fX) {
+        const int tot = (int)(B * H);
+        h->begin(PS_FINAL);
+        k_final_fx<<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, h->d_fX);
+        h->end();
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(out->fX, h->d_fX, B * H * P.nt * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    }
+    if (out->cost) CU(cudaMemcpyAsync(out->cost, h->W.cost0, B * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (out->cost_hist) CU(cudaMemcpyAsync(out->cost_hist, h->W.cost_hist, B * nit * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (out->alpha_hist) CU(cudaMemcpyAsync(out->alpha_hist, h->W.alpha_hist, B * nit * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (out->iters) CU(cudaMemcpyAsync(out->iters, h->W.iters, B * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    if (out->status) CU(cudaMemcpyAsync(out->status, h->W.status, B * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    if (out->lambda && h->last_solver == 2) CU(cudaMemcpyAsync(out->lambda, h->W.lam, B * (H - 1) * h->W.nc * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+int ilqrb_solve_recursive(ilqrb_handle h, const double* U0, const ilqrb_solve_opts* opts, ilqrb_result* out) {
+    int rc;
+    if ((rc = ilqrb_upload_u0(h, U0))) return rc;
+    if ((rc = ilqrb_run_recursive(h, opts))) return rc;
+    return ilqrb_download(h, out);
+}
+int ilqrb_solve_al(ilqrb_handle h, const double* U0, const ilqrb_al_desc* al, const ilqrb_solve_opts* opts, ilqrb_result* out) {
+    int rc;
+    if ((rc = ilqrb_upload_u0(h, U0))) return rc;
+    if ((rc = ilqrb_run_al(h, al, opts))) return rc;
+    return ilqrb_download(h, out);
+}
+
+int ilqrb_run_batch(ilqrb_handle h, const ilqrb_batch_desc* bd, const ilqrb_solve_opts* opts) {
+    if (!h || !opts) return fail(ILQRB_EINVAL, "null argument");
+    CU(cudaSetDevice(h->device));
+    std::string err;
+    int rc = batch_run(h->stream, h->hp, h->dp, h->W, h->BW, bd, opts, err, [h](int slot) { h->begin(PS_BATCH_FP + slot); }, [h]() { h->end(); });
+    if (rc) return fail(rc, err);
+    h->last_nb_iter = opts->nb_iter;
+    h->last_solver = 3;
+    return 0;
+}
+int ilqrb_solve_batch(ilqrb_handle h, const double* u0, const ilqrb_batch_desc* bd, const ilqrb_solve_opts* opts, ilqrb_result* out) {
+    int rc;
+    if ((rc = ilqrb_upload_u0(h, u0))) return rc;
+    if ((rc = ilqrb_run_batch(h, bd, opts))) return rc;
+    return ilqrb_download(h, out);
+}
+
+int ilqrb_rollout(ilqrb_handle h, const double* U, double* X, double* fX, double* J, double* cost) {
+    if (!h) return fail(ILQRB_EINVAL, "null handle");
+    CU(cudaSetDevice(h->device));
+    int rc;
+    if ((rc = ilqrb_upload_u0(h, U))) return rc;
+    if ((rc = launch_init(h))) return rc;
+    const DevProblem& P = h->hp;
+    const size_t B = P.B;
+    const int H = P.H;
+    if ((rc = download_packed(h, X, h->W.X, B * H, P.n, h->W.ns, nullptr, 1))) return rc;
+    const int tot = (int)(B * H);
+    if (fX) {
+        k_final_fx<<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, h->d_fX);
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(fX, h->d_fX, B * H * P.nt * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    }
+    if (J) {
+        const size_t el = B * H * P.r * P.n;
+        if ((rc = ensure_pack(h, el))) return rc;
+        k_rollout_jac<<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, h->d_pack);
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(J, h->d_pack, el * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    }
+    if (cost) CU(cudaMemcpyAsync(cost, h->W.cost0, B * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+int ilqrb_kinematics(ilqrb_handle h, int robot, int nq, const double* q, const double* dq, double* x, double* quat, double* J, double* dx, double* w) {
+    if (!h) return fail(ILQRB_EINVAL, "null handle");
+    if (robot < 0 || robot >= h->hp.n_robots) return fail(ILQRB_EINVAL, "robot out of range");
+    if (nq < 1 || !q) return fail(ILQRB_EINVAL, "no configurations");
+    CU(cudaSetDevice(h->device));
+    const int dof = h->hp.robots[robot].dof;
+    const size_t in = (size_t)nq * dof, outn = (size_t)nq * (3 + 4 + 6 * dof + 3 + 3);
+    double* buf = nullptr;
+    CU(cudaMalloc(&buf, (2 * in + outn) * sizeof(double)));
+    double *dq_d = buf + in, *ox = buf + 2 * in, *oq = ox + (size_t)nq * 3, *oJ = oq + (size_t)nq * 4, *odx = oJ + (size_t)nq * 6 * dof, *ow = odx + (size_t)nq * 3;
+    cudaMemcpyAsync(buf, q, in * sizeof(double), cudaMemcpyHostToDevice, h->stream);
+    if (dq) cudaMemcpyAsync(dq_d, dq, in * sizeof(double), cudaMemcpyHostToDevice, h->stream);
+    else cudaMemsetAsync(dq_d, 0, in * sizeof(double), h->stream);
+    h->begin(PS_MISC);
+    k_kinematics<<<(nq + 127) / 128, 128, 0, h->stream>>>(h->dp, robot, nq, buf, dq_d, ox, oq, oJ, odx, ow);
+    h->end();
+    if (x) cudaMemcpyAsync(x, ox, (size_t)nq * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+    if (quat) cudaMemcpyAsync(quat, oq, (size_t)nq * 4 * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+    if (J) cudaMemcpyAsync(J, oJ, (size_t)nq * 6 * dof * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+    if (dx) cudaMemcpyAsync(dx, odx, (size_t)nq * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+    if (w) cudaMemcpyAsync(w, ow, (size_t)nq * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+    cudaError_t e = cudaStreamSynchronize(h->stream);
+    cudaFree(buf);
+    if (e != cudaSuccess) return fail(ILQRB_ECUDA, std::string("kinematics: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+int ilqrb_set_profiling(ilqrb_handle h, int enabled) {
+    if (!h) return fail(ILQRB_EINVAL, "null handle");
+    h->resolve();
+    h->prof = enabled != 0;
+    return 0;
+}
+int ilqrb_get_profile(ilqrb_handle h, ilqrb_profile* out) {
+    if (!h || !out) return fail(ILQRB_EINVAL, "null argument");
+    h->resolve();
+    for (int i = 0; i < ILQRB_PROF_SLOTS; i++) {
+        out->ms[i] = h->prof_ms[i];
+        out->launches[i] = h->prof_n[i];
+        out->name[i] = kProfNames[i];
+    }
+    return 0;
+}
+int ilqrb_reset_profile(ilqrb_handle h) {
+    if (!h) return fail(ILQRB_EINVAL, "null handle");
+    h->resolve();
+    for (int i = 0; i < ILQRB_PROF_SLOTS; i++) {
+        h->prof_ms[i] = 0;
+        h->prof_n[i] = 0;
+    }
+    return 0;
+}
+int64_t ilqrb_launch_count(ilqrb_handle h) { return h ? h->launches : 0; }
+
+}  // extern "C"

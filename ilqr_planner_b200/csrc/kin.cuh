@@ -1,0 +1,639 @@
+// kin.cuh — per-thread (scalar) kinematics, task residuals and running cost for the batched iLQR kernels.
+//
+// Everything here is what ONE thread evaluates for ONE state vector: KDL-chain forward kinematics + geometric
+// Jacobian, Robot2D kinematics, the TransformedSimulationInterface view, the S^3 log-map residual of
+// PosOrnKeypoint / SpacetimeKeypoint, and System::cost.  The reference functions replaced are cited per block
+// (IP/ = ilqr_planner/ilqr_planner/ in the reference tree).
+//
+// The functions are __host__ __device__ so that tests/ can compile them for the host and check them against the
+// oracle without a GPU (tests/host_emul); the product only ever calls them from kernels.
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#include "../../include/ilqrb.h"
+
+#ifdef __CUDACC__
+#define HD __host__ __device__ __forceinline__
+#define HDN __host__ __device__ __noinline__
+#else
+#define HD inline
+#define HDN inline
+#endif
+
+namespace ilqrb {
+
+constexpr int MAXN = 32;   // state size bound (nb_deriv * dof + time)
+constexpr int MAXM = 16;   // control size bound
+constexpr int RDOF = ILQRB_MAX_ROBOT_DOF;  // joints of one KDL chain
+constexpr int MAX_RT = 13; // residual size of one task (6*nd + time)
+constexpr int MAX_NTT = 15;// target size of one task (7*nd + time)
+
+// ---- flattened problem description living in device global memory (built by api.cu) -----------------------
+struct DevRobot {
+    int kind, dof, n_segments, pad_;
+    ilqrb_segment segs[ILQRB_MAX_SEGMENTS];
+    double lengths[RDOF + 1];
+};
+struct DevTask {
+    int robot, joint_offset, has_transform, n_keypoints;
+    double T[16];
+    int kp_timestep[ILQRB_MAX_KEYPOINTS];
+    const double* kp_target;     // [B][Kp][15]
+    const double* kp_precision;  // [B|1][Kp][r_t][r_t]
+    int precision_per_problem, limits_set;
+    int nt_t, r_t;               // target / residual size of this task
+    int fx_off, r_off;           // offsets inside the stacked fx / residual
+    double r_diag[MAXM];
+    double state_max[MAXN], state_min[MAXN];
+    int limit_weight[MAXN];
+};
+struct DevProblem {
+    int sys_kind, nb_deriv, H, B, dof, n_robots, n_tasks, time;
+    int n, m, nt, r;
+    int n_kp_steps;                         // distinct keypoint timesteps over all tasks
+    int kp_steps[ILQRB_MAX_TASKS * ILQRB_MAX_KEYPOINTS];
+    int any_limits;
+    double dt;
+    double r_diag[MAXM];
+    DevRobot robots[ILQRB_MAX_TASKS];
+    DevTask tasks[ILQRB_MAX_TASKS];
+    const double* q0;   // [B][dof]
+    const double* dq0;  // [B][dof]
+};
+
+// ---- small fixed-size helpers ----------------------------------------------------------------------------
+HD void mat3_mul(const double* A, const double* B, double* C) {
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) C[3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
+}
+HD void mat3_vec(const double* A, const double* v, double* o) {
+#pragma unroll
+    for (int i = 0; i < 3; i++) o[i] = A[3 * i] * v[0] + A[3 * i + 1] * v[1] + A[3 * i + 2] * v[2];
+}
+HD void mat3T_vec(const double* A, const double* v, double* o) {  // A^T v
+#pragma unroll
+    for (int i = 0; i < 3; i++) o[i] = A[i] * v[0] + A[3 + i] * v[1] + A[6 + i] * v[2];
+}
+HD void cross3(const double* a, const double* b, double* o) {
+    o[0] = a[1] * b[2] - a[2] * b[1];
+    o[1] = a[2] * b[0] - a[0] * b[2];
+    o[2] = a[0] * b[1] - a[1] * b[0];
+}
+
+// KDL Rotation::Rot2(rotvec, angle), rotvec normalised (orocos_kdl frames.cpp)
+HD void kdl_rot2(const double* v, double angle, double* R) {
+    double st, ct;
+    sincos(angle, &st, &ct);
+    double vt = 1 - ct;
+    double m_vt_0 = vt * v[0], m_vt_1 = vt * v[1], m_vt_2 = vt * v[2];
+    double m_st_0 = v[0] * st, m_st_1 = v[1] * st, m_st_2 = v[2] * st;
+    double m_vt_0_1 = m_vt_0 * v[1], m_vt_0_2 = m_vt_0 * v[2], m_vt_1_2 = m_vt_1 * v[2];
+    R[0] = ct + m_vt_0 * v[0];
+    R[1] = -m_st_2 + m_vt_0_1;
+    R[2] = m_st_1 + m_vt_0_2;
+    R[3] = m_st_2 + m_vt_0_1;
+    R[4] = ct + m_vt_1 * v[1];
+    R[5] = -m_st_0 + m_vt_1_2;
+    R[6] = -m_st_1 + m_vt_0_2;
+    R[7] = m_st_0 + m_vt_1_2;
+    R[8] = ct + m_vt_2 * v[2];
+}
+
+// KDL Rotation::GetQuaternion (frames.cpp) written into (w,x,y,z) order as KDLRobot.cpp:103 does
+HD void kdl_get_quaternion(const double* R, double* q) {
+    double trace = R[0] + R[4] + R[8];
+    double w, x, y, z;
+    if (trace > 1E-12) {
+        double s = 0.5 / sqrt(trace + 1.0);
+        w = 0.25 / s;
+        x = (R[7] - R[5]) * s;
+        y = (R[2] - R[6]) * s;
+        z = (R[3] - R[1]) * s;
+    } else if (R[0] > R[4] && R[0] > R[8]) {
+        double s = 2.0 * sqrt(1.0 + R[0] - R[4] - R[8]);
+        w = (R[7] - R[5]) / s;
+        x = 0.25 * s;
+        y = (R[1] + R[3]) / s;
+        z = (R[2] + R[6]) / s;
+    } else if (R[4] > R[8]) {
+        double s = 2.0 * sqrt(1.0 + R[4] - R[0] - R[8]);
+        w = (R[2] - R[6]) / s;
+        x = (R[1] + R[3]) / s;
+        y = 0.25 * s;
+        z = (R[5] + R[7]) / s;
+    } else {
+        double s = 2.0 * sqrt(1.0 + R[8] - R[0] - R[4]);
+        w = (R[3] - R[1]) / s;
+        x = (R[2] + R[6]) / s;
+        y = (R[5] + R[7]) / s;
+        z = 0.25 * s;
+    }
+    q[0] = w;
+    q[1] = x;
+    q[2] = y;
+    q[3] = z;
+}
+
+// Eigen Quaterniond::toRotationMatrix and Quaterniond(Matrix3d) — TransformedSimulationInterface.cpp:94-103
+HD void eig_quat_to_rot(const double* q, double* R) {
+    const double w = q[0], x = q[1], y = q[2], z = q[3];
+    const double tx = 2 * x, ty = 2 * y, tz = 2 * z;
+    const double twx = tx * w, twy = ty * w, twz = tz * w;
+    const double txx = tx * x, txy = ty * x, txz = tz * x;
+    const double tyy = ty * y, tyz = tz * y, tzz = tz * z;
+    R[0] = 1 - (tyy + tzz);
+    R[1] = txy - twz;
+    R[2] = txz + twy;
+    R[3] = txy + twz;
+    R[4] = 1 - (txx + tzz);
+    R[5] = tyz - twx;
+    R[6] = txz - twy;
+    R[7] = tyz + twx;
+    R[8] = 1 - (txx + tyy);
+}
+HD void eig_rot_to_quat(const double* M, double* q) {
+    double t = M[0] + M[4] + M[8];
+    if (t > 0) {
+        t = sqrt(t + 1.0);
+        q[0] = 0.5 * t;
+        t = 0.5 / t;
+        q[1] = (M[7] - M[5]) * t;
+        q[2] = (M[2] - M[6]) * t;
+        q[3] = (M[3] - M[1]) * t;
+    } else {
+        int i = 0;
+        if (M[4] > M[0]) i = 1;
+        if (M[8] > M[4 * i]) i = 2;
+        int j = (i + 1) % 3, k = (j + 1) % 3;
+        t = sqrt(M[4 * i] - M[4 * j] - M[4 * k] + 1.0);
+        double v[3];
+        v[i] = 0.5 * t;
+        t = 0.5 / t;
+        q[0] = (M[3 * k + j] - M[3 * j + k]) * t;
+        v[j] = (M[3 * j + i] + M[3 * i + j]) * t;
+        v[k] = (M[3 * k + i] + M[3 * i + k]) * t;
+        q[1] = v[0];
+        q[2] = v[1];
+        q[3] = v[2];
+    }
+}
+
+// ---- robot kinematics ---------------------------------------------------------------------------------
+struct EEState {
+    double x[3];     // EE position (Robot2D: x[2] unused)
+    double quat[4];  // (w,x,y,z)
+    double dx[3];    // Jv dq
+    double w[3];     // Jw dq
+    double Jv[RDOF][3];  // geometric Jacobian columns, linear rows
+    double Jw[RDOF][3];  // angular rows
+};
+
+// sim::KDLRobot::updateKinematics (KDLRobot.cpp:83-115): ChainJntToJacSolver::JntToJac + ChainFkSolverPos_recursive::
+// JntToCart + Rotation::GetQuaternion, one sweep (both KDL solvers compute the same frame products).
+// The dead dJ/dt (KDLRobot.cpp:112) is not evaluated.
+HD void kdl_update_kinematics(const ilqrb_segment* segs, int nseg, int dof, const double* q, const double* dq, EEState& e) {
+    double TR[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, Tp[3] = {0, 0, 0};
+#pragma unroll
+    for (int c = 0; c < RDOF; c++)
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+            e.Jv[c][i] = 0;
+            e.Jw[c][i] = 0;
+        }
+    int j = 0;
+    for (int s = 0; s < nseg; s++) {
+        const ilqrb_segment& sg = segs[s];
+        double Rj[9], pj[3];
+        const int jt = sg.joint_type;
+        if (jt == ILQRB_JOINT_ROT) {
+            kdl_rot2(sg.axis, q[j], Rj);
+            pj[0] = sg.origin[0];
+            pj[1] = sg.origin[1];
+            pj[2] = sg.origin[2];
+        } else if (jt == ILQRB_JOINT_TRANS) {
+            Rj[0] = Rj[4] = Rj[8] = 1;
+            Rj[1] = Rj[2] = Rj[3] = Rj[5] = Rj[6] = Rj[7] = 0;
+            pj[0] = sg.origin[0] + sg.axis[0] * q[j];
+            pj[1] = sg.origin[1] + sg.axis[1] * q[j];
+            pj[2] = sg.origin[2] + sg.axis[2] * q[j];
+        } else {
+            Rj[0] = Rj[4] = Rj[8] = 1;
+            Rj[1] = Rj[2] = Rj[3] = Rj[5] = Rj[6] = Rj[7] = 0;
+            pj[0] = pj[1] = pj[2] = 0;
+        }
+        // Segment::pose = joint.pose(q) * tip ; total = T_tmp * pose
+        double Rs[9], ps[3], ref[3];
+        mat3_mul(Rj, sg.tip_R, Rs);
+        mat3_vec(Rj, sg.tip_p, ref);  // joint.pose(q).M * f_tip.p (also the twist reference point)
+        ps[0] = ref[0] + pj[0];
+        ps[1] = ref[1] + pj[1];
+        ps[2] = ref[2] + pj[2];
+        double totR[9], totp[3], tmp[3];
+        mat3_mul(TR, Rs, totR);
+        mat3_vec(TR, ps, tmp);
+        totp[0] = tmp[0] + Tp[0];
+        totp[1] = tmp[1] + Tp[1];
+        totp[2] = tmp[2] + Tp[2];
+        double tv[3] = {0, 0, 0}, tw[3] = {0, 0, 0};
+        if (jt != ILQRB_JOINT_FIXED) {
+            double vel[3] = {0, 0, 0}, rot[3] = {0, 0, 0};
+            if (jt == ILQRB_JOINT_ROT) {
+                rot[0] = sg.axis[0] * 1.0;
+                rot[1] = sg.axis[1] * 1.0;
+                rot[2] = sg.axis[2] * 1.0;
+            } else {
+                vel[0] = sg.axis[0] * 1.0;
+                vel[1] = sg.axis[1] * 1.0;
+                vel[2] = sg.axis[2] * 1.0;
+            }
+            double cr[3], v2[3];
+            cross3(rot, ref, cr);
+            v2[0] = vel[0] + cr[0];
+            v2[1] = vel[1] + cr[1];
+            v2[2] = vel[2] + cr[2];
+            mat3_vec(TR, v2, tv);
+            mat3_vec(TR, rot, tw);
+        }
+        // changeRefPoint of all existing columns
+        double dp[3] = {totp[0] - Tp[0], totp[1] - Tp[1], totp[2] - Tp[2]};
+#pragma unroll
+        for (int c = 0; c < RDOF; c++) {
+            if (c < j) {
+                double cr[3];
+                cross3(e.Jw[c], dp, cr);
+                e.Jv[c][0] += cr[0];
+                e.Jv[c][1] += cr[1];
+                e.Jv[c][2] += cr[2];
+            }
+        }
+        if (jt != ILQRB_JOINT_FIXED) {
+#pragma unroll
+            for (int c = 0; c < RDOF; c++)
+                if (c == j) {
+#pragma unroll
+                    for (int i = 0; i < 3; i++) {
+                        e.Jv[c][i] = tv[i];
+                        e.Jw[c][i] = tw[i];
+                    }
+                }
+            j++;
+        }
+#pragma unroll
+        for (int i = 0; i < 9; i++) TR[i] = totR[i];
+        Tp[0] = totp[0];
+        Tp[1] = totp[1];
+        Tp[2] = totp[2];
+    }
+    e.x[0] = Tp[0];
+    e.x[1] = Tp[1];
+    e.x[2] = Tp[2];
+    kdl_get_quaternion(TR, e.quat);
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        double sv = 0, sw = 0;
+#pragma unroll
+        for (int c = 0; c < RDOF; c++)
+            if (c < dof) {
+                sv += e.Jv[c][i] * dq[c];
+                sw += e.Jw[c][i] * dq[c];
+            }
+        e.dx[i] = sv;
+        e.w[i] = sw;
+    }
+}
+
+// sim::Robot2D::updateKinematics (2DRobot.cpp:28-70): absolute-angle FK, forward-difference Jacobian (Q13/Q14)
+HD void robot2d_fkine(const double* lengths, int dof, const double* q, int bump, double dqv, double* xy) {
+    double x0 = 0, x1 = 0;
+    for (int i = 0; i < dof; i++) {
+        double qi = q[i];
+        if (i == bump) qi += dqv;
+        double s, c;
+        sincos(qi, &s, &c);
+        x0 += lengths[i] * c;
+        x1 += lengths[i] * s;
+    }
+    xy[0] = x0;
+    xy[1] = x1;
+}
+HD void robot2d_update_kinematics(const double* lengths, int dof, const double* q, const double* dq, EEState& e) {
+    double xy[2];
+    robot2d_fkine(lengths, dof, q, -1, 0.0, xy);
+    e.x[0] = xy[0];
+    e.x[1] = xy[1];
+    e.x[2] = 0;
+    e.quat[0] = 1;
+    e.quat[1] = e.quat[2] = e.quat[3] = 0;
+    const double d = M_PI * 1e-3;
+    for (int c = 0; c < RDOF; c++) {
+        e.Jv[c][0] = e.Jv[c][1] = e.Jv[c][2] = 0;
+        e.Jw[c][0] = e.Jw[c][1] = e.Jw[c][2] = 0;
+        if (c < dof) {
+            double np[2];
+            robot2d_fkine(lengths, dof, q, c, d, np);
+            e.Jv[c][0] = (np[0] - xy[0]) / d;
+            e.Jv[c][1] = (np[1] - xy[1]) / d;
+        }
+    }
+    for (int i = 0; i < 3; i++) {
+        double sv = 0;
+        for (int c = 0; c < dof; c++) sv += e.Jv[c][i] * dq[c];
+        e.dx[i] = sv;
+        e.w[i] = 0;
+    }
+}
+
+// sim::TransformedSimulationInterface getters (TransformedSimulationInterface.cpp:53-103) applied in place
+HD void apply_transform(const double* T, int dof, EEState& e) {
+    const double R[9] = {T[0], T[1], T[2], T[4], T[5], T[6], T[8], T[9], T[10]};
+    double d[3] = {e.x[0] - T[3], e.x[1] - T[7], e.x[2] - T[11]}, o[3];
+    mat3T_vec(R, d, o);
+    e.x[0] = o[0];
+    e.x[1] = o[1];
+    e.x[2] = o[2];
+    mat3T_vec(R, e.dx, o);
+    e.dx[0] = o[0];
+    e.dx[1] = o[1];
+    e.dx[2] = o[2];
+    mat3T_vec(R, e.w, o);
+    e.w[0] = o[0];
+    e.w[1] = o[1];
+    e.w[2] = o[2];
+    double Rb[9], Rd[9];
+    eig_quat_to_rot(e.quat, Rb);
+    const double Rt[9] = {R[0], R[3], R[6], R[1], R[4], R[7], R[2], R[5], R[8]};
+    mat3_mul(Rt, Rb, Rd);
+    eig_rot_to_quat(Rd, e.quat);
+#pragma unroll
+    for (int c = 0; c < RDOF; c++)
+        if (c < dof) {
+            mat3T_vec(R, e.Jv[c], o);
+            e.Jv[c][0] = o[0];
+            e.Jv[c][1] = o[1];
+            e.Jv[c][2] = o[2];
+            mat3T_vec(R, e.Jw[c], o);
+            e.Jw[c][0] = o[0];
+            e.Jw[c][1] = o[1];
+            e.Jw[c][2] = o[2];
+        }
+}
+
+// ---- S^3 helpers: IP/include/ilqr_planner/utils/sd.h ---------------------------------------------------
+HD bool is_zero4(const double* v) { return fabs(v[0]) <= 1e-12 && fabs(v[1]) <= 1e-12 && fabs(v[2]) <= 1e-12 && fabs(v[3]) <= 1e-12; }
+HD double dot4(const double* a, const double* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2] + a[3] * b[3]; }
+HD double sd_distance(const double* x, const double* y) {  // sd.h:48-62
+    double dist = dot4(x, y);
+    if (dist > 1) dist = 1;
+    else if (dist < -1) dist = -1;
+    double ac = acos(dist);
+    if (dist < 0) ac -= M_PI;
+    return ac;
+}
+HD void sd_logmap(const double* base_in, const double* y_in, double* out) {  // sd.h:67-82
+    if (is_zero4(base_in) || is_zero4(y_in)) {
+        out[0] = out[1] = out[2] = out[3] = 0;
+        return;
+    }
+    double nb = sqrt(dot4(base_in, base_in)), ny = sqrt(dot4(y_in, y_in));
+    double base[4], y[4], temp[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        base[i] = base_in[i] / nb;
+        y[i] = y_in[i] / ny;
+    }
+    double by = dot4(base, y);
+#pragma unroll
+    for (int i = 0; i < 4; i++) temp[i] = y[i] - by * base[i];
+    double tn = sqrt(dot4(temp, temp));
+    if (tn == 0) {
+        out[0] = out[1] = out[2] = out[3] = 0;
+        return;
+    }
+    double d = sd_distance(base, y);
+#pragma unroll
+    for (int i = 0; i < 4; i++) out[i] = d * temp[i] / tn;
+}
+HD void sd_transport(const double* v, const double* base1, const double* base2, double* out) {  // sd.h:87-99
+    out[0] = v[0];
+    out[1] = v[1];
+    out[2] = v[2];
+    out[3] = v[3];
+    if (is_zero4(base1) || is_zero4(base2)) return;
+    double d = sd_distance(base1, base2);
+    double dist_square = d * d;
+    if (dist_square == 0) return;
+    double l12[4], l21[4];
+    sd_logmap(base1, base2, l12);
+    sd_logmap(base2, base1, l21);
+    double f = dot4(l12, v) / dist_square;
+#pragma unroll
+    for (int i = 0; i < 4; i++) out[i] = v[i] - f * (l12[i] + l21[i]);
+}
+// -2 * H(q*) * v, H = dQuatToDxJac (sd.h:23-27)
+HD void minus2H_times(const double* q, const double* v, double* o) {
+    o[0] = (-2.0 * -q[1]) * v[0] + (-2.0 * q[0]) * v[1] + (-2.0 * -q[3]) * v[2] + (-2.0 * q[2]) * v[3];
+    o[1] = (-2.0 * -q[2]) * v[0] + (-2.0 * q[3]) * v[1] + (-2.0 * q[0]) * v[2] + (-2.0 * -q[1]) * v[3];
+    o[2] = (-2.0 * -q[3]) * v[0] + (-2.0 * -q[2]) * v[1] + (-2.0 * q[1]) * v[2] + (-2.0 * q[0]) * v[3];
+}
+
+// ---- task evaluation -----------------------------------------------------------------------------------
+// EE state of task `tk` at the joint state (q, dq) of the whole system (robot view + optional transform).
+HD void task_ee(const DevProblem& P, const DevTask& tk, const double* q, const double* dq, EEState& e) {
+    const DevRobot& rb = P.robots[tk.robot];
+    if (rb.kind == ILQRB_ROBOT_2D) robot2d_update_kinematics(rb.lengths, rb.dof, q + tk.joint_offset, dq + tk.joint_offset, e);
+    else kdl_update_kinematics(rb.segs, rb.n_segments, rb.dof, q + tk.joint_offset, dq + tk.joint_offset, e);
+    if (tk.has_transform) apply_transform(tk.T, rb.dof, e);
+}
+
+// task vector f(x) of one task: PosOrnPlannerSys::getFxJac (PosOrnPlannerSys.cpp:80-102), PosOrnTimePlannerSys::getFxJac
+// (PosOrnTimePlannerSys.cpp:85-112); layout [p, quat, (dp, dquat), (t)]; POSITION: [p, (dp)]
+HD void task_fx(const DevProblem& P, const DevTask& tk, const EEState& e, double t, double* fx) {
+    if (P.sys_kind == ILQRB_SYS_POSITION) {
+        const int car = tk.nt_t / P.nb_deriv;
+        for (int i = 0; i < car; i++) fx[i] = e.x[i];
+        if (P.nb_deriv == 2)
+            for (int i = 0; i < car; i++) fx[car + i] = e.dx[i];
+        return;
+    }
+    fx[0] = e.x[0];
+    fx[1] = e.x[1];
+    fx[2] = e.x[2];
+    fx[3] = e.quat[0];
+    fx[4] = e.quat[1];
+    fx[5] = e.quat[2];
+    fx[6] = e.quat[3];
+    int o = 7;
+    if (P.nb_deriv == 2) {
+        fx[7] = e.dx[0];
+        fx[8] = e.dx[1];
+        fx[9] = e.dx[2];
+        // SimulationInterface::getEEAngVelQuat = (.5 * H(quat)^T) * w   (SimulationInterface.cpp:69-73)
+        const double* qq = e.quat;
+        fx[10] = (.5 * -qq[1]) * e.w[0] + (.5 * -qq[2]) * e.w[1] + (.5 * -qq[3]) * e.w[2];
+        fx[11] = (.5 * qq[0]) * e.w[0] + (.5 * qq[3]) * e.w[1] + (.5 * -qq[2]) * e.w[2];
+        fx[12] = (.5 * -qq[3]) * e.w[0] + (.5 * qq[0]) * e.w[1] + (.5 * qq[1]) * e.w[2];
+        fx[13] = (.5 * qq[2]) * e.w[0] + (.5 * -qq[1]) * e.w[1] + (.5 * qq[0]) * e.w[2];
+        o = 14;
+    }
+    if (P.time) fx[o] = t;
+}
+
+// Keypoint::diff — PosOrnKeypoint.cpp:24-45, SpacetimeKeypoint.cpp:19-24; tg = one ILQRB_KP_STRIDE record
+HD void task_residual(const DevProblem& P, const DevTask& tk, const double* fx, const double* tg, double* res) {
+    const int nd = P.nb_deriv;
+    if (P.sys_kind == ILQRB_SYS_POSITION) {
+        const int car = tk.nt_t / nd;
+        bool zero = true;
+        for (int i = 0; i < tk.nt_t; i++) zero = zero && (fabs(fx[i]) <= 1e-12);
+        for (int i = 0; i < tk.r_t; i++) res[i] = 0;
+        if (!zero) {
+            for (int i = 0; i < car; i++) res[i] = tg[i] - fx[i];
+            if (nd == 2)
+                for (int i = 0; i < car; i++) res[car + i] = tg[7 + i] - fx[car + i];
+        }
+        return;
+    }
+    const int ns = 7 * nd;  // size of the PosOrn part
+    bool zero = true;
+    for (int i = 0; i < ns; i++) zero = zero && (fabs(fx[i]) <= 1e-12);
+    for (int i = 0; i < 6 * nd; i++) res[i] = 0;
+    if (!zero) {
+        res[0] = tg[0] - fx[0];
+        res[1] = tg[1] - fx[1];
+        res[2] = tg[2] - fx[2];
+        double lg[4];
+        sd_logmap(tg + 3, fx + 3, lg);
+        minus2H_times(tg + 3, lg, res + 3);
+        if (nd == 2) {
+            res[6] = tg[7] - fx[7];
+            res[7] = tg[8] - fx[8];
+            res[8] = tg[9] - fx[9];
+            double tr[4], dd[4];
+            sd_transport(fx + 10, fx + 3, tg + 3, tr);
+            dd[0] = tg[10] - tr[0];
+            dd[1] = tg[11] - tr[1];
+            dd[2] = tg[12] - tr[2];
+            dd[3] = tg[13] - tr[3];
+            minus2H_times(tg + 3, dd, res + 9);
+        }
+    }
+    if (P.time) res[6 * nd] = tg[14] - fx[ns];
+}
+
+// Task Jacobian rows of one task (r_t x n, row-major into J with leading dimension ldj):
+// PosOrnPlannerSys::getFxJac J = Jkdl or blockdiag(J,J) (PosOrnPlannerSys.cpp:87-101); time: trailing 1
+// (PosOrnTimePlannerSys.cpp:91-111); composite robots: zero outside the arm's columns; POSITION: Jt rows only.
+HD void task_jacobian(const DevProblem& P, const DevTask& tk, const EEState& e, double* J, int ldj) {
+    const DevRobot& rb = P.robots[tk.robot];
+    const int nd = P.nb_deriv, dof = P.dof;
+    for (int i = 0; i < tk.r_t; i++)
+        for (int j = 0; j < P.n; j++) J[i * ldj + j] = 0;
+    const int rows = (P.sys_kind == ILQRB_SYS_POSITION) ? tk.nt_t / nd : 6;
+    for (int blk = 0; blk < nd; blk++)
+        for (int c = 0; c < rb.dof; c++) {
+            const int col = blk * dof + tk.joint_offset + c;
+            for (int i = 0; i < rows; i++) {
+                double v = (i < 3) ? e.Jv[c][i] : e.Jw[c][i - 3];
+                J[(blk * rows + i) * ldj + col] = v;
+            }
+        }
+    if (P.time) J[(tk.r_t - 1) * ldj + (P.n - 1)] = 1;
+}
+
+// System::inspectJointLimit (System.cpp:121-142): returns q_i (and whether L_ii = penalty_ = 1) for state entry i
+HD double limit_q(const DevTask& tk, int i, double xi, bool& active) {
+    active = false;
+    if (tk.limit_weight[i] != 0) {
+        if (xi > tk.state_max[i]) {
+            active = true;
+            return tk.state_max[i] - xi;
+        } else if (xi < tk.state_min[i]) {
+            active = true;
+            return tk.state_min[i] - xi;
+        }
+    }
+    return 0.0;
+}
+
+// which keypoint (index) task tk has at timestep k, or -1  (System::getKeypoint, System.cpp:96-101)
+HD int task_kp_at(const DevTask& tk, int k) {
+    int found = -1;
+    for (int i = 0; i < tk.n_keypoints; i++)
+        if (tk.kp_timestep[i] == k) found = i;
+    return found;
+}
+
+// System::cost (System.cpp:213-234) summed over tasks as SequentialSystem::cost does (SequentialSystem.cpp:143-149).
+// x: state (n), u: control (m) — u = nullptr means zeros (cost_F, System.cpp:236-238).
+template <int N>
+HD double stage_cost(const DevProblem& P, int b, const double* x, const double* u, int k) {
+    double total = 0;
+    const int dof = P.dof;
+    for (int t = 0; t < P.n_tasks; t++) {
+        const DevTask& tk = P.tasks[t];
+        double c = 0;
+        const int kp = task_kp_at(tk, k);
+        if (kp >= 0) {
+            double dqz[MAXM];
+            const double* dq = x + dof;
+            if (P.nb_deriv == 1) {
+                for (int i = 0; i < dof; i++) dqz[i] = 0;
+                dq = dqz;
+            }
+            EEState e;
+            task_ee(P, tk, x, dq, e);
+            double fx[MAX_NTT], res[MAX_RT];
+            task_fx(P, tk, e, P.time ? x[P.n - 1] : 0.0, fx);
+            const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
+            task_residual(P, tk, fx, tg, res);
+            const int r = tk.r_t;
+            const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + kp) * r * r;
+            double dQd = 0;
+            for (int j = 0; j < r; j++) {
+                double v = 0;
+                for (int i = 0; i < r; i++) v += res[i] * Q[i * r + j];
+                dQd += v * res[j];
+            }
+            double uRu = 0;
+            if (u)
+                for (int j = 0; j < P.m; j++) uRu += (u[j] * tk.r_diag[j]) * u[j];
+            c += dQd + uRu;
+        }
+        if (tk.limits_set) {
+            double qLq = 0;
+            for (int i = 0; i < P.n; i++) {
+                bool act;
+                double qi = limit_q(tk, i, x[i], act);
+                if (act) qLq += (qi * 1.0) * qi;
+            }
+            c += qLq;
+        }
+        total += c;
+    }
+    return total;
+}
+
+// One integrator step: PosOrnPlannerSys::forwardPass (PosOrnPlannerSys.cpp:114-138) / PosOrnTimePlannerSys::forwardPass
+// (PosOrnTimePlannerSys.cpp:149-184) via SimulationInterface::sendVel / sendAcc (SimulationInterface.cpp:19-31).
+HD void dynamics_step(const DevProblem& P, double* x, const double* u) {
+    const int dof = P.dof;
+    double dt = P.dt;
+    if (P.time) {
+        const double s = u[P.m - 1];
+        dt = s * s;
+    }
+    if (P.nb_deriv == 1) {
+        for (int i = 0; i < dof; i++) x[i] += dt * u[i] + dt * dt / 2 * 0.0;
+    } else {
+        for (int i = 0; i < dof; i++) {
+            x[i] += dt * x[dof + i] + dt * dt / 2 * u[i];
+            x[dof + i] += dt * u[i];
+        }
+    }
+    if (P.time) x[P.n - 1] += dt;
+}
+
+}  // namespace ilqrb

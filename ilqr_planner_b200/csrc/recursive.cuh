@@ -1,0 +1,642 @@
+// recursive.cuh — kernels of the Recursive / AL iLQR solve path (ILQRRecursive.cpp:21-181, AL-ILQR.cpp:50-232).
+//
+//   k_rollout_init   initial rollout + cost                         ILQRRecursive.cpp:41-56
+//   k_kp_derivs      l_x, l_xx of the task cost at keypoint steps    System.cpp:248-272,286-308
+//   k_backward       Riccati recursion, one problem per warp (DMMA)  ILQRRecursive.cpp:69-97 (+ AL terms AL-ILQR.cpp:110-145)
+//   k_linesearch     all 11 alpha candidates rolled out in parallel  ILQRRecursive.cpp:101-155
+//   k_accept         sequential-rule selection, accept, early stop   ILQRRecursive.cpp:155-176 (+ AL-ILQR.cpp:189-208)
+//   k_final_fx       f(X) of the returned trajectory                 ILQRRecursive.cpp:37,51 (f_X)
+#pragma once
+#include "kin.cuh"
+#include "wmat.cuh"
+
+namespace ilqrb {
+
+constexpr int NCAND = ILQRB_N_ALPHA;  // 11
+constexpr int CAND_LANES = 16;        // lanes reserved per problem in k_linesearch
+constexpr int MAX_NC = 32;            // AL constraint rows per step
+
+// device work buffers of one handle (padded strides: ns = even(n), ms = even(m))
+struct Work {
+    int ns, ms;            // padded row strides of X / U,d ; K rows have stride ns
+    double* X;             // [B][H][ns]
+    double* U;             // [B][H-1][ms]
+    double* K;             // [B][H-1][m][ns]   time-forward index
+    double* d;             // [B][H-1][ms]
+    double* Uc;            // [B][H-1][NCAND][ms]  candidate controls
+    double* cost_c;        // [B][NCAND]
+    double* dun_c;         // [B][NCAND]  sum_k |du_k|
+    double* cost0;         // [B]
+    double* LX;            // [B][S][n]        keypoint l_x
+    double* LXX;           // [B][S][n][n]     keypoint l_xx
+    double* cost_hist;     // [B][nb_iter]
+    double* alpha_hist;    // [B][nb_iter]
+    double* alpha_last;    // [B]
+    int* done;             // [B]
+    int* iters;            // [B]
+    int* status;           // [B]
+    // AL
+    int nc, al_per_step;
+    const double* alA;     // [(H-1)|1][nc][n+m]
+    const double* alb;     // [(H-1)|1][nc]
+    double* lam;           // [B][H-1][nc]
+    double* Cs;            // [B][H-1][nc]
+    unsigned* mask;        // [B][H-1]  active-set bits (Ik diagonal without the penalty factor)
+};
+
+__device__ __forceinline__ double alpha_of(int c) { return 1.0 / (double)(1 << c); }
+
+// x0 = [q0, (dq0), (0)]   (PosOrnPlannerSys.cpp:61-69, PosOrnTimePlannerSys.cpp:55-62)
+template <int N>
+__device__ __forceinline__ void load_x0(const DevProblem& P, int b, double* x) {
+#pragma unroll
+    for (int i = 0; i < N; i++) x[i] = 0.0;
+#pragma unroll
+    for (int i = 0; i < N; i++) {
+        if (i < P.dof) x[i] = P.q0[(size_t)b * P.dof + i];
+        else if (P.nb_deriv == 2 && i < 2 * P.dof) x[i] = P.dq0[(size_t)b * P.dof + i - P.dof];
+    }
+}
+
+// one integrator step with the reference's operation order and no FMA contraction
+// (SimulationInterface.cpp:19-31: q += dt*dq + dt*dt/2*ddq ; dq += dt*ddq ; t += dt)
+template <int N>
+__device__ __forceinline__ void step_state(const DevProblem& P, double* x, const double* u) {
+    const int dof = P.dof;
+    double dt = P.dt;
+    if (P.time) {
+        const double s = u[P.m - 1];
+        dt = __dmul_rn(s, s);
+    }
+    const double hdt2 = __dmul_rn(dt, dt) / 2;
+    if (P.nb_deriv == 1) {
+#pragma unroll
+        for (int i = 0; i < N; i++)
+            if (i < dof) x[i] = __dadd_rn(x[i], __dadd_rn(__dmul_rn(dt, u[i]), __dmul_rn(hdt2, 0.0)));
+    } else {
+#pragma unroll
+        for (int i = 0; i < N / 2; i++)
+            if (i < dof) {
+                // x[dof+i] with a compile-time-bounded scan keeps x in registers
+                double v = 0.0;
+#pragma unroll
+                for (int j = 0; j < N; j++)
+                    if (j == dof + i) v = x[j];
+                x[i] = __dadd_rn(x[i], __dadd_rn(__dmul_rn(dt, v), __dmul_rn(hdt2, u[i])));
+                const double vn = __dadd_rn(v, __dmul_rn(dt, u[i]));
+#pragma unroll
+                for (int j = 0; j < N; j++)
+                    if (j == dof + i) x[j] = vn;
+            }
+    }
+    if (P.time) {
+#pragma unroll
+        for (int j = 0; j < N; j++)
+            if (j == P.n - 1) x[j] = __dadd_rn(x[j], dt);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// initial rollout: one thread per problem
+template <int N, int M>
+__global__ void __launch_bounds__(128) k_rollout_init(const DevProblem* __restrict__ Pp, Work W) {
+    const DevProblem& P = *Pp;
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= P.B) return;
+    const int H = P.H;
+    double x[N], u[M];
+    load_x0<N>(P, b, x);
+    double cost = 0.0;
+    for (int k = 0; k < H; k++) {
+        double* Xk = W.X + ((size_t)b * H + k) * W.ns;
+#pragma unroll
+        for (int i = 0; i < N; i++)
+            if (i < W.ns) Xk[i] = (i < P.n) ? x[i] : 0.0;
+        if (k == H - 1) break;
+        const double* Uk = W.U + ((size_t)b * (H - 1) + k) * W.ms;
+#pragma unroll
+        for (int i = 0; i < M; i++) u[i] = (i < P.m) ? Uk[i] : 0.0;
+        cost += stage_cost<N>(P, b, x, u, k);
+        step_state<N>(P, x, u);
+    }
+    cost += stage_cost<N>(P, b, x, nullptr, H - 1);
+    W.cost0[b] = cost;
+    W.done[b] = 0;
+    W.iters[b] = 0;
+    W.status[b] = isnan(cost) ? ILQRB_ST_NAN_COST : 0;
+    W.alpha_last[b] = 1.0;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// keypoint derivatives of the accepted trajectory: one thread per (problem, keypoint step)
+//   l_x  = sum_tasks ((-J^T) Q) diff      System.cpp:252-260
+//   l_xx = sum_tasks (J^T Q) J            System.cpp:290-296
+__global__ void __launch_bounds__(64) k_kp_derivs(const DevProblem* __restrict__ Pp, Work W) {
+    const DevProblem& P = *Pp;
+    const int S = P.n_kp_steps;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P.B * S) return;
+    const int b = idx / S, s = idx % S;
+    if (W.done[b]) return;
+    const int k = P.kp_steps[s], n = P.n, dof = P.dof;
+    const double* x = W.X + ((size_t)b * P.H + k) * W.ns;
+    double* lx = W.LX + ((size_t)b * S + s) * n;
+    double* lxx = W.LXX + ((size_t)b * S + s) * n * n;
+    for (int i = 0; i < n; i++) lx[i] = 0.0;
+    for (int i = 0; i < n * n; i++) lxx[i] = 0.0;
+    double xs[MAXN], dqz[MAXM];
+    for (int i = 0; i < n; i++) xs[i] = x[i];
+    for (int i = 0; i < dof; i++) dqz[i] = 0.0;
+    for (int t = 0; t < P.n_tasks; t++) {
+        const DevTask& tk = P.tasks[t];
+        const int kp = task_kp_at(tk, k);
+        if (kp < 0) continue;
+        EEState e;
+        task_ee(P, tk, xs, P.nb_deriv == 2 ? xs + dof : dqz, e);
+        double fx[MAX_NTT], res[MAX_RT];
+        task_fx(P, tk, e, P.time ? xs[n - 1] : 0.0, fx);
+        const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
+        task_residual(P, tk, fx, tg, res);
+        const int r = tk.r_t;
+        const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + kp) * r * r;
+        double J[MAX_RT * MAXN];
+        task_jacobian(P, tk, e, J, n);
+        // column i of J (= row i of J^T):  jq = (J^T Q)[i][:]
+        for (int i = 0; i < n; i++) {
+            double jq[MAX_RT], njq[MAX_RT];
+            for (int c = 0; c < r; c++) {
+                double a = 0.0, na = 0.0;
+                for (int a2 = 0; a2 < r; a2++) {
+                    a += J[a2 * n + i] * Q[a2 * r + c];
+                    na += (-1.0 * J[a2 * n + i]) * Q[a2 * r + c];
+                }
+                jq[c] = a;
+                njq[c] = na;
+            }
+            double g = 0.0;
+            for (int c = 0; c < r; c++) g += njq[c] * res[c];
+            lx[i] += g;
+            for (int j = 0; j < n; j++) {
+                double h = 0.0;
+                for (int c = 0; c < r; c++) h += jq[c] * J[c * n + j];
+                lxx[i * n + j] += h;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// line search: all NCAND candidates of a problem rolled out by adjacent lanes
+//   du = K (x' - x) + alpha d ; u' = u + du ; x'+ = f(x', u') ; cost += l(x', u')      ILQRRecursive.cpp:124-154
+template <int N, int M>
+__global__ void __launch_bounds__(128) k_linesearch(const DevProblem* __restrict__ Pp, Work W, int line_search) {
+    const DevProblem& P = *Pp;
+    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b = gid / CAND_LANES, c = gid % CAND_LANES;
+    if (b >= P.B || c >= NCAND) return;
+    if (W.done[b]) return;
+    if (!line_search && c > 0) return;
+    const int H = P.H, n = P.n, m = P.m, ns = W.ns, ms = W.ms;
+    const double alpha = alpha_of(c);
+    double x[N], u[M];
+    load_x0<N>(P, b, x);
+    double cost = 0.0, dun = 0.0;
+    for (int k = 0; k < H - 1; k++) {
+        const size_t bk = (size_t)b * (H - 1) + k;
+        const double* Xk = W.X + ((size_t)b * H + k) * ns;
+        const double* Kk = W.K + bk * m * ns;
+        const double* dk = W.d + bk * ms;
+        const double* Uk = W.U + bk * ms;
+        double dx[N];
+#pragma unroll
+        for (int j = 0; j < N; j++) dx[j] = (j < n) ? __dsub_rn(x[j], Xk[j]) : 0.0;
+        double nrm2 = 0.0;
+#pragma unroll
+        for (int i = 0; i < M; i++) {
+            u[i] = 0.0;
+            if (i < m) {
+                double acc = 0.0;
+#pragma unroll
+                for (int j = 0; j < N; j++)
+                    if (j < n) acc += Kk[i * ns + j] * dx[j];
+                const double du = acc + alpha * dk[i];
+                nrm2 += du * du;
+                u[i] = Uk[i] + du;
+            }
+        }
+        dun += sqrt(nrm2);
+        double* Uo = W.Uc + (bk * NCAND + c) * ms;
+#pragma unroll
+        for (int i = 0; i < M; i++)
+            if (i < ms) Uo[i] = u[i];
+        cost += stage_cost<N>(P, b, x, u, k);
+        step_state<N>(P, x, u);
+    }
+    cost += stage_cost<N>(P, b, x, nullptr, H - 1);
+    W.cost_c[(size_t)b * NCAND + c] = cost;
+    W.dun_c[(size_t)b * NCAND + c] = dun;
+}
+
+// AL: constraint values and active set of the current trajectory (AL-ILQR.cpp:21-44,71-73,189-191) and, when `upd`,
+// the multiplier update lambda = max(0, lambda + penalty * C) (AL-ILQR.cpp:202-208).  One warp per problem.
+__device__ __forceinline__ void al_constraints(const DevProblem& P, const Work& W, int b, int lane, bool upd, double penalty_next) {
+    const int H = P.H, n = P.n, m = P.m, ns = W.ns, ms = W.ms;
+    const int nc = W.nc, nsu = n + m;
+    for (int k = 0; k < H - 1; k++) {
+        const size_t bk = (size_t)b * (H - 1) + k;
+        const double* Ac = W.alA + (size_t)(W.al_per_step ? k : 0) * nc * nsu;
+        const double* bc = W.alb + (size_t)(W.al_per_step ? k : 0) * nc;
+        const double* Xk = W.X + ((size_t)b * H + k) * ns;
+        const double* Uk = W.U + bk * ms;
+        bool act = false;
+        if (lane < nc) {
+            double g = 0.0;
+            for (int j = 0; j < n; j++) g += Ac[lane * nsu + j] * Xk[j];
+            for (int j = 0; j < m; j++) g += Ac[lane * nsu + n + j] * Uk[j];
+            g = g - bc[lane];
+            const double lam = W.lam[bk * nc + lane];
+            act = !(g < 0 && lam == 0);
+            W.Cs[bk * nc + lane] = g;
+            if (upd) {
+                const double v = lam + penalty_next * g;
+                W.lam[bk * nc + lane] = (v < 0.0) ? 0.0 : v;  // cwiseMax(0)
+            }
+        }
+        const unsigned bits = __ballot_sync(0xffffffffu, act);
+        if (lane == 0) W.mask[bk] = bits;
+    }
+}
+__global__ void __launch_bounds__(128) k_al_init(const DevProblem* __restrict__ Pp, Work W) {
+    const DevProblem& P = *Pp;
+    const int lane = threadIdx.x & 31;
+    const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (b >= P.B) return;
+    al_constraints(P, W, b, lane, false, 0.0);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// accept: one warp per problem.
+//   candidate choice = the reference's do/while (ILQRRecursive.cpp:107-155): first alpha in 1, 1/2, .. whose cost is
+//   not (>= cost0 or NaN); alpha = 2^-10 is taken unconditionally (Q2).  Then X,U <- candidate; early-stop test
+//   (ILQRRecursive.cpp:174: alpha*sqrt(sum|du|) < 1e-3 && cost < 1e-3 ; AL-ILQR.cpp:225 without the cost test).
+//   AL: Cs / active set of the accepted rollout (AL-ILQR.cpp:189-191) and multiplier update (AL-ILQR.cpp:202-208).
+template <int N, int M>
+__global__ void __launch_bounds__(128) k_accept(const DevProblem* __restrict__ Pp, Work W, int it, int nb_iter, int line_search, int early_stop, int al,
+                                                int lag_update_step, double penalty_next) {
+    const DevProblem& P = *Pp;
+    const int lane = threadIdx.x & 31;
+    const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (b >= P.B) return;
+    if (W.done[b]) return;
+    const int H = P.H, n = P.n, m = P.m, ns = W.ns, ms = W.ms, dof = P.dof;
+    const double cost0 = W.cost0[b];
+    int sel = 0;
+    if (line_search) {
+        sel = NCAND - 1;
+        for (int c = 0; c < NCAND; c++) {
+            const double cc = W.cost_c[(size_t)b * NCAND + c];
+            if (!((cc >= cost0) || isnan(cc))) {
+                sel = c;
+                break;
+            }
+        }
+    }
+    const double alpha = alpha_of(sel);
+    const double newCost = W.cost_c[(size_t)b * NCAND + sel];
+    const double dun = W.dun_c[(size_t)b * NCAND + sel];
+    // copy U and recompute X with the same recurrence as the candidate rollout
+    double xq = 0.0, xv = 0.0, xt = 0.0;  // lane i < dof owns joint i ; lane 0 also owns t
+    if (lane < dof) {
+        xq = P.q0[(size_t)b * dof + lane];
+        if (P.nb_deriv == 2) xv = P.dq0[(size_t)b * dof + lane];
+    }
+    for (int k = 0; k < H - 1; k++) {
+        const size_t bk = (size_t)b * (H - 1) + k;
+        const double* Uo = W.Uc + (bk * NCAND + sel) * ms;
+        double uu = 0.0;
+        if (lane < ms) {
+            uu = Uo[lane];
+            W.U[bk * ms + lane] = uu;
+        }
+        double dt = P.dt;
+        if (P.time) {
+            const double s = __shfl_sync(0xffffffffu, uu, m - 1);
+            dt = __dmul_rn(s, s);
+        }
+        const double hdt2 = __dmul_rn(dt, dt) / 2;
+        if (lane < dof) {
+            if (P.nb_deriv == 1) {
+                xq = __dadd_rn(xq, __dadd_rn(__dmul_rn(dt, uu), __dmul_rn(hdt2, 0.0)));
+            } else {
+                xq = __dadd_rn(xq, __dadd_rn(__dmul_rn(dt, xv), __dmul_rn(hdt2, uu)));
+                xv = __dadd_rn(xv, __dmul_rn(dt, uu));
+            }
+        }
+        xt = __dadd_rn(xt, dt);
+        double* Xn = W.X + ((size_t)b * H + k + 1) * ns;
+        if (lane < dof) {
+            Xn[lane] = xq;
+            if (P.nb_deriv == 2) Xn[dof + lane] = xv;
+        }
+        if (P.time && lane == 0) Xn[n - 1] = xt;
+    }
+    __syncwarp();
+    if (al) al_constraints(P, W, b, lane, ((it + 1) % lag_update_step) == 0, penalty_next);
+    if (lane == 0) {
+        W.cost0[b] = newCost;
+        W.cost_hist[(size_t)b * nb_iter + it] = newCost;
+        W.alpha_hist[(size_t)b * nb_iter + it] = alpha;
+        W.alpha_last[b] = alpha;
+        W.iters[b] = it + 1;
+        int st = W.status[b];
+        if (isnan(newCost)) st |= ILQRB_ST_NAN_COST;
+        bool stop = early_stop && (alpha * sqrt(dun) < 1e-3) && (al || newCost < 1e-3);
+        if (stop) {
+            st |= ILQRB_ST_EARLY_STOP;
+            W.done[b] = 1;
+        }
+        W.status[b] = st;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// f(X) for the returned trajectory: one thread per (problem, timestep)
+__global__ void __launch_bounds__(128) k_final_fx(const DevProblem* __restrict__ Pp, Work W, double* __restrict__ fX) {
+    const DevProblem& P = *Pp;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P.B * P.H) return;
+    const int b = idx / P.H, k = idx % P.H;
+    const int n = P.n, dof = P.dof;
+    const double* x = W.X + ((size_t)b * P.H + k) * W.ns;
+    double xs[MAXN], dqs[MAXM];
+    for (int i = 0; i < n; i++) xs[i] = x[i];
+    // f_X[k] comes from forwardPass(k-1): the robot's dq is the last command (nd=1: u_{k-1}; k=0: dq0) — only the
+    // velocity part of fx depends on it, which exists for nb_deriv == 2 where dq is part of the state.
+    for (int i = 0; i < dof; i++) dqs[i] = (P.nb_deriv == 2) ? xs[dof + i] : 0.0;
+    double* out = fX + (size_t)idx * P.nt;
+    for (int t = 0; t < P.n_tasks; t++) {
+        const DevTask& tk = P.tasks[t];
+        EEState e;
+        task_ee(P, tk, xs, dqs, e);
+        task_fx(P, tk, e, P.time ? xs[n - 1] : 0.0, out + tk.fx_off);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// backward Riccati pass: one problem per warp, all blocks in shared memory, products on the FP64 tensor pipe.
+// NXT, NUT: 8-tiles of the (augmented) state and control dimensions: 8*NXT >= n+1, 8*NUT >= m.
+// The vectors ride in column n of the state-indexed matrices:  Paug = [P | p], QuxQu = [Qux | Qu], Kd = [K | d].
+template <int NXT, int NUT>
+struct BwdSmem {
+    static constexpr int NX = 8 * NXT, NU = 8 * NUT, LDX = NX + 4, LDU = NU + 4;
+    static constexpr int SZ_XX = NX * LDX, SZ_UX = NU * LDX, SZ_XU = NX * LDU, SZ_UU = NU * LDU;
+    // per warp: Paug, AtP, QxxQx (XX) ; BtP, QuxQu, Kd (UX) ; Qxu (XU) ; Quu (UU).
+    // KtQuu reuses AtP and Inv reuses BtP (both dead by then; XX >= XU and UX >= UU because NX >= NU).
+    static_assert(NXT >= NUT, "state tiles must cover control tiles");
+    static constexpr int PER_WARP = 3 * SZ_XX + 3 * SZ_UX + 1 * SZ_XU + 1 * SZ_UU;
+    static constexpr int DYN = SZ_XX + SZ_XU;  // A_aug, B
+};
+
+template <int NXT, int NUT, bool TIME, bool AL, int WARPS, int MINB>
+__global__ void __launch_bounds__(32 * WARPS, MINB) k_backward(const DevProblem* __restrict__ Pp, Work W, double penalty_frozen) {
+    using S = BwdSmem<NXT, NUT>;
+    constexpr int NX = S::NX, NU = S::NU, LDX = S::LDX, LDU = S::LDU;
+    extern __shared__ double smem[];
+    const DevProblem& P = *Pp;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int b = blockIdx.x * WARPS + wid;
+    const int n = P.n, m = P.m, H = P.H, ns = W.ns, ms = W.ms, dof = P.dof;
+    // dynamics matrices: shared by the block when constant, per warp for time systems
+    double* Aaug = smem + (TIME ? (size_t)wid * S::DYN : 0);
+    double* Bm = Aaug + S::SZ_XX;
+    double* base = smem + (TIME ? WARPS : 1) * S::DYN + (size_t)wid * S::PER_WARP;
+    double* Paug = base;
+    double* AtP = Paug + S::SZ_XX;
+    double* QxxQx = AtP + S::SZ_XX;
+    double* BtP = QxxQx + S::SZ_XX;
+    double* QuxQu = BtP + S::SZ_UX;
+    double* Kd = QuxQu + S::SZ_UX;
+    double* Qxu = Kd + S::SZ_UX;
+    double* Quu = Qxu + S::SZ_XU;
+    double* KtQuu = AtP;  // alias (AtP is dead once Qxu is formed)
+    double* Inv = BtP;    // alias (BtP is dead once Quu is formed)
+
+    // ---- A_aug = blockdiag(A, 1), B  (PosOrnPlannerSys.cpp:115-128) ----
+    if (!TIME) {
+        for (int e = threadIdx.x; e < NX * LDX; e += 32 * WARPS) {
+            const int i = e / LDX, j = e % LDX;
+            double v = 0.0;
+            if (i == j && i <= n) v = 1.0;
+            if (P.nb_deriv == 2 && i < dof && j == dof + i) v = 1.0 * P.dt;
+            Aaug[e] = v;
+        }
+        for (int e = threadIdx.x; e < NX * LDU; e += 32 * WARPS) {
+            const int i = e / LDU, j = e % LDU;
+            double v = 0.0;
+            if (P.nb_deriv == 1) {
+                if (i == j && i < dof) v = 1.0 * P.dt;
+            } else {
+                if (i < dof && j == i) v = 1.0 * P.dt * P.dt / 2;
+                if (i >= dof && i < 2 * dof && j == i - dof) v = 1.0 * P.dt;
+            }
+            Bm[e] = v;
+        }
+        __syncthreads();
+    }
+    if (b >= P.B) return;
+    if (W.done[b]) return;
+
+    // l_xx | l_x of timestep k into dst (NX x LDX):  keypoint part from k_kp_derivs + joint-limit part (System.cpp:263-269,299-305)
+    auto fill_L = [&](double* dst, int k) {
+        int s = -1;
+        for (int i = 0; i < P.n_kp_steps; i++)
+            if (P.kp_steps[i] == k) s = i;
+        const double* lx = s >= 0 ? W.LX + ((size_t)b * P.n_kp_steps + s) * n : nullptr;
+        const double* lxx = s >= 0 ? W.LXX + ((size_t)b * P.n_kp_steps + s) * n * n : nullptr;
+        for (int e = lane; e < NX * LDX; e += 32) {
+            const int i = e / LDX, j = e % LDX;
+            double v = 0.0;
+            if (s >= 0 && i < n) {
+                if (j < n) v = lxx[i * n + j];
+                else if (j == n) v = lx[i];
+            }
+            dst[e] = v;
+        }
+        __syncwarp();
+        if (P.any_limits) {
+            const double* Xk = W.X + ((size_t)b * H + k) * ns;
+            if (lane < n) {
+                for (int t = 0; t < P.n_tasks; t++) {
+                    const DevTask& tk = P.tasks[t];
+                    if (!tk.limits_set) continue;
+                    bool act;
+                    const double q = limit_q(tk, lane, Xk[lane], act);
+                    if (act) {
+                        dst[lane * LDX + lane] += 1.0 * 1.0;      // L^T L
+                        dst[lane * LDX + n] += -1.0 * q;          // -L^T q
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    };
+
+    // terminal: P = cost_F_xx, p = cost_F_x  (ILQRRecursive.cpp:69-71)
+    fill_L(Paug, H - 1);
+    bool spd = true;
+
+    for (int k = H - 2; k >= 0; k--) {
+        const size_t bk = (size_t)b * (H - 1) + k;
+        const double* Uk = W.U + bk * ms;
+        if (TIME) {
+            // per-step dynamics (PosOrnTimePlannerSys.cpp:149-177), from the accepted trajectory (Q15: post-step velocity)
+            const double sq = Uk[m - 1];
+            const double dt = sq * sq;
+            const double* Xn = W.X + ((size_t)b * H + k + 1) * ns;
+            for (int e = lane; e < NX * LDX; e += 32) {
+                const int i = e / LDX, j = e % LDX;
+                double v = 0.0;
+                if (i == j && i <= n) v = 1.0;
+                if (P.nb_deriv == 2 && i < dof && j == dof + i) v = dt * 1.0;
+                Aaug[e] = v;
+            }
+            for (int e = lane; e < NX * LDU; e += 32) {
+                const int i = e / LDU, j = e % LDU;
+                double v = 0.0;
+                if (P.nb_deriv == 1) {
+                    if (i < dof && j == i) v = 1.0 * dt;
+                    if (i < dof && j == m - 1) v = 2 * sq * Uk[i];
+                } else {
+                    if (i < dof && j == i) v = 1.0 * dt * dt / 2;
+                    if (i >= dof && i < 2 * dof && j == i - dof) v = 1.0 * dt;
+                    if (i < dof && j == m - 1) v = 2 * sq * Xn[dof + i] + 2 * sq * sq * sq * Uk[i];
+                    if (i >= dof && i < 2 * dof && j == m - 1) v = 2 * sq * Uk[i - dof];
+                }
+                if (i == n - 1 && j == m - 1) v = 2 * sq;
+                Bm[e] = v;
+            }
+        }
+        // QuxQu <- [cost_ux = 0 | cost_u = R u]  (System.cpp:274-280) ; QxxQx <- [l_xx | l_x]
+        for (int e = lane; e < NU * LDX; e += 32) {
+            const int i = e / LDX, j = e % LDX;
+            QuxQu[e] = (j == n && i < m) ? P.r_diag[i] * Uk[i] : 0.0;
+        }
+        fill_L(QxxQx, k);  // ends with __syncwarp
+
+        // BtP = B^T [P|p]
+        wm_gemm<NUT, NXT, NXT, true, false, false, false>(BtP, LDX, Bm, LDU, Paug, LDX, lane);
+        // [Qux|Qu] += BtP A_aug           ILQRRecursive.cpp:82,86
+        wm_gemm<NUT, NXT, NXT, false, false, true, false>(QuxQu, LDX, BtP, LDX, Aaug, LDX, lane);
+        // Quu = R + BtP B                 ILQRRecursive.cpp:83
+        for (int e = lane; e < NU * LDU; e += 32) {
+            const int i = e / LDU, j = e % LDU;
+            Quu[e] = (i == j && i < m) ? P.r_diag[i] : 0.0;
+        }
+        __syncwarp();
+        wm_gemm<NUT, NUT, NXT, false, false, true, false>(Quu, LDU, BtP, LDX, Bm, LDU, lane);
+        // AtP = A^T [P|p] ; [Qxx|Qx] += AtP A_aug ; Qxu = AtP B      ILQRRecursive.cpp:84,85,87
+        wm_gemm<NXT, NXT, NXT, true, false, false, false>(AtP, LDX, Aaug, LDX, Paug, LDX, lane);
+        wm_gemm<NXT, NXT, NXT, false, false, true, false>(QxxQx, LDX, AtP, LDX, Aaug, LDX, lane);
+        wm_gemm<NXT, NUT, NXT, false, false, false, false>(Qxu, LDU, AtP, LDX, Bm, LDU, lane);
+
+        if (AL) {
+            // AL terms (AL-ILQR.cpp:116-134): ckx = A[:, :n], cku = A[:, n:], Ik = penalty * diag(active), lic = lambda + Ik c
+            const int nc = W.nc, nsu = n + m;
+            const double* Ac = W.alA + (size_t)(W.al_per_step ? k : 0) * nc * nsu;
+            const unsigned bits = W.mask[bk];
+            const double* lam = W.lam + bk * nc;
+            const double* cs = W.Cs + bk * nc;
+            // element loops: every lane owns entries (i, j) of the four Q blocks
+            for (int e = lane; e < m * (n + 1); e += 32) {  // Qux | Qu
+                const int i = e / (n + 1), j = e % (n + 1);
+                double acc = 0.0;
+                for (int r = 0; r < nc; r++) {
+                    const double ik = ((bits >> r) & 1u) ? penalty_frozen : 0.0;
+                    const double cu = Ac[r * nsu + n + i];
+                    if (j < n) acc += (cu * ik) * Ac[r * nsu + j];
+                    else acc += cu * (lam[r] + ik * cs[r]);
+                }
+                QuxQu[i * LDX + j] += acc;
+            }
+            for (int e = lane; e < m * m; e += 32) {  // Quu
+                const int i = e / m, j = e % m;
+                double acc = 0.0;
+                for (int r = 0; r < nc; r++) {
+                    const double ik = ((bits >> r) & 1u) ? penalty_frozen : 0.0;
+                    acc += (Ac[r * nsu + n + i] * ik) * Ac[r * nsu + n + j];
+                }
+                Quu[i * LDU + j] += acc;
+            }
+            for (int e = lane; e < n * (n + 1); e += 32) {  // Qxx | Qx
+                const int i = e / (n + 1), j = e % (n + 1);
+                double acc = 0.0;
+                for (int r = 0; r < nc; r++) {
+                    const double ik = ((bits >> r) & 1u) ? penalty_frozen : 0.0;
+                    const double cx = Ac[r * nsu + i];
+                    if (j < n) acc += (cx * ik) * Ac[r * nsu + j];
+                    else acc += cx * (lam[r] + ik * cs[r]);
+                }
+                QxxQx[i * LDX + j] += acc;
+            }
+            for (int e = lane; e < n * m; e += 32) {  // Qxu
+                const int i = e / m, j = e % m;
+                double acc = 0.0;
+                for (int r = 0; r < nc; r++) {
+                    const double ik = ((bits >> r) & 1u) ? penalty_frozen : 0.0;
+                    acc += (Ac[r * nsu + i] * ik) * Ac[r * nsu + n + j];
+                }
+                Qxu[i * LDU + j] += acc;
+            }
+            __syncwarp();
+        }
+
+        // Inv = (Quu + 1e-6 I)^-1        ILQRRecursive.cpp:89
+        for (int e = lane; e < NU * LDU; e += 32) {
+            const int i = e / LDU, j = e % LDU;
+            double v = Quu[e];
+            if (i == j) v = (i < m) ? v + 1e-6 * 1.0 : 1.0;
+            Inv[e] = v;
+        }
+        __syncwarp();
+        spd = wm_inverse_spd<NUT>(Inv, LDU, m, lane) && spd;
+        // [K|d] = -(Inv [Qux|Qu])          ILQRRecursive.cpp:90-91
+        wm_gemm<NUT, NXT, NUT, false, false, false, true>(Kd, LDX, Inv, LDU, QuxQu, LDX, lane);
+        // stream K, d to global (time-forward index)
+        {
+            double* Kg = W.K + bk * m * ns;
+            for (int e = lane; e < m * (ns / 2); e += 32) {
+                const int i = e / (ns / 2), j2 = e % (ns / 2);
+                double2 v = *reinterpret_cast<const double2*>(Kd + i * LDX + 2 * j2);
+                if (2 * j2 + 1 >= n) v.y = 0.0;
+                *reinterpret_cast<double2*>(Kg + i * ns + 2 * j2) = v;
+            }
+            if (lane < ms) W.d[bk * ms + lane] = (lane < m) ? Kd[lane * LDX + n] : 0.0;
+        }
+        // KtQuu = K^T Quu   (row n carries d^T Quu and is discarded below)
+        wm_gemm<NXT, NUT, NUT, true, false, false, false>(KtQuu, LDU, Kd, LDX, Quu, LDU, lane);
+        // [P|p] = (([Qxx|Qx] + KtQuu [K|d]) + K^T [Qux|Qu]) + Qxu [K|d]      ILQRRecursive.cpp:93-94
+        {
+            const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+            for (int rt = 0; rt < NXT; rt++)
+#pragma unroll
+                for (int ct = 0; ct < NXT; ct++) {
+                    double a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0, c0 = 0.0, c1 = 0.0;
+                    wm_tile_acc<NUT, false, false>(a0, a1, KtQuu, LDU, Kd, LDX, rt, ct, g, t);
+                    wm_tile_acc<NUT, true, false>(b0, b1, Kd, LDX, QuxQu, LDX, rt, ct, g, t);
+                    wm_tile_acc<NUT, false, false>(c0, c1, Qxu, LDU, Kd, LDX, rt, ct, g, t);
+                    const int i = 8 * rt + g, j = 8 * ct + 2 * t;
+                    const double2 q = *reinterpret_cast<const double2*>(QxxQx + i * LDX + j);
+                    double v0 = ((q.x + a0) + b0) + c0;
+                    double v1 = ((q.y + a1) + b1) + c1;
+                    if (i >= n || j > n) v0 = 0.0;
+                    if (i >= n || j + 1 > n) v1 = 0.0;
+                    *reinterpret_cast<double2*>(Paug + i * LDX + j) = make_double2(v0, v1);
+                }
+            __syncwarp();
+        }
+    }
+    if (!spd && lane == 0) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
+}
+
+}  // namespace ilqrb

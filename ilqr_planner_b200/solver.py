@@ -1,0 +1,169 @@
+"""Thin Python front of the C ABI: one `Handle` = one batch of problems resident on one GPU."""
+import ctypes as C
+
+import numpy as np
+
+from . import cabi
+from .problem import ProblemBatch, ResultBuffers
+
+
+def make_al_desc(A, b, lambda0, lag_update_step, penalty, scaling_factor):
+    A = np.ascontiguousarray(np.asarray(A, dtype=np.float64))
+    b = np.ascontiguousarray(np.asarray(b, dtype=np.float64))
+    lam = np.ascontiguousarray(np.asarray(lambda0, dtype=np.float64))
+    per_step = 1 if A.ndim == 3 else 0
+    al = cabi.ALDesc(A.shape[-2], per_step, cabi.dptr(A), cabi.dptr(b), cabi.dptr(lam), int(lag_update_step), 0, float(penalty), float(scaling_factor))
+    al._keep = (A, b, lam)
+    return al
+
+
+def make_batch_desc(Q=None, psi=None):
+    Q = None if Q is None else np.ascontiguousarray(np.asarray(Q, dtype=np.float64))
+    psi = None if psi is None else np.ascontiguousarray(np.asarray(psi, dtype=np.float64))
+    bd = cabi.BatchDesc(cabi.dptr(Q), cabi.dptr(psi), 0 if psi is None else psi.shape[1], 0)
+    bd._keep = (Q, psi)
+    return bd
+
+
+def opts(nb_iter, line_search=True, early_stop=False):
+    return cabi.SolveOpts(int(nb_iter), int(bool(line_search)), int(bool(early_stop)), 0)
+
+
+class Handle:
+    def __init__(self, pb: ProblemBatch, device=0, stream=None):
+        self.pb = pb
+        self.lib = cabi.load()
+        self.desc = pb.to_desc()
+        self.h = C.c_void_p()
+        cabi.check(self.lib.ilqrb_create(C.byref(self.desc), int(device), C.byref(self.h)))
+        if stream is not None:
+            cabi.check(self.lib.ilqrb_set_stream(self.h, C.c_void_p(stream)))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.ilqrb_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _u(self, U0):
+        if U0 is None:
+            return None
+        return np.ascontiguousarray(np.asarray(U0, dtype=np.float64).reshape(self.pb.batch, (self.pb.horizon - 1) * self.pb.m))
+
+    # ---- solvers: host buffers in, host buffers out
+    def solve_recursive(self, U0, nb_iter, line_search=True, early_stop=False, out=None):
+        out = out or ResultBuffers(self.pb, nb_iter, "recursive")
+        U0 = self._u(U0)
+        o = opts(nb_iter, line_search, early_stop)
+        cabi.check(self.lib.ilqrb_solve_recursive(self.h, cabi.dptr(U0), C.byref(o), C.byref(out.res)))
+        return out
+
+    def solve_al(self, U0, A, b, lambda0, nb_iter, lag_update_step, penalty, scaling_factor, line_search=True, early_stop=False, out=None):
+        al = make_al_desc(A, b, lambda0, lag_update_step, penalty, scaling_factor)
+        out = out or ResultBuffers(self.pb, nb_iter, "al", nc=al.nc)
+        U0 = self._u(U0)
+        o = opts(nb_iter, line_search, early_stop)
+        cabi.check(self.lib.ilqrb_solve_al(self.h, cabi.dptr(U0), C.byref(al), C.byref(o), C.byref(out.res)))
+        return out
+
+    def solve_batch(self, u0, nb_iter, early_stop=False, Q=None, psi=None, out=None):
+        bd = make_batch_desc(Q, psi)
+        out = out or ResultBuffers(self.pb, nb_iter, "batch")
+        u0 = self._u(u0)
+        o = opts(nb_iter, True, early_stop)
+        cabi.check(self.lib.ilqrb_solve_batch(self.h, cabi.dptr(u0), C.byref(bd), C.byref(o), C.byref(out.res)))
+        return out
+
+    # ---- split entry points (upload once / run async / download)
+    def upload_u0(self, U0):
+        self._u0_keep = self._u(U0)
+        cabi.check(self.lib.ilqrb_upload_u0(self.h, cabi.dptr(self._u0_keep)))
+
+    def run_recursive(self, nb_iter, line_search=True, early_stop=False):
+        o = opts(nb_iter, line_search, early_stop)
+        cabi.check(self.lib.ilqrb_run_recursive(self.h, C.byref(o)))
+
+    def run_al(self, al, nb_iter, line_search=True, early_stop=False):
+        o = opts(nb_iter, line_search, early_stop)
+        cabi.check(self.lib.ilqrb_run_al(self.h, C.byref(al), C.byref(o)))
+
+    def run_batch(self, bd, nb_iter, early_stop=False):
+        o = opts(nb_iter, True, early_stop)
+        cabi.check(self.lib.ilqrb_run_batch(self.h, C.byref(bd), C.byref(o)))
+
+    def download(self, out):
+        cabi.check(self.lib.ilqrb_download(self.h, C.byref(out.res)))
+        return out
+
+    def synchronize(self):
+        cabi.check(self.lib.ilqrb_synchronize(self.h))
+
+    # ---- test hooks
+    def rollout(self, U):
+        pb = self.pb
+        B, H = pb.batch, pb.horizon
+        U = np.ascontiguousarray(np.asarray(U, dtype=np.float64).reshape(B, H - 1, pb.m))
+        X, fX, J, cost = np.empty((B, H, pb.n)), np.empty((B, H, pb.nt)), np.empty((B, H, pb.r, pb.n)), np.empty(B)
+        cabi.check(self.lib.ilqrb_rollout(self.h, cabi.dptr(U), cabi.dptr(X), cabi.dptr(fX), cabi.dptr(J), cabi.dptr(cost)))
+        return X, fX, J, cost
+
+    def kinematics(self, robot, q, dq=None):
+        dof = self.pb.robots[robot].dof
+        q = np.ascontiguousarray(np.asarray(q, dtype=np.float64).reshape(-1, dof))
+        nq = q.shape[0]
+        dq = np.zeros_like(q) if dq is None else np.ascontiguousarray(np.asarray(dq, dtype=np.float64).reshape(-1, dof))
+        x, quat, J, dx, w = np.zeros((nq, 3)), np.zeros((nq, 4)), np.zeros((nq, 6, dof)), np.zeros((nq, 3)), np.zeros((nq, 3))
+        cabi.check(self.lib.ilqrb_kinematics(self.h, robot, nq, cabi.dptr(q), cabi.dptr(dq), cabi.dptr(x), cabi.dptr(quat), cabi.dptr(J),
+                                             cabi.dptr(dx), cabi.dptr(w)))
+        return x, quat, J, dx, w
+
+    # ---- profiling
+    def set_profiling(self, on):
+        cabi.check(self.lib.ilqrb_set_profiling(self.h, int(on)))
+
+    def reset_profile(self):
+        cabi.check(self.lib.ilqrb_reset_profile(self.h))
+
+    def profile(self):
+        p = cabi.Profile()
+        cabi.check(self.lib.ilqrb_get_profile(self.h, C.byref(p)))
+        return {p.name[i].decode(): (p.ms[i], p.launches[i]) for i in range(cabi.PROF_SLOTS) if p.launches[i] > 0}
+
+    def launch_count(self):
+        return int(self.lib.ilqrb_launch_count(self.h))
+
+
+def chain_from_urdf(urdf, base, tip, transform_rpy=(0, 0, 0), transform_xyz=(0, 0, 0), is_path=False):
+    """URDF -> (segment dicts, dof) via the library's host builder ilqrb_chain_from_urdf"""
+    lib = cabi.load()
+    segs = (cabi.Segment * cabi.MAX_SEGMENTS)()
+    n, dof = C.c_int(0), C.c_int(0)
+    rpy = np.ascontiguousarray(np.asarray(transform_rpy, dtype=np.float64))
+    xyz = np.ascontiguousarray(np.asarray(transform_xyz, dtype=np.float64))
+    cabi.check(lib.ilqrb_chain_from_urdf(urdf.encode(), int(is_path), base.encode(), tip.encode(), cabi.dptr(rpy), cabi.dptr(xyz), segs,
+                                         cabi.MAX_SEGMENTS, C.byref(n), C.byref(dof)))
+    out = []
+    for i in range(n.value):
+        s = segs[i]
+        out.append(dict(joint_type=int(s.joint_type), axis=np.array(s.axis[:]), origin=np.array(s.origin[:]), tip_R=np.array(s.tip_R[:]),
+                        tip_p=np.array(s.tip_p[:])))
+    return out, dof.value
+
+
+def build_psi(kind, dim, K):
+    lib = cabi.load()
+    cols = 2 * K if kind == "linear" else K
+    out = np.zeros((dim, cols))
+    cabi.check(lib.ilqrb_build_psi(kind.encode(), int(dim), int(K), cabi.dptr(out)))
+    return out
