@@ -1,0 +1,283 @@
+#!/usr/bin/env python
+"""bench.py — iLQR problems solved/sec on B200 (BASELINE.json metric), one JSON line on stdout.
+
+A "step" = one batched Recursive-iLQR solve (20 iterations, line search on, no early stop) of configs[1]:
+4096 synthetic 7-DoF position+quaternion reaching problems, T=100, per GPU (weak scaling: every rank solves its own
+4096 problems; no collective on the data path, one final gather of the costs).
+
+  value     whole-job solves/s with U0 already resident in HBM (device-timed with CUDA events on the solve stream)
+  e2e       same metric through the C ABI call ilqrb_solve_recursive with pinned HOST buffers (H2D of U0 and D2H of
+            X, f(X), U, K, d, cost, traces inside the timed region)
+  roofline  dominant kernel (riccati_backward): algorithmic bytes / measured launch duration vs measured HBM peak;
+            roofline_fp64 adds algorithmic FP64 flops vs a DFMA peak measured here
+  cpu_baseline / --impl reference: the CPU oracle (restatement of the reference's Eigen/KDL path; the reference itself
+            cannot be built here) on all host cores, bounded sample of the same workload
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NB_ITER = 20
+BATCH_PER_GPU = 4096
+HORIZON = 100
+METRIC = "iLQR problems solved/sec (7-DoF, T=100, Recursive, 20 iterations)"
+UNIT = "solves/s"
+
+
+def workload_config(n_gpus, batch):
+    return {"workload": "configs[1]: synthetic 7-DoF KDL chain, PosOrn system, Recursive iLQR, T=100, 20 iterations, line search on, "
+                        "no early stop, batch %d per GPU" % batch,
+            "batch_per_gpu": batch, "global_batch": batch * n_gpus, "horizon": HORIZON, "nb_iter": NB_ITER, "parallelism": "problem-batch dp%d" % n_gpus,
+            "l2": "no flush: the per-iteration working set (candidate controls 250 MB + gains 159 MB + trajectories) exceeds the 126 MB L2"}
+
+
+class ClockSampler:
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.samples = []
+        self.reasons = set()
+        self._stop = threading.Event()
+        self._t = None
+
+    def _run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        while not self._stop.is_set():
+            try:
+                o = subprocess.run(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + q, "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in o.strip().split(",")]
+                self.samples.append((float(f[0]), float(f[1])))
+                for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], f[2:6]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def start(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=6)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": sorted(self.reasons)}
+        sm = sorted(s[0] for s in self.samples)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.samples[0][1], "reasons": sorted(self.reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            d = json.load(open(p))
+            return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_baseline_run(batch, threads=None):
+    """the oracle over `batch` problems of the workload on all host threads -> (solves/s, threads, seconds)"""
+    from ilqr_planner_b200 import synth
+    from oracle import oracle
+    threads = threads or oracle.hardware_threads() or os.cpu_count() or 1
+    pb = synth.config2(batch=batch, horizon=HORIZON)
+    t0 = time.perf_counter()
+    out = oracle.solve_recursive(pb, None, NB_ITER, True, False, threads=threads)
+    dt = time.perf_counter() - t0
+    return batch / dt, threads, dt, out
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    sample = 16 * max(1, (os.cpu_count() or 8) // 4)
+    for _ in range(args.warmup):
+        cpu_baseline_run(max(sample // 4, 8))
+    tot_t, tot_n, threads = 0.0, 0, 1
+    for _ in range(args.steps):
+        v, threads, dt, _ = cpu_baseline_run(sample)
+        tot_t += dt
+        tot_n += sample
+    value = tot_n / tot_t
+    desc = "each step = %d problems of the workload (of %d) solved by the CPU oracle on %d host threads" % (sample, BATCH_PER_GPU, threads)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args.gpus, BATCH_PER_GPU),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def dfma_peak_tflops(torch):
+    """FP64 peak proxy measured here: torch fp64 matmul 4096^3 (cuBLAS DGEMM), best of 5 — MEASURED_PEAKS.json has no FP64 entry"""
+    try:
+        a = torch.randn(4096, 4096, dtype=torch.float64, device="cuda")
+        b = torch.randn(4096, 4096, dtype=torch.float64, device="cuda")
+        best = 1e9
+        for _ in range(6):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch.matmul(a, b)
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return 2 * 4096 ** 3 / (best * 1e-3) / 1e12
+    except Exception:
+        return None
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=BATCH_PER_GPU, help="problems per GPU (default: the BASELINE config)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from ilqr_planner_b200 import synth
+    from ilqr_planner_b200.problem import ResultBuffers
+    from ilqr_planner_b200.solver import Handle
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    B = args.batch
+    pb = synth.config2(batch=B, horizon=HORIZON, offset=rank * B)
+    stream = torch.cuda.Stream()
+    h = Handle(pb, device=local_rank, stream=stream.cuda_stream)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput ("value") -----------------------------------------------------------------
+    h.upload_u0(None)
+    for _ in range(args.warmup):
+        h.run_recursive(NB_ITER, True, False)
+    h.synchronize()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    l0 = h.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+        for _ in range(args.steps):
+            h.run_recursive(NB_ITER, True, False)
+        e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = h.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = world * B * args.steps / (ms_max * 1e-3)
+
+    # ---- end to end through the host-buffer C ABI call ("e2e") ----------------------------------------------------
+    out = ResultBuffers(pb, NB_ITER, "recursive", pinned=True)
+    u0_pinned = torch.zeros((B, (HORIZON - 1) * pb.m), dtype=torch.float64).pin_memory()
+    u0 = u0_pinned.numpy()
+    h.solve_recursive(u0, NB_ITER, True, False, out=out)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record(stream)
+    for _ in range(args.steps):
+        h.solve_recursive(u0, NB_ITER, True, False, out=out)
+    e1.record(stream)
+    barrier()
+    ms_e2e = max(e0.elapsed_time(e1), 1e3 * (time.perf_counter() - t0) * 0.0)
+    t = torch.tensor([ms_e2e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_e2e = float(t.item())
+    e2e_value = world * B * args.steps / (ms_e2e * 1e-3)
+    h2d = u0.nbytes
+    d2h = sum(a.nbytes for a in (out.X, out.fX, out.U, out.K, out.d, out.cost, out.cost_hist, out.alpha_hist, out.iters, out.status))
+
+    # ---- final gather of the per-problem costs (the only collective; outside the data path) -----------------------
+    cost_t = torch.from_numpy(out.cost.copy()).cuda()
+    if world > 1:
+        gathered = [torch.empty_like(cost_t) for _ in range(world)] if rank == 0 else None
+        dist.gather(cost_t, gathered, dst=0)
+        all_cost = torch.cat(gathered).cpu().numpy() if rank == 0 else None
+    else:
+        all_cost = out.cost
+    # ---- per-kernel durations with event pairs (separate pass, not part of `value`) -------------------------------
+    h.set_profiling(True)
+    h.reset_profile()
+    h.run_recursive(NB_ITER, True, False)
+    prof = h.profile()
+    h.set_profiling(False)
+
+    if rank == 0:
+        n, m, H = pb.n, pb.m, pb.horizon
+        hbm_peak, peak_src = measured_peaks()
+        bw_ms, bw_n = prof.get("riccati_backward", (0.0, 1))
+        bw_avg_s = bw_ms / max(bw_n, 1) * 1e-3
+        # algorithmic bytes of one backward launch: write K,d once; read X,U once; read keypoint l_x,l_xx (SURVEY 8d share of the 133 KB/iteration)
+        alg_bytes = B * 8.0 * ((H - 1) * (m * n + m) + H * n + (H - 1) * m + 2 * (n * n + n))
+        flops_step = 4 * m * n * n + 2 * m * n * n + 2 * m * m * n + 4 * n ** 3 + 2 * n ** 3 + 2 * n * n * m + 2 * m * n + 2 * n * n + 2 * m ** 3 + 2 * m * m * n + 2 * m * m \
+            + (2 * n * m * m + 6 * n * n * m + 3 * n * n) + 6 * n * m
+        alg_flops = B * (H - 1) * float(flops_step)
+        achieved = alg_bytes / bw_avg_s / 1e9 if bw_avg_s > 0 else None
+        fp64_peak = dfma_peak_tflops(torch)
+        tot_ms = sum(v[0] for v in prof.values())
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
+                "ms_per_iteration": ms_max / args.steps / NB_ITER, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": workload_config(world, B), "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
+                "gpu_launches": int(launches),
+                "roofline": {"kernel": "k_backward (riccati_backward)", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                             "frac": (achieved / hbm_peak) if achieved else None, "traffic": None, "peak_source": peak_src,
+                             "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": bw_avg_s * 1e3, "share_of_step": bw_ms / tot_ms if tot_ms else None},
+                "roofline_fp64": {"kernel": "k_backward", "bound": "fp64", "algorithmic_flops_per_launch": alg_flops,
+                                  "achieved": alg_flops / bw_avg_s / 1e12 if bw_avg_s > 0 else None, "peak": fp64_peak, "unit": "TFLOP/s",
+                                  "frac": (alg_flops / bw_avg_s / 1e12 / fp64_peak) if (bw_avg_s > 0 and fp64_peak) else None,
+                                  "peak_source": "cuBLAS DGEMM 4096^3 measured in this run"},
+                "kernel_ms_per_solve": {k: v[0] for k, v in prof.items()},
+                "final_cost_mean": float(np.nanmean(all_cost)), "problems_with_nan": int(np.isnan(all_cost).sum())}
+        if world == 1 and not args.no_cpu_baseline:
+            sample = 512
+            v, threads, dt, ref = cpu_baseline_run(sample)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": "first %d problems of the workload, all %d iterations, CPU oracle on %d threads, %.1f s" % (sample, NB_ITER, threads, dt)}
+            # same problems -> same answers (sanity, not a timing)
+            line["cpu_gpu_cost_max_rel_diff"] = float(np.nanmax(np.abs(ref.cost - out.cost[:sample]) / np.maximum(np.abs(ref.cost), 1e-300)))
+        print(json.dumps(line), flush=True)
+    h.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
