@@ -38,6 +38,8 @@ def load():
     lib.oracle_solve_batch.argtypes = [P(cabi.ProblemDesc), cabi.c_double_p, P(cabi.BatchDesc), P(cabi.SolveOpts), P(cabi.Result), C.c_int]
     lib.oracle_rollout.argtypes = [P(cabi.ProblemDesc), cabi.c_double_p, cabi.c_double_p, cabi.c_double_p, cabi.c_double_p, cabi.c_double_p, C.c_int]
     lib.oracle_kinematics.argtypes = [P(cabi.ProblemDesc), C.c_int, C.c_int] + [cabi.c_double_p] * 7
+    lib.oracle_set_margin_out.argtypes = [cabi.c_double_p]
+    lib.oracle_set_margin_out.restype = None
     _lib = lib
     return lib
 
@@ -51,13 +53,28 @@ def hardware_threads():
     return int(load().oracle_hardware_threads())
 
 
+class _margins:
+    """attach a [B][nb_iter] `margin_hist` (line-search decision margins, a test aid) to the result of a solve"""
+
+    def __init__(self, out, pb, nb_iter):
+        self.out = out
+        out.margin_hist = np.full((pb.batch, max(nb_iter, 1)), np.nan)
+
+    def __enter__(self):
+        load().oracle_set_margin_out(cabi.dptr(self.out.margin_hist))
+
+    def __exit__(self, *a):
+        load().oracle_set_margin_out(cabi.dptr(None))
+
+
 def solve_recursive(pb, U0, nb_iter, line_search=True, early_stop=False, threads=1):
     from ilqr_planner_b200.problem import ResultBuffers
     d = pb.to_desc()
     out = ResultBuffers(pb, nb_iter, "recursive")
     opts = cabi.SolveOpts(nb_iter, int(line_search), int(early_stop), 0)
     U0 = None if U0 is None else np.ascontiguousarray(np.asarray(U0, dtype=np.float64).reshape(pb.batch, pb.horizon - 1, pb.m))
-    _check(load().oracle_solve_recursive(C.byref(d), cabi.dptr(U0), C.byref(opts), C.byref(out.res), threads))
+    with _margins(out, pb, nb_iter):
+        _check(load().oracle_solve_recursive(C.byref(d), cabi.dptr(U0), C.byref(opts), C.byref(out.res), threads))
     return out
 
 
@@ -79,7 +96,8 @@ def solve_al(pb, U0, A, b, lambda0, nb_iter, lag_update_step, penalty, scaling_f
     out = ResultBuffers(pb, nb_iter, "al", nc=al.nc)
     opts = cabi.SolveOpts(nb_iter, int(line_search), int(early_stop), 0)
     U0 = None if U0 is None else np.ascontiguousarray(np.asarray(U0, dtype=np.float64).reshape(pb.batch, pb.horizon - 1, pb.m))
-    _check(load().oracle_solve_al(C.byref(d), cabi.dptr(U0), C.byref(al), C.byref(opts), C.byref(out.res), threads))
+    with _margins(out, pb, nb_iter):
+        _check(load().oracle_solve_al(C.byref(d), cabi.dptr(U0), C.byref(al), C.byref(opts), C.byref(out.res), threads))
     return out
 
 
@@ -98,7 +116,8 @@ def solve_batch(pb, u0, nb_iter, early_stop=False, Q=None, psi=None, threads=1):
     out = ResultBuffers(pb, nb_iter, "batch")
     opts = cabi.SolveOpts(nb_iter, 1, int(early_stop), 0)
     u0 = None if u0 is None else np.ascontiguousarray(np.asarray(u0, dtype=np.float64).reshape(pb.batch, -1))
-    _check(load().oracle_solve_batch(C.byref(d), cabi.dptr(u0), C.byref(bd), C.byref(opts), C.byref(out.res), threads))
+    with _margins(out, pb, nb_iter):
+        _check(load().oracle_solve_batch(C.byref(d), cabi.dptr(u0), C.byref(bd), C.byref(opts), C.byref(out.res), threads))
     return out
 
 

@@ -33,18 +33,21 @@ def rel(a, b, scale=None):
     return float(np.nanmax(np.abs(a - b)) / s)
 
 
-def decisive_prefix(ref_cost_hist, ref_alpha_hist, iters):
-    """Number of leading iterations whose line-search decision is not a tie at FP64 noise level.
+TIE = 1e-9  # = the cost tolerance: a line-search comparison closer than this is not decided by the algorithm but by rounding
 
-    Once a problem has converged, successive costs differ by ~1e-16 relative and `newCost >= cost0` is decided by
-    rounding noise: from the first iteration whose accepted cost moved by less than 1e-11
-    relative, alpha sequences are compared no further (costs and trajectories still are)."""
-    n = int(iters)
-    for i in range(1, n):
-        prev, cur = ref_cost_hist[i - 1], ref_cost_hist[i]
-        if np.isnan(cur) or np.isnan(prev):
-            return i
-        if abs(cur - prev) <= 1e-11 * abs(prev):
+
+def decisive_prefix(ref, b):
+    """Number of leading iterations of problem b whose line-search decisions are not ties.
+
+    The oracle reports, per iteration, the smallest relative distance |candidate cost - incumbent cost| / |incumbent|
+    over the candidates its sequential line search evaluated (`margin_hist`, oracle/ilqr_oracle.cpp trackMargin).
+    `newCost >= cost0` with a margin below the 1e-9 cost tolerance is decided by FP64 rounding, and
+    after such a tie the two runs may follow different (equally valid) branches: alpha sequences are compared up to the
+    first tie, costs and trajectories over the whole solve."""
+    n = int(ref.iters[b])
+    for i in range(n):
+        mg = ref.margin_hist[b, i]
+        if np.isnan(ref.cost_hist[b, i]) or not (mg >= TIE):
             return i
     return n
 
@@ -82,7 +85,7 @@ def _check_recursive(pb, u0, nb_iter, oracle, early_stop=False):
     assert np.array_equal(out.iters, ref.iters)
     assert rel(out.cost_hist, ref.cost_hist) < RTOL
     for b in range(pb.batch):
-        k = decisive_prefix(ref.cost_hist[b], ref.alpha_hist[b], ref.iters[b])
+        k = decisive_prefix(ref, b)
         assert np.array_equal(out.alpha_hist[b, :k], ref.alpha_hist[b, :k]), "problem %d alpha sequence" % b
     assert rel(out.X, ref.X) < RTOL
     assert rel(out.U, ref.U) < 10 * RTOL
@@ -159,7 +162,7 @@ def test_config3_al_ilqr(oracle_lib):
     ref = oracle_lib.solve_al(pb, None, al["A"], al["b"], al["lambda0"], nb, al["lag_update_step"], al["penalty"], al["scaling_factor"], True, False, threads=8)
     assert rel(out.cost_hist, ref.cost_hist) < RTOL
     for b in range(pb.batch):
-        k = decisive_prefix(ref.cost_hist[b], ref.alpha_hist[b], ref.iters[b])
+        k = decisive_prefix(ref, b)
         assert np.array_equal(out.alpha_hist[b, :k], ref.alpha_hist[b, :k])
     assert rel(out.X, ref.X) < RTOL and rel(out.U, ref.U) < 10 * RTOL
     assert rel(out.lam, ref.lam, scale=max(np.abs(ref.lam).max(), 1e-6)) < 1e-8
