@@ -5,11 +5,13 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
 
 #include "batch.cuh"
+#include "fused1.cuh"
 #include "recursive.cuh"
 
 using namespace ilqrb;
@@ -222,6 +224,44 @@ int launch_backward(ilqrb_handle h, bool al, double pf) {
     return 0;
 }
 
+// ---- fast path (fused1.cuh): single integrator, no time state, no AL ---------------------------------------
+bool fast_n1_applies(ilqrb_handle h, bool al) {
+    static const bool forced_generic = getenv("ILQRB_GENERIC") != nullptr;  // A/B switch for tests and profiling
+    const DevProblem& P = h->hp;
+    return !forced_generic && !al && P.nb_deriv == 1 && !P.time && P.n == P.m && P.n + 1 <= 16;
+}
+template <int NT, int WARPS, int MINB>
+int launch_backward_n1_t(ilqrb_handle h) {
+    const size_t smem = (size_t)WARPS * BwdN1Smem<NT>::PER_WARP * sizeof(double);
+    auto kern = k_backward_n1<NT, WARPS, MINB>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    const int B = h->hp.B;
+    kern<<<(B + WARPS - 1) / WARPS, 32 * WARPS, smem, h->stream>>>(h->dp, h->W);
+    return 0;
+}
+int launch_backward_n1(ilqrb_handle h) {
+    h->begin(PS_BACKWARD);
+    int rc = (h->hp.n + 1 <= 8) ? launch_backward_n1_t<1, 4, 7>(h) : launch_backward_n1_t<2, 4, 2>(h);
+    h->end();
+    if (rc) return rc;
+    CU(cudaGetLastError());
+    return 0;
+}
+int launch_forward_n1(ilqrb_handle h, int it, int nb_iter, int line_search, int early_stop) {
+    const int B = h->hp.B;
+    constexpr int WARPS = 4;
+    h->begin(PS_LINESEARCH);
+    if (h->hp.n + 1 <= 8) k_forward_n1<1, WARPS><<<(B + WARPS - 1) / WARPS, 32 * WARPS, 0, h->stream>>>(h->dp, h->W, it, nb_iter, line_search, early_stop);
+    else k_forward_n1<2, WARPS><<<(B + WARPS - 1) / WARPS, 32 * WARPS, 0, h->stream>>>(h->dp, h->W, it, nb_iter, line_search, early_stop);
+    h->end();
+    CU(cudaGetLastError());
+    return 0;
+}
+
 int ensure_iter_capacity(ilqrb_handle h, int nb_iter) {
     if (nb_iter <= h->cap_iter) return 0;
     int rc;
@@ -407,6 +447,16 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
         k_al_init<<<(B * 32 + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W);
         h->end();
         CU(cudaGetLastError());
+    }
+    if (fast_n1_applies(h, al != nullptr)) {
+        if (opts->nb_iter > 0 && (rc = launch_derivs(h))) return rc;  // later iterations: k_forward_n1 phase F
+        for (int it = 0; it < opts->nb_iter; it++) {
+            if ((rc = launch_backward_n1(h))) return rc;
+            if ((rc = launch_forward_n1(h, it, opts->nb_iter, opts->line_search, opts->early_stop))) return rc;
+        }
+        h->last_nb_iter = opts->nb_iter;
+        h->last_solver = 1;
+        return 0;
     }
     for (int it = 0; it < opts->nb_iter; it++) {
         if ((rc = launch_derivs(h))) return rc;

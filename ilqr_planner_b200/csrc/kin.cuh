@@ -568,7 +568,8 @@ HD int task_kp_at(const DevTask& tk, int k) {
 
 // System::cost (System.cpp:213-234) summed over tasks as SequentialSystem::cost does (SequentialSystem.cpp:143-149).
 // x: state (n), u: control (m) — u = nullptr means zeros (cost_F, System.cpp:236-238).
-template <int N>
+// LIM = false leaves the joint-limit term out (the fast path accumulates it separately over all steps).
+template <int N, bool LIM = true>
 HD double stage_cost(const DevProblem& P, int b, const double* x, const double* u, int k) {
     double total = 0;
     const int dof = P.dof;
@@ -602,7 +603,7 @@ HD double stage_cost(const DevProblem& P, int b, const double* x, const double* 
                 for (int j = 0; j < P.m; j++) uRu += (u[j] * tk.r_diag[j]) * u[j];
             c += dQd + uRu;
         }
-        if (tk.limits_set) {
+        if (LIM && tk.limits_set) {
             double qLq = 0;
             for (int i = 0; i < P.n; i++) {
                 bool act;

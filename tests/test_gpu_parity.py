@@ -82,17 +82,24 @@ def _check_recursive(pb, u0, nb_iter, oracle, early_stop=False):
     with _handle(pb) as h:
         out = h.solve_recursive(u0, nb_iter, True, early_stop)
     ref = oracle.solve_recursive(pb, u0, nb_iter, True, early_stop, threads=8)
-    assert np.array_equal(out.iters, ref.iters)
     assert rel(out.cost_hist, ref.cost_hist) < RTOL
+    assert rel(out.cost, ref.cost) < RTOL
+    # problems whose every line-search decision is decisive must match in everything the reference returns;
+    # after a declared tie the two runs may sit on different (equally valid) branches: those problems are held to the
+    # cost tolerance above and to a loose trajectory bound only.
+    dec = np.array([decisive_prefix(ref, b) == int(ref.iters[b]) for b in range(pb.batch)])
+    assert dec.sum() >= pb.batch // 2, "too few decisive problems (%d of %d) for this test to mean anything" % (dec.sum(), pb.batch)
     for b in range(pb.batch):
         k = decisive_prefix(ref, b)
         assert np.array_equal(out.alpha_hist[b, :k], ref.alpha_hist[b, :k]), "problem %d alpha sequence" % b
-    assert rel(out.X, ref.X) < RTOL
-    assert rel(out.U, ref.U) < 10 * RTOL
-    assert rel(out.fX, ref.fX) < RTOL
-    assert rel(out.K, ref.K) < 10 * RTOL
-    assert rel(out.d, ref.d, scale=np.abs(ref.U).max() + np.abs(ref.d).max()) < RTOL
-    assert rel(out.cost, ref.cost) < RTOL
+    assert np.array_equal(out.iters[dec], ref.iters[dec])
+    assert rel(out.X[dec], ref.X[dec]) < RTOL
+    assert rel(out.U[dec], ref.U[dec]) < 10 * RTOL
+    assert rel(out.fX[dec], ref.fX[dec]) < RTOL
+    assert rel(out.K[dec], ref.K[dec]) < 10 * RTOL
+    assert rel(out.d[dec], ref.d[dec], scale=np.abs(ref.U).max() + np.abs(ref.d).max()) < RTOL
+    if (~dec).any():
+        assert rel(out.X[~dec], ref.X[~dec]) < 1e-6
     return out, ref
 
 
