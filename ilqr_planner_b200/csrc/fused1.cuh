@@ -21,6 +21,7 @@
 //                   X is re-integrated from U with the reference's operation order, and l_x / l_xx of the keypoint
 //                   steps of the accepted trajectory are produced for the next backward pass.
 #pragma once
+#include "kin_lean.cuh"
 #include "recursive.cuh"
 
 namespace ilqrb {
@@ -47,17 +48,31 @@ __device__ __forceinline__ void st_c(double* M, const double (&e)[NT][NT][2], in
         for (int ct = 0; ct < NT; ct++) *reinterpret_cast<double2*>(M + (8 * rt + g) * LD + 8 * ct + 2 * t) = make_double2(e[rt][ct][0], e[rt][ct][1]);
 }
 
-// In-register inverse of the leading m x m block of an (8NT)^2 matrix held in accumulator layout: Gauss-Jordan
-// without pivoting (Quu + 1e-6 I is symmetric positive definite in normal operation; replaces the PartialPivLU
-// inverse of ILQRRecursive.cpp:89).  Pivot row / column / element travel by warp shuffles; no shared memory, no
-// barrier.  Entries outside the leading block are left untouched.  Returns false if a pivot was <= 0 or NaN.
-template <int NT>
-__device__ __forceinline__ bool gj_inverse_regs(double (&e)[NT][NT][2], int m, int g, int t) {
+// 1/x to full double precision: MUFU.RCP64H seed (2^-23) + two Newton steps; no slow path (x is a pivot of an SPD
+// matrix in normal operation; NaN / non-positive pivots are reported through the status word).
+__device__ __forceinline__ double fast_rcp(double x) {
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    double e = fma(-x, y, 1.0);
+    y = fma(y, e, y);
+    e = fma(-x, y, 1.0);
+    y = fma(y, e, y);
+    return y;
+}
+
+// In-register inverse of an (8NT)^2 matrix held in accumulator layout whose leading m x m block is the matrix to
+// invert and whose remaining rows / columns are those of the identity: Gauss-Jordan without pivoting (Quu + 1e-6 I is
+// symmetric positive definite in normal operation; replaces the PartialPivLU inverse of ILQRRecursive.cpp:89).
+// Pivot row / column / element travel by warp shuffles; no shared memory, no barrier.  M > 0: m known at compile time.
+// Returns false if a pivot was <= 0 or NaN.
+template <int NT, int M>
+__device__ __forceinline__ bool gj_inverse_regs(double (&e)[NT][NT][2], int m_rt, int g, int t) {
     constexpr unsigned FULL = 0xffffffffu;
+    const int m = M > 0 ? M : m_rt;
     bool ok = true;
 #pragma unroll
     for (int k = 0; k < 8 * NT; k++) {
-        if (k < m) {  // warp-uniform
+        if (k < m) {  // warp-uniform (compile-time when M > 0)
             const int kt = k >> 3, kg = k & 7, kh = k & 1;
             double rowk[NT][2], colk[NT];
 #pragma unroll
@@ -69,21 +84,24 @@ __device__ __forceinline__ bool gj_inverse_regs(double (&e)[NT][NT][2], int m, i
             for (int rt = 0; rt < NT; rt++) colk[rt] = __shfl_sync(FULL, e[rt][kt][kh], 4 * g + (kg >> 1));
             const double pkk = __shfl_sync(FULL, e[kt][kt][kh], 4 * kg + (kg >> 1));
             if (!(pkk > 0.0)) ok = false;
-            const double piv = 1.0 / pkk;
+            const double piv = fast_rcp(pkk);
+            const bool pcol = (t == (kg >> 1));  // this lane owns column k in slot kh of column tile kt
 #pragma unroll
             for (int rt = 0; rt < NT; rt++) {
-                const int i = 8 * rt + g;
+                const bool prow = (rt == kt) && (g == kg);  // this lane owns row k
+                const double f = prow ? -1.0 : colk[rt];
 #pragma unroll
                 for (int ct = 0; ct < NT; ct++)
 #pragma unroll
                     for (int h = 0; h < 2; h++) {
-                        const int j = 8 * ct + 2 * t + h;
                         const double rkj = rowk[ct][h] * piv;
-                        double v;
-                        if (i == k) v = (j == k) ? piv : rkj;
-                        else if (j == k) v = -colk[rt] * piv;
-                        else v = e[rt][ct][h] - colk[rt] * rkj;
-                        if (i < m && j < m) e[rt][ct][h] = v;
+                        const double base = prow ? 0.0 : e[rt][ct][h];
+                        double v = fma(-f, rkj, base);  // row k: rkj ; other rows: e - colk * rkj
+                        if (ct == kt && h == kh) {      // compile-time: the slot that can hold column k
+                            const double cv = prow ? piv : (-colk[rt]) * piv;
+                            v = pcol ? cv : v;
+                        }
+                        e[rt][ct][h] = v;
                     }
             }
         }
@@ -100,7 +118,8 @@ struct BwdN1Smem {
 // ------------------------------------------------------------------------------------------------------------
 // backward Riccati pass, A = I, B = dt I.  Augmented layout: column n of the state-indexed matrices carries the
 // vector ([P|p], [Qux|Qu], [Qxx|Qx], [K|d]); rows >= n and columns > n are kept at exact zero.
-template <int NT, int WARPS, int MINB>
+// DOF > 0: n = m = DOF at compile time; DOF == 0: read from the problem.
+template <int NT, int DOF, int WARPS, int MINB>
 __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProblem* __restrict__ Pp, Work W) {
     using S = BwdN1Smem<NT>;
     constexpr int LD = S::LD, SZ = S::SZ;
@@ -111,7 +130,8 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
     if (b >= P.B) return;
     if (W.done[b]) return;
     const int g = lane >> 2, t = lane & 3;
-    const int n = P.n, m = P.m, H = P.H, ns = W.ns, ms = W.ms;
+    const int n = DOF > 0 ? DOF : P.n, m = n, H = P.H;
+    const int ns = (n + 1) & ~1, ms = ns;
     const double dt = 1.0 * P.dt;  // B = Identity * dt
     double* sInv = smem + (size_t)wid * S::PER_WARP;
     double* sQux = sInv + SZ;
@@ -125,11 +145,32 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
 
     const double* Xb = W.X + (size_t)b * H * ns;
     const double* Ub = W.U + (size_t)b * (H - 1) * ms;
+    const int S_kp = P.n_kp_steps;
+
+    // joint limits of the first limit-carrying task live in registers (weight 0 -> +-inf); further tasks: slow loop
+    int l0 = -1, l1 = -1;
+    if (P.any_limits)
+        for (int ti = P.n_tasks - 1; ti >= 0; ti--)
+            if (P.tasks[ti].limits_set) {
+                l1 = l0;
+                l0 = ti;
+            }
+    double lmx[NT], lmn[NT];
+#pragma unroll
+    for (int rt = 0; rt < NT; rt++) {
+        const int i = 8 * rt + g;
+        lmx[rt] = INFINITY;
+        lmn[rt] = -INFINITY;
+        if (l0 >= 0 && i < n && P.tasks[l0].limit_weight[i] != 0) {
+            lmx[rt] = P.tasks[l0].state_max[i];
+            lmn[rt] = P.tasks[l0].state_min[i];
+        }
+    }
 
     // e += [l_xx | l_x] of keypoint step index s (k_kp_derivs / k_forward_n1 wrote them)    System.cpp:252-260,290-296
     auto add_kp = [&](double (&e)[NT][NT][2], int s) {
-        const double* lx = W.LX + ((size_t)b * P.n_kp_steps + s) * n;
-        const double* lxx = W.LXX + ((size_t)b * P.n_kp_steps + s) * n * n;
+        const double* lx = W.LX + ((size_t)b * S_kp + s) * n;
+        const double* lxx = W.LXX + ((size_t)b * S_kp + s) * n * n;
 #pragma unroll
         for (int rt = 0; rt < NT; rt++) {
             const int i = 8 * rt + g;
@@ -145,26 +186,35 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
                 }
         }
     };
-    // e += [L^T L | -L^T q] of the joint-limit penalty at state row values xr          System.cpp:263-269,299-305
+    // e += [L^T L | -L^T q] with L = diag(violated), q = limit - x                      System.cpp:121-142,263-269,299-305
+    auto add_lq = [&](double (&e)[NT][NT][2], int rt, double q) {
+        const int i = 8 * rt + g;
+#pragma unroll
+        for (int ct = 0; ct < NT; ct++)
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const int j = 8 * ct + 2 * t + h;
+                if (j == i) e[rt][ct][h] += 1.0 * 1.0;
+                else if (j == n) e[rt][ct][h] += -1.0 * q;
+            }
+    };
     auto add_limits = [&](double (&e)[NT][NT][2], const double (&xr)[NT]) {
-        for (int tk_i = 0; tk_i < P.n_tasks; tk_i++) {
-            const DevTask& tk = P.tasks[tk_i];
-            if (!tk.limits_set) continue;
 #pragma unroll
-            for (int rt = 0; rt < NT; rt++) {
-                const int i = 8 * rt + g;
-                if (i < n) {
-                    bool act;
-                    const double q = limit_q(tk, i, xr[rt], act);
-                    if (act) {
+        for (int rt = 0; rt < NT; rt++) {
+            if (xr[rt] > lmx[rt]) add_lq(e, rt, lmx[rt] - xr[rt]);
+            else if (xr[rt] < lmn[rt]) add_lq(e, rt, lmn[rt] - xr[rt]);
+        }
+        if (l1 >= 0) {  // more than one sub-system with limits (SequentialSystem.cpp:119-165 sums them)
+            for (int ti = l1; ti < P.n_tasks; ti++) {
+                const DevTask& tk = P.tasks[ti];
+                if (!tk.limits_set) continue;
 #pragma unroll
-                        for (int ct = 0; ct < NT; ct++)
-#pragma unroll
-                            for (int h = 0; h < 2; h++) {
-                                const int j = 8 * ct + 2 * t + h;
-                                if (j == i) e[rt][ct][h] += 1.0 * 1.0;
-                                else if (j == n) e[rt][ct][h] += -1.0 * q;
-                            }
+                for (int rt = 0; rt < NT; rt++) {
+                    const int i = 8 * rt + g;
+                    if (i < n) {
+                        bool act;
+                        const double q = limit_q(tk, i, xr[rt], act);
+                        if (act) add_lq(e, rt, q);
                     }
                 }
             }
@@ -181,12 +231,14 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
     for (int rt = 0; rt < NT; rt++)
 #pragma unroll
         for (int ct = 0; ct < NT; ct++) Pa[rt][ct][0] = Pa[rt][ct][1] = 0.0;
-    int sp = P.n_kp_steps - 1;
-    if (sp >= 0 && P.kp_steps[sp] == H - 1) {
+    int sp = S_kp - 1;
+    int next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
+    if (next_kp == H - 1) {
         add_kp(Pa, sp);
         sp--;
+        next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
     }
-    if (P.any_limits) {
+    if (l0 >= 0) {
         double xr[NT];
         load_rows(Xb, ns, H - 1, n, xr);
         add_limits(Pa, xr);
@@ -195,9 +247,10 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
     load_rows(Ub, ms, H - 2, m, un);
     load_rows(Xb, ns, H - 2, n, xn);
     bool spd = true;
+    double* Kg = W.K + ((size_t)b * (H - 1) + (H - 2)) * m * ns;  // walks backwards with k
+    double* dg = W.d + ((size_t)b * (H - 1) + (H - 2)) * ms;
 
-    for (int k = H - 2; k >= 0; k--) {
-        const size_t bk = (size_t)b * (H - 1) + k;
+    for (int k = H - 2; k >= 0; k--, Kg -= m * ns, dg -= ms) {
         double u[NT], x[NT];
 #pragma unroll
         for (int rt = 0; rt < NT; rt++) {
@@ -206,11 +259,11 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
         }
         if (k > 0) {  // prefetch the next step's control / state rows
             load_rows(Ub, ms, k - 1, m, un);
-            load_rows(Xb, ns, k - 1, n, xn);
+            if (l0 >= 0) load_rows(Xb, ns, k - 1, n, xn);
         }
         // [Qux|Qu] = [0 | R u] + (B^T [P|p]) A_aug ;  Quu = R + (B^T P) B ;  [Qxx|Qx] = [l_xx|l_x] + (A^T [P|p]) A_aug
         // Qxu = (A^T P) B = P*dt has the same entries as Qux = dt*P                     ILQRRecursive.cpp:82-87
-        double Qa[NT][NT][2], Qu2[NT][NT][2], Qx[NT][NT][2];
+        double Qa[NT][NT][2], Qu2[NT][NT][2], Qx[NT][NT][2], Inv[NT][NT][2];
 #pragma unroll
         for (int rt = 0; rt < NT; rt++) {
             const int i = 8 * rt + g;
@@ -223,30 +276,21 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
                     Qa[rt][ct][h] = (j == n) ? Rrow[rt] * u[rt] + bp : bp;
                     double quu = bp * dt;
                     if (i == j) quu = Rrow[rt] + quu;
-                    Qu2[rt][ct][h] = (i < m && j < m) ? quu : 0.0;
+                    quu = (j < m) ? quu : 0.0;  // rows >= m of [P|p] are zero already
+                    Qu2[rt][ct][h] = quu;
+                    // Quu + 1e-6 I, identity outside the leading block                    ILQRRecursive.cpp:89
+                    Inv[rt][ct][h] = (i == j) ? ((i < m) ? quu + 1e-6 * 1.0 : 1.0) : quu;
                     Qx[rt][ct][h] = Pa[rt][ct][h];
                 }
         }
-        if (sp >= 0 && P.kp_steps[sp] == k) {
+        if (k == next_kp) {
             add_kp(Qx, sp);
             sp--;
+            next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
         }
-        if (P.any_limits) add_limits(Qx, x);
+        if (l0 >= 0) add_limits(Qx, x);
 
-        // Inv = (Quu + 1e-6 I)^-1                                                        ILQRRecursive.cpp:89
-        double Inv[NT][NT][2];
-#pragma unroll
-        for (int rt = 0; rt < NT; rt++)
-#pragma unroll
-            for (int ct = 0; ct < NT; ct++)
-#pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const int i = 8 * rt + g, j = 8 * ct + 2 * t + h;
-                    double v = Qu2[rt][ct][h];
-                    if (i == j) v = (i < m) ? v + 1e-6 * 1.0 : 1.0;
-                    Inv[rt][ct][h] = v;
-                }
-        spd = gj_inverse_regs<NT>(Inv, m, g, t) && spd;
+        spd = gj_inverse_regs<NT, DOF>(Inv, m, g, t) && spd;
         st_c<NT, LD>(sInv, Inv, g, t);
         st_c<NT, LD>(sQux, Qa, g, t);
         st_c<NT, LD>(sQuu, Qu2, g, t);
@@ -270,9 +314,8 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
                 for (int kt = 0; kt < NT; kt++)
 #pragma unroll
                     for (int s = 0; s < 2; s++) dmma884(c0, c1, ld_a<LD>(sInv, rt, kt, s, g, t), bQ[kt][s][ct]);
-                const bool row = 8 * rt + g < m;
-                Kd[rt][ct][0] = row ? -c0 : 0.0;
-                Kd[rt][ct][1] = row ? -c1 : 0.0;
+                Kd[rt][ct][0] = -c0;  // rows >= m: identity rows of Inv times zero rows of [Qux|Qu] = 0
+                Kd[rt][ct][1] = -c1;
             }
         st_c<NT, LD>(sKd, Kd, g, t);
         // stream K, d to global (time-forward index)
@@ -283,12 +326,9 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
 #pragma unroll
                 for (int ct = 0; ct < NT; ct++) {
                     const int j = 8 * ct + 2 * t;
-                    if (j < ns) {
-                        double2 v = make_double2(j < n ? Kd[rt][ct][0] : 0.0, j + 1 < n ? Kd[rt][ct][1] : 0.0);
-                        *reinterpret_cast<double2*>(W.K + (bk * m + i) * ns + j) = v;
-                    }
-                    if (j == n) W.d[bk * ms + i] = Kd[rt][ct][0];
-                    else if (j + 1 == n) W.d[bk * ms + i] = Kd[rt][ct][1];
+                    if (j < ns) *reinterpret_cast<double2*>(Kg + i * ns + j) = make_double2(Kd[rt][ct][0], j + 1 < n ? Kd[rt][ct][1] : 0.0);
+                    if (j == n) dg[i] = Kd[rt][ct][0];
+                    else if (j + 1 == n) dg[i] = Kd[rt][ct][1];
                 }
             }
         }
@@ -355,159 +395,180 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-// column j of the task Jacobian (r_t entries) — same content as task_jacobian(), one column at a time
-__device__ __forceinline__ void task_jac_col(const DevProblem& P, const DevTask& tk, const EEState& e, int j, double* col) {
-    const DevRobot& rb = P.robots[tk.robot];
-    const int nd = P.nb_deriv, dof = P.dof;
-    for (int a = 0; a < tk.r_t; a++) col[a] = 0.0;
-    const int rows = (P.sys_kind == ILQRB_SYS_POSITION) ? tk.nt_t / nd : 6;
-    if (j < nd * dof) {
-        const int blk = j / dof, c = j - blk * dof - tk.joint_offset;
-        if (c >= 0 && c < rb.dof)
-            for (int a = 0; a < rows; a++) col[blk * rows + a] = (a < 3) ? e.Jv[c][a] : e.Jw[c][a - 3];
-    }
-    if (P.time && j == P.n - 1) col[tk.r_t - 1] = 1.0;
+// per-warp shared memory of k_forward_n1 (doubles): deviation controls of the whole horizon, deviation states at the
+// keypoint steps, candidate x keypoint costs, one Jacobian column per lane
+__host__ __device__ inline int fwd_n1_smem_doubles(int H, int ns, int S) {
+    const int du = (H - 1) * ns > 32 * 6 ? (H - 1) * ns : 32 * 6;  // the Jacobian columns of phase F reuse the sDU area
+    return du + S * ns + NCAND * S;
 }
 
-// row i of l_xx and entry i of l_x at keypoint-step index s of the current trajectory (System.cpp:252-260,290-296):
-//   l_x = sum_tasks ((-J^T) Q) diff ,  l_xx = sum_tasks (J^T Q) J
-__device__ __noinline__ void kp_deriv_row(const DevProblem& P, const Work& W, int b, int s, int i) {
-    const int k = P.kp_steps[s], n = P.n, dof = P.dof;
-    const double* x = W.X + ((size_t)b * P.H + k) * W.ns;
-    double xs[MAXN], dqz[MAXM], row[MAXN];
-    for (int a = 0; a < n; a++) {
-        xs[a] = x[a];
-        row[a] = 0.0;
-    }
-    for (int a = 0; a < dof; a++) dqz[a] = 0.0;
-    double lxi = 0.0;
-    for (int ti = 0; ti < P.n_tasks; ti++) {
-        const DevTask& tk = P.tasks[ti];
-        const int kp = task_kp_at(tk, k);
-        if (kp < 0) continue;
-        EEState e;
-        task_ee(P, tk, xs, P.nb_deriv == 2 ? xs + dof : dqz, e);
-        double fx[MAX_NTT], res[MAX_RT];
-        task_fx(P, tk, e, P.time ? xs[n - 1] : 0.0, fx);
-        const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
-        task_residual(P, tk, fx, tg, res);
-        const int r = tk.r_t;
-        const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + kp) * r * r;
-        double Ji[MAX_RT], jq[MAX_RT];
-        task_jac_col(P, tk, e, i, Ji);
-        double gsum = 0.0;
-        for (int c = 0; c < r; c++) {
-            double a = 0.0, na = 0.0;
-            for (int a2 = 0; a2 < r; a2++) {
-                a += Ji[a2] * Q[a2 * r + c];
-                na += (-1.0 * Ji[a2]) * Q[a2 * r + c];
-            }
-            jq[c] = a;
-            gsum += na * res[c];
-        }
-        lxi += gsum;
-        for (int j = 0; j < n; j++) {
-            double Jj[MAX_RT];
-            task_jac_col(P, tk, e, j, Jj);
-            double h = 0.0;
-            for (int c = 0; c < r; c++) h += jq[c] * Jj[c];
-            row[j] += h;
-        }
-    }
-    W.LX[((size_t)b * P.n_kp_steps + s) * n + i] = lxi;
-    double* out = W.LXX + (((size_t)b * P.n_kp_steps + s) * n + i) * n;
-    for (int j = 0; j < n; j++) out[j] = row[j];
-}
-
-// joint-limit cost q^T L q of one state vector element (System.cpp:225-231), summed over the tasks that set limits
-__device__ __forceinline__ double limit_cost_elem(const DevProblem& P, int i, double xi, bool& any) {
-    double c = 0.0;
-    for (int ti = 0; ti < P.n_tasks; ti++) {
-        const DevTask& tk = P.tasks[ti];
-        if (!tk.limits_set) continue;
-        bool act;
-        const double q = limit_q(tk, i, xi, act);
-        if (act) {
-            c += (q * 1.0) * q;
-            any = true;
-        }
-    }
-    return c;
-}
-
-// ------------------------------------------------------------------------------------------------------------
-// forward pass: line search over all candidates, accept, derivatives of the accepted trajectory.
-// Scratch (per problem, inside W.Uc): DX [H][ns] and DU [H-1][ms] = the alpha = 1 closed-loop deviation.
-template <int NT, int WARPS>
-__global__ void __launch_bounds__(32 * WARPS) k_forward_n1(const DevProblem* __restrict__ Pp, Work W, int it, int nb_iter, int line_search, int early_stop) {
+// forward pass: line search over all candidates, accept, derivatives of the accepted trajectory.  One warp per block.
+template <int NT, int DOF, int MINB>
+__global__ void __launch_bounds__(32, MINB) k_forward_n1(const DevProblem* __restrict__ Pp, Work W, int it, int nb_iter, int line_search, int early_stop) {
     constexpr int NX = 8 * NT;
     constexpr unsigned FULL = 0xffffffffu;
-    __shared__ double s_cc[WARPS][NCAND][MAX_KP_STEPS];
+    constexpr int PF = (NT == 1) ? 4 : 3;  // register ring of gain fragments, in steps (L2 prefetch runs further ahead)
+    extern __shared__ double smem[];
     const DevProblem& P = *Pp;
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int b = blockIdx.x * WARPS + wid;
-    if (b >= P.B) return;
+    const int lane = threadIdx.x;
+    const int b = blockIdx.x;
     if (W.done[b]) return;
-    const int H = P.H, n = P.n, m = P.m, ns = W.ns, ms = W.ms, dof = P.dof, S = P.n_kp_steps;
+    const int g = lane >> 2, t = lane & 3;
+    const int n = DOF > 0 ? DOF : P.n, m = n, dof = n, H = P.H, S = P.n_kp_steps;
+    const int ns = (n + 1) & ~1, ms = ns;
     const double dt = P.dt;
-    double* DX = W.Uc + (size_t)b * (H - 1) * NCAND * ms;
-    double* DU = DX + (size_t)H * ns;
+    double* sDU = smem;                   // [H-1][ms]  alpha = 1 control deviation
+    double* sDXk = sDU + (H - 1) * ms;    // [S][ns]    alpha = 1 state deviation at the keypoint steps
+    double* s_cc = sDXk + S * ns;         // [NCAND][S]
+    double* s_J = sDU;                    // [32][6]    phase F only, when sDU is dead
     double* Xb = W.X + (size_t)b * H * ns;
     double* Ub = W.U + (size_t)b * (H - 1) * ms;
     const double* Kb = W.K + (size_t)b * (H - 1) * m * ns;
     const double* db = W.d + (size_t)b * (H - 1) * ms;
 
-    // ---- phase A: alpha = 1 deviation rollout.  lane i < n owns dx_i and row i of K_k.
-    //      du = K (x' - x) + d ; x'+ = x' + dt u'     (ILQRRecursive.cpp:124-136 with alpha = 1, minus the nominal)
-    {
-        double dx = 0.0;
-        if (lane < ns) DX[lane] = 0.0;
-        double kc[NX], dc = 0.0;
-        auto loadK = [&](int k, double (&kr)[NX], double& dd) {
-            if (lane < m) {
-                const double2* p = reinterpret_cast<const double2*>(Kb + ((size_t)k * m + lane) * ns);
+    // joint limits of the first limit-carrying task in registers (weight 0 -> +-inf), as in k_backward_n1
+    int l0 = -1, l1 = -1;
+    if (P.any_limits)
+        for (int ti = P.n_tasks - 1; ti >= 0; ti--)
+            if (P.tasks[ti].limits_set) {
+                l1 = l0;
+                l0 = ti;
+            }
+    double lmx[NT], lmn[NT];
 #pragma unroll
-                for (int j2 = 0; j2 < NX / 2; j2++)
-                    if (2 * j2 < ns) {
-                        const double2 v = p[j2];
-                        kr[2 * j2] = v.x;
-                        kr[2 * j2 + 1] = v.y;
-                    }
-                dd = db[(size_t)k * ms + lane];
+    for (int rt = 0; rt < NT; rt++) {
+        const int i = 8 * rt + g;
+        lmx[rt] = INFINITY;
+        lmn[rt] = -INFINITY;
+        if (l0 >= 0 && i < n && P.tasks[l0].limit_weight[i] != 0) {
+            lmx[rt] = P.tasks[l0].state_max[i];
+            lmn[rt] = P.tasks[l0].state_min[i];
+        }
+    }
+
+    // ---- phase A: alpha = 1 deviation rollout on the FP64 tensor pipe.
+    //      du = K (x' - x) + d ; x'+ = x' + dt u'     (ILQRRecursive.cpp:124-136 with alpha = 1, minus the nominal)
+    //      K_k is the A operand straight from global memory (prefetched PF steps ahead), dx the B operand (all eight
+    //      columns equal), so every lane of row group g ends up with du_g.  Along the way: is any joint limit violated
+    //      at either end of the candidate segment [x, x + dx]?  (if not, no candidate pays a limit penalty)
+    bool viol = (l1 >= 0);  // several limit-carrying sub-systems: always take the exact path below
+    if (l0 >= 0) {          // the initial state is common to all candidates but still pays its penalty
+#pragma unroll
+        for (int rt = 0; rt < NT; rt++) {
+            const int i = 8 * rt + g;
+            const double x00 = (i < n) ? Xb[i] : 0.0;
+            viol = viol || (x00 > lmx[rt]) || (x00 < lmn[rt]);
+        }
+    }
+    {
+        // L2 prefetch stream, PFD steps ahead of the register ring: lanes 0-3 cover the 4 cache lines a gain matrix can
+        // straddle, lane 4 the feed-forward row, lane 5 the control row (phases C, E), lane 6 the state row
+        constexpr int PFD = 24;
+        const char* pf_ptr = nullptr;
+        int pf_stride = 0;
+        if (lane < 4) {
+            pf_ptr = reinterpret_cast<const char*>(Kb) + lane * 128;
+            pf_stride = m * ns * 8;
+            if (lane * 128 >= pf_stride) pf_ptr = nullptr;
+        } else if (lane == 4) {
+            pf_ptr = reinterpret_cast<const char*>(db);
+            pf_stride = ms * 8;
+        } else if (lane == 5) {
+            pf_ptr = reinterpret_cast<const char*>(Ub);
+            pf_stride = ms * 8;
+        } else if (lane == 6 && l0 >= 0) {
+            pf_ptr = reinterpret_cast<const char*>(Xb + ns);
+            pf_stride = ns * 8;
+        }
+        auto prefetch_step = [&](int k) {
+            if (pf_ptr != nullptr && k < H - 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf_ptr + (size_t)k * pf_stride));
+        };
+        for (int k = 0; k < PFD; k++) prefetch_step(k);
+
+        // per-lane validity of the fragment entries and running pointers
+        bool vrow[NT], vcol[NT][2];
+#pragma unroll
+        for (int rt = 0; rt < NT; rt++) {
+            vrow[rt] = 8 * rt + g < m;
+#pragma unroll
+            for (int s = 0; s < 2; s++) vcol[rt][s] = 8 * rt + 4 * s + t < n;
+        }
+        const double* pK = Kb + g * ns + t;   // + rt*8*ns + kt*8 + s*4, advances m*ns per step
+        const double* pD = db + g;            // + rt*8, advances ms per step
+        const double* pX = Xb + ns + g;       // state k+1, + rt*8, advances ns per step
+        double aK[PF][NT][NT][2], aD[PF][NT], aX[PF][NT];
+        auto loadK = [&](int k, double (&a)[NT][NT][2], double (&dd)[NT], double (&xx)[NT]) {
+            const bool in = k < H - 1;
+            const double* qK = pK + (size_t)k * m * ns;
+#pragma unroll
+            for (int rt = 0; rt < NT; rt++) {
+                dd[rt] = (in && vrow[rt]) ? __ldcs(pD + (size_t)k * ms + 8 * rt) : 0.0;
+                xx[rt] = (in && vrow[rt] && l0 >= 0) ? pX[(size_t)k * ns + 8 * rt] : 0.0;
+#pragma unroll
+                for (int kt = 0; kt < NT; kt++)
+#pragma unroll
+                    for (int s = 0; s < 2; s++) a[rt][kt][s] = (in && vrow[rt] && vcol[kt][s]) ? __ldcs(qK + rt * 8 * ns + kt * 8 + s * 4) : 0.0;
             }
         };
 #pragma unroll
-        for (int j = 0; j < NX; j++) kc[j] = 0.0;
-        loadK(0, kc, dc);
-        for (int k = 0; k < H - 1; k++) {
-            double kn[NX], dn = 0.0;
+        for (int pp = 0; pp < PF; pp++) loadK(pp, aK[pp], aD[pp], aX[pp]);
+        double dxr[NT], bx[NT][2];
 #pragma unroll
-            for (int j = 0; j < NX; j++) kn[j] = 0.0;
-            if (k + 1 < H - 1) loadK(k + 1, kn, dn);
-            double a0 = 0.0, a1 = 0.0;
+        for (int rt = 0; rt < NT; rt++) {
+            dxr[rt] = 0.0;
+            bx[rt][0] = bx[rt][1] = 0.0;
+        }
+        int skp = 0;
+        int next_kp = S > 0 ? P.kp_steps[0] : -1;
+        if (next_kp == 0) {  // a keypoint on the initial state: dx = 0
+            if (lane < ns) sDXk[lane] = 0.0;
+            skp++;
+            next_kp = skp < S ? P.kp_steps[skp] : -1;
+        }
+        for (int k0 = 0; k0 < H - 1; k0 += PF) {
 #pragma unroll
-            for (int j = 0; j < NX; j += 2) {
-                if (j < n) a0 += kc[j] * __shfl_sync(FULL, dx, j);
-                if (j + 1 < n) a1 += kc[j + 1] * __shfl_sync(FULL, dx, j + 1);
+            for (int pp = 0; pp < PF; pp++) {
+                const int k = k0 + pp;
+                if (k < H - 1) {
+                    prefetch_step(k + PFD);
+#pragma unroll
+                    for (int rt = 0; rt < NT; rt++) {
+                        double c0 = 0.0, c1 = 0.0;
+#pragma unroll
+                        for (int kt = 0; kt < NT; kt++)
+#pragma unroll
+                            for (int s = 0; s < 2; s++) dmma884(c0, c1, aK[pp][rt][kt][s], bx[kt][s]);
+                        const double du = c0 + aD[pp][rt];
+                        dxr[rt] = dxr[rt] + dt * du;
+                        if (t == 0 && 8 * rt + g < ms) sDU[k * ms + 8 * rt + g] = du;
+                        const double x0 = aX[pp][rt], x1 = x0 + dxr[rt];  // state k+1 (state 0 is fixed and shared)
+                        viol = viol || (x0 > lmx[rt]) || (x0 < lmn[rt]) || (x1 > lmx[rt]) || (x1 < lmn[rt]);
+                    }
+                    if (k + 1 == next_kp) {
+#pragma unroll
+                        for (int rt = 0; rt < NT; rt++)
+                            if (t == 0 && 8 * rt + g < ns) sDXk[skp * ns + 8 * rt + g] = dxr[rt];
+                        skp++;
+                        next_kp = skp < S ? P.kp_steps[skp] : -1;
+                    }
+#pragma unroll
+                    for (int kt = 0; kt < NT; kt++)
+#pragma unroll
+                        for (int s = 0; s < 2; s++) bx[kt][s] = __shfl_sync(FULL, dxr[kt], 4 * (4 * s + t));
+                    loadK(k + PF, aK[pp], aD[pp], aX[pp]);
+                }
             }
-            const double du = (lane < m) ? (a0 + a1) + dc : 0.0;
-            if (lane < ms) DU[(size_t)k * ms + lane] = du;
-            if (lane < dof) dx = dx + dt * du;
-            if (lane < ns) DX[(size_t)(k + 1) * ns + lane] = (lane < n) ? dx : 0.0;
-#pragma unroll
-            for (int j = 0; j < NX; j++) kc[j] = kn[j];
-            dc = dn;
         }
     }
     __syncwarp();
 
-    // ---- phase B: terms that run over every step, lanes stride over k
-    double dun1 = 0.0;  // sum_k |du_k| at alpha = 1 (early-stop test, ILQRRecursive.cpp:129,174)
+    // ---- phase B: sum_k |du_k| at alpha = 1 (early-stop test, ILQRRecursive.cpp:129,174); exact limit penalties if needed
+    double dun1 = 0.0;
     if (early_stop) {
         for (int k = lane; k < H - 1; k += 32) {
             double s2 = 0.0;
             for (int i = 0; i < m; i++) {
-                const double v = DU[(size_t)k * ms + i];
+                const double v = sDU[k * ms + i];
                 s2 += v * v;
             }
             dun1 += sqrt(s2);
@@ -515,40 +576,65 @@ __global__ void __launch_bounds__(32 * WARPS) k_forward_n1(const DevProblem* __r
         dun1 = warp_sum(dun1);
     }
     const int ncand = line_search ? NCAND : 1;
-    double lim_mine = 0.0;  // lane c < ncand: joint-limit cost of candidate c over the whole horizon
-    if (P.any_limits) {
-        // the candidates lie on the segment [x, x + dx]: if neither end violates a limit, none of them does
-        bool viol = false;
-        for (int k = lane; k < H; k += 32)
-            for (int i = 0; i < n; i++) {
-                const double x0 = Xb[(size_t)k * ns + i], x1 = x0 + DX[(size_t)k * ns + i];
-                limit_cost_elem(P, i, x0, viol);
-                limit_cost_elem(P, i, x1, viol);
+    double lim_mine = 0.0;  // lane c < ncand: joint-limit cost of candidate c over the whole horizon (System.cpp:225-231)
+    if (__any_sync(FULL, viol)) {
+        // rare: lane i < n walks the horizon for state entry i, rebuilding dx_i from du_i, one accumulator per candidate
+        double acc[NCAND];
+#pragma unroll
+        for (int c = 0; c < NCAND; c++) acc[c] = 0.0;
+        if (lane < n) {
+            double dxi = 0.0;
+            for (int k = 0; k < H; k++) {
+                const double xi = Xb[(size_t)k * ns + lane];
+#pragma unroll
+                for (int c = 0; c < NCAND; c++) {
+                    const double xc = xi + alpha_of(c) * dxi;
+                    for (int ti = 0; ti < P.n_tasks; ti++) {
+                        const DevTask& tk = P.tasks[ti];
+                        if (!tk.limits_set) continue;
+                        bool act;
+                        const double q = limit_q(tk, lane, xc, act);
+                        if (act) acc[c] += (q * 1.0) * q;
+                    }
+                }
+                if (k < H - 1) dxi = dxi + dt * sDU[k * ms + lane];
             }
-        if (__any_sync(FULL, viol)) {
-            for (int c = 0; c < ncand; c++) {
-                const double alpha = alpha_of(c);
-                double acc = 0.0;
-                bool dummy = false;
-                for (int k = lane; k < H; k += 32)
-                    for (int i = 0; i < n; i++) acc += limit_cost_elem(P, i, Xb[(size_t)k * ns + i] + alpha * DX[(size_t)k * ns + i], dummy);
-                acc = warp_sum(acc);
-                if (lane == c) lim_mine = acc;
-            }
+        }
+#pragma unroll
+        for (int c = 0; c < NCAND; c++) {
+            const double v = warp_sum(acc[c]);
+            if (lane == c) lim_mine = v;
         }
     }
 
-    // ---- phase C: task cost of every (candidate, keypoint step) pair, one pair per lane
-    for (int idx = lane; idx < ncand * S; idx += 32) {
-        const int c = idx / S, s = idx % S, k = P.kp_steps[s];
+    // ---- phase C: task cost of every (candidate, keypoint step) pair, one pair per lane      System.cpp:213-222
+    for (int base = 0; base < ncand * S; base += 32) {
+        const int idx = base + lane;
+        const bool act = idx < ncand * S;
+        const int c = act ? idx / S : 0, s = act ? idx % S : 0, k = P.kp_steps[s];
         const double alpha = alpha_of(c);
-        double x[NX], u[NX];
-#pragma unroll
-        for (int i = 0; i < NX; i++) {
-            x[i] = (i < n) ? Xb[(size_t)k * ns + i] + alpha * DX[(size_t)k * ns + i] : 0.0;
-            u[i] = (i < m && k < H - 1) ? Ub[(size_t)k * ms + i] + alpha * DU[(size_t)k * ms + i] : 0.0;
+        const double* xk = Xb + (size_t)k * ns;
+        const double* dxk = sDXk + s * ns;
+        double cost = 0.0;
+        for (int ti = 0; ti < P.n_tasks; ti++) {
+            const DevTask& tk = P.tasks[ti];
+            const int kp = task_kp_at(tk, k);
+            if (kp < 0) continue;
+            const int off = tk.joint_offset;
+            double fx[7], Jc[6], res[6];
+            lean_task_eval(P, tk, [&](int j) { return xk[off + j] + alpha * dxk[off + j]; }, -1, fx, Jc);
+            double cst = lean_task_cost(P, tk, b, kp, fx, res);
+            if (k < H - 1) {
+                double uRu = 0.0;
+                for (int j = 0; j < m; j++) {
+                    const double uj = Ub[(size_t)k * ms + j] + alpha * sDU[k * ms + j];
+                    uRu += (uj * tk.r_diag[j]) * uj;
+                }
+                cst += uRu;
+            }
+            cost += cst;
         }
-        s_cc[wid][c][s] = stage_cost<NX, false>(P, b, x, k < H - 1 ? u : nullptr, k);
+        if (act) s_cc[c * S + s] = cost;
     }
     __syncwarp();
 
@@ -556,7 +642,7 @@ __global__ void __launch_bounds__(32 * WARPS) k_forward_n1(const DevProblem* __r
     const double cost0 = W.cost0[b];
     double tot = 0.0;
     if (lane < ncand) {
-        for (int s = 0; s < S; s++) tot += s_cc[wid][lane][s];
+        for (int s = 0; s < S; s++) tot += s_cc[lane * S + s];
         tot += lim_mine;
     }
     const bool good = (lane < ncand) && !((tot >= cost0) || isnan(tot));
@@ -566,23 +652,102 @@ __global__ void __launch_bounds__(32 * WARPS) k_forward_n1(const DevProblem* __r
     const double newCost = __shfl_sync(FULL, tot, sel);
     const double alpha = alpha_of(sel);
 
-    // ---- phase E: accept.  U += alpha du ; X re-integrated from U (SimulationInterface.cpp:19-31 operation order)
-    for (int e = lane; e < (H - 1) * ms; e += 32) Ub[e] = Ub[e] + alpha * DU[e];
-    __syncwarp();
+    // ---- phase E: accept.  u += alpha du ; x re-integrated from u with the reference's operation order
+    //      (SimulationInterface.cpp:19-31).  Lane i < dof walks the horizon for joint i, loads batched eight steps deep.
     if (lane < dof) {
         double xq = P.q0[(size_t)b * dof + lane];
         const double hdt2 = __dmul_rn(dt, dt) / 2;
-        for (int k = 0; k < H - 1; k++) {
-            const double uu = Ub[(size_t)k * ms + lane];
-            xq = __dadd_rn(xq, __dadd_rn(__dmul_rn(dt, uu), __dmul_rn(hdt2, 0.0)));
-            Xb[(size_t)(k + 1) * ns + lane] = xq;
+        for (int k0 = 0; k0 < H - 1; k0 += 8) {
+            double uu[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) uu[j] = (k0 + j < H - 1) ? Ub[(size_t)(k0 + j) * ms + lane] : 0.0;
+#pragma unroll
+            for (int j = 0; j < 8; j++)
+                if (k0 + j < H - 1) {
+                    const double un = uu[j] + alpha * sDU[(k0 + j) * ms + lane];
+                    Ub[(size_t)(k0 + j) * ms + lane] = un;
+                    xq = __dadd_rn(xq, __dadd_rn(__dmul_rn(dt, un), __dmul_rn(hdt2, 0.0)));
+                    Xb[(size_t)(k0 + j + 1) * ns + lane] = xq;
+                }
         }
     }
     __syncwarp();
 
-    // ---- phase F: l_x, l_xx at the keypoint steps of the accepted trajectory; bookkeeping
-    if (it + 1 < nb_iter)
-        for (int idx = lane; idx < S * n; idx += 32) kp_deriv_row(P, W, b, idx / n, idx % n);
+    // ---- phase F: l_x = sum_tasks ((-J^T) Q) diff, l_xx = sum_tasks (J^T Q) J at the keypoint steps of the accepted
+    //      trajectory (System.cpp:252-260,290-296).  Lane (sg, i): keypoint step s0 + sg, state column i; every lane
+    //      forms its own Jacobian column and reads the others' through shared memory.
+    if (it + 1 < nb_iter) {
+        constexpr int GRP = 32 / NX;
+        const int sg = lane / NX, i = lane % NX;
+        for (int s0 = 0; s0 < S; s0 += GRP) {
+            const int s = s0 + sg;
+            const bool act = (s < S) && (i < n);
+            const int k = P.kp_steps[s < S ? s : 0];
+            const double* xk = Xb + (size_t)k * ns;
+            double lxi = 0.0, row[NX];
+#pragma unroll
+            for (int j = 0; j < NX; j++) row[j] = 0.0;
+            for (int ti = 0; ti < P.n_tasks; ti++) {
+                const DevTask& tk = P.tasks[ti];
+                const int kp = task_kp_at(tk, k);
+                const bool has = act && kp >= 0;
+                if (!__any_sync(FULL, has)) continue;
+                const int off = tk.joint_offset, r = tk.r_t;
+                const int cj_ = i - off;
+                const int cj = (cj_ >= 0 && cj_ < P.robots[tk.robot].dof) ? cj_ : -1;
+                double fx[7], Jc[6], res[6], jq[6];
+#pragma unroll
+                for (int a = 0; a < 6; a++) res[a] = 0.0;
+                lean_task_eval(P, tk, [&](int j) { return xk[off + j]; }, cj, fx, Jc);
+                if (kp >= 0) {
+                    const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
+                    task_residual(P, tk, fx, tg, res);
+                }
+                const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + (kp >= 0 ? kp : 0)) * r * r;
+                double gsum = 0.0;
+#pragma unroll
+                for (int c = 0; c < 6; c++) {
+                    double a = 0.0, na = 0.0;
+                    if (c < r) {
+#pragma unroll
+                        for (int a2 = 0; a2 < 6; a2++)
+                            if (a2 < r) {
+                                const double qv = Q[a2 * r + c];
+                                a += Jc[a2] * qv;
+                                na += (-1.0 * Jc[a2]) * qv;
+                            }
+                    }
+                    jq[c] = a;
+                    gsum += na * res[c];
+                }
+#pragma unroll
+                for (int a = 0; a < 6; a++) s_J[lane * 6 + a] = has ? Jc[a] : 0.0;
+                __syncwarp();
+                if (has) {
+                    lxi += gsum;
+#pragma unroll
+                    for (int j = 0; j < NX; j++) {
+                        if (j < n) {
+                            const double* Jj = s_J + (sg * NX + j) * 6;
+                            double h = 0.0;
+#pragma unroll
+                            for (int c = 0; c < 6; c++)
+                                if (c < r) h += jq[c] * Jj[c];
+                            row[j] += h;
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+            if (act) {
+                W.LX[((size_t)b * S + s) * n + i] = lxi;
+                double* out = W.LXX + (((size_t)b * S + s) * n + i) * n;
+#pragma unroll
+                for (int j = 0; j < NX; j++)
+                    if (j < n) out[j] = row[j];
+            }
+        }
+    }
     if (lane == 0) {
         W.cost0[b] = newCost;
         W.cost_hist[(size_t)b * nb_iter + it] = newCost;

@@ -228,12 +228,13 @@ int launch_backward(ilqrb_handle h, bool al, double pf) {
 bool fast_n1_applies(ilqrb_handle h, bool al) {
     static const bool forced_generic = getenv("ILQRB_GENERIC") != nullptr;  // A/B switch for tests and profiling
     const DevProblem& P = h->hp;
-    return !forced_generic && !al && P.nb_deriv == 1 && !P.time && P.n == P.m && P.n + 1 <= 16;
+    return !forced_generic && !al && P.nb_deriv == 1 && !P.time && P.n == P.m && P.n + 1 <= 16 &&
+           (size_t)fwd_n1_smem_doubles(P.H, h->W.ns, P.n_kp_steps) * sizeof(double) <= 200 * 1024;
 }
-template <int NT, int WARPS, int MINB>
+template <int NT, int DOF, int WARPS, int MINB>
 int launch_backward_n1_t(ilqrb_handle h) {
     const size_t smem = (size_t)WARPS * BwdN1Smem<NT>::PER_WARP * sizeof(double);
-    auto kern = k_backward_n1<NT, WARPS, MINB>;
+    auto kern = k_backward_n1<NT, DOF, WARPS, MINB>;
     static bool attr_set = false;
     if (!attr_set) {
         CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -245,19 +246,40 @@ int launch_backward_n1_t(ilqrb_handle h) {
 }
 int launch_backward_n1(ilqrb_handle h) {
     h->begin(PS_BACKWARD);
-    int rc = (h->hp.n + 1 <= 8) ? launch_backward_n1_t<1, 4, 7>(h) : launch_backward_n1_t<2, 4, 2>(h);
+    const int n = h->hp.n;
+    int rc;
+    if (n == 7) rc = launch_backward_n1_t<1, 7, 4, 7>(h);
+    else if (n == 14) rc = launch_backward_n1_t<2, 14, 4, 2>(h);
+    else if (n + 1 <= 8) rc = launch_backward_n1_t<1, 0, 4, 7>(h);
+    else rc = launch_backward_n1_t<2, 0, 4, 2>(h);
     h->end();
     if (rc) return rc;
     CU(cudaGetLastError());
     return 0;
 }
+template <int NT, int DOF, int MINB>
+int launch_forward_n1_t(ilqrb_handle h, int it, int nb_iter, int line_search, int early_stop) {
+    const DevProblem& P = h->hp;
+    const size_t smem = (size_t)fwd_n1_smem_doubles(P.H, h->W.ns, P.n_kp_steps) * sizeof(double);
+    auto kern = k_forward_n1<NT, DOF, MINB>;
+    static size_t attr_smem = 0;
+    if (smem > attr_smem) {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_smem = smem;
+    }
+    kern<<<P.B, 32, smem, h->stream>>>(h->dp, h->W, it, nb_iter, line_search, early_stop);
+    return 0;
+}
 int launch_forward_n1(ilqrb_handle h, int it, int nb_iter, int line_search, int early_stop) {
-    const int B = h->hp.B;
-    constexpr int WARPS = 4;
+    const int n = h->hp.n;
+    int rc;
     h->begin(PS_LINESEARCH);
-    if (h->hp.n + 1 <= 8) k_forward_n1<1, WARPS><<<(B + WARPS - 1) / WARPS, 32 * WARPS, 0, h->stream>>>(h->dp, h->W, it, nb_iter, line_search, early_stop);
-    else k_forward_n1<2, WARPS><<<(B + WARPS - 1) / WARPS, 32 * WARPS, 0, h->stream>>>(h->dp, h->W, it, nb_iter, line_search, early_stop);
+    if (n == 7) rc = launch_forward_n1_t<1, 7, 28>(h, it, nb_iter, line_search, early_stop);
+    else if (n == 14) rc = launch_forward_n1_t<2, 14, 12>(h, it, nb_iter, line_search, early_stop);
+    else if (n + 1 <= 8) rc = launch_forward_n1_t<1, 0, 28>(h, it, nb_iter, line_search, early_stop);
+    else rc = launch_forward_n1_t<2, 0, 12>(h, it, nb_iter, line_search, early_stop);
     h->end();
+    if (rc) return rc;
     CU(cudaGetLastError());
     return 0;
 }
@@ -548,6 +570,23 @@ int ilqrb_create(const ilqrb_problem_desc* d, int device, ilqrb_handle* out) {
             if (nj != rb.dof) {
                 ilqrb_destroy(h);
                 return fail(ILQRB_EINVAL, "robot.dof does not match the chain's movable joints");
+            }
+            // compacted chain: a fixed segment's pose is its tip frame, so it folds into the tip of the segment before it
+            o.n_lean = 0;
+            for (int s = 0; s < rb.n_segments; s++) {
+                const ilqrb_segment& sg = rb.segments[s];
+                if (sg.joint_type == ILQRB_JOINT_FIXED && o.n_lean > 0) {
+                    ilqrb_segment& pv = o.lean[o.n_lean - 1];
+                    double R[9], p[3];
+                    for (int i = 0; i < 3; i++) {
+                        for (int j = 0; j < 3; j++) R[3 * i + j] = pv.tip_R[3 * i] * sg.tip_R[j] + pv.tip_R[3 * i + 1] * sg.tip_R[3 + j] + pv.tip_R[3 * i + 2] * sg.tip_R[6 + j];
+                        p[i] = pv.tip_R[3 * i] * sg.tip_p[0] + pv.tip_R[3 * i + 1] * sg.tip_p[1] + pv.tip_R[3 * i + 2] * sg.tip_p[2] + pv.tip_p[i];
+                    }
+                    std::memcpy(pv.tip_R, R, sizeof(R));
+                    std::memcpy(pv.tip_p, p, sizeof(p));
+                } else {
+                    o.lean[o.n_lean++] = sg;
+                }
             }
         } else if (rb.kind == ILQRB_ROBOT_2D) {
             for (int c = 0; c < rb.dof; c++) o.lengths[c] = rb.lengths[c];

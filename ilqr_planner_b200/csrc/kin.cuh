@@ -34,6 +34,8 @@ struct DevRobot {
     int kind, dof, n_segments, pad_;
     ilqrb_segment segs[ILQRB_MAX_SEGMENTS];
     double lengths[RDOF + 1];
+    int n_lean, pad2_;                        // compacted chain (fixed segments folded into the preceding tip frame)
+    ilqrb_segment lean[ILQRB_MAX_SEGMENTS];  // used by kin_lean.cuh
 };
 struct DevTask {
     int robot, joint_offset, has_transform, n_keypoints;

@@ -83,7 +83,9 @@ def _check_recursive(pb, u0, nb_iter, oracle, early_stop=False):
         out = h.solve_recursive(u0, nb_iter, True, early_stop)
     ref = oracle.solve_recursive(pb, u0, nb_iter, True, early_stop, threads=8)
     assert rel(out.cost_hist, ref.cost_hist) < RTOL
-    assert rel(out.cost, ref.cost) < RTOL
+    # the final cost is held to the same absolute scale as the trace (a cost of 1e-7 is a sum of squared residuals of
+    # 3e-4: a 1e-12 trajectory difference already moves it by 1e-8 of itself)
+    assert rel(out.cost, ref.cost, scale=float(np.nanmax(np.abs(ref.cost_hist)))) < RTOL
     # problems whose every line-search decision is decisive must match in everything the reference returns;
     # after a declared tie the two runs may sit on different (equally valid) branches: those problems are held to the
     # cost tolerance above and to a loose trajectory bound only.
