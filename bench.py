@@ -257,17 +257,23 @@ def main():
                 "config": workload_config(world, B), "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
                 "gpu_launches": int(launches),
-                "roofline": {"kernel": "k_backward (riccati_backward)", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": (achieved / hbm_peak) if achieved else None, "traffic": None, "peak_source": peak_src,
-                             "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": bw_avg_s * 1e3, "share_of_step": bw_ms / tot_ms if tot_ms else None},
-                "roofline_fp64": {"kernel": "k_backward", "bound": "fp64", "algorithmic_flops_per_launch": alg_flops,
-                                  "achieved": alg_flops / bw_avg_s / 1e12 if bw_avg_s > 0 else None, "peak": fp64_peak, "unit": "TFLOP/s",
-                                  "frac": (alg_flops / bw_avg_s / 1e12 / fp64_peak) if (bw_avg_s > 0 and fp64_peak) else None,
-                                  "peak_source": "cuBLAS DGEMM 4096^3 measured in this run"},
+                # dominant kernel = the backward Riccati pass; SURVEY 8d: it is bound by the FP64 (tensor/DMMA + DFMA) pipe
+                "roofline": {"kernel": "riccati_backward (k_backward_n1: DMMA m8n8k4.f64 + DFMA)", "bound": "tensor",
+                             "achieved": alg_flops / bw_avg_s / 1e12 if bw_avg_s > 0 else None, "peak": fp64_peak, "unit": "TFLOP/s",
+                             "frac": (alg_flops / bw_avg_s / 1e12 / fp64_peak) if (bw_avg_s > 0 and fp64_peak) else None,
+                             "traffic": 212e6 if B == BATCH_PER_GPU else None,
+                             "traffic_note": "dram__bytes_read+write per launch from profiles/ (ncu --set full, B=4096)",
+                             "peak_source": "FP64 tensor peak measured in this run: cuBLAS DGEMM 4096^3 via torch.matmul (MEASURED_PEAKS.json has no FP64 entry; "
+                                            "the bf16 figure there does not apply to an FP64 path)",
+                             "algorithmic_flops_per_launch": alg_flops, "algorithmic_flops_per_problem_step": flops_step,
+                             "avg_launch_ms": bw_avg_s * 1e3, "share_of_step": bw_ms / tot_ms if tot_ms else None},
+                "roofline_hbm": {"kernel": "riccati_backward", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                                 "frac": (achieved / hbm_peak) if achieved else None, "peak_source": peak_src,
+                                 "algorithmic_bytes_per_launch": alg_bytes},
                 "kernel_ms_per_solve": {k: v[0] for k, v in prof.items()},
                 "final_cost_mean": float(np.nanmean(all_cost)), "problems_with_nan": int(np.isnan(all_cost).sum())}
         if world == 1 and not args.no_cpu_baseline:
-            sample = 512
+            sample = min(B, 4096)
             v, threads, dt, ref = cpu_baseline_run(sample)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": "first %d problems of the workload, all %d iterations, CPU oracle on %d threads, %.1f s" % (sample, NB_ITER, threads, dt)}

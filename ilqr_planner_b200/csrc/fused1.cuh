@@ -60,13 +60,14 @@ __device__ __forceinline__ double fast_rcp(double x) {
     return y;
 }
 
-// In-register inverse of an (8NT)^2 matrix held in accumulator layout whose leading m x m block is the matrix to
-// invert and whose remaining rows / columns are those of the identity: Gauss-Jordan without pivoting (Quu + 1e-6 I is
-// symmetric positive definite in normal operation; replaces the PartialPivLU inverse of ILQRRecursive.cpp:89).
-// Pivot row / column / element travel by warp shuffles; no shared memory, no barrier.  M > 0: m known at compile time.
-// Returns false if a pivot was <= 0 or NaN.
+// Solve (L) X = Rr in registers, both (8NT)^2 matrices in accumulator layout: Gauss-Jordan elimination of the augmented
+// matrix [L | Rr] without pivoting and without row scaling (rows are divided by their diagonal once, at the end).
+// L = Quu + 1e-6 I in its leading m x m block (symmetric positive definite in normal operation) and identity outside;
+// replaces the PartialPivLU inverse and the two products of ILQRRecursive.cpp:89-91.  Pivot row / column / element
+// travel by warp shuffles; no shared memory, no barrier.  M > 0: m known at compile time.  On return Rr = L^-1 Rr.
+// Returns false if a pivot was <= 0, infinite or NaN.
 template <int NT, int M>
-__device__ __forceinline__ bool gj_inverse_regs(double (&e)[NT][NT][2], int m_rt, int g, int t) {
+__device__ __forceinline__ bool gj_solve_regs(double (&L)[NT][NT][2], double (&Rr)[NT][NT][2], int m_rt, int g, int t) {
     constexpr unsigned FULL = 0xffffffffu;
     const int m = M > 0 ? M : m_rt;
     bool ok = true;
@@ -74,36 +75,46 @@ __device__ __forceinline__ bool gj_inverse_regs(double (&e)[NT][NT][2], int m_rt
     for (int k = 0; k < 8 * NT; k++) {
         if (k < m) {  // warp-uniform (compile-time when M > 0)
             const int kt = k >> 3, kg = k & 7, kh = k & 1;
-            double rowk[NT][2], colk[NT];
+            const double pkk = __shfl_sync(FULL, L[kt][kt][kh], 4 * kg + (kg >> 1));
+            double rl[NT][2], rr[NT][2], colk[NT];
 #pragma unroll
             for (int ct = 0; ct < NT; ct++) {
-                rowk[ct][0] = __shfl_sync(FULL, e[kt][ct][0], 4 * kg + t);
-                rowk[ct][1] = __shfl_sync(FULL, e[kt][ct][1], 4 * kg + t);
+                if (ct >= kt) {  // columns left of the pivot tile are dead
+                    rl[ct][0] = __shfl_sync(FULL, L[kt][ct][0], 4 * kg + t);
+                    rl[ct][1] = __shfl_sync(FULL, L[kt][ct][1], 4 * kg + t);
+                }
+                rr[ct][0] = __shfl_sync(FULL, Rr[kt][ct][0], 4 * kg + t);
+                rr[ct][1] = __shfl_sync(FULL, Rr[kt][ct][1], 4 * kg + t);
             }
 #pragma unroll
-            for (int rt = 0; rt < NT; rt++) colk[rt] = __shfl_sync(FULL, e[rt][kt][kh], 4 * g + (kg >> 1));
-            const double pkk = __shfl_sync(FULL, e[kt][kt][kh], 4 * kg + (kg >> 1));
-            if (!(pkk > 0.0)) ok = false;
+            for (int rt = 0; rt < NT; rt++) colk[rt] = __shfl_sync(FULL, L[rt][kt][kh], 4 * g + (kg >> 1));
+            const int hi = __double2hiint(pkk);
+            ok = ok && (hi > 0) && (hi < 0x7ff00000);
             const double piv = fast_rcp(pkk);
-            const bool pcol = (t == (kg >> 1));  // this lane owns column k in slot kh of column tile kt
 #pragma unroll
             for (int rt = 0; rt < NT; rt++) {
-                const bool prow = (rt == kt) && (g == kg);  // this lane owns row k
-                const double f = prow ? -1.0 : colk[rt];
+                const bool prow = (rt == kt) && (g == kg);  // this lane owns row k: left as it is
+                const double f = prow ? 0.0 : colk[rt] * piv;
 #pragma unroll
                 for (int ct = 0; ct < NT; ct++)
 #pragma unroll
                     for (int h = 0; h < 2; h++) {
-                        const double rkj = rowk[ct][h] * piv;
-                        const double base = prow ? 0.0 : e[rt][ct][h];
-                        double v = fma(-f, rkj, base);  // row k: rkj ; other rows: e - colk * rkj
-                        if (ct == kt && h == kh) {      // compile-time: the slot that can hold column k
-                            const double cv = prow ? piv : (-colk[rt]) * piv;
-                            v = pcol ? cv : v;
-                        }
-                        e[rt][ct][h] = v;
+                        if (ct >= kt) L[rt][ct][h] = fma(-f, rl[ct][h], L[rt][ct][h]);
+                        Rr[rt][ct][h] = fma(-f, rr[ct][h], Rr[rt][ct][h]);
                     }
             }
+        }
+    }
+    // divide every row by its diagonal entry: (i, i) lives in lane (g, g>>1), slot g&1 of tile [rt][rt]
+#pragma unroll
+    for (int rt = 0; rt < NT; rt++) {
+        const double mine = (g & 1) ? L[rt][rt][1] : L[rt][rt][0];
+        const double dgi = __shfl_sync(FULL, mine, 4 * g + ((g >> 1) & 3));
+        const double inv = fast_rcp(dgi);
+#pragma unroll
+        for (int ct = 0; ct < NT; ct++) {
+            Rr[rt][ct][0] *= inv;
+            Rr[rt][ct][1] *= inv;
         }
     }
     return ok;
@@ -112,32 +123,25 @@ __device__ __forceinline__ bool gj_inverse_regs(double (&e)[NT][NT][2], int m_rt
 template <int NT>
 struct BwdN1Smem {
     static constexpr int NX = 8 * NT, LD = NX + 4, SZ = NX * LD;
-    static constexpr int PER_WARP = 5 * SZ;  // Inv, [Qux|Qu], Quu, [K|d], K^T Quu
+    static constexpr int PER_WARP = 4 * SZ;  // [Qux|Qu], Quu, [K|d], Quu [K|d] + [Qux|Qu]
 };
 
 // ------------------------------------------------------------------------------------------------------------
 // backward Riccati pass, A = I, B = dt I.  Augmented layout: column n of the state-indexed matrices carries the
 // vector ([P|p], [Qux|Qu], [Qxx|Qx], [K|d]); rows >= n and columns > n are kept at exact zero.
 // DOF > 0: n = m = DOF at compile time; DOF == 0: read from the problem.
-template <int NT, int DOF, int WARPS, int MINB>
-__global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProblem* __restrict__ Pp, Work W) {
+template <int NT, int DOF>
+__device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work& W, int b, int lane, double* wsmem) {
     using S = BwdN1Smem<NT>;
     constexpr int LD = S::LD, SZ = S::SZ;
-    extern __shared__ double smem[];
-    const DevProblem& P = *Pp;
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int b = blockIdx.x * WARPS + wid;
-    if (b >= P.B) return;
-    if (W.done[b]) return;
     const int g = lane >> 2, t = lane & 3;
     const int n = DOF > 0 ? DOF : P.n, m = n, H = P.H;
     const int ns = (n + 1) & ~1, ms = ns;
     const double dt = 1.0 * P.dt;  // B = Identity * dt
-    double* sInv = smem + (size_t)wid * S::PER_WARP;
-    double* sQux = sInv + SZ;
+    double* sQux = wsmem;
     double* sQuu = sQux + SZ;
     double* sKd = sQuu + SZ;
-    double* sKtQ = sKd + SZ;
+    double* sM = sKd + SZ;
 
     double Rrow[NT];
 #pragma unroll
@@ -290,33 +294,18 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
         }
         if (l0 >= 0) add_limits(Qx, x);
 
-        spd = gj_inverse_regs<NT, DOF>(Inv, m, g, t) && spd;
-        st_c<NT, LD>(sInv, Inv, g, t);
         st_c<NT, LD>(sQux, Qa, g, t);
         st_c<NT, LD>(sQuu, Qu2, g, t);
-        __syncwarp();
-
-        // [K|d] = -(Inv [Qux|Qu])                                                        ILQRRecursive.cpp:90-91
-        double bQ[NT][2][NT];
-#pragma unroll
-        for (int kt = 0; kt < NT; kt++)
-#pragma unroll
-            for (int s = 0; s < 2; s++)
-#pragma unroll
-                for (int ct = 0; ct < NT; ct++) bQ[kt][s][ct] = ld_b<LD>(sQux, kt, s, ct, g, t);
+        // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]                                            ILQRRecursive.cpp:89-91
         double Kd[NT][NT][2];
 #pragma unroll
         for (int rt = 0; rt < NT; rt++)
 #pragma unroll
             for (int ct = 0; ct < NT; ct++) {
-                double c0 = 0.0, c1 = 0.0;
-#pragma unroll
-                for (int kt = 0; kt < NT; kt++)
-#pragma unroll
-                    for (int s = 0; s < 2; s++) dmma884(c0, c1, ld_a<LD>(sInv, rt, kt, s, g, t), bQ[kt][s][ct]);
-                Kd[rt][ct][0] = -c0;  // rows >= m: identity rows of Inv times zero rows of [Qux|Qu] = 0
-                Kd[rt][ct][1] = -c1;
+                Kd[rt][ct][0] = -Qa[rt][ct][0];
+                Kd[rt][ct][1] = -Qa[rt][ct][1];
             }
+        spd = gj_solve_regs<NT, DOF>(Inv, Kd, m, g, t) && spd;
         st_c<NT, LD>(sKd, Kd, g, t);
         // stream K, d to global (time-forward index)
 #pragma unroll
@@ -334,34 +323,31 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
         }
         __syncwarp();
 
-        // K^T Quu  (row n = d^T Quu is produced too and masked out of P below)
-        double kb[NT][2][NT], bU[NT][2][NT];
+        // [M|mv] = Quu [K|d] + [Qux|Qu]   (= K^T-free half of ILQRRecursive.cpp:93-94: K^T Quu K + K^T Qux = K^T M)
+        double kb[NT][2][NT];
 #pragma unroll
         for (int kt = 0; kt < NT; kt++)
 #pragma unroll
             for (int s = 0; s < 2; s++)
 #pragma unroll
-                for (int ct = 0; ct < NT; ct++) {
-                    kb[kt][s][ct] = ld_b<LD>(sKd, kt, s, ct, g, t);  // B fragment of [K|d] == A fragment of [K|d]^T
-                    bU[kt][s][ct] = ld_b<LD>(sQuu, kt, s, ct, g, t);
-                }
-        double KtQ[NT][NT][2];
+                for (int ct = 0; ct < NT; ct++) kb[kt][s][ct] = ld_b<LD>(sKd, kt, s, ct, g, t);  // B fragment of [K|d] == A fragment of [K|d]^T
+        double Mm[NT][NT][2];
 #pragma unroll
         for (int rt = 0; rt < NT; rt++)
 #pragma unroll
             for (int ct = 0; ct < NT; ct++) {
-                double c0 = 0.0, c1 = 0.0;
+                double c0 = Qa[rt][ct][0], c1 = Qa[rt][ct][1];
 #pragma unroll
                 for (int kt = 0; kt < NT; kt++)
 #pragma unroll
-                    for (int s = 0; s < 2; s++) dmma884(c0, c1, kb[kt][s][rt], bU[kt][s][ct]);
-                KtQ[rt][ct][0] = c0;
-                KtQ[rt][ct][1] = c1;
+                    for (int s = 0; s < 2; s++) dmma884(c0, c1, ld_a<LD>(sQuu, rt, kt, s, g, t), kb[kt][s][ct]);
+                Mm[rt][ct][0] = c0;
+                Mm[rt][ct][1] = c1;
             }
-        st_c<NT, LD>(sKtQ, KtQ, g, t);
+        st_c<NT, LD>(sM, Mm, g, t);
         __syncwarp();
 
-        // [P|p] = [Qxx|Qx] + (K^T Quu)[K|d] + K^T [Qux|Qu] + Qxu [K|d]                   ILQRRecursive.cpp:93-94
+        // [P|p] = [Qxx|Qx] + K^T [M|mv] + Qxu [K|d]     (row n = d^T [M|mv] is produced too and masked out)
 #pragma unroll
         for (int rt = 0; rt < NT; rt++)
 #pragma unroll
@@ -370,11 +356,7 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
 #pragma unroll
                 for (int kt = 0; kt < NT; kt++)
 #pragma unroll
-                    for (int s = 0; s < 2; s++) dmma884(c0, c1, ld_a<LD>(sKtQ, rt, kt, s, g, t), kb[kt][s][ct]);
-#pragma unroll
-                for (int kt = 0; kt < NT; kt++)
-#pragma unroll
-                    for (int s = 0; s < 2; s++) dmma884(c0, c1, kb[kt][s][rt], bQ[kt][s][ct]);
+                    for (int s = 0; s < 2; s++) dmma884(c0, c1, kb[kt][s][rt], ld_b<LD>(sM, kt, s, ct, g, t));
 #pragma unroll
                 for (int kt = 0; kt < NT; kt++)
 #pragma unroll
@@ -386,6 +368,17 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
         __syncwarp();  // shared operands are rewritten by the next step
     }
     if (!spd && lane == 0) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
+}
+
+template <int NT, int DOF, int WARPS, int MINB>
+__global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
+    extern __shared__ double smem[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int bl = blockIdx.x * WARPS + wid;
+    if (bl >= nB) return;
+    const int b = b0 + bl;
+    if (W.done[b]) return;
+    backward_n1_body<NT, DOF>(*Pp, W, b, lane, smem + (size_t)wid * BwdN1Smem<NT>::PER_WARP);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -403,16 +396,12 @@ __host__ __device__ inline int fwd_n1_smem_doubles(int H, int ns, int S) {
 }
 
 // forward pass: line search over all candidates, accept, derivatives of the accepted trajectory.  One warp per block.
-template <int NT, int DOF, int MINB>
-__global__ void __launch_bounds__(32, MINB) k_forward_n1(const DevProblem* __restrict__ Pp, Work W, int it, int nb_iter, int line_search, int early_stop) {
+// returns true when the early-stop rule fired for this problem
+template <int NT, int DOF>
+__device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work& W, int b, int lane, double* smem, int it, int nb_iter, int line_search, int early_stop) {
     constexpr int NX = 8 * NT;
     constexpr unsigned FULL = 0xffffffffu;
     constexpr int PF = (NT == 1) ? 4 : 3;  // register ring of gain fragments, in steps (L2 prefetch runs further ahead)
-    extern __shared__ double smem[];
-    const DevProblem& P = *Pp;
-    const int lane = threadIdx.x;
-    const int b = blockIdx.x;
-    if (W.done[b]) return;
     const int g = lane >> 2, t = lane & 3;
     const int n = DOF > 0 ? DOF : P.n, m = n, dof = n, H = P.H, S = P.n_kp_steps;
     const int ns = (n + 1) & ~1, ms = ns;
@@ -748,6 +737,7 @@ __global__ void __launch_bounds__(32, MINB) k_forward_n1(const DevProblem* __res
             }
         }
     }
+    const bool stop = early_stop && (alpha * sqrt(alpha * dun1) < 1e-3) && (newCost < 1e-3);  // ILQRRecursive.cpp:174
     if (lane == 0) {
         W.cost0[b] = newCost;
         W.cost_hist[(size_t)b * nb_iter + it] = newCost;
@@ -756,12 +746,21 @@ __global__ void __launch_bounds__(32, MINB) k_forward_n1(const DevProblem* __res
         W.iters[b] = it + 1;
         int st = W.status[b];
         if (isnan(newCost)) st |= ILQRB_ST_NAN_COST;
-        if (early_stop && (alpha * sqrt(alpha * dun1) < 1e-3) && (newCost < 1e-3)) {
+        if (stop) {
             st |= ILQRB_ST_EARLY_STOP;
             W.done[b] = 1;
         }
         W.status[b] = st;
     }
+    return stop;
+}
+
+template <int NT, int DOF, int MINB>
+__global__ void __launch_bounds__(32, MINB) k_forward_n1(const DevProblem* __restrict__ Pp, Work W, int b0, int it, int nb_iter, int line_search, int early_stop) {
+    extern __shared__ double smem[];
+    const int b = b0 + blockIdx.x;
+    if (W.done[b]) return;
+    forward_n1_body<NT, DOF>(*Pp, W, b, threadIdx.x, smem, it, nb_iter, line_search, early_stop);
 }
 
 }  // namespace ilqrb

@@ -3,6 +3,7 @@
 // solve path runs in the CUDA kernels of recursive.cuh / batch.cuh.  There is no CPU fallback.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -66,6 +67,26 @@ struct ilqrb_handle_s {
     double prof_ms[ILQRB_PROF_SLOTS] = {0};
     int64_t prof_n[ILQRB_PROF_SLOTS] = {0};
     int64_t launches = 0;
+    bool downloaded = false;  // the last run already sent its results to the host (per group)
+    // problem groups of the fast path (one stream each)
+    static constexpr int MAX_GROUPS = 8;
+    int n_groups = 0;
+    cudaStream_t gstream[MAX_GROUPS] = {nullptr};
+    cudaEvent_t ev_start = nullptr, ev_stagger[MAX_GROUPS] = {nullptr}, ev_done[MAX_GROUPS] = {nullptr};
+    int ensure_groups(int G) {
+        if (!ev_start && cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming) != cudaSuccess) return fail(ILQRB_ECUDA, "cudaEventCreate");
+        int least = 0, greatest = 0;
+        cudaDeviceGetStreamPriorityRange(&least, &greatest);  // numerically lower = higher priority
+        for (; n_groups < G; n_groups++) {
+            // earlier groups get higher priority: they finish first and their results travel while later groups compute
+            const int prio = std::min(least, greatest + n_groups);
+            if (cudaStreamCreateWithPriority(&gstream[n_groups], cudaStreamNonBlocking, prio) != cudaSuccess ||
+                cudaEventCreateWithFlags(&ev_stagger[n_groups], cudaEventDisableTiming) != cudaSuccess ||
+                cudaEventCreateWithFlags(&ev_done[n_groups], cudaEventDisableTiming) != cudaSuccess)
+                return fail(ILQRB_ECUDA, "could not create the group streams");
+        }
+        return 0;
+    }
 
     template <class T>
     int alloc(T** p, size_t count) {
@@ -232,7 +253,7 @@ bool fast_n1_applies(ilqrb_handle h, bool al) {
            (size_t)fwd_n1_smem_doubles(P.H, h->W.ns, P.n_kp_steps) * sizeof(double) <= 200 * 1024;
 }
 template <int NT, int DOF, int WARPS, int MINB>
-int launch_backward_n1_t(ilqrb_handle h) {
+int launch_backward_n1_t(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
     const size_t smem = (size_t)WARPS * BwdN1Smem<NT>::PER_WARP * sizeof(double);
     auto kern = k_backward_n1<NT, DOF, WARPS, MINB>;
     static bool attr_set = false;
@@ -240,25 +261,24 @@ int launch_backward_n1_t(ilqrb_handle h) {
         CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
-    const int B = h->hp.B;
-    kern<<<(B + WARPS - 1) / WARPS, 32 * WARPS, smem, h->stream>>>(h->dp, h->W);
+    kern<<<(nB + WARPS - 1) / WARPS, 32 * WARPS, smem, st>>>(h->dp, h->W, b0, nB);
     return 0;
 }
-int launch_backward_n1(ilqrb_handle h) {
+int launch_backward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
     h->begin(PS_BACKWARD);
     const int n = h->hp.n;
     int rc;
-    if (n == 7) rc = launch_backward_n1_t<1, 7, 4, 7>(h);
-    else if (n == 14) rc = launch_backward_n1_t<2, 14, 4, 2>(h);
-    else if (n + 1 <= 8) rc = launch_backward_n1_t<1, 0, 4, 7>(h);
-    else rc = launch_backward_n1_t<2, 0, 4, 2>(h);
+    if (n == 7) rc = launch_backward_n1_t<1, 7, 4, 7>(h, b0, nB, st);
+    else if (n == 14) rc = launch_backward_n1_t<2, 14, 4, 2>(h, b0, nB, st);
+    else if (n + 1 <= 8) rc = launch_backward_n1_t<1, 0, 4, 7>(h, b0, nB, st);
+    else rc = launch_backward_n1_t<2, 0, 4, 2>(h, b0, nB, st);
     h->end();
     if (rc) return rc;
     CU(cudaGetLastError());
     return 0;
 }
 template <int NT, int DOF, int MINB>
-int launch_forward_n1_t(ilqrb_handle h, int it, int nb_iter, int line_search, int early_stop) {
+int launch_forward_n1_t(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop) {
     const DevProblem& P = h->hp;
     const size_t smem = (size_t)fwd_n1_smem_doubles(P.H, h->W.ns, P.n_kp_steps) * sizeof(double);
     auto kern = k_forward_n1<NT, DOF, MINB>;
@@ -267,21 +287,25 @@ int launch_forward_n1_t(ilqrb_handle h, int it, int nb_iter, int line_search, in
         CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_smem = smem;
     }
-    kern<<<P.B, 32, smem, h->stream>>>(h->dp, h->W, it, nb_iter, line_search, early_stop);
+    kern<<<nB, 32, smem, st>>>(h->dp, h->W, b0, it, nb_iter, line_search, early_stop);
     return 0;
 }
-int launch_forward_n1(ilqrb_handle h, int it, int nb_iter, int line_search, int early_stop) {
+int launch_forward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop) {
     const int n = h->hp.n;
     int rc;
     h->begin(PS_LINESEARCH);
-    if (n == 7) rc = launch_forward_n1_t<1, 7, 28>(h, it, nb_iter, line_search, early_stop);
-    else if (n == 14) rc = launch_forward_n1_t<2, 14, 12>(h, it, nb_iter, line_search, early_stop);
-    else if (n + 1 <= 8) rc = launch_forward_n1_t<1, 0, 28>(h, it, nb_iter, line_search, early_stop);
-    else rc = launch_forward_n1_t<2, 0, 12>(h, it, nb_iter, line_search, early_stop);
+    if (n == 7) rc = launch_forward_n1_t<1, 7, 28>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+    else if (n == 14) rc = launch_forward_n1_t<2, 14, 12>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+    else if (n + 1 <= 8) rc = launch_forward_n1_t<1, 0, 28>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+    else rc = launch_forward_n1_t<2, 0, 12>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
     h->end();
     if (rc) return rc;
     CU(cudaGetLastError());
     return 0;
+}
+unsigned env_uint(const char* name, unsigned dflt) {
+    const char* v = getenv(name);
+    return v ? (unsigned)strtoul(v, nullptr, 10) : dflt;
 }
 
 int ensure_iter_capacity(ilqrb_handle h, int nb_iter) {
@@ -377,20 +401,23 @@ __global__ void k_kinematics(const DevProblem* __restrict__ Pp, int robot, int n
         for (int c = 0; c < rb.dof; c++) J[((size_t)i * 6 + a) * rb.dof + c] = a < 3 ? e.Jv[c][a] : e.Jw[c][a - 3];
 }
 
-int launch_init(ilqrb_handle h) {
-    const int B = h->hp.B;
+int launch_init(ilqrb_handle h, int b0 = 0, int nB = -1, cudaStream_t st = nullptr) {
+    if (nB < 0) nB = h->hp.B;
+    if (!st) st = h->stream;
     h->begin(PS_ROLLOUT_INIT);
-#define CALL(N, M) k_rollout_init<N, M><<<(B + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W)
+#define CALL(N, M) k_rollout_init<N, M><<<(nB + 127) / 128, 128, 0, st>>>(h->dp, h->W, b0, nB)
     DISPATCH_NM(size_class(h->hp.n, h->hp.m), CALL)
 #undef CALL
     h->end();
     CU(cudaGetLastError());
     return 0;
 }
-int launch_derivs(ilqrb_handle h) {
-    const int tot = h->hp.B * h->hp.n_kp_steps;
+int launch_derivs(ilqrb_handle h, int b0 = 0, int nB = -1, cudaStream_t st = nullptr) {
+    if (nB < 0) nB = h->hp.B;
+    if (!st) st = h->stream;
+    const int tot = nB * h->hp.n_kp_steps;
     h->begin(PS_KP_DERIVS);
-    k_kp_derivs<<<(tot + 63) / 64, 64, 0, h->stream>>>(h->dp, h->W);
+    k_kp_derivs<<<(tot + 63) / 64, 64, 0, st>>>(h->dp, h->W, b0, nB);
     h->end();
     CU(cudaGetLastError());
     return 0;
@@ -416,7 +443,51 @@ int launch_accept(ilqrb_handle h, int it, int nb_iter, int line_search, int earl
     return 0;
 }
 
-int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solve_opts* opts) {
+// Results of problems [b0, b0+nB) packed and sent to the caller's buffers, all asynchronous on `st`.  Every output has
+// its own slice of one staging buffer (problem-major), so ranges never wait for one another.
+int enqueue_download_range(ilqrb_handle h, const ilqrb_result* out, int b0, int nB, int nit, cudaStream_t st) {
+    const DevProblem& P = h->hp;
+    const size_t B = P.B;
+    const int H = P.H, n = P.n, m = P.m;
+    const size_t eX = (size_t)H * n, eU = (size_t)(H - 1) * m, eK = (size_t)(H - 1) * m * n;
+    int rc = ensure_pack(h, B * (eX + 2 * eU + eK));
+    if (rc) return rc;
+    double* sX = h->d_pack;
+    double* sU = sX + B * eX;
+    double* sK = sU + B * eU;
+    double* sD = sK + B * eK;
+    auto pack = [&](double* host, double* stage, const double* src, size_t per_problem_rows, int w, int stride, const double* scale, int rpp) -> int {
+        if (!host) return 0;
+        const size_t rows = (size_t)nB * per_problem_rows, tot = rows * w;
+        double* dst = stage + (size_t)b0 * per_problem_rows * w;
+        k_pack<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(dst, src + (size_t)b0 * per_problem_rows * stride, rows, w, stride, scale ? scale + b0 : nullptr, rpp);
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(host + (size_t)b0 * per_problem_rows * w, dst, tot * sizeof(double), cudaMemcpyDeviceToHost, st));
+        return 0;
+    };
+    if ((rc = pack(out->X, sX, h->W.X, H, n, h->W.ns, nullptr, 1))) return rc;
+    if ((rc = pack(out->U, sU, h->W.U, H - 1, m, h->W.ms, nullptr, 1))) return rc;
+    if ((rc = pack(out->K, sK, h->W.K, (size_t)(H - 1) * m, n, h->W.ns, nullptr, 1))) return rc;
+    // ds are returned multiplied by the accepted alpha (ILQRRecursive.cpp:128,144,162)
+    if ((rc = pack(out->d, sD, h->W.d, H - 1, m, h->W.ms, h->last_nb_iter > 0 ? h->W.alpha_last : nullptr, H - 1))) return rc;
+    if (out->fX) {
+        const int tot = nB * H;
+        k_final_fx<<<(tot + 127) / 128, 128, 0, st>>>(h->dp, h->W, h->d_fX, b0, nB);
+        CU(cudaGetLastError());
+        const size_t off = (size_t)b0 * H * P.nt;
+        CU(cudaMemcpyAsync(out->fX + off, h->d_fX + off, (size_t)nB * H * P.nt * sizeof(double), cudaMemcpyDeviceToHost, st));
+    }
+    if (out->cost) CU(cudaMemcpyAsync(out->cost + b0, h->W.cost0 + b0, nB * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (out->cost_hist) CU(cudaMemcpyAsync(out->cost_hist + (size_t)b0 * nit, h->W.cost_hist + (size_t)b0 * nit, (size_t)nB * nit * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (out->alpha_hist) CU(cudaMemcpyAsync(out->alpha_hist + (size_t)b0 * nit, h->W.alpha_hist + (size_t)b0 * nit, (size_t)nB * nit * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (out->iters) CU(cudaMemcpyAsync(out->iters + b0, h->W.iters + b0, nB * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (out->status) CU(cudaMemcpyAsync(out->status + b0, h->W.status + b0, nB * sizeof(int), cudaMemcpyDeviceToHost, st));
+    return 0;
+}
+
+// out_async != nullptr: the caller wants the results in host buffers; the fast path then sends each problem group's
+// results as soon as that group has finished (sets h->downloaded).
+int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solve_opts* opts, const ilqrb_result* out_async = nullptr) {
     if (!opts) return fail(ILQRB_EINVAL, "null opts");
     if (opts->nb_iter < 0) return fail(ILQRB_EINVAL, "nb_iter < 0");
     CU(cudaSetDevice(h->device));
@@ -471,10 +542,48 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
         CU(cudaGetLastError());
     }
     if (fast_n1_applies(h, al != nullptr)) {
-        if (opts->nb_iter > 0 && (rc = launch_derivs(h))) return rc;  // later iterations: k_forward_n1 phase F
-        for (int it = 0; it < opts->nb_iter; it++) {
-            if ((rc = launch_backward_n1(h))) return rc;
-            if ((rc = launch_forward_n1(h, it, opts->nb_iter, opts->line_search, opts->early_stop))) return rc;
+        if (opts->nb_iter > 0 && (rc = launch_derivs(h))) return rc;  // later iterations: phase F of the forward pass
+        // The batch is split into G groups of problems, each on its own stream, the first backward pass of group g+1
+        // held back until group g has finished its own: from then on the FP64-bound backward pass of one group shares
+        // the SMs with the latency-bound forward pass of another.  (Profiling mode: one group, per-kernel event pairs.)
+        int G = h->prof ? 1 : (int)env_uint("ILQRB_GROUPS", out_async ? 8 : 3);
+        if (G > ilqrb_handle_s::MAX_GROUPS) G = ilqrb_handle_s::MAX_GROUPS;
+        if (G < 1 || B < 64 * G) G = 1;
+        if (G == 1) {
+            for (int it = 0; it < opts->nb_iter; it++) {
+                if ((rc = launch_backward_n1(h, 0, B, h->stream))) return rc;
+                if ((rc = launch_forward_n1(h, 0, B, h->stream, it, opts->nb_iter, opts->line_search, opts->early_stop))) return rc;
+            }
+        } else if (opts->nb_iter > 0) {
+            if ((rc = h->ensure_groups(G))) return rc;
+            CU(cudaEventRecord(h->ev_start, h->stream));
+            for (int gi = 0; gi < G; gi++) CU(cudaStreamWaitEvent(h->gstream[gi], h->ev_start, 0));
+            // stagger: group g+1 starts once group g has finished `stag` iterations (0: its first backward pass only).
+            // Measured on B200 (C2, B=4096): a longer stagger buys PCIe/compute overlap for host outputs but loses the
+            // same time to SMs running below the ~4096 resident problems they need, so the default stays 0.
+            int stag = (int)env_uint("ILQRB_STAGGER_ITERS", 0);
+            if (stag >= opts->nb_iter) stag = opts->nb_iter - 1;
+            for (int gi = 0; gi < G; gi++) {
+                const int b0 = (int)((long long)B * gi / G), b1 = (int)((long long)B * (gi + 1) / G);
+                cudaStream_t st = h->gstream[gi];
+                if (gi > 0) CU(cudaStreamWaitEvent(st, h->ev_stagger[gi - 1], 0));
+                for (int it = 0; it < opts->nb_iter; it++) {
+                    if ((rc = launch_backward_n1(h, b0, b1 - b0, st))) return rc;
+                    if (stag == 0 && it == 0 && gi + 1 < G) CU(cudaEventRecord(h->ev_stagger[gi], st));
+                    if ((rc = launch_forward_n1(h, b0, b1 - b0, st, it, opts->nb_iter, opts->line_search, opts->early_stop))) return rc;
+                    if (stag > 0 && it == stag - 1 && gi + 1 < G) CU(cudaEventRecord(h->ev_stagger[gi], st));
+                }
+            }
+            h->last_nb_iter = opts->nb_iter;
+            for (int gi = 0; gi < G; gi++) {
+                if (out_async) {
+                    const int b0 = (int)((long long)B * gi / G), b1 = (int)((long long)B * (gi + 1) / G);
+                    if ((rc = enqueue_download_range(h, out_async, b0, b1 - b0, std::max(opts->nb_iter, 1), h->gstream[gi]))) return rc;
+                    h->downloaded = true;
+                }
+                CU(cudaEventRecord(h->ev_done[gi], h->gstream[gi]));
+                CU(cudaStreamWaitEvent(h->stream, h->ev_done[gi], 0));
+            }
         }
         h->last_nb_iter = opts->nb_iter;
         h->last_solver = 1;
@@ -687,6 +796,13 @@ int ilqrb_destroy(ilqrb_handle h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (void* p : h->allocs) cudaFree(p);
     for (auto e : h->ev_pool) cudaEventDestroy(e);
+    for (int gi = 0; gi < h->n_groups; gi++) {
+        cudaStreamSynchronize(h->gstream[gi]);
+        cudaStreamDestroy(h->gstream[gi]);
+        cudaEventDestroy(h->ev_stagger[gi]);
+        cudaEventDestroy(h->ev_done[gi]);
+    }
+    if (h->ev_start) cudaEventDestroy(h->ev_start);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return 0;
@@ -768,7 +884,7 @@ int ilqrb_download(ilqrb_handle h, ilqrb_result* out) {
     if (out->fX) {
         const int tot = (int)(B * H);
         h->begin(PS_FINAL);
-        k_final_fx<<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, h->d_fX);
+        k_final_fx<<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, h->d_fX, 0, (int)B);
         h->end();
         CU(cudaGetLastError());
         CU(cudaMemcpyAsync(out->fX, h->d_fX, B * H * P.nt * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
@@ -785,8 +901,14 @@ int ilqrb_download(ilqrb_handle h, ilqrb_result* out) {
 
 int ilqrb_solve_recursive(ilqrb_handle h, const double* U0, const ilqrb_solve_opts* opts, ilqrb_result* out) {
     int rc;
+    if (!h || !out) return fail(ILQRB_EINVAL, "null argument");
     if ((rc = ilqrb_upload_u0(h, U0))) return rc;
-    if ((rc = ilqrb_run_recursive(h, opts))) return rc;
+    h->downloaded = false;
+    if ((rc = run_recursive_like(h, nullptr, opts, out))) return rc;
+    if (h->downloaded) {  // every group has queued its own device-to-host copies; the solve stream waits for them
+        CU(cudaStreamSynchronize(h->stream));
+        return 0;
+    }
     return ilqrb_download(h, out);
 }
 int ilqrb_solve_al(ilqrb_handle h, const double* U0, const ilqrb_al_desc* al, const ilqrb_solve_opts* opts, ilqrb_result* out) {
@@ -825,7 +947,7 @@ int ilqrb_rollout(ilqrb_handle h, const double* U, double* X, double* fX, double
     if ((rc = download_packed(h, X, h->W.X, B * H, P.n, h->W.ns, nullptr, 1))) return rc;
     const int tot = (int)(B * H);
     if (fX) {
-        k_final_fx<<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, h->d_fX);
+        k_final_fx<<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, h->d_fX, 0, (int)B);
         CU(cudaGetLastError());
         CU(cudaMemcpyAsync(fX, h->d_fX, B * H * P.nt * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     }

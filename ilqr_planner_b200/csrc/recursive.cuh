@@ -99,10 +99,11 @@ __device__ __forceinline__ void step_state(const DevProblem& P, double* x, const
 // ------------------------------------------------------------------------------------------------------------
 // initial rollout: one thread per problem
 template <int N, int M>
-__global__ void __launch_bounds__(128) k_rollout_init(const DevProblem* __restrict__ Pp, Work W) {
+__global__ void __launch_bounds__(128) k_rollout_init(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
     const DevProblem& P = *Pp;
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= P.B) return;
+    const int bl = blockIdx.x * blockDim.x + threadIdx.x;
+    if (bl >= nB) return;
+    const int b = b0 + bl;
     const int H = P.H;
     double x[N], u[M];
     load_x0<N>(P, b, x);
@@ -131,12 +132,12 @@ __global__ void __launch_bounds__(128) k_rollout_init(const DevProblem* __restri
 // keypoint derivatives of the accepted trajectory: one thread per (problem, keypoint step)
 //   l_x  = sum_tasks ((-J^T) Q) diff      System.cpp:252-260
 //   l_xx = sum_tasks (J^T Q) J            System.cpp:290-296
-__global__ void __launch_bounds__(64) k_kp_derivs(const DevProblem* __restrict__ Pp, Work W) {
+__global__ void __launch_bounds__(64) k_kp_derivs(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
     const DevProblem& P = *Pp;
     const int S = P.n_kp_steps;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P.B * S) return;
-    const int b = idx / S, s = idx % S;
+    if (idx >= nB * S) return;
+    const int b = b0 + idx / S, s = idx % S;
     if (W.done[b]) return;
     const int k = P.kp_steps[s], n = P.n, dof = P.dof;
     const double* x = W.X + ((size_t)b * P.H + k) * W.ns;
@@ -361,11 +362,12 @@ __global__ void __launch_bounds__(128) k_accept(const DevProblem* __restrict__ P
 
 // ------------------------------------------------------------------------------------------------------------
 // f(X) for the returned trajectory: one thread per (problem, timestep)
-__global__ void __launch_bounds__(128) k_final_fx(const DevProblem* __restrict__ Pp, Work W, double* __restrict__ fX) {
+__global__ void __launch_bounds__(128) k_final_fx(const DevProblem* __restrict__ Pp, Work W, double* __restrict__ fX, int b0, int nB) {
     const DevProblem& P = *Pp;
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P.B * P.H) return;
-    const int b = idx / P.H, k = idx % P.H;
+    const int idx0 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx0 >= nB * P.H) return;
+    const int b = b0 + idx0 / P.H, k = idx0 % P.H;
+    const size_t idx = (size_t)b * P.H + k;
     const int n = P.n, dof = P.dof;
     const double* x = W.X + ((size_t)b * P.H + k) * W.ns;
     double xs[MAXN], dqs[MAXM];
