@@ -1,22 +1,775 @@
-// batch.cuh — BatchILQR / BatchILQRCP path (BatchILQR.cpp:110-173, BatchILQRCP.cpp:109-174).  (stub: filled in next)
+// batch.cuh — BatchILQR / BatchILQRCP path (BatchILQR.cpp:22-173, BatchILQRCP.cpp:21-174, System.cpp:111-211,321-361).
+//
+// Per iteration and problem (single-integrator systems, with or without a time state: A = I, so the reference's
+// `M = [A M, B]` recursion of buildSuJL keeps the B blocks as they are):
+//
+//   k_batch_fp        fpBatch for the current controls AND for the 11 line-search candidates u + alpha du in one launch
+//                     (thread = problem x candidate): rollout, task vector / residual at the keypoint rows, pre-step
+//                     joint-limit terms (Q4), cost  e^T Q e + u^T R u + ql^T L ql ; candidate 0 (alpha = 0) also
+//                     writes J, e, L, ql of the linearisation.
+//   k_batch_assemble  W = J^T Q J + L, g = J^T Q e + L ql, the dense sensitivity matrix Su with the reference's column
+//                     shift (Q3: row block of x_i is [0, B_1, .., B_{i-1}]), T = W Su, rhs = Su^T g - R u.
+//   k_batch_syrk      lstq_A = Su^T T + R, dense N x N, FP64 tensor pipe (DMMA m8n8k4).          BatchILQR.cpp:130
+//   k_batch_chol      in-place blocked Cholesky of lstq_A (one CTA per problem; diagonal block and panel in shared
+//                     memory, trailing update on DMMA) — replaces `lstq_A.inverse()` (PartialPivLU) :132
+//   k_batch_trsv      du = lstq_A^-1 rhs by the two triangular solves.
+//   CP variant        lstq_A = (Su Psi)^T W (Su Psi) + Psi^T R Psi is nw x nw: one warp per problem factors and solves
+//                     it in shared memory (k_batch_cp).                                          BatchILQRCP.cpp:129-133
+//   k_batch_select    sequential line-search rule over the 11 candidate costs (accept if cost < cost0 or alpha < 1e-3,
+//                     :135-157), u update, trace (the PRE-step cost is what the reference prints, :160), early stop.
 #pragma once
+#include <algorithm>
 #include <functional>
 #include <string>
+#include <vector>
 
 #include "kin.cuh"
 #include "recursive.cuh"
 
 namespace ilqrb {
 
-struct BatchWork {
-    double* u = nullptr;  // [B][N]
+constexpr int BNC = NCAND + 1;  // candidate 0 = current controls (alpha = 0), 1..11 = alpha 1, 1/2, .., 2^-10
+
+struct BatchDev {  // POD view passed to the kernels
+    // sizes
+    int N = 0, Np = 0, S = 0, Sn = 0, SnP = 0, Sr = 0, nw = 0, cp = 0, chunk = 0;  // Np = N padded to 64, SnP = Sn padded to 4
+    // whole batch
+    double* u = nullptr;      // [B][N]
+    double* du = nullptr;     // [B][N]
+    double* cc = nullptr;     // [B][BNC] candidate costs (0: cost0)
+    double* Qfull = nullptr;  // [Sr][Sr] shared precision override, or nullptr
+    double* psi = nullptr;    // [N][nw]
+    double* psiRpsi = nullptr;  // [nw][nw]  Psi^T R Psi
+    // per chunk of problems
+    double* Jt = nullptr;   // [C][S][r][n]
+    double* e = nullptr;    // [C][Sr]
+    double* Ld = nullptr;   // [C][S][n]  diagonal of L (0 / penalty)
+    double* ql = nullptr;   // [C][S][n]
+    double* Wm = nullptr;   // [C][Sn][Sn]
+    double* g = nullptr;    // [C][Sn]
+    double* Su = nullptr;   // [C][SnP][Np]  (rows >= Sn and columns >= N are zero)
+    double* T = nullptr;    // [C][SnP][Np]
+    double* A = nullptr;    // [C][Np][Np]
+    double* rhs = nullptr;  // [C][Np]
+};
+struct BatchWork : BatchDev {
+    bool allocated = false;
+    std::vector<void*> allocs;
 };
 
-inline int batch_run(cudaStream_t, const DevProblem&, const DevProblem*, Work&, BatchWork&, const ilqrb_batch_desc*, const ilqrb_solve_opts*, std::string& err,
-                     std::function<void(int)>, std::function<void()>) {
-    err = "Batch solvers not built yet";
-    return ILQRB_EUNSUPPORTED;
+__device__ __forceinline__ double batch_alpha(int c) { return c == 0 ? 0.0 : 1.0 / (double)(1 << (c - 1)); }
+
+// B block of the dynamics for the control u_j (row a, column c):  PosOrnPlannerSys.cpp:117-121 (dt I) and
+// PosOrnTimePlannerSys.cpp:154-176 for nb_deriv = 1 (dt = s^2 ; last column [2 s u ; 2 s])
+__device__ __forceinline__ double batch_B_entry(const DevProblem& P, const double* uj, int a, int c) {
+    const int dof = P.dof, m = P.m, n = P.n;
+    if (!P.time) return (a == c && a < dof) ? 1.0 * P.dt : 0.0;
+    const double s = uj[m - 1];
+    double v = 0.0;
+    if (a < dof && c == a) v = 1.0 * (s * s);
+    if (a < dof && c == m - 1) v = 2 * s * uj[a];
+    if (a == n - 1 && c == m - 1) v = 2 * s;
+    return v;
 }
-inline int batch_download(cudaStream_t, const DevProblem&, BatchWork&, ilqrb_result*, int) { return ILQRB_EUNSUPPORTED; }
+
+// ------------------------------------------------------------------------------------------------------------
+// fpBatch + cost for candidate c of problem b (System.cpp:181-211, BatchILQR.cpp:134,141-147)
+__global__ void __launch_bounds__(64) k_batch_fp(const DevProblem* __restrict__ Pp, Work W, BatchDev BW, int b0, int nB, int first_iter) {
+    const DevProblem& P = *Pp;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= nB * BNC) return;
+    const int bl = idx / BNC, c = idx % BNC, b = b0 + bl;
+    if (W.done[b]) return;
+    if (first_iter && c > 0) return;  // before the first solve there is no step to try
+    const int H = P.H, n = P.n, m = P.m, dof = P.dof, S = BW.S, N = BW.N;
+    const double alpha = batch_alpha(c);
+    const double* u = BW.u + (size_t)b * N;
+    const double* du = BW.du + (size_t)b * N;
+    double x[MAXN], xprev[MAXN], uk[MAXM];
+    for (int i = 0; i < MAXN; i++) x[i] = xprev[i] = 0.0;
+    for (int i = 0; i < dof; i++) x[i] = P.q0[(size_t)b * dof + i];
+    double uRu = 0.0, qLq = 0.0;
+    double evec[MAX_KP_STEPS * MAX_RT];
+    int s = 0;
+    for (int row = 0; row < H; row++) {
+        if (s < S && P.kp_steps[s] == row) {
+            // task vector, residual (and for candidate 0 the Jacobian) at the keypoint row
+            double dqz[MAXM];
+            for (int i = 0; i < dof; i++) dqz[i] = 0.0;
+            for (int ti = 0; ti < P.n_tasks; ti++) {
+                const DevTask& tk = P.tasks[ti];
+                EEState ee;
+                task_ee(P, tk, x, dqz, ee);
+                double fx[MAX_NTT], res[MAX_RT];
+                task_fx(P, tk, ee, P.time ? x[n - 1] : 0.0, fx);
+                const int kp = task_kp_at(tk, row);
+                for (int a = 0; a < tk.r_t; a++) res[a] = 0.0;
+                if (kp >= 0) {
+                    const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
+                    task_residual(P, tk, fx, tg, res);
+                }
+                for (int a = 0; a < tk.r_t; a++) evec[s * P.r + tk.r_off + a] = res[a];
+                if (c == 0) {
+                    double* Jo = BW.Jt + (((size_t)bl * S + s) * P.r + tk.r_off) * n;
+                    task_jacobian(P, tk, ee, Jo, n);
+                }
+            }
+            // joint-limit terms of the row come from the state BEFORE the step that produced it (System.cpp:158, Q4)
+            // (a SequentialSystem has its own limits disabled, SequentialSystem.cpp:16-17, and fpBatch never asks its
+            //  sub-systems: only a plain single system contributes here)
+            for (int i = 0; i < n; i++) {
+                double ld = 0.0, qv = 0.0;
+                if (row > 0 && P.n_tasks == 1)
+                    for (int ti = 0; ti < P.n_tasks; ti++) {
+                        const DevTask& tk = P.tasks[ti];
+                        if (!tk.limits_set) continue;
+                        bool act;
+                        const double q = limit_q(tk, i, xprev[i], act);
+                        if (act) {
+                            ld += 1.0;
+                            qv = q;  // one limit-carrying system per state entry (Sequential systems disable their own limits)
+                        }
+                    }
+                qLq += (qv * ld) * qv;
+                if (c == 0) {
+                    BW.Ld[((size_t)bl * S + s) * n + i] = ld;
+                    BW.ql[((size_t)bl * S + s) * n + i] = qv;
+                }
+            }
+            s++;
+        }
+        if (row == H - 1) break;
+        for (int i = 0; i < m; i++) {
+            uk[i] = u[(size_t)row * m + i] + alpha * du[(size_t)row * m + i];
+            uRu += (uk[i] * P.r_diag[i]) * uk[i];
+        }
+        for (int i = 0; i < n; i++) xprev[i] = x[i];
+        dynamics_step(P, x, uk);
+    }
+    // e^T Q e
+    const int Sr = S * P.r;
+    double eQe = 0.0;
+    if (BW.Qfull) {
+        for (int j = 0; j < Sr; j++) {
+            double v = 0.0;
+            for (int i = 0; i < Sr; i++) v += evec[i] * BW.Qfull[(size_t)i * Sr + j];
+            eQe += v * evec[j];
+        }
+    } else {
+        for (int ss = 0; ss < S; ss++)
+            for (int ti = 0; ti < P.n_tasks; ti++) {
+                const DevTask& tk = P.tasks[ti];
+                const int kp = task_kp_at(tk, P.kp_steps[ss]);
+                if (kp < 0) continue;
+                const int r = tk.r_t;
+                const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + kp) * r * r;
+                const double* ev = evec + ss * P.r + tk.r_off;
+                for (int j = 0; j < r; j++) {
+                    double v = 0.0;
+                    for (int i = 0; i < r; i++) v += ev[i] * Q[i * r + j];
+                    eQe += v * ev[j];
+                }
+            }
+    }
+    BW.cc[(size_t)b * BNC + c] = (eQe + uRu) + qLq;
+    if (c == 0)
+        for (int i = 0; i < Sr; i++) BW.e[(size_t)bl * Sr + i] = evec[i];
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// block-diagonal precision of the keypoint rows (System::getQMatrix(true), System.cpp:341-361 / SequentialSystem.cpp:229-272)
+__device__ __forceinline__ double batch_q_elem(const DevProblem& P, const BatchDev& BW, int b, int i, int j) {
+    if (BW.Qfull) return BW.Qfull[(size_t)i * BW.Sr + j];
+    const int si = i / P.r, sj = j / P.r;
+    if (si != sj) return 0.0;
+    const int ci = i % P.r, cj = j % P.r;
+    for (int ti = 0; ti < P.n_tasks; ti++) {
+        const DevTask& tk = P.tasks[ti];
+        if (ci >= tk.r_off && ci < tk.r_off + tk.r_t) {
+            if (cj < tk.r_off || cj >= tk.r_off + tk.r_t) return 0.0;
+            const int kp = task_kp_at(tk, P.kp_steps[si]);
+            if (kp < 0) return 0.0;
+            const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + kp) * tk.r_t * tk.r_t;
+            return Q[(ci - tk.r_off) * tk.r_t + (cj - tk.r_off)];
+        }
+    }
+    return 0.0;
+}
+
+// W = J^T Q J + L, g = J^T Q e + L ql (BatchILQR.cpp:130-131); Su, T = W Su, rhs = Su^T g - R u.  One block per problem.
+// Shared memory: JQ [Sn][Sr], W [Sn][Sn], g [Sn].
+__global__ void __launch_bounds__(256) k_batch_assemble(const DevProblem* __restrict__ Pp, Work W, BatchDev BW, int b0) {
+    extern __shared__ double sm[];
+    const DevProblem& P = *Pp;
+    const int bl = blockIdx.x, b = b0 + bl;
+    if (W.done[b]) return;
+    const int n = P.n, m = P.m, r = P.r, S = BW.S, Sn = BW.Sn, Sr = BW.Sr, N = BW.N, Np = BW.Np;
+    double* sJQ = sm;             // [Sn][Sr]
+    double* sW = sJQ + Sn * Sr;   // [Sn][Sn]
+    double* sg = sW + Sn * Sn;    // [Sn]
+    const double* Jt = BW.Jt + (size_t)bl * S * r * n;
+    const double* e = BW.e + (size_t)bl * Sr;
+    const double* Ld = BW.Ld + (size_t)bl * Sn;
+    const double* ql = BW.ql + (size_t)bl * Sn;
+    for (int idx = threadIdx.x; idx < Sn * Sr; idx += blockDim.x) {
+        const int ia = idx / Sr, j = idx % Sr, s = ia / n, a = ia % n;
+        double v = 0.0;
+        for (int c = 0; c < r; c++) v += Jt[((size_t)s * r + c) * n + a] * batch_q_elem(P, BW, b, s * r + c, j);
+        sJQ[idx] = v;
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < Sn * Sn; idx += blockDim.x) {
+        const int ia = idx / Sn, jb = idx % Sn, s2 = jb / n, bb = jb % n;
+        double v = 0.0;
+        for (int c = 0; c < r; c++) v += sJQ[ia * Sr + s2 * r + c] * Jt[((size_t)s2 * r + c) * n + bb];
+        if (ia == jb) v += Ld[ia];
+        sW[idx] = v;
+        BW.Wm[(size_t)bl * Sn * Sn + idx] = v;
+    }
+    for (int ia = threadIdx.x; ia < Sn; ia += blockDim.x) {
+        double v = 0.0;
+        for (int j = 0; j < Sr; j++) v += sJQ[ia * Sr + j] * e[j];
+        v += Ld[ia] * ql[ia];
+        sg[ia] = v;
+        BW.g[(size_t)bl * Sn + ia] = v;
+    }
+    __syncthreads();
+    // columns of Su / T / rhs.  Row block s of Su is [0, B_1, .., B_{t_s - 1}, 0 ..]: column block j = control u_j holds
+    // the B of control u_{j-1} (BatchILQR.cpp:71-94 with ABJLs[0].B = 0, Q3)
+    const double* u = BW.u + (size_t)b * N;
+    double* Su = BW.Su + (size_t)bl * BW.SnP * Np;
+    double* T = BW.T + (size_t)bl * BW.SnP * Np;
+    for (int col = threadIdx.x; col < Np; col += blockDim.x) {
+        const int j = col / m, c = col % m;
+        double rhs = 0.0;
+        if (col < N) {
+            for (int ia = 0; ia < Sn; ia++) {
+                const int s = ia / n, a = ia % n;
+                double v = 0.0;
+                if (j >= 1 && j <= P.kp_steps[s] - 1) v = batch_B_entry(P, u + (size_t)(j - 1) * m, a, c);
+                Su[(size_t)ia * Np + col] = v;
+                rhs += v * sg[ia];
+            }
+            for (int ia = 0; ia < Sn; ia++) {
+                double tv = 0.0;
+                for (int kb = 0; kb < Sn; kb++) {
+                    const int s = kb / n, a = kb % n;
+                    if (j >= 1 && j <= P.kp_steps[s] - 1) tv += sW[ia * Sn + kb] * batch_B_entry(P, u + (size_t)(j - 1) * m, a, c);
+                }
+                T[(size_t)ia * Np + col] = tv;
+            }
+            rhs -= P.r_diag[c] * u[col];
+        } else {
+            for (int ia = 0; ia < Sn; ia++) {
+                Su[(size_t)ia * Np + col] = 0.0;
+                T[(size_t)ia * Np + col] = 0.0;
+            }
+        }
+        BW.rhs[(size_t)bl * Np + col] = rhs;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// lstq_A = Su^T T + R  (BatchILQR.cpp:130), lower triangle incl. diagonal blocks, FP64 tensor pipe.
+// A is row-major [Np][Np]; padded rows/columns (>= N) get the identity so that the factorisation passes through them.
+// One warp per 8 x 64 strip of the output: the A fragments (Su^T rows) are reused across the eight column tiles.
+__global__ void __launch_bounds__(128) k_batch_syrk(const DevProblem* __restrict__ Pp, Work W, BatchDev BW, int b0) {
+    const DevProblem& P = *Pp;
+    const int bl = blockIdx.y, b = b0 + bl;
+    if (W.done[b]) return;
+    const int Np = BW.Np, N = BW.N, SnP = BW.SnP, m = P.m;
+    const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int strips = Np / 64, rtiles = Np / 8;
+    const int wid = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (wid >= rtiles * strips) return;
+    const int it = wid / strips, js = wid % strips;
+    const int i0 = it * 8, j0 = js * 64;
+    if (j0 > i0) return;  // strictly upper strip: never read
+    const double* Su = BW.Su + (size_t)bl * SnP * Np;
+    const double* T = BW.T + (size_t)bl * SnP * Np;
+    double* A = BW.A + (size_t)bl * Np * Np;
+    double c0[8], c1[8];
+#pragma unroll
+    for (int ct = 0; ct < 8; ct++) c0[ct] = c1[ct] = 0.0;
+    for (int ks = 0; ks < SnP / 4; ks++) {
+        const double a = Su[(size_t)(4 * ks + t) * Np + i0 + g];  // (Su^T)[i0+g][4ks+t]
+#pragma unroll
+        for (int ct = 0; ct < 8; ct++) {
+            const double bb = T[(size_t)(4 * ks + t) * Np + j0 + 8 * ct + g];
+            dmma884(c0[ct], c1[ct], a, bb);
+        }
+    }
+    const int i = i0 + g;
+#pragma unroll
+    for (int ct = 0; ct < 8; ct++) {
+        const int j = j0 + 8 * ct + 2 * t;
+        double v0 = c0[ct], v1 = c1[ct];
+        if (i == j) v0 += (i < N) ? P.r_diag[i % m] : 1.0;
+        if (i == j + 1) v1 += (i < N) ? P.r_diag[i % m] : 1.0;
+        *reinterpret_cast<double2*>(A + (size_t)i * Np + j) = make_double2(v0, v1);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// In-place blocked Cholesky A = L L^T (lower, row-major) of one problem per CTA: 256 threads, block size 64.
+//   per panel k0:  D = A[k0:k0+64, k0:k0+64] factored in shared memory (right-looking, 64 steps);
+//                  Linv = D^-1 (lower) by 64 independent forward substitutions;
+//                  panel rows  L21 = A21 Linv^T            (DMMA, C = X Y^T form)
+//                  trailing    A22 -= L21 L21^T  (lower)   (DMMA, same form, read-modify-write through L2)
+// Replaces `lstq_A.inverse()` (Eigen PartialPivLU, BatchILQR.cpp:132): lstq_A = R + Su^T W Su is symmetric positive
+// definite (R > 0).  A non-positive pivot sets ILQRB_ST_QUU_NOT_SPD and the factorisation carries on with NaNs.
+constexpr int CH_NB = 64, CH_LD = 68;
+
+// C(64x64 at Cg, leading dim ldc) = beta_old * C + sign * X Y^T with X, Y 64 x 64 in shared memory (leading dim CH_LD).
+// 8 warps: warp w owns rows 8w..8w+7, all eight column tiles.  lower_only: skip tiles strictly above the diagonal.
+template <bool ACCUM>
+__device__ __forceinline__ void ch_xyT(double* Cg, int ldc, const double* sX, const double* sY, double sign, bool lower_only, int warp, int lane) {
+    const int g = lane >> 2, t = lane & 3;
+    double a[16];
+#pragma unroll
+    for (int ks = 0; ks < 16; ks++) a[ks] = sX[(8 * warp + g) * CH_LD + 4 * ks + t];
+#pragma unroll
+    for (int ct = 0; ct < 8; ct++) {
+        if (lower_only && ct > warp) continue;
+        double c0 = 0.0, c1 = 0.0;
+#pragma unroll
+        for (int ks = 0; ks < 16; ks++) dmma884(c0, c1, a[ks], sY[(8 * ct + g) * CH_LD + 4 * ks + t]);
+        double2* dst = reinterpret_cast<double2*>(Cg + (size_t)(8 * warp + g) * ldc + 8 * ct + 2 * t);
+        if (ACCUM) {
+            const double2 o = *dst;
+            *dst = make_double2(o.x + sign * c0, o.y + sign * c1);
+        } else {
+            *dst = make_double2(sign * c0, sign * c1);
+        }
+    }
+}
+__device__ __forceinline__ void ch_load64(double* sdst, const double* Ag, int lda, int tid) {
+    for (int e = tid; e < 64 * 32; e += 256) {
+        const int r = e >> 5, c2 = e & 31;
+        const double2 v = *reinterpret_cast<const double2*>(Ag + (size_t)r * lda + 2 * c2);
+        sdst[r * CH_LD + 2 * c2] = v.x;
+        sdst[r * CH_LD + 2 * c2 + 1] = v.y;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_batch_chol(Work W, BatchDev BW, int b0) {
+    extern __shared__ double sm[];
+    double* sD = sm;                    // diagonal block / its factor
+    double* sX = sD + 64 * CH_LD;       // row block operand
+    double* sY = sX + 64 * CH_LD;       // Linv, then column block operand
+    const int bl = blockIdx.x, b = b0 + bl;
+    if (W.done[b]) return;
+    const int Np = BW.Np, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    double* A = BW.A + (size_t)bl * Np * Np;
+    __shared__ int s_bad;
+    if (tid == 0) s_bad = 0;
+    for (int k0 = 0; k0 < Np; k0 += CH_NB) {
+        __syncthreads();
+        ch_load64(sD, A + (size_t)k0 * Np + k0, Np, tid);
+        __syncthreads();
+        // factor the diagonal block (lower part)
+        for (int j = 0; j < 64; j++) {
+            __syncthreads();  // rank-1 update of step j-1 complete
+            const double djj = sD[j * CH_LD + j];
+            __syncthreads();  // everybody holds the pivot before it is overwritten
+            const double d = sqrt(djj);
+            if (tid == 0) {
+                if (!(djj > 0.0)) s_bad = 1;
+                sD[j * CH_LD + j] = d;
+            }
+            if (tid > j && tid < 64) sD[tid * CH_LD + j] /= d;
+            __syncthreads();
+            // rank-1 update of the trailing lower triangle: elements (i, k) with j < k <= i < 64
+            for (int e = tid; e < 64 * 64; e += 256) {
+                const int i = e >> 6, k = e & 63;
+                if (k > j && k <= i) sD[i * CH_LD + k] -= sD[i * CH_LD + j] * sD[k * CH_LD + j];
+            }
+        }
+        __syncthreads();
+        // write the factor back (upper part of the block zeroed) ; Linv into sY by forward substitution, one column per thread
+        for (int e = tid; e < 64 * 64; e += 256) {
+            const int i = e >> 6, k = e & 63;
+            const double v = (k <= i) ? sD[i * CH_LD + k] : 0.0;
+            sD[i * CH_LD + k] = v;
+            A[(size_t)(k0 + i) * Np + k0 + k] = v;
+        }
+        __syncthreads();
+        if (tid < 64) {
+            const int j = tid;  // column j of the inverse: L x = e_j
+            for (int i = 0; i < 64; i++) {
+                double acc = (i == j) ? 1.0 : 0.0;
+                for (int k = j; k < i; k++) acc -= sD[i * CH_LD + k] * sY[k * CH_LD + j];
+                sY[i * CH_LD + j] = (i < j) ? 0.0 : acc / sD[i * CH_LD + i];
+            }
+        }
+        __syncthreads();
+        // panel: L21 = A21 Linv^T, 64 rows at a time
+        for (int I = k0 + CH_NB; I < Np; I += 64) {
+            ch_load64(sX, A + (size_t)I * Np + k0, Np, tid);
+            __syncthreads();
+            ch_xyT<false>(A + (size_t)I * Np + k0, Np, sX, sY, 1.0, false, warp, lane);
+            __syncthreads();
+        }
+        // trailing update: A22 -= L21 L21^T (lower block triangle)
+        for (int I = k0 + CH_NB; I < Np; I += 64) {
+            ch_load64(sX, A + (size_t)I * Np + k0, Np, tid);
+            for (int J = k0 + CH_NB; J <= I; J += 64) {
+                __syncthreads();
+                ch_load64(sY, A + (size_t)J * Np + k0, Np, tid);
+                __syncthreads();
+                ch_xyT<true>(A + (size_t)I * Np + J, Np, sX, sY, -1.0, J == I, warp, lane);
+            }
+            __syncthreads();
+        }
+    }
+    __syncthreads();
+    if (tid == 0 && s_bad) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// du = (L L^T)^-1 rhs : forward then backward substitution, one CTA (256 threads) per problem, 64-wide blocks.
+__global__ void __launch_bounds__(256) k_batch_trsv(Work W, BatchDev BW, int b0) {
+    extern __shared__ double sm[];
+    double* sD = sm;              // [64][CH_LD]
+    double* y = sD + 64 * CH_LD;  // [Np]
+    const int bl = blockIdx.x, b = b0 + bl;
+    if (W.done[b]) return;
+    const int Np = BW.Np, N = BW.N, tid = threadIdx.x;
+    const double* A = BW.A + (size_t)bl * Np * Np;
+    for (int i = tid; i < Np; i += 256) y[i] = BW.rhs[(size_t)bl * Np + i];
+    // L z = rhs
+    for (int k0 = 0; k0 < Np; k0 += 64) {
+        __syncthreads();
+        ch_load64(sD, A + (size_t)k0 * Np + k0, Np, tid);
+        __syncthreads();
+        for (int j = 0; j < 64; j++) {
+            if (tid == 0) y[k0 + j] /= sD[j * CH_LD + j];
+            __syncthreads();
+            if (tid > j && tid < 64) y[k0 + tid] -= sD[tid * CH_LD + j] * y[k0 + j];
+            __syncthreads();
+        }
+        for (int i = k0 + 64 + tid; i < Np; i += 256) {
+            const double* row = A + (size_t)i * Np + k0;
+            double acc = 0.0;
+#pragma unroll 8
+            for (int k = 0; k < 64; k++) acc += row[k] * y[k0 + k];
+            y[i] -= acc;
+        }
+    }
+    // L^T x = z
+    for (int k0 = Np - 64; k0 >= 0; k0 -= 64) {
+        __syncthreads();
+        ch_load64(sD, A + (size_t)k0 * Np + k0, Np, tid);
+        __syncthreads();
+        for (int j = 63; j >= 0; j--) {
+            if (tid == 0) y[k0 + j] /= sD[j * CH_LD + j];
+            __syncthreads();
+            if (tid < j) y[k0 + tid] -= sD[j * CH_LD + tid] * y[k0 + j];
+            __syncthreads();
+        }
+        for (int c = tid; c < k0; c += 256) {
+            double acc = 0.0;
+#pragma unroll 8
+            for (int i = 0; i < 64; i++) acc += A[(size_t)(k0 + i) * Np + c] * y[k0 + i];
+            y[c] -= acc;
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < N; i += 256) BW.du[(size_t)b * N + i] = y[i];
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// control primitives (BatchILQRCP.cpp:129-133): lstq_A = ((Psi^T Su^T) W) Su Psi + (Psi^T R) Psi,
+// lstq_B = (Psi^T Su^T) g - (Psi^T R) u, dw = lstq_A^-1 lstq_B (partial-pivot elimination, as PartialPivLU), du = Psi dw.
+// One block of 128 threads per problem.  Shared memory: SP [Sn][nw], WS [Sn][nw], Aw [nw][nw+1].
+__global__ void __launch_bounds__(128) k_batch_cp(const DevProblem* __restrict__ Pp, Work W, BatchDev BW, int b0) {
+    extern __shared__ double sm[];
+    const DevProblem& P = *Pp;
+    const int bl = blockIdx.x, b = b0 + bl;
+    if (W.done[b]) return;
+    const int Sn = BW.Sn, nw = BW.nw, N = BW.N, Np = BW.Np, m = P.m, tid = threadIdx.x;
+    double* sSP = sm;                 // Su Psi
+    double* sWS = sSP + Sn * nw;      // W (Su Psi)
+    double* sA = sWS + Sn * nw;       // [nw][nw+1] augmented system
+    const double* Su = BW.Su + (size_t)bl * BW.SnP * Np;
+    const double* Wm = BW.Wm + (size_t)bl * Sn * Sn;
+    const double* gv = BW.g + (size_t)bl * Sn;
+    const double* u = BW.u + (size_t)b * N;
+    for (int idx = tid; idx < Sn * nw; idx += blockDim.x) {
+        const int k = idx / nw, w = idx % nw;
+        double v = 0.0;
+        for (int col = 0; col < N; col++) v += Su[(size_t)k * Np + col] * BW.psi[(size_t)col * nw + w];
+        sSP[idx] = v;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < Sn * nw; idx += blockDim.x) {
+        const int k = idx / nw, w = idx % nw;
+        double v = 0.0;
+        for (int k2 = 0; k2 < Sn; k2++) v += Wm[k * Sn + k2] * sSP[k2 * nw + w];
+        sWS[idx] = v;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < nw * (nw + 1); idx += blockDim.x) {
+        const int w = idx / (nw + 1), w2 = idx % (nw + 1);
+        double v = 0.0;
+        if (w2 < nw) {
+            for (int k = 0; k < Sn; k++) v += sSP[k * nw + w] * sWS[k * nw + w2];
+            v += BW.psiRpsi[w * nw + w2];
+        } else {
+            for (int k = 0; k < Sn; k++) v += sSP[k * nw + w] * gv[k];
+            double ru = 0.0;
+            for (int col = 0; col < N; col++) ru += (BW.psi[(size_t)col * nw + w] * P.r_diag[col % m]) * u[col];
+            v -= ru;
+        }
+        sA[idx] = v;
+    }
+    __syncthreads();
+    if (tid == 0) {  // nw is small (number of primitives x m): Gaussian elimination with partial pivoting
+        const int ld = nw + 1;
+        for (int k = 0; k < nw; k++) {
+            int piv = k;
+            double best = fabs(sA[k * ld + k]);
+            for (int i = k + 1; i < nw; i++)
+                if (fabs(sA[i * ld + k]) > best) {
+                    best = fabs(sA[i * ld + k]);
+                    piv = i;
+                }
+            if (piv != k)
+                for (int j = 0; j < ld; j++) {
+                    const double tmp = sA[k * ld + j];
+                    sA[k * ld + j] = sA[piv * ld + j];
+                    sA[piv * ld + j] = tmp;
+                }
+            const double d = sA[k * ld + k];
+            for (int i = k + 1; i < nw; i++) {
+                const double f = sA[i * ld + k] / d;
+                for (int j = k; j < ld; j++) sA[i * ld + j] -= f * sA[k * ld + j];
+            }
+        }
+        for (int k = nw - 1; k >= 0; k--) {
+            double acc = sA[k * ld + nw];
+            for (int j = k + 1; j < nw; j++) acc -= sA[k * ld + j] * sA[j * ld + nw];
+            sA[k * ld + nw] = acc / sA[k * ld + k];
+        }
+    }
+    __syncthreads();
+    for (int col = tid; col < N; col += blockDim.x) {
+        double v = 0.0;
+        for (int w = 0; w < nw; w++) v += BW.psi[(size_t)col * nw + w] * sA[w * (nw + 1) + nw];
+        BW.du[(size_t)b * N + col] = v;
+    }
+}
+
+// Su-only variant of the assemble kernel is not needed: k_batch_assemble also serves the CP path (T and rhs unused there).
+
+// ------------------------------------------------------------------------------------------------------------
+// line-search decision, accept, trace, early stop (BatchILQR.cpp:135-170).  One thread per problem.
+__global__ void k_batch_select(const DevProblem* __restrict__ Pp, Work W, BatchDev BW, int b0, int nB, int it, int nb_iter, int early_stop) {
+    const int bl = blockIdx.x * blockDim.x + threadIdx.x;
+    if (bl >= nB) return;
+    const int b = b0 + bl;
+    if (W.done[b]) return;
+    const int N = BW.N;
+    const double* cc = BW.cc + (size_t)b * BNC;
+    const double cost0 = cc[0];
+    int sel = NCAND;  // alpha = 2^-10 < 1e-3 is accepted whatever its cost
+    for (int c = 1; c <= NCAND; c++)
+        if (cc[c] < cost0) {
+            sel = c;
+            break;
+        }
+    const double alpha = batch_alpha(sel);
+    double* u = BW.u + (size_t)b * N;
+    const double* du = BW.du + (size_t)b * N;
+    double nrm = 0.0;
+    for (int i = 0; i < N; i++) {
+        nrm += du[i] * du[i];
+        u[i] = u[i] + alpha * du[i];
+    }
+    W.cost_hist[(size_t)b * nb_iter + it] = cost0;  // the reference prints the PRE-step cost (:160)
+    W.alpha_hist[(size_t)b * nb_iter + it] = alpha;
+    W.cost0[b] = cost0;
+    W.iters[b] = it + 1;
+    int st = W.status[b];
+    if (isnan(cost0)) st |= ILQRB_ST_NAN_COST;
+    if (early_stop && alpha * sqrt(nrm) < 1e-3) {
+        st |= ILQRB_ST_EARLY_STOP;
+        W.done[b] = 1;
+    }
+    W.status[b] = st;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// host orchestration
+__global__ void k_bfill(double* p, size_t n, double v) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+__global__ void k_bpack_u(double* __restrict__ dst, const double* __restrict__ src, size_t rows, int w, int stride) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * w) return;
+    dst[i] = src[(i / w) * stride + (i % w)];
+}
+
+#define BCU(call)                                                              \
+    do {                                                                       \
+        cudaError_t e_ = (call);                                               \
+        if (e_ != cudaSuccess) {                                               \
+            err = std::string(#call) + ": " + cudaGetErrorString(e_);          \
+            return ILQRB_ECUDA;                                                \
+        }                                                                      \
+    } while (0)
+
+template <class T>
+inline int batch_alloc(BatchWork& BW, T** p, size_t count, std::string& err) {
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T));
+    if (e != cudaSuccess) {
+        err = std::string("cudaMalloc (batch solver workspace): ") + cudaGetErrorString(e);
+        return ILQRB_ENOMEM;
+    }
+    BW.allocs.push_back(q);
+    *p = (T*)q;
+    return 0;
+}
+inline void batch_free(BatchWork& BW) {
+    for (void* p : BW.allocs) cudaFree(p);
+    BW = BatchWork();
+}
+
+// solver::BatchILQR::solve / BatchILQRCP::solve for the whole batch, chunk by chunk (the dense N x N workspaces of a
+// chunk must fit the workspace budget, ILQRB_BATCH_WS_GB, default 24 GB).  `begin(slot)` / `end()` bracket every launch.
+inline int batch_run(cudaStream_t st, const DevProblem& P, const DevProblem* dp, Work& W, BatchWork& BW, const ilqrb_batch_desc* bd,
+                     const ilqrb_solve_opts* opts, std::string& err, std::function<void(int)> begin, std::function<void()> end) {
+    if (P.nb_deriv != 1) {
+        err = "Batch solvers: only single-integrator systems (nb_deriv = 1) are built on the GPU";
+        return ILQRB_EUNSUPPORTED;
+    }
+    int n_kp_total = 0;
+    for (int t = 0; t < P.n_tasks; t++) n_kp_total += P.tasks[t].n_keypoints;
+    if (n_kp_total != P.n_kp_steps) {
+        err = "Batch solvers: sub-systems with keypoints at the same timestep (duplicate row blocks, SURVEY Q16) are not built";
+        return ILQRB_EUNSUPPORTED;
+    }
+    const int B = P.B, H = P.H, n = P.n, m = P.m, r = P.r, S = P.n_kp_steps;
+    const int N = (H - 1) * m, Np = (N + 63) / 64 * 64, Sn = S * n, SnP = (Sn + 3) / 4 * 4, Sr = S * r;
+    const int nw = (bd && bd->psi) ? bd->nw : 0, cp = nw > 0;
+    if (cp && nw > 128) {
+        err = "BatchILQRCP: more than 128 primitive weights";
+        return ILQRB_EUNSUPPORTED;
+    }
+    if (Sr > MAX_KP_STEPS * MAX_RT) {
+        err = "Batch solvers: too many keypoint rows";
+        return ILQRB_EUNSUPPORTED;
+    }
+    if (BW.allocated && (BW.N != N || BW.nw != nw || BW.S != S)) batch_free(BW);
+    int rc;
+    if (!BW.allocated) {
+        BW.N = N; BW.Np = Np; BW.S = S; BW.Sn = Sn; BW.SnP = SnP; BW.Sr = Sr; BW.nw = nw; BW.cp = cp;
+        const char* ev = getenv("ILQRB_BATCH_WS_GB");
+        const double budget = (ev ? atof(ev) : 24.0) * 1e9;
+        const double per = 8.0 * ((cp ? 0.0 : (double)Np * Np) + 2.0 * SnP * Np + Np + (double)S * r * n + Sr + 2.0 * Sn + (double)Sn * Sn + Sn + (double)Sn * std::max(nw, 1));
+        BW.chunk = (int)std::max(1.0, std::min((double)B, budget / per));
+        const size_t C = BW.chunk;
+        if ((rc = batch_alloc(BW, &BW.u, (size_t)B * N, err)) || (rc = batch_alloc(BW, &BW.du, (size_t)B * N, err)) || (rc = batch_alloc(BW, &BW.cc, (size_t)B * BNC, err)) ||
+            (rc = batch_alloc(BW, &BW.Jt, C * S * r * n, err)) || (rc = batch_alloc(BW, &BW.e, C * Sr, err)) || (rc = batch_alloc(BW, &BW.Ld, C * Sn, err)) ||
+            (rc = batch_alloc(BW, &BW.ql, C * Sn, err)) || (rc = batch_alloc(BW, &BW.Wm, C * Sn * Sn, err)) || (rc = batch_alloc(BW, &BW.g, C * Sn, err)) ||
+            (rc = batch_alloc(BW, &BW.Su, C * SnP * Np, err)) || (rc = batch_alloc(BW, &BW.T, C * SnP * Np, err)) || (rc = batch_alloc(BW, &BW.rhs, C * Np, err)))
+            return rc;
+        if (!cp && (rc = batch_alloc(BW, &BW.A, C * Np * Np, err))) return rc;
+        if (cp && ((rc = batch_alloc(BW, &BW.psi, (size_t)N * nw, err)) || (rc = batch_alloc(BW, &BW.psiRpsi, (size_t)nw * nw, err)))) return rc;
+        if ((rc = batch_alloc(BW, &BW.Qfull, (size_t)Sr * Sr, err))) return rc;
+        BCU(cudaMemsetAsync(BW.Su, 0, C * SnP * Np * sizeof(double), st));
+        BCU(cudaMemsetAsync(BW.T, 0, C * SnP * Np * sizeof(double), st));
+        BW.allocated = true;
+    }
+    // solver-constructor inputs: Q override (BatchILQR.cpp:27-33), Psi (BatchILQRCP.cpp:21-32)
+    BatchDev K = BW;  // kernel argument copy (Qfull pointer nulled when there is no override)
+    if (bd && bd->Q) BCU(cudaMemcpyAsync(BW.Qfull, bd->Q, (size_t)Sr * Sr * sizeof(double), cudaMemcpyHostToDevice, st));
+    else K.Qfull = nullptr;
+    if (cp) {
+        BCU(cudaMemcpyAsync(BW.psi, bd->psi, (size_t)N * nw * sizeof(double), cudaMemcpyHostToDevice, st));
+        std::vector<double> prp((size_t)nw * nw, 0.0);
+        for (int w = 0; w < nw; w++)
+            for (int w2 = 0; w2 < nw; w2++) {
+                double v = 0.0;
+                for (int col = 0; col < N; col++) v += (bd->psi[(size_t)col * nw + w] * P.r_diag[col % m]) * bd->psi[(size_t)col * nw + w2];
+                prp[(size_t)w * nw + w2] = v;
+            }
+        BCU(cudaMemcpyAsync(BW.psiRpsi, prp.data(), prp.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+        BCU(cudaStreamSynchronize(st));  // prp is a stack-lifetime buffer
+    }
+    // state: u <- W.U (padded rows -> compact), traces, flags
+    const int nit = std::max(opts->nb_iter, 1);
+    {
+        const size_t tot = (size_t)B * N;
+        k_bpack_u<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(BW.u, W.U, (size_t)B * (H - 1), m, W.ms);
+        BCU(cudaMemsetAsync(BW.du, 0, tot * sizeof(double), st));
+        const size_t nh = (size_t)B * nit;
+        k_bfill<<<(unsigned)((nh + 255) / 256), 256, 0, st>>>(W.cost_hist, nh, NAN);
+        k_bfill<<<(unsigned)((nh + 255) / 256), 256, 0, st>>>(W.alpha_hist, nh, NAN);
+        BCU(cudaMemsetAsync(W.done, 0, B * sizeof(int), st));
+        BCU(cudaMemsetAsync(W.iters, 0, B * sizeof(int), st));
+        BCU(cudaMemsetAsync(W.status, 0, B * sizeof(int), st));
+        BCU(cudaMemsetAsync(W.cost0, 0, B * sizeof(double), st));
+    }
+    static bool attr_set = false;
+    const size_t smem_chol = 3 * 64 * CH_LD * sizeof(double), smem_trsv = (64 * CH_LD + Np) * sizeof(double);
+    const size_t smem_asm = ((size_t)Sn * Sr + (size_t)Sn * Sn + Sn) * sizeof(double), smem_cp = (2 * (size_t)Sn * std::max(nw, 1) + (size_t)nw * (nw + 1)) * sizeof(double);
+    if (!attr_set) {
+        BCU(cudaFuncSetAttribute(k_batch_chol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_chol));
+        attr_set = true;
+    }
+    if (smem_trsv > 48 * 1024) BCU(cudaFuncSetAttribute(k_batch_trsv, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_trsv));
+    if (smem_asm > 48 * 1024) BCU(cudaFuncSetAttribute(k_batch_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_asm));
+    if (smem_cp > 48 * 1024) BCU(cudaFuncSetAttribute(k_batch_cp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cp));
+    for (int b0 = 0; b0 < B; b0 += BW.chunk) {
+        const int nB = std::min(BW.chunk, B - b0);
+        const unsigned fp_grid = (unsigned)(((size_t)nB * BNC + 63) / 64);
+        for (int it = 0; it < opts->nb_iter; it++) {
+            begin(0);
+            k_batch_fp<<<fp_grid, 64, 0, st>>>(dp, W, K, b0, nB, 1);
+            end();
+            begin(1);
+            k_batch_assemble<<<nB, 256, smem_asm, st>>>(dp, W, K, b0);
+            end();
+            if (!cp) {
+                begin(2);
+                k_batch_syrk<<<dim3((unsigned)((Np / 8) * (Np / 64) + 3) / 4, nB), 128, 0, st>>>(dp, W, K, b0);
+                end();
+                begin(3);
+                k_batch_chol<<<nB, 256, smem_chol, st>>>(W, K, b0);
+                end();
+                begin(3);
+                k_batch_trsv<<<nB, 256, smem_trsv, st>>>(W, K, b0);
+                end();
+            } else {
+                begin(3);
+                k_batch_cp<<<nB, 128, smem_cp, st>>>(dp, W, K, b0);
+                end();
+            }
+            begin(0);
+            k_batch_fp<<<fp_grid, 64, 0, st>>>(dp, W, K, b0, nB, 0);
+            end();
+            begin(4);
+            k_batch_select<<<(nB + 127) / 128, 128, 0, st>>>(dp, W, K, b0, nB, it, nit, opts->early_stop);
+            end();
+            BCU(cudaGetLastError());
+        }
+    }
+    return 0;
+}
+
+inline int batch_download(cudaStream_t st, const DevProblem& P, BatchWork& BW, ilqrb_result* out, const Work& W, int nit, std::string& err) {
+    const size_t B = P.B;
+    if (out->U) BCU(cudaMemcpyAsync(out->U, BW.u, B * BW.N * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (out->cost) BCU(cudaMemcpyAsync(out->cost, W.cost0, B * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (out->cost_hist) BCU(cudaMemcpyAsync(out->cost_hist, W.cost_hist, B * nit * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (out->alpha_hist) BCU(cudaMemcpyAsync(out->alpha_hist, W.alpha_hist, B * nit * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (out->iters) BCU(cudaMemcpyAsync(out->iters, W.iters, B * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (out->status) BCU(cudaMemcpyAsync(out->status, W.status, B * sizeof(int), cudaMemcpyDeviceToHost, st));
+    BCU(cudaStreamSynchronize(st));
+    return 0;
+}
 
 }  // namespace ilqrb

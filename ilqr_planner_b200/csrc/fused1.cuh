@@ -26,7 +26,7 @@
 
 namespace ilqrb {
 
-constexpr int MAX_KP_STEPS = ILQRB_MAX_TASKS * ILQRB_MAX_KEYPOINTS;
+
 
 // ---- DMMA fragment loads from a row-major shared-memory matrix with leading dimension LD -------------------
 //   A (8x4 slice s of k-tile kt, row tile rt):  M[8rt+g][8kt+4s+t]

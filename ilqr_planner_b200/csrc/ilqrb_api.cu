@@ -637,7 +637,6 @@ int ilqrb_create(const ilqrb_problem_desc* d, int device, ilqrb_handle* out) {
     h->device = device;
     h->dims = dm;
     std::memset(&h->W, 0, sizeof(Work));
-    std::memset(&h->BW, 0, sizeof(BatchWork));
     cudaError_t se = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (se != cudaSuccess) {
         delete h;
@@ -795,6 +794,7 @@ int ilqrb_destroy(ilqrb_handle h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (void* p : h->allocs) cudaFree(p);
+    batch_free(h->BW);
     for (auto e : h->ev_pool) cudaEventDestroy(e);
     for (int gi = 0; gi < h->n_groups; gi++) {
         cudaStreamSynchronize(h->gstream[gi]);
@@ -873,7 +873,11 @@ int ilqrb_download(ilqrb_handle h, ilqrb_result* out) {
     const size_t B = P.B;
     const int H = P.H, n = P.n, m = P.m, nit = std::max(h->last_nb_iter, 1);
     int rc;
-    if (h->last_solver == 3) return batch_download(h->stream, P, h->BW, out, nit);
+    if (h->last_solver == 3) {
+        std::string err;
+        rc = batch_download(h->stream, P, h->BW, out, h->W, nit, err);
+        return rc ? fail(rc, err) : 0;
+    }
     if ((rc = download_packed(h, out->X, h->W.X, B * H, n, h->W.ns, nullptr, 1))) return rc;
     if ((rc = download_packed(h, out->U, h->W.U, B * (H - 1), m, h->W.ms, nullptr, 1))) return rc;
     if (h->last_solver == 1) {
@@ -922,7 +926,9 @@ int ilqrb_run_batch(ilqrb_handle h, const ilqrb_batch_desc* bd, const ilqrb_solv
     if (!h || !opts) return fail(ILQRB_EINVAL, "null argument");
     CU(cudaSetDevice(h->device));
     std::string err;
-    int rc = batch_run(h->stream, h->hp, h->dp, h->W, h->BW, bd, opts, err, [h](int slot) { h->begin(PS_BATCH_FP + slot); }, [h]() { h->end(); });
+    int rc = ensure_iter_capacity(h, std::max(opts->nb_iter, 1));
+    if (rc) return rc;
+    rc = batch_run(h->stream, h->hp, h->dp, h->W, h->BW, bd, opts, err, [h](int slot) { h->begin(PS_BATCH_FP + slot); }, [h]() { h->end(); });
     if (rc) return fail(rc, err);
     h->last_nb_iter = opts->nb_iter;
     h->last_solver = 3;

@@ -15,6 +15,7 @@ namespace ilqrb {
 constexpr int NCAND = ILQRB_N_ALPHA;  // 11
 constexpr int CAND_LANES = 16;        // lanes reserved per problem in k_linesearch
 constexpr int MAX_NC = 32;            // AL constraint rows per step
+constexpr int MAX_KP_STEPS = ILQRB_MAX_TASKS * ILQRB_MAX_KEYPOINTS;  // distinct keypoint timesteps of a system
 
 // device work buffers of one handle (padded strides: ns = even(n), ms = even(m))
 struct Work {

@@ -231,3 +231,79 @@ def test_errors_are_loud():
     pb = synth.config2(batch=2)
     with pytest.raises(RuntimeError, match="device index"):
         Handle(pb, device=99)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# (3) Batch / control-primitive Batch solvers (BatchILQR.cpp, BatchILQRCP.cpp): single-integrator systems on the GPU
+GOLD_BATCH = [c["name"] for c in tc.goldens()["cases"] if c["solver"] in ("batch", "batch_cp") and c["system"]["nb_deriv"] == 1]
+
+
+def _distinct_steps(c):
+    steps = [k for t in c["system"]["tasks"] for k in t["kp_timestep"]]
+    return len(steps) == len(set(steps))
+
+
+@pytest.mark.parametrize("name", GOLD_BATCH)
+def test_batch_notebook_trace_on_gpu(name):
+    g = tc.goldens()
+    c = tc.golden_case(name)
+    pb = tc.problem_from_spec(c["system"], g["chains"])
+    u0 = tc.case_u0(c, pb)
+    psi = tc.case_psi(c, pb) if c["solver"] == "batch_cp" else None
+    with _handle(pb) as h:
+        if not _distinct_steps(c):
+            with pytest.raises(RuntimeError, match="same timestep"):  # declared unsupported, loudly
+                h.solve_batch(u0, c["nb_iter"], c["early_stop"], Q=c["Q"], psi=psi)
+            return
+        out = h.solve_batch(u0, c["nb_iter"], c["early_stop"], Q=c["Q"], psi=psi)
+    got = tc.trace_lines(out.cost_hist[0], out.alpha_hist[0], out.iters[0])
+    exp = tc.norm_trace(c["trace"])
+    assert len(got) == len(exp), "iteration count %d != %d" % (len(got), len(exp))
+    for i, (a, b) in enumerate(zip(got, exp)):
+        assert a["alpha"] == b["alpha"], "iteration %d alpha %s != %s" % (i + 1, a["alpha"], b["alpha"])
+        if a["cost"] != b["cost"]:  # one unit of the 6th printed digit (dense N x N solve: Cholesky here, LU inverse there)
+            assert abs(float(a["cost"]) - float(b["cost"])) <= 2e-6 * abs(float(b["cost"])), "iteration %d cost %s != %s" % (i + 1, a["cost"], b["cost"])
+
+
+def _check_batch(pb, u0, nb_iter, oracle, psi=None, early_stop=False, ctol=1e-8, utol=1e-7):
+    """Tolerances: the step comes out of a dense solve whose matrix R + Su^T W Su has condition number 1e5 (R = 1e-5
+    against O(1) task curvature) to 1e7 (time systems: the time column of B is large).  The reference forms an explicit
+    LU inverse there (relative error ~ cond * eps), this path a Cholesky / pivoted elimination: both answers are equally
+    valid to ~cond * eps, and the difference compounds over iterations.  Hence 1e-8 / 1e-7 (cost / u) for plain systems
+    and 1e-6 / 1e-5 for time systems instead of the Recursive solver's 1e-9."""
+    with _handle(pb) as h:
+        out = h.solve_batch(u0, nb_iter, early_stop, psi=psi)
+    ref = oracle.solve_batch(pb, u0, nb_iter, early_stop, psi=psi, threads=8)
+    assert rel(out.cost_hist, ref.cost_hist) < ctol
+    for b in range(pb.batch):
+        k = decisive_prefix(ref, b)
+        assert np.array_equal(out.alpha_hist[b, :k], ref.alpha_hist[b, :k]), "problem %d alpha sequence" % b
+    dec = np.array([decisive_prefix(ref, b) == int(ref.iters[b]) for b in range(pb.batch)])
+    assert dec.sum() >= pb.batch // 2
+    # u comes out of a dense N x N solve with condition number ~1e5 (R = 1e-5 against O(1) task curvature)
+    assert rel(out.U[dec], ref.U[dec]) < utol
+    return out, ref
+
+
+def test_batch_ilqr_time_system_vs_oracle(oracle_lib):
+    """C4 shape at a size the oracle finishes in seconds: PosOrnTime, N = 8 * 39 = 312"""
+    from ilqr_planner_b200 import synth
+    pb = synth.config4(batch=6, horizon=40)
+    _check_batch(pb, synth.u0_time(pb), 5, oracle_lib, ctol=1e-6, utol=1e-5)
+
+
+def test_batch_ilqr_cp_time_system_vs_oracle(oracle_lib):
+    from ilqr_planner_b200 import synth
+    from ilqr_planner_b200.solver import build_psi
+    pb = synth.config4(batch=6, horizon=40)
+    psi = np.kron(build_psi("unitstep", pb.horizon - 1, 2), np.identity(pb.m))
+    _check_batch(pb, synth.u0_time(pb), 8, oracle_lib, psi=psi, ctol=1e-6, utol=1e-5)
+
+
+def test_batch_ilqr_posorn_vs_oracle(oracle_lib):
+    from ilqr_planner_b200 import synth
+    pb = synth.config2(batch=6, horizon=50)
+    _check_batch(pb, None, 5, oracle_lib)
+    from ilqr_planner_b200.solver import build_psi
+    psi = np.kron(build_psi("rbf", pb.horizon - 1, 4), np.identity(pb.m))
+    _check_batch(pb, None, 6, oracle_lib, psi=psi, early_stop=True)
