@@ -35,7 +35,8 @@ def workload_config(n_gpus, batch):
     return {"workload": "configs[1]: synthetic 7-DoF KDL chain, PosOrn system, Recursive iLQR, T=100, 20 iterations, line search on, "
                         "no early stop, batch %d per GPU" % batch,
             "batch_per_gpu": batch, "global_batch": batch * n_gpus, "horizon": HORIZON, "nb_iter": NB_ITER, "parallelism": "problem-batch dp%d" % n_gpus,
-            "l2": "no flush: the per-iteration working set (candidate controls 250 MB + gains 159 MB + trajectories) exceeds the 126 MB L2"}
+            "l2": "no flush: every iteration streams the 159 MB of gains (written by the backward pass, read by the forward pass) plus "
+                  "26 MB of trajectories through the 126 MB L2, so no launch re-times a cached working set"}
 
 
 class ClockSampler:
@@ -47,6 +48,26 @@ class ClockSampler:
         self._t = None
 
     def _run(self):
+        # NVML directly (a sample costs ~0.1 ms); nvidia-smi as the fallback
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            hdl = pynvml.nvmlDeviceGetHandleByIndex(self.idx)
+            mx = float(pynvml.nvmlDeviceGetMaxClockInfo(hdl, pynvml.NVML_CLOCK_SM))
+            bits = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
+            while not self._stop.is_set():
+                self.samples.append((float(pynvml.nvmlDeviceGetClockInfo(hdl, pynvml.NVML_CLOCK_SM)), mx))
+                try:
+                    r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(hdl)
+                except Exception:
+                    r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(hdl)
+                for name, bit in bits.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                self._stop.wait(0.005)
+            return
+        except Exception:
+            pass
         q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
         while not self._stop.is_set():
             try:
@@ -139,7 +160,7 @@ def dfma_peak_tflops(torch):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH_PER_GPU, help="problems per GPU (default: the BASELINE config)")
