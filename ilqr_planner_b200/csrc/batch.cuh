@@ -1,7 +1,13 @@
 // batch.cuh — BatchILQR / BatchILQRCP path (BatchILQR.cpp:22-173, BatchILQRCP.cpp:21-174, System.cpp:111-211,321-361).
 //
-// Per iteration and problem (single-integrator systems, with or without a time state: A = I, so the reference's
-// `M = [A M, B]` recursion of buildSuJL keeps the B blocks as they are):
+// Per iteration and problem.  The reference's `M = [A M, B]` recursion of buildSuJL (BatchILQR.cpp:62-98) makes the
+// column block j of the row block of keypoint step t equal to A_{t-1} .. A_{j+1} B_j (B_j = dynamics B of control u_{j-1},
+// B_0 = 0: the column shift Q3).  The integrator chains of the planners have closed-form products, so Su is written
+// directly: single integrators A = I; double integrators A_l = [[I, dt_l I], [0, I]] => (prod A) B = B_q + tau B_v with
+// tau = sum of the dt_l in between (batch_Su_entry).
+// Keypoint slots: the reference indexes residuals / precisions by the time-sorted keypoint list WITH duplicates
+// (truncateStates, diffBatch, getQMatrix(true)) but packs J, L and Su by DISTINCT timestep, leaving the trailing
+// blocks zero (Q16).  BatchDev::vp / vds carry that mapping; without duplicates both indexings coincide.
 //
 //   k_batch_fp        fpBatch for the current controls AND for the 11 line-search candidates u + alpha du in one launch
 //                     (thread = problem x candidate): rollout, task vector / residual at the keypoint rows, pre-step
@@ -33,6 +39,10 @@ constexpr int BNC = NCAND + 1;  // candidate 0 = current controls (alpha = 0), 1
 struct BatchDev {  // POD view passed to the kernels
     // sizes
     int N = 0, Np = 0, S = 0, Sn = 0, SnP = 0, Sr = 0, nw = 0, cp = 0, chunk = 0;  // Np = N padded to 64, SnP = Sn padded to 4
+    // S = distinct keypoint timesteps (row blocks of J, L, Su: Sn = S n); nk = keypoints incl. duplicates (slots of e, Q: Sr = nk r)
+    int nk = 0;
+    int vp[MAX_KP_STEPS];   // slot -> timestep (sorted, duplicates kept)
+    int vds[MAX_KP_STEPS];  // slot -> index of that timestep in P.kp_steps
     // whole batch
     double* u = nullptr;      // [B][N]
     double* du = nullptr;     // [B][N]
@@ -41,6 +51,7 @@ struct BatchDev {  // POD view passed to the kernels
     double* psi = nullptr;    // [N][nw]
     double* psiRpsi = nullptr;  // [nw][nw]  Psi^T R Psi
     // per chunk of problems
+    double* X = nullptr;    // [C][H][n]  states of the current controls (double-integrator time systems: B needs the post-step velocity)
     double* Jt = nullptr;   // [C][S][r][n]
     double* e = nullptr;    // [C][Sr]
     double* Ld = nullptr;   // [C][S][n]  diagonal of L (0 / penalty)
@@ -72,6 +83,29 @@ __device__ __forceinline__ double batch_B_entry(const DevProblem& P, const doubl
     return v;
 }
 
+// (A_{ts-1} .. A_{j+1}) B_j, entry (a, c): the column block j (1 <= j <= ts-1) of the row block of keypoint step ts.
+// u: controls of the problem, X: its states [H][n], cs: prefix sums of dt (cs[l] = dt_1 + .. + dt_l, dt_l = step of u_{l-1}).
+// PosOrnPlannerSys.cpp:114-138, PosOrnTimePlannerSys.cpp:149-184 (Q15: the time column uses the POST-step velocity).
+__device__ __forceinline__ double batch_Su_entry(const DevProblem& P, const double* u, const double* X, const double* cs, int ts, int j, int a, int c) {
+    const int dof = P.dof, m = P.m, n = P.n;
+    const double* uj = u + (size_t)(j - 1) * m;
+    if (P.nb_deriv == 1) return batch_B_entry(P, uj, a, c);
+    double dt = P.dt, sq = 0.0, tau = (double)(ts - 1 - j) * P.dt;
+    if (P.time) {
+        sq = uj[m - 1];
+        dt = sq * sq;
+        tau = cs[ts - 1] - cs[j];
+        if (a == n - 1) return c == m - 1 ? 2 * sq : 0.0;
+    }
+    const int i = a < dof ? a : a - dof;
+    double bv = (c == i) ? 1.0 * dt : 0.0;
+    if (P.time && c == m - 1) bv = 2 * sq * uj[i];
+    if (a >= dof) return bv;
+    double bq = (c == i) ? 1.0 * dt * dt / 2 : 0.0;
+    if (P.time && c == m - 1) bq = 2 * sq * X[(size_t)j * n + dof + i] + 2 * sq * sq * sq * uj[i];
+    return bq + tau * bv;
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // fpBatch + cost for candidate c of problem b (System.cpp:181-211, BatchILQR.cpp:134,141-147)
 __global__ void __launch_bounds__(64) k_batch_fp(const DevProblem* __restrict__ Pp, Work W, BatchDev BW, int b0, int nB, int first_iter) {
@@ -88,10 +122,14 @@ __global__ void __launch_bounds__(64) k_batch_fp(const DevProblem* __restrict__ 
     double x[MAXN], xprev[MAXN], uk[MAXM];
     for (int i = 0; i < MAXN; i++) x[i] = xprev[i] = 0.0;
     for (int i = 0; i < dof; i++) x[i] = P.q0[(size_t)b * dof + i];
+    if (P.nb_deriv == 2)
+        for (int i = 0; i < dof; i++) x[dof + i] = P.dq0[(size_t)b * dof + i];
     double uRu = 0.0, qLq = 0.0;
     double evec[MAX_KP_STEPS * MAX_RT];
     int s = 0;
     for (int row = 0; row < H; row++) {
+        if (c == 0)
+            for (int i = 0; i < n; i++) BW.X[((size_t)bl * H + row) * n + i] = x[i];
         if (s < S && P.kp_steps[s] == row) {
             // task vector, residual (and for candidate 0 the Jacobian) at the keypoint row
             double dqz[MAXM];
@@ -99,7 +137,7 @@ __global__ void __launch_bounds__(64) k_batch_fp(const DevProblem* __restrict__ 
             for (int ti = 0; ti < P.n_tasks; ti++) {
                 const DevTask& tk = P.tasks[ti];
                 EEState ee;
-                task_ee(P, tk, x, dqz, ee);
+                task_ee(P, tk, x, P.nb_deriv == 2 ? x + dof : dqz, ee);
                 double fx[MAX_NTT], res[MAX_RT];
                 task_fx(P, tk, ee, P.time ? x[n - 1] : 0.0, fx);
                 const int kp = task_kp_at(tk, row);
@@ -146,24 +184,24 @@ __global__ void __launch_bounds__(64) k_batch_fp(const DevProblem* __restrict__ 
         for (int i = 0; i < n; i++) xprev[i] = x[i];
         dynamics_step(P, x, uk);
     }
-    // e^T Q e
-    const int Sr = S * P.r;
+    // e^T Q e over the keypoint slots (duplicates counted as often as they appear, Q16)
+    const int Sr = BW.Sr, rr = P.r;
     double eQe = 0.0;
     if (BW.Qfull) {
         for (int j = 0; j < Sr; j++) {
             double v = 0.0;
-            for (int i = 0; i < Sr; i++) v += evec[i] * BW.Qfull[(size_t)i * Sr + j];
-            eQe += v * evec[j];
+            for (int i = 0; i < Sr; i++) v += evec[BW.vds[i / rr] * rr + i % rr] * BW.Qfull[(size_t)i * Sr + j];
+            eQe += v * evec[BW.vds[j / rr] * rr + j % rr];
         }
     } else {
-        for (int ss = 0; ss < S; ss++)
+        for (int ss = 0; ss < BW.nk; ss++)
             for (int ti = 0; ti < P.n_tasks; ti++) {
                 const DevTask& tk = P.tasks[ti];
-                const int kp = task_kp_at(tk, P.kp_steps[ss]);
+                const int kp = task_kp_at(tk, BW.vp[ss]);
                 if (kp < 0) continue;
                 const int r = tk.r_t;
                 const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + kp) * r * r;
-                const double* ev = evec + ss * P.r + tk.r_off;
+                const double* ev = evec + BW.vds[ss] * rr + tk.r_off;
                 for (int j = 0; j < r; j++) {
                     double v = 0.0;
                     for (int i = 0; i < r; i++) v += ev[i] * Q[i * r + j];
@@ -173,7 +211,7 @@ __global__ void __launch_bounds__(64) k_batch_fp(const DevProblem* __restrict__ 
     }
     BW.cc[(size_t)b * BNC + c] = (eQe + uRu) + qLq;
     if (c == 0)
-        for (int i = 0; i < Sr; i++) BW.e[(size_t)bl * Sr + i] = evec[i];
+        for (int i = 0; i < Sr; i++) BW.e[(size_t)bl * Sr + i] = evec[BW.vds[i / rr] * rr + i % rr];
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -187,7 +225,7 @@ __device__ __forceinline__ double batch_q_elem(const DevProblem& P, const BatchD
         const DevTask& tk = P.tasks[ti];
         if (ci >= tk.r_off && ci < tk.r_off + tk.r_t) {
             if (cj < tk.r_off || cj >= tk.r_off + tk.r_t) return 0.0;
-            const int kp = task_kp_at(tk, P.kp_steps[si]);
+            const int kp = task_kp_at(tk, BW.vp[si]);
             if (kp < 0) return 0.0;
             const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + kp) * tk.r_t * tk.r_t;
             return Q[(ci - tk.r_off) * tk.r_t + (cj - tk.r_off)];
@@ -197,7 +235,7 @@ __device__ __forceinline__ double batch_q_elem(const DevProblem& P, const BatchD
 }
 
 // W = J^T Q J + L, g = J^T Q e + L ql (BatchILQR.cpp:130-131); Su, T = W Su, rhs = Su^T g - R u.  One block per problem.
-// Shared memory: JQ [Sn][Sr], W [Sn][Sn], g [Sn].
+// Shared memory: JQ [Sn][Sr], W [Sn][Sn], g [Sn], cs [H] (prefix sums of dt).
 __global__ void __launch_bounds__(256) k_batch_assemble(const DevProblem* __restrict__ Pp, Work W, BatchDev BW, int b0) {
     extern __shared__ double sm[];
     const DevProblem& P = *Pp;
@@ -207,6 +245,7 @@ __global__ void __launch_bounds__(256) k_batch_assemble(const DevProblem* __rest
     double* sJQ = sm;             // [Sn][Sr]
     double* sW = sJQ + Sn * Sr;   // [Sn][Sn]
     double* sg = sW + Sn * Sn;    // [Sn]
+    double* scs = sg + Sn;        // [H]
     const double* Jt = BW.Jt + (size_t)bl * S * r * n;
     const double* e = BW.e + (size_t)bl * Sr;
     const double* Ld = BW.Ld + (size_t)bl * Sn;
@@ -234,9 +273,20 @@ __global__ void __launch_bounds__(256) k_batch_assemble(const DevProblem* __rest
         BW.g[(size_t)bl * Sn + ia] = v;
     }
     __syncthreads();
-    // columns of Su / T / rhs.  Row block s of Su is [0, B_1, .., B_{t_s - 1}, 0 ..]: column block j = control u_j holds
+    // columns of Su / T / rhs.  Row block s of Su is [0, A..A B_1, .., B_{t_s - 1}, 0 ..]: column block j = control u_j holds
     // the B of control u_{j-1} (BatchILQR.cpp:71-94 with ABJLs[0].B = 0, Q3)
     const double* u = BW.u + (size_t)b * N;
+    const double* X = BW.X + (size_t)bl * P.H * n;
+    if (threadIdx.x == 0) {
+        double acc = 0.0;
+        scs[0] = 0.0;
+        for (int l = 1; l < P.H; l++) {
+            const double sq = P.time ? u[(size_t)(l - 1) * m + m - 1] : 0.0;
+            acc += P.time ? sq * sq : P.dt;
+            scs[l] = acc;
+        }
+    }
+    __syncthreads();
     double* Su = BW.Su + (size_t)bl * BW.SnP * Np;
     double* T = BW.T + (size_t)bl * BW.SnP * Np;
     for (int col = threadIdx.x; col < Np; col += blockDim.x) {
@@ -246,16 +296,13 @@ __global__ void __launch_bounds__(256) k_batch_assemble(const DevProblem* __rest
             for (int ia = 0; ia < Sn; ia++) {
                 const int s = ia / n, a = ia % n;
                 double v = 0.0;
-                if (j >= 1 && j <= P.kp_steps[s] - 1) v = batch_B_entry(P, u + (size_t)(j - 1) * m, a, c);
+                if (j >= 1 && j <= P.kp_steps[s] - 1) v = batch_Su_entry(P, u, X, scs, P.kp_steps[s], j, a, c);
                 Su[(size_t)ia * Np + col] = v;
                 rhs += v * sg[ia];
             }
             for (int ia = 0; ia < Sn; ia++) {
                 double tv = 0.0;
-                for (int kb = 0; kb < Sn; kb++) {
-                    const int s = kb / n, a = kb % n;
-                    if (j >= 1 && j <= P.kp_steps[s] - 1) tv += sW[ia * Sn + kb] * batch_B_entry(P, u + (size_t)(j - 1) * m, a, c);
-                }
+                for (int kb = 0; kb < Sn; kb++) tv += sW[ia * Sn + kb] * Su[(size_t)kb * Np + col];  // this thread's own column
                 T[(size_t)ia * Np + col] = tv;
             }
             rhs -= P.r_diag[c] * u[col];
@@ -641,38 +688,42 @@ inline void batch_free(BatchWork& BW) {
 // chunk must fit the workspace budget, ILQRB_BATCH_WS_GB, default 24 GB).  `begin(slot)` / `end()` bracket every launch.
 inline int batch_run(cudaStream_t st, const DevProblem& P, const DevProblem* dp, Work& W, BatchWork& BW, const ilqrb_batch_desc* bd,
                      const ilqrb_solve_opts* opts, std::string& err, std::function<void(int)> begin, std::function<void()> end) {
-    if (P.nb_deriv != 1) {
-        err = "Batch solvers: only single-integrator systems (nb_deriv = 1) are built on the GPU";
-        return ILQRB_EUNSUPPORTED;
-    }
-    int n_kp_total = 0;
-    for (int t = 0; t < P.n_tasks; t++) n_kp_total += P.tasks[t].n_keypoints;
-    if (n_kp_total != P.n_kp_steps) {
-        err = "Batch solvers: sub-systems with keypoints at the same timestep (duplicate row blocks, SURVEY Q16) are not built";
+    // keypoint slots (time-sorted, duplicates kept) and their distinct-step index
+    std::vector<int> vp;
+    for (int t = 0; t < P.n_tasks; t++)
+        for (int k = 0; k < P.tasks[t].n_keypoints; k++) vp.push_back(P.tasks[t].kp_timestep[k]);
+    std::stable_sort(vp.begin(), vp.end());
+    const int nk = (int)vp.size();
+    if (nk != P.n_kp_steps && P.n_tasks == 1 && P.any_limits) {
+        err = "Batch solvers: a single system with joint limits and several keypoints at the same timestep is not built (SURVEY Q16)";
         return ILQRB_EUNSUPPORTED;
     }
     const int B = P.B, H = P.H, n = P.n, m = P.m, r = P.r, S = P.n_kp_steps;
-    const int N = (H - 1) * m, Np = (N + 63) / 64 * 64, Sn = S * n, SnP = (Sn + 3) / 4 * 4, Sr = S * r;
+    const int N = (H - 1) * m, Np = (N + 63) / 64 * 64, Sn = S * n, SnP = (Sn + 3) / 4 * 4, Sr = nk * r;
     const int nw = (bd && bd->psi) ? bd->nw : 0, cp = nw > 0;
     if (cp && nw > 128) {
         err = "BatchILQRCP: more than 128 primitive weights";
         return ILQRB_EUNSUPPORTED;
     }
-    if (Sr > MAX_KP_STEPS * MAX_RT) {
+    if (S * r > MAX_KP_STEPS * MAX_RT || nk > MAX_KP_STEPS) {
         err = "Batch solvers: too many keypoint rows";
         return ILQRB_EUNSUPPORTED;
     }
-    if (BW.allocated && (BW.N != N || BW.nw != nw || BW.S != S)) batch_free(BW);
+    if (BW.allocated && (BW.N != N || BW.nw != nw || BW.S != S || BW.nk != nk)) batch_free(BW);
     int rc;
     if (!BW.allocated) {
-        BW.N = N; BW.Np = Np; BW.S = S; BW.Sn = Sn; BW.SnP = SnP; BW.Sr = Sr; BW.nw = nw; BW.cp = cp;
+        BW.N = N; BW.Np = Np; BW.S = S; BW.Sn = Sn; BW.SnP = SnP; BW.Sr = Sr; BW.nw = nw; BW.cp = cp; BW.nk = nk;
+        for (int i = 0; i < nk; i++) {
+            BW.vp[i] = vp[i];
+            BW.vds[i] = (int)(std::find(P.kp_steps, P.kp_steps + S, vp[i]) - P.kp_steps);
+        }
         const char* ev = getenv("ILQRB_BATCH_WS_GB");
         const double budget = (ev ? atof(ev) : 24.0) * 1e9;
-        const double per = 8.0 * ((cp ? 0.0 : (double)Np * Np) + 2.0 * SnP * Np + Np + (double)S * r * n + Sr + 2.0 * Sn + (double)Sn * Sn + Sn + (double)Sn * std::max(nw, 1));
+        const double per = 8.0 * ((cp ? 0.0 : (double)Np * Np) + 2.0 * SnP * Np + Np + (double)H * n + (double)S * r * n + Sr + 2.0 * Sn + (double)Sn * Sn + Sn + (double)Sn * std::max(nw, 1));
         BW.chunk = (int)std::max(1.0, std::min((double)B, budget / per));
         const size_t C = BW.chunk;
         if ((rc = batch_alloc(BW, &BW.u, (size_t)B * N, err)) || (rc = batch_alloc(BW, &BW.du, (size_t)B * N, err)) || (rc = batch_alloc(BW, &BW.cc, (size_t)B * BNC, err)) ||
-            (rc = batch_alloc(BW, &BW.Jt, C * S * r * n, err)) || (rc = batch_alloc(BW, &BW.e, C * Sr, err)) || (rc = batch_alloc(BW, &BW.Ld, C * Sn, err)) ||
+            (rc = batch_alloc(BW, &BW.X, C * H * n, err)) || (rc = batch_alloc(BW, &BW.Jt, C * S * r * n, err)) || (rc = batch_alloc(BW, &BW.e, C * Sr, err)) || (rc = batch_alloc(BW, &BW.Ld, C * Sn, err)) ||
             (rc = batch_alloc(BW, &BW.ql, C * Sn, err)) || (rc = batch_alloc(BW, &BW.Wm, C * Sn * Sn, err)) || (rc = batch_alloc(BW, &BW.g, C * Sn, err)) ||
             (rc = batch_alloc(BW, &BW.Su, C * SnP * Np, err)) || (rc = batch_alloc(BW, &BW.T, C * SnP * Np, err)) || (rc = batch_alloc(BW, &BW.rhs, C * Np, err)))
             return rc;
@@ -715,7 +766,7 @@ inline int batch_run(cudaStream_t st, const DevProblem& P, const DevProblem* dp,
     }
     static bool attr_set = false;
     const size_t smem_chol = 3 * 64 * CH_LD * sizeof(double), smem_trsv = (64 * CH_LD + Np) * sizeof(double);
-    const size_t smem_asm = ((size_t)Sn * Sr + (size_t)Sn * Sn + Sn) * sizeof(double), smem_cp = (2 * (size_t)Sn * std::max(nw, 1) + (size_t)nw * (nw + 1)) * sizeof(double);
+    const size_t smem_asm = ((size_t)Sn * Sr + (size_t)Sn * Sn + Sn + H) * sizeof(double), smem_cp = (2 * (size_t)Sn * std::max(nw, 1) + (size_t)nw * (nw + 1)) * sizeof(double);
     if (!attr_set) {
         BCU(cudaFuncSetAttribute(k_batch_chol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_chol));
         attr_set = true;

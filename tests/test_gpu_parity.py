@@ -235,12 +235,7 @@ def test_errors_are_loud():
 
 # ---------------------------------------------------------------------------------------------------------------
 # (3) Batch / control-primitive Batch solvers (BatchILQR.cpp, BatchILQRCP.cpp): single-integrator systems on the GPU
-GOLD_BATCH = [c["name"] for c in tc.goldens()["cases"] if c["solver"] in ("batch", "batch_cp") and c["system"]["nb_deriv"] == 1]
-
-
-def _distinct_steps(c):
-    steps = [k for t in c["system"]["tasks"] for k in t["kp_timestep"]]
-    return len(steps) == len(set(steps))
+GOLD_BATCH = [c["name"] for c in tc.goldens()["cases"] if c["solver"] in ("batch", "batch_cp")]
 
 
 @pytest.mark.parametrize("name", GOLD_BATCH)
@@ -251,10 +246,6 @@ def test_batch_notebook_trace_on_gpu(name):
     u0 = tc.case_u0(c, pb)
     psi = tc.case_psi(c, pb) if c["solver"] == "batch_cp" else None
     with _handle(pb) as h:
-        if not _distinct_steps(c):
-            with pytest.raises(RuntimeError, match="same timestep"):  # declared unsupported, loudly
-                h.solve_batch(u0, c["nb_iter"], c["early_stop"], Q=c["Q"], psi=psi)
-            return
         out = h.solve_batch(u0, c["nb_iter"], c["early_stop"], Q=c["Q"], psi=psi)
     got = tc.trace_lines(out.cost_hist[0], out.alpha_hist[0], out.iters[0])
     exp = tc.norm_trace(c["trace"])
@@ -307,3 +298,20 @@ def test_batch_ilqr_posorn_vs_oracle(oracle_lib):
     from ilqr_planner_b200.solver import build_psi
     psi = np.kron(build_psi("rbf", pb.horizon - 1, 4), np.identity(pb.m))
     _check_batch(pb, None, 6, oracle_lib, psi=psi, early_stop=True)
+
+
+def test_batch_ilqr_double_integrator_vs_oracle(oracle_lib):
+    """nb_deriv = 2: the column blocks of Su are A..A B products (closed form on the device, matrix recursion in the oracle)"""
+    from ilqr_planner_b200 import synth
+    from ilqr_planner_b200.solver import build_psi
+    pb = synth.config3(batch=6, horizon=40)
+    _check_batch(pb, None, 5, oracle_lib, ctol=1e-6, utol=1e-5)
+    psi = np.kron(build_psi("unitstep", pb.horizon - 1, 3), np.identity(pb.m))
+    _check_batch(pb, None, 6, oracle_lib, psi=psi, ctol=1e-6, utol=1e-5)
+
+
+def test_batch_ilqr_dual_task_vs_oracle(oracle_lib):
+    """two tasks on a 14-joint state (C5 shape): stacked residual rows, keypoints of the two sub-systems at the same steps"""
+    from ilqr_planner_b200 import synth
+    pb = synth.config5(batch=4, horizon=30)
+    _check_batch(pb, None, 4, oracle_lib)

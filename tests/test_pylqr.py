@@ -174,8 +174,6 @@ def test_tutorial_solve_through_pylqr(name):
         lam0 = [lam[k] if lam.ndim == 2 else lam for k in range(H - 1)]
         X, fX, U = AL_ILQR(s, cons, lam0).solve(u0, c["nb_iter"], c["lag_update_step"], c["penalty"], c["scaling_factor"], c["line_search"], c["early_stop"], cb)
     else:
-        steps = [k for t in sp["tasks"] for k in t["kp_timestep"]]
-        unsupported = sp["nb_deriv"] != 1 or len(steps) != len(set(steps))
         exact = False
         if c["solver"] == "batch_cp":
             class _PB:  # case_psi only needs m
@@ -186,10 +184,6 @@ def test_tutorial_solve_through_pylqr(name):
             pl = BatchILQRCP(s, psi) if c["Q"] is None else BatchILQRCP(s, np.asarray(c["Q"]), psi)
         else:
             pl = BatchILQR(s) if c["Q"] is None else BatchILQR(s, np.asarray(c["Q"]))
-        if unsupported:
-            with pytest.raises(RuntimeError):
-                pl.solve(c["nb_iter"], u0.reshape(-1), c["early_stop"], cb)
-            return
         u = pl.solve(c["nb_iter"], u0.reshape(-1), c["early_stop"], cb)
         assert u.shape == ((H - 1) * m,)
     got, exp = parse_trace(cb.messages), tc.norm_trace(c["trace"])
