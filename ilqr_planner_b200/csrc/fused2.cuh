@@ -1,0 +1,261 @@
+// fused2.cuh — fast path of the Recursive solver for DOUBLE-integrator systems without a time state
+// (PosOrnPlannerSys nb_deriv = 2, PosOrnPlannerSys.cpp:122-128):  x = [q; v],  A = [[I, dt I], [0, I]],  B = [dt^2/2 I; dt I],
+// n = 2 dof, m = dof <= 7.  One problem per warp, everything in registers in the DMMA accumulator layout.
+//
+// Padded state index: q_i -> i, v_i -> 8 + i, so that each dof x dof block of a state-indexed matrix is its own 8x8
+// tile and the augmented column (the vector that rides along: p, Qx, Qu, d) is column 15 = local column 7 of the
+// second column tile.  With this layout the products with A and B are tile-wise scalings and sums:
+//   B^T [P|p] = [M1 M2],  M1 = c2 P11 + dt P21,  M2 = c2 P12 + dt P22          (c2 = dt^2/2)
+//   [Qux|Qu]  = [M1, dt M1 + M2] + [0 | R u]        Quu = R + c2 M1 + dt M2
+//   A^T [P|p] = N,  N1c = P1c,  N2c = dt P1c + P2c ;   [Qxx|Qx] = [l_xx|l_x] + [Nr1, dt Nr1 + Nr2] ;   Qxu = c2 Nr1 + dt Nr2
+// Only [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu] (in-register Gauss-Jordan) and P' = Qxx + K^T (Quu K + Qux) + Qxu K
+// (20 DMMA m8n8k4.f64 per step) remain as dense work (ILQRRecursive.cpp:69-97).
+#pragma once
+#include "fused1.cuh"
+
+namespace ilqrb {
+
+// (L) X = [R0 R1] in registers: L one 8x8 tile (leading m x m block, identity outside), R two tiles side by side.
+// Gauss-Jordan without pivoting, rows divided by their diagonal at the end (see gj_solve_regs).
+template <int M>
+__device__ __forceinline__ bool gj_solve_1x2(double (&L)[2], double (&R)[2][2], int m_rt, int g, int t) {
+    constexpr unsigned FULL = 0xffffffffu;
+    const int m = M > 0 ? M : m_rt;
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        if (k < m) {
+            const int kh = k & 1;
+            const double pkk = __shfl_sync(FULL, L[kh], 4 * k + (k >> 1));
+            const double l0 = __shfl_sync(FULL, L[0], 4 * k + t), l1 = __shfl_sync(FULL, L[1], 4 * k + t);
+            const double r00 = __shfl_sync(FULL, R[0][0], 4 * k + t), r01 = __shfl_sync(FULL, R[0][1], 4 * k + t);
+            const double r10 = __shfl_sync(FULL, R[1][0], 4 * k + t), r11 = __shfl_sync(FULL, R[1][1], 4 * k + t);
+            const double colk = __shfl_sync(FULL, L[kh], 4 * g + (k >> 1));
+            const int hi = __double2hiint(pkk);
+            ok = ok && (hi > 0) && (hi < 0x7ff00000);
+            const double f = (g == k) ? 0.0 : colk * fast_rcp(pkk);
+            L[0] = fma(-f, l0, L[0]);
+            L[1] = fma(-f, l1, L[1]);
+            R[0][0] = fma(-f, r00, R[0][0]);
+            R[0][1] = fma(-f, r01, R[0][1]);
+            R[1][0] = fma(-f, r10, R[1][0]);
+            R[1][1] = fma(-f, r11, R[1][1]);
+        }
+    }
+    const double mine = (g & 1) ? L[1] : L[0];
+    const double inv = fast_rcp(__shfl_sync(FULL, mine, 4 * g + ((g >> 1) & 3)));
+    R[0][0] *= inv;
+    R[0][1] *= inv;
+    R[1][0] *= inv;
+    R[1][1] *= inv;
+    return ok;
+}
+
+struct BwdN2Smem {
+    static constexpr int LDW = 20, LDQ = 12;                 // 8 x 16 matrices / the 8 x 8 Quu
+    static constexpr int SZW = 8 * LDW, SZQ = 8 * LDQ;
+    static constexpr int PER_WARP = 2 * SZW + 3 * SZQ;       // [K|d], Quu [K|d] + [Qux|Qu], Quu, Qxu (16 x 8)
+};
+
+// fragment loads of the 8 x 16 matrices (row-major, leading dimension LDW)
+__device__ __forceinline__ double ld_bw(const double* M, int s, int c, int g, int t) { return M[(4 * s + t) * BwdN2Smem::LDW + 8 * c + g]; }
+__device__ __forceinline__ void st_w(double* M, const double (&e)[2][2], int g, int t) {
+#pragma unroll
+    for (int c = 0; c < 2; c++) *reinterpret_cast<double2*>(M + g * BwdN2Smem::LDW + 8 * c + 2 * t) = make_double2(e[c][0], e[c][1]);
+}
+
+template <int DOF>
+__device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work& W, int b, int lane, double* wsmem) {
+    using S = BwdN2Smem;
+    const int g = lane >> 2, t = lane & 3;
+    const int dof = DOF > 0 ? DOF : P.dof, n = 2 * dof, m = dof, H = P.H;
+    const int ns = W.ns, ms = W.ms;
+    const double dt = 1.0 * P.dt, c2 = 1.0 * P.dt * P.dt / 2;
+    double* sKd = wsmem;
+    double* sM = sKd + S::SZW;
+    double* sQuu = sM + S::SZW;
+    double* sQxu = sQuu + S::SZQ;  // 16 x 8
+    const bool rowv = g < dof;  // this lane's row is a real control / state row of its tile
+    const double Rg = rowv ? P.r_diag[g] : 0.0;
+    const double* Xb = W.X + (size_t)b * H * ns;
+    const double* Ub = W.U + (size_t)b * (H - 1) * ms;
+    const int S_kp = P.n_kp_steps;
+
+    // e += [l_xx | l_x] of keypoint step index s ; natural index of (tile r, local i) is r dof + i      System.cpp:252-260,290-296
+    auto add_kp = [&](double (&e)[2][2][2], int s) {
+        const double* lx = W.LX + ((size_t)b * S_kp + s) * n;
+        const double* lxx = W.LXX + ((size_t)b * S_kp + s) * n * n;
+        if (!rowv) return;
+#pragma unroll
+        for (int r = 0; r < 2; r++)
+#pragma unroll
+            for (int c = 0; c < 2; c++)
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int jl = 2 * t + h;
+                    if (jl < dof) e[r][c][h] += lxx[(r * dof + g) * n + c * dof + jl];
+                    else if (c == 1 && jl == 7) e[r][c][h] += lx[r * dof + g];
+                }
+    };
+    // joint limits (System.cpp:121-142,263-269,299-305): e += [L^T L | -L^T q], L = diag(violated), q = limit - x
+    auto add_limits = [&](double (&e)[2][2][2], int k) {
+        if (!P.any_limits || !rowv) return;
+        const double* Xk = Xb + (size_t)k * ns;
+        for (int ti = 0; ti < P.n_tasks; ti++) {
+            const DevTask& tk = P.tasks[ti];
+            if (!tk.limits_set) continue;
+#pragma unroll
+            for (int r = 0; r < 2; r++) {
+                bool act;
+                const double q = limit_q(tk, r * dof + g, Xk[r * dof + g], act);
+                if (act) {
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        if (2 * t + h == g) e[r][r][h] += 1.0 * 1.0;
+                        if (2 * t + h == 7) e[r][1][h] += -1.0 * q;
+                    }
+                }
+            }
+        }
+    };
+
+    // terminal: P = cost_F_xx, p = cost_F_x   (ILQRRecursive.cpp:69-71)
+    double Pa[2][2][2];
+#pragma unroll
+    for (int r = 0; r < 2; r++)
+#pragma unroll
+        for (int c = 0; c < 2; c++) Pa[r][c][0] = Pa[r][c][1] = 0.0;
+    int sp = S_kp - 1;
+    int next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
+    if (next_kp == H - 1) {
+        add_kp(Pa, sp);
+        sp--;
+        next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
+    }
+    add_limits(Pa, H - 1);
+    bool spd = true;
+    double* Kg = W.K + ((size_t)b * (H - 1) + (H - 2)) * m * ns;
+    double* dg = W.d + ((size_t)b * (H - 1) + (H - 2)) * ms;
+    double un = rowv ? Ub[(size_t)(H - 2) * ms + g] : 0.0;
+
+    for (int k = H - 2; k >= 0; k--, Kg -= m * ns, dg -= ms) {
+        const double u = un;
+        if (k > 0) un = rowv ? Ub[(size_t)(k - 1) * ms + g] : 0.0;
+        double Qa[2][2], Quu[2], Lr[2], Qx[2][2][2], Qxu[2][2];
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int jl = 2 * t + h;
+            // separate multiplies and adds (no FMA contraction): the same roundings as the reference's dense products,
+            // whose other terms are exact zeros
+            const double m1 = __dadd_rn(__dmul_rn(c2, Pa[0][0][h]), __dmul_rn(dt, Pa[1][0][h]));  // B^T P, columns of q
+            const double m2 = __dadd_rn(__dmul_rn(c2, Pa[0][1][h]), __dmul_rn(dt, Pa[1][1][h]));  // B^T [P|p], columns of v and the vector
+            Qa[0][h] = m1;
+            const double qv = __dadd_rn(__dmul_rn(m1, dt), m2);
+            Qa[1][h] = (jl == 7) ? __dadd_rn(__dmul_rn(Rg, u), qv) : qv;
+            double quu = __dadd_rn(__dmul_rn(m1, c2), __dmul_rn(m2, dt));
+            if (jl == g) quu = __dadd_rn(Rg, quu);
+            quu = (jl < dof && rowv) ? quu : 0.0;
+            Quu[h] = quu;
+            Lr[h] = (jl == g) ? (rowv ? quu + 1e-6 * 1.0 : 1.0) : quu;  // Quu + 1e-6 I, identity outside          ILQRRecursive.cpp:89
+            const double n20 = __dadd_rn(__dmul_rn(dt, Pa[0][0][h]), Pa[1][0][h]);  // A^T [P|p], second row block
+            const double n21 = __dadd_rn(__dmul_rn(dt, Pa[0][1][h]), Pa[1][1][h]);
+            // Qxu = (A^T P) B, from P itself: NOT Qux^T — the transposed shortcut leaves the antisymmetric rounding part of P
+            // without the cross terms that damp it, E' = A^T E A + (BK)^T E (BK), and that mode grows along the horizon
+            Qxu[0][h] = (jl < dof) ? __dadd_rn(__dmul_rn(Pa[0][0][h], c2), __dmul_rn(Pa[0][1][h], dt)) : 0.0;
+            Qxu[1][h] = (jl < dof) ? __dadd_rn(__dmul_rn(n20, c2), __dmul_rn(n21, dt)) : 0.0;
+            Qx[0][0][h] = Pa[0][0][h];
+            Qx[1][0][h] = n20;
+            Qx[0][1][h] = __dadd_rn(__dmul_rn(Pa[0][0][h], dt), Pa[0][1][h]);
+            Qx[1][1][h] = __dadd_rn(__dmul_rn(n20, dt), n21);
+        }
+        if (k == next_kp) {
+            add_kp(Qx, sp);
+            sp--;
+            next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
+        }
+        add_limits(Qx, k);
+
+        *reinterpret_cast<double2*>(sQuu + g * S::LDQ + 2 * t) = make_double2(Quu[0], Quu[1]);
+#pragma unroll
+        for (int r = 0; r < 2; r++) *reinterpret_cast<double2*>(sQxu + (8 * r + g) * S::LDQ + 2 * t) = make_double2(Qxu[r][0], Qxu[r][1]);
+        // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]                                            ILQRRecursive.cpp:89-91
+        double Kd[2][2] = {{-Qa[0][0], -Qa[0][1]}, {-Qa[1][0], -Qa[1][1]}};
+        spd = gj_solve_1x2<DOF>(Lr, Kd, m, g, t) && spd;
+#pragma unroll
+        for (int c = 0; c < 2; c++)
+#pragma unroll
+            for (int h = 0; h < 2; h++)
+                if (!rowv) Kd[c][h] = 0.0;
+        st_w(sKd, Kd, g, t);
+        if (rowv) {  // stream K (m x n, natural column order) and d
+#pragma unroll
+            for (int c = 0; c < 2; c++)
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int jl = 2 * t + h;
+                    if (jl < dof) Kg[g * ns + c * dof + jl] = Kd[c][h];
+                    else if (c == 1 && jl == 7) dg[g] = Kd[c][h];
+                }
+        }
+        __syncwarp();
+
+        // [M|mv] = Quu [K|d] + [Qux|Qu]   (K^T Quu K + K^T Qux = K^T M, ILQRRecursive.cpp:93-94)
+        double kb[2][2], qa[2];  // B fragments of [K|d] (= A fragments of [K|d]^T), A fragments of Quu
+#pragma unroll
+        for (int s = 0; s < 2; s++) {
+            qa[s] = sQuu[g * S::LDQ + 4 * s + t];
+#pragma unroll
+            for (int c = 0; c < 2; c++) kb[s][c] = ld_bw(sKd, s, c, g, t);
+        }
+        double Mm[2][2];
+#pragma unroll
+        for (int c = 0; c < 2; c++) {
+            double c0 = Qa[c][0], c1 = Qa[c][1];
+#pragma unroll
+            for (int s = 0; s < 2; s++) dmma884(c0, c1, qa[s], kb[s][c]);
+            Mm[c][0] = c0;
+            Mm[c][1] = c1;
+        }
+        st_w(sM, Mm, g, t);
+        __syncwarp();
+
+        // [P|p] = [Qxx|Qx] + K^T [M|mv] + Qxu [K|d]
+        double mb[2][2], xa[2][2];  // B fragments of [M|mv]; A fragments of Qxu
+#pragma unroll
+        for (int s = 0; s < 2; s++)
+#pragma unroll
+            for (int c = 0; c < 2; c++) {
+                mb[s][c] = ld_bw(sM, s, c, g, t);
+                xa[s][c] = sQxu[(8 * c + g) * S::LDQ + 4 * s + t];
+            }
+#pragma unroll
+        for (int r = 0; r < 2; r++)
+#pragma unroll
+            for (int c = 0; c < 2; c++) {
+                double c0 = Qx[r][c][0], c1 = Qx[r][c][1];
+#pragma unroll
+                for (int s = 0; s < 2; s++) dmma884(c0, c1, kb[s][r], mb[s][c]);
+#pragma unroll
+                for (int s = 0; s < 2; s++) dmma884(c0, c1, xa[s][r], kb[s][c]);
+                // keep rows >= dof (incl. the d row the transposed fragment drags in) and unused columns at exact zero
+                const int j0 = 2 * t;
+                Pa[r][c][0] = (rowv && (j0 < dof || (c == 1 && j0 == 7))) ? c0 : 0.0;
+                Pa[r][c][1] = (rowv && (j0 + 1 < dof || (c == 1 && j0 + 1 == 7))) ? c1 : 0.0;
+            }
+        __syncwarp();
+    }
+    if (!spd && lane == 0) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
+}
+
+template <int DOF, int WARPS, int MINB>
+__global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n2(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
+    extern __shared__ double smem[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int bl = blockIdx.x * WARPS + wid;
+    if (bl >= nB) return;
+    const int b = b0 + bl;
+    if (W.done[b]) return;
+    backward_n2_body<DOF>(*Pp, W, b, lane, smem + (size_t)wid * BwdN2Smem::PER_WARP);
+}
+
+}  // namespace ilqrb

@@ -13,6 +13,7 @@
 
 #include "batch.cuh"
 #include "fused1.cuh"
+#include "fused2.cuh"
 #include "recursive.cuh"
 
 using namespace ilqrb;
@@ -234,10 +235,30 @@ int launch_backward_ta(ilqrb_handle h, double pf) {
         default: return launch_backward_t<4, 2, TIME, AL, 2, 1>(h, pf);
     }
 }
+// double-integrator fast backward pass (fused2.cuh): nb_deriv = 2, no time state, no AL terms, dof <= 7
+bool fast_n2_applies(ilqrb_handle h, bool al) {
+    static const bool force_generic = getenv("ILQRB_GENERIC") != nullptr;
+    const DevProblem& P = h->hp;
+    return !force_generic && !al && !P.time && P.nb_deriv == 2 && P.dof <= 7 && P.n == 2 * P.dof && P.m == P.dof;
+}
+template <int DOF, int WARPS, int MINB>
+int launch_backward_n2_t(ilqrb_handle h) {
+    const size_t smem = (size_t)WARPS * BwdN2Smem::PER_WARP * sizeof(double);
+    auto kern = k_backward_n2<DOF, WARPS, MINB>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    const int B = h->hp.B;
+    kern<<<(B + WARPS - 1) / WARPS, 32 * WARPS, smem, h->stream>>>(h->dp, h->W, 0, B);
+    return 0;
+}
 int launch_backward(ilqrb_handle h, bool al, double pf) {
     h->begin(PS_BACKWARD);
     int rc;
-    if (h->hp.time) rc = al ? launch_backward_ta<true, true>(h, pf) : launch_backward_ta<true, false>(h, pf);
+    if (fast_n2_applies(h, al)) rc = h->hp.dof == 7 ? launch_backward_n2_t<7, 4, 4>(h) : launch_backward_n2_t<0, 4, 4>(h);
+    else if (h->hp.time) rc = al ? launch_backward_ta<true, true>(h, pf) : launch_backward_ta<true, false>(h, pf);
     else rc = al ? launch_backward_ta<false, true>(h, pf) : launch_backward_ta<false, false>(h, pf);
     h->end();
     if (rc) return rc;
