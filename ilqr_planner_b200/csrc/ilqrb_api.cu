@@ -443,9 +443,35 @@ int launch_derivs(ilqrb_handle h, int b0 = 0, int nB = -1, cudaStream_t st = nul
     CU(cudaGetLastError());
     return 0;
 }
-int launch_linesearch(ilqrb_handle h, int line_search) {
+// affine line search (k_linesearch_affine): linear dynamics, no AL terms
+template <int N, int M>
+int launch_linesearch_affine_t(ilqrb_handle h, int line_search) {
+    const DevProblem& P = h->hp;
+    const size_t smem = 4 * (size_t)ls_affine_smem_doubles(P.H, h->W.ns, h->W.ms) * sizeof(double);
+    auto kern = k_linesearch_affine<N, M>;
+    static size_t attr = 0;
+    if (smem > attr) {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr = smem;
+    }
+    kern<<<(P.B + 3) / 4, 128, smem, h->stream>>>(h->dp, h->W, line_search);
+    return 0;
+}
+int launch_linesearch(ilqrb_handle h, int line_search, bool al) {
     const int tot = h->hp.B * CAND_LANES;
     h->begin(PS_LINESEARCH);
+    static const bool force_generic = getenv("ILQRB_GENERIC") != nullptr;
+    const size_t need = 4 * (size_t)ls_affine_smem_doubles(h->hp.H, h->W.ns, h->W.ms) * sizeof(double);
+    if (!force_generic && !al && !h->hp.time && need <= 200 * 1024) {
+        int rc = 0;
+#define CALL(N, M) rc = launch_linesearch_affine_t<N, M>(h, line_search)
+        DISPATCH_NM(size_class(h->hp.n, h->hp.m), CALL)
+#undef CALL
+        h->end();
+        if (rc) return rc;
+        CU(cudaGetLastError());
+        return 0;
+    }
 #define CALL(N, M) k_linesearch<N, M><<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, line_search)
     DISPATCH_NM(size_class(h->hp.n, h->hp.m), CALL)
 #undef CALL
@@ -613,7 +639,7 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
     for (int it = 0; it < opts->nb_iter; it++) {
         if ((rc = launch_derivs(h))) return rc;
         if ((rc = launch_backward(h, al != nullptr, pen_frozen))) return rc;
-        if ((rc = launch_linesearch(h, opts->line_search))) return rc;
+        if ((rc = launch_linesearch(h, opts->line_search, al != nullptr))) return rc;
         double pen_next = pen;
         bool upd = false;
         if (al) {

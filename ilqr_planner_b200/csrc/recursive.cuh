@@ -239,6 +239,182 @@ __global__ void __launch_bounds__(128) k_linesearch(const DevProblem* __restrict
     W.dun_c[(size_t)b * NCAND + c] = dun;
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// line search for systems with LINEAR dynamics (no time state) and no AL terms: one warp per problem.
+// With x+ = A x + B u the candidate of step length alpha is affine in alpha, x'(alpha) = x + alpha dx, u'(alpha) = u + alpha du,
+// where (dx, du) is the alpha = 1 closed-loop deviation du_k = K_k dx_k + d_k, dx_{k+1} = A dx_k + B du_k.  The warp rolls
+// that deviation out ONCE (lane i owns control row i and joint i), keeps it in shared memory, and the 11 candidates then
+// only differ in cost terms: lane c evaluates candidate c at the keypoint steps (every step if some joint limit is violated
+// at either end of a segment [x, x + dx]: box limits are convex, so otherwise no candidate violates one).
+// Selection follows k_accept's rule; only the SELECTED candidate's controls are written (k_accept applies the same rule
+// to the same costs and reads that slot).  Replaces k_linesearch's 11 full rollouts (ILQRRecursive.cpp:101-155).
+__host__ __device__ inline int ls_affine_smem_doubles(int H, int ns, int ms) { return (H - 1) * ms + (MAX_KP_STEPS + 2) * ns + MAX_KP_STEPS * NCAND; }
+
+template <int N, int M>
+__global__ void __launch_bounds__(128, 4) k_linesearch_affine(const DevProblem* __restrict__ Pp, Work W, int line_search) {
+    extern __shared__ double ls_smem[];
+    constexpr unsigned FULL = 0xffffffffu;
+    const DevProblem& P = *Pp;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int b = blockIdx.x * 4 + wid;
+    if (b >= P.B) return;
+    if (W.done[b]) return;
+    const int H = P.H, n = P.n, m = P.m, ns = W.ns, ms = W.ms, dof = P.dof, S = P.n_kp_steps;
+    double* sDU = ls_smem + (size_t)wid * ls_affine_smem_doubles(H, ns, ms);  // [H-1][ms]  du of every step
+    double* sKX = sDU + (size_t)(H - 1) * ms;                                  // [S][ns]    dx at the keypoint steps
+    double* sX2 = sKX + (size_t)MAX_KP_STEPS * ns;                             // [2][ns]    dx of the current step (double buffer)
+    double* sCk = sX2 + 2 * ns;                                                // [S][NCAND] keypoint-step costs
+    const double dt = P.dt, hdt2 = __dmul_rn(dt, dt) / 2;
+    const double* Kb = W.K + (size_t)b * (H - 1) * m * ns;
+    const double* db = W.d + (size_t)b * (H - 1) * ms;
+    const double* Xb = W.X + (size_t)b * H * ns;
+
+    // ---- phase A: deviation rollout; limits checked on the fly at both ends of every segment --------------------------
+    for (int j = lane; j < 2 * ns; j += 32) sX2[j] = 0.0;
+    double dq = 0.0, dv = 0.0, dsum = 0.0;  // lane i < dof: deviation of joint i
+    bool viol = false;
+    auto check = [&](int k) {  // lane i < dof: state entries i and dof + i of step k
+        if (!P.any_limits || lane >= dof) return;
+        for (int t = 0; t < P.n_tasks; t++) {
+            const DevTask& tk = P.tasks[t];
+            if (!tk.limits_set) continue;
+            bool a0, a1;
+            const double xq = Xb[(size_t)k * ns + lane];
+            limit_q(tk, lane, xq, a0);
+            limit_q(tk, lane, xq + dq, a1);
+            viol = viol || a0 || a1;
+            if (P.nb_deriv == 2) {
+                const double xv = Xb[(size_t)k * ns + dof + lane];
+                limit_q(tk, dof + lane, xv, a0);
+                limit_q(tk, dof + lane, xv + dv, a1);
+                viol = viol || a0 || a1;
+            }
+        }
+    };
+    double kcur[N], knext[N];
+    if (lane < m) {
+#pragma unroll
+        for (int j = 0; j < N; j++) kcur[j] = (j < n) ? __ldcs(Kb + (size_t)lane * ns + j) : 0.0;
+    }
+    int sq = 0;  // next keypoint step index
+    if (S > 0 && P.kp_steps[0] == 0) {
+        for (int j = lane; j < ns; j += 32) sKX[j] = 0.0;
+        sq = 1;
+    }
+    check(0);
+    __syncwarp();
+    for (int k = 0; k < H - 1; k++) {
+        const double* cur = sX2 + (k & 1) * ns;
+        double* nxt = sX2 + ((k + 1) & 1) * ns;
+        double du = 0.0;
+        if (lane < m) {
+            if (k + 1 < H - 1) {  // next step's gain row is in flight while this one is used
+                const double* Kn = Kb + ((size_t)(k + 1) * m + lane) * ns;
+#pragma unroll
+                for (int j = 0; j < N; j++) knext[j] = (j < n) ? __ldcs(Kn + j) : 0.0;
+                if (k + 9 < H - 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(Kb + ((size_t)(k + 9) * m + lane) * ns));
+            }
+            double acc = 0.0;
+#pragma unroll
+            for (int j = 0; j < N; j++)
+                if (j < n) acc += kcur[j] * cur[j];
+            du = acc + db[(size_t)k * ms + lane];
+            sDU[(size_t)k * ms + lane] = du;
+#pragma unroll
+            for (int j = 0; j < N; j++) kcur[j] = knext[j];
+        } else if (lane < ms) {
+            sDU[(size_t)k * ms + lane] = 0.0;
+        }
+        double nrm2 = du * du;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) nrm2 += __shfl_xor_sync(FULL, nrm2, o);
+        dsum += sqrt(nrm2);
+        if (lane < dof) {
+            if (P.nb_deriv == 1) {
+                dq = __dadd_rn(dq, __dmul_rn(dt, du));
+                nxt[lane] = dq;
+            } else {
+                dq = __dadd_rn(dq, __dadd_rn(__dmul_rn(dt, dv), __dmul_rn(hdt2, du)));
+                dv = __dadd_rn(dv, __dmul_rn(dt, du));
+                nxt[lane] = dq;
+                nxt[dof + lane] = dv;
+            }
+        }
+        check(k + 1);
+        __syncwarp();
+        if (sq < S && P.kp_steps[sq] == k + 1) {
+            for (int j = lane; j < ns; j += 32) sKX[(size_t)sq * ns + j] = nxt[j];
+            sq++;
+        }
+    }
+    viol = __any_sync(FULL, viol);
+    __syncwarp();
+    // ---- phase B: candidate costs -----------------------------------------------------------------------------------------
+    // no limit violated: only keypoint steps cost anything; lane = (keypoint step, candidate) pair, summed per candidate in
+    // step order (the other steps add exact zeros in the reference's running sum).  Otherwise lane = candidate walks every
+    // step, re-integrating its deviation from du.
+    const bool mine = lane < NCAND && (line_search || lane == 0);
+    auto cost_at = [&](int k, double alpha, const double* dx) -> double {
+        const double* Xk = Xb + (size_t)k * ns;
+        double x[N], u[M];
+#pragma unroll
+        for (int j = 0; j < N; j++) x[j] = (j < n) ? __dadd_rn(Xk[j], __dmul_rn(alpha, dx[j])) : 0.0;
+        if (k < H - 1) {
+            const double* Uk = W.U + ((size_t)b * (H - 1) + k) * ms;
+#pragma unroll
+            for (int i = 0; i < M; i++) u[i] = (i < m) ? __dadd_rn(Uk[i], __dmul_rn(alpha, sDU[(size_t)k * ms + i])) : 0.0;
+        }
+        return stage_cost<N>(P, b, x, k < H - 1 ? u : nullptr, k);
+    };
+    double cost = 0.0;
+    if (!viol) {
+        const int ncand = line_search ? NCAND : 1;
+        for (int p = lane; p < S * ncand; p += 32) {
+            const int q = p / ncand, c = p % ncand;
+            sCk[q * NCAND + c] = cost_at(P.kp_steps[q], alpha_of(c), sKX + (size_t)q * ns);
+        }
+        __syncwarp();
+        if (mine)
+            for (int q = 0; q < S; q++) cost += sCk[q * NCAND + lane];
+    } else if (mine) {
+        double dx[N];
+#pragma unroll
+        for (int j = 0; j < N; j++) dx[j] = 0.0;
+        for (int k = 0; k < H; k++) {
+            cost += cost_at(k, alpha_of(lane), dx);
+            if (k < H - 1) {
+#pragma unroll
+                for (int i = 0; i < N / 2; i++)
+                    if (i < dof) {
+                        const double du = sDU[(size_t)k * ms + i];
+                        if (P.nb_deriv == 1) {
+                            dx[i] = __dadd_rn(dx[i], __dmul_rn(dt, du));
+                        } else {
+                            dx[i] = __dadd_rn(dx[i], __dadd_rn(__dmul_rn(dt, dx[dof + i]), __dmul_rn(hdt2, du)));
+                            dx[dof + i] = __dadd_rn(dx[dof + i], __dmul_rn(dt, du));
+                        }
+                    }
+            }
+        }
+    }
+    if (mine) {
+        W.cost_c[(size_t)b * NCAND + lane] = cost;
+        W.dun_c[(size_t)b * NCAND + lane] = alpha_of(lane) * dsum;
+    }
+    // ---- selection (the rule of k_accept) and the selected candidate's controls -------------------------------------------
+    const double cost0 = W.cost0[b];
+    const bool good = mine && !((cost >= cost0) || isnan(cost));
+    const unsigned okm = __ballot_sync(FULL, good);
+    int sel = 0;
+    if (line_search) sel = okm ? (__ffs(okm) - 1) : NCAND - 1;
+    const double asel = alpha_of(sel);
+    for (int e = lane; e < (H - 1) * ms; e += 32) {
+        const int k = e / ms, i = e % ms;
+        const size_t bk = (size_t)b * (H - 1) + k;
+        W.Uc[(bk * NCAND + sel) * ms + i] = (i < m) ? __dadd_rn(W.U[bk * ms + i], __dmul_rn(asel, sDU[e])) : 0.0;
+    }
+}
+
 // AL: constraint values and active set of the current trajectory (AL-ILQR.cpp:21-44,71-73,189-191) and, when `upd`,
 // the multiplier update lambda = max(0, lambda + penalty * C) (AL-ILQR.cpp:202-208).  One warp per problem.
 __device__ __forceinline__ void al_constraints(const DevProblem& P, const Work& W, int b, int lane, bool upd, double penalty_next) {
