@@ -462,7 +462,7 @@ int launch_linesearch(ilqrb_handle h, int line_search, bool al) {
     h->begin(PS_LINESEARCH);
     static const bool force_generic = getenv("ILQRB_GENERIC") != nullptr;
     const size_t need = 4 * (size_t)ls_affine_smem_doubles(h->hp.H, h->W.ns, h->W.ms) * sizeof(double);
-    if (!force_generic && !al && !h->hp.time && need <= 200 * 1024) {
+    if (!force_generic && !al && !h->hp.time && h->hp.m <= 8 && need <= 200 * 1024) {
         int rc = 0;
 #define CALL(N, M) rc = launch_linesearch_affine_t<N, M>(h, line_search)
         DISPATCH_NM(size_class(h->hp.n, h->hp.m), CALL)

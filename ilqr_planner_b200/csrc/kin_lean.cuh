@@ -189,6 +189,78 @@ __device__ __forceinline__ void lean_task_eval(const DevProblem& P, const DevTas
     Jc[5] = Jw[2];
 }
 
+// FK sweep that also accumulates the tip twist of joint rates dq(j) without forming the Jacobian:
+//   w = sum_j dq_j z_j (ROT) ,  v = w x p_tip - sum_j dq_j (z_j x o_j) + sum_j dq_j z_j (TRANS)
+// which is J dq with the closed-form columns above (KDLRobot.cpp:104-105: dx = Jt dq, w = Jr dq).
+template <class QF, class DQF>
+__device__ __forceinline__ void lean_kdl_fk_twist(const ilqrb_segment* __restrict__ segs, int nseg, QF q, DQF dq, double* p, double* R, double* v, double* w) {
+    double TR[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, Tp[3] = {0, 0, 0};
+    double ws[3] = {0, 0, 0}, ms[3] = {0, 0, 0}, ls[3] = {0, 0, 0};
+    int j = 0;
+    for (int s = 0; s < nseg; s++) {
+        const ilqrb_segment& sg = segs[s];
+        const int jt = sg.joint_type;
+        double ps[3] = {sg.tip_p[0], sg.tip_p[1], sg.tip_p[2]};
+        if (jt != ILQRB_JOINT_FIXED) {
+            const double ax[3] = {sg.axis[0], sg.axis[1], sg.axis[2]};
+            const double og[3] = {sg.origin[0], sg.origin[1], sg.origin[2]};
+            double z[3], o3[3];
+            mat3_vec(TR, ax, z);
+            mat3_vec(TR, og, o3);
+            o3[0] += Tp[0];
+            o3[1] += Tp[1];
+            o3[2] += Tp[2];
+            const double qj = q(j), dqj = dq(j);
+            if (jt == ILQRB_JOINT_ROT) {
+                double zo[3];
+                cross3(z, o3, zo);
+                for (int a = 0; a < 3; a++) {
+                    ws[a] += dqj * z[a];
+                    ms[a] += dqj * zo[a];
+                }
+                double Rj[9], t3[3];
+                kdl_rot2(ax, qj, Rj);
+                mat3_vec(Rj, ps, t3);
+                ps[0] = t3[0] + og[0];
+                ps[1] = t3[1] + og[1];
+                ps[2] = t3[2] + og[2];
+                double w3[3];
+                mat3_vec(TR, ps, w3);
+                Tp[0] += w3[0];
+                Tp[1] += w3[1];
+                Tp[2] += w3[2];
+                mat3_rmul_inplace(TR, Rj);
+            } else {
+                for (int a = 0; a < 3; a++) ls[a] += dqj * z[a];
+                ps[0] += og[0] + ax[0] * qj;
+                ps[1] += og[1] + ax[1] * qj;
+                ps[2] += og[2] + ax[2] * qj;
+                double w3[3];
+                mat3_vec(TR, ps, w3);
+                Tp[0] += w3[0];
+                Tp[1] += w3[1];
+                Tp[2] += w3[2];
+            }
+            j++;
+        } else {
+            double w3[3];
+            mat3_vec(TR, ps, w3);
+            Tp[0] += w3[0];
+            Tp[1] += w3[1];
+            Tp[2] += w3[2];
+        }
+        mat3_rmul_inplace(TR, sg.tip_R);
+    }
+    for (int i = 0; i < 9; i++) R[i] = TR[i];
+    double wp[3];
+    cross3(ws, Tp, wp);
+    for (int a = 0; a < 3; a++) {
+        p[a] = Tp[a];
+        w[a] = ws[a];
+        v[a] = wp[a] - ms[a] + ls[a];
+    }
+}
+
 // d^T Q d of task tk at keypoint kp for task vector fx   (System.cpp:216-220)
 __device__ __forceinline__ double lean_task_cost(const DevProblem& P, const DevTask& tk, int b, int kp, const double* fx, double* res) {
     const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
@@ -202,6 +274,77 @@ __device__ __forceinline__ double lean_task_cost(const DevProblem& P, const DevT
         dQd += v * res[j];
     }
     return dQd;
+}
+
+// System::cost at timestep k (System.cpp:213-234) like kin.cuh stage_cost, with the lean sweeps for KDL robots under a
+// PosOrn(-Time) system (1st and 2nd order); anything else goes to stage_cost.  x: state (n), u: control or nullptr.
+template <int N>
+__device__ __forceinline__ double lean_stage_cost(const DevProblem& P, int b, const double* x, const double* u, int k) {
+    bool lean_ok = P.sys_kind != ILQRB_SYS_POSITION;
+    for (int t = 0; t < P.n_tasks; t++) lean_ok = lean_ok && P.robots[P.tasks[t].robot].kind == ILQRB_ROBOT_KDL;
+    if (!lean_ok) return stage_cost<N>(P, b, x, u, k);
+    double total = 0;
+    const int dof = P.dof;
+    for (int t = 0; t < P.n_tasks; t++) {
+        const DevTask& tk = P.tasks[t];
+        double c = 0;
+        const int kp = task_kp_at(tk, k);
+        if (kp >= 0) {
+            const DevRobot& rb = P.robots[tk.robot];
+            const double* qb = x + tk.joint_offset;
+            const double* vb = x + dof + tk.joint_offset;
+            const bool second = P.nb_deriv == 2;
+            double p[3], R[9], v[3], w[3], quat[4];
+            lean_kdl_fk_twist(rb.lean, rb.n_lean, [&](int j) { return qb[j]; }, [&](int j) { return second ? vb[j] : 0.0; }, p, R, v, w);
+            kdl_get_quaternion(R, quat);
+            if (tk.has_transform) {  // TransformedSimulationInterface.cpp:53-103
+                const double* T = tk.T;
+                const double Rt[9] = {T[0], T[1], T[2], T[4], T[5], T[6], T[8], T[9], T[10]};
+                const double dd[3] = {p[0] - T[3], p[1] - T[7], p[2] - T[11]};
+                double o3[3];
+                mat3T_vec(Rt, dd, o3);
+                p[0] = o3[0], p[1] = o3[1], p[2] = o3[2];
+                double Rb[9], Rd[9];
+                eig_quat_to_rot(quat, Rb);
+                const double RtT[9] = {Rt[0], Rt[3], Rt[6], Rt[1], Rt[4], Rt[7], Rt[2], Rt[5], Rt[8]};
+                mat3_mul(RtT, Rb, Rd);
+                eig_rot_to_quat(Rd, quat);
+                mat3T_vec(Rt, v, o3);
+                v[0] = o3[0], v[1] = o3[1], v[2] = o3[2];
+                mat3T_vec(Rt, w, o3);
+                w[0] = o3[0], w[1] = o3[1], w[2] = o3[2];
+            }
+            double fx[MAX_NTT], res[MAX_RT];
+            fx[0] = p[0], fx[1] = p[1], fx[2] = p[2];
+            fx[3] = quat[0], fx[4] = quat[1], fx[5] = quat[2], fx[6] = quat[3];
+            int o = 7;
+            if (second) {  // SimulationInterface::getEEAngVelQuat = (.5 * H(quat)^T) * w   (SimulationInterface.cpp:69-73)
+                fx[7] = v[0], fx[8] = v[1], fx[9] = v[2];
+                fx[10] = (.5 * -quat[1]) * w[0] + (.5 * -quat[2]) * w[1] + (.5 * -quat[3]) * w[2];
+                fx[11] = (.5 * quat[0]) * w[0] + (.5 * quat[3]) * w[1] + (.5 * -quat[2]) * w[2];
+                fx[12] = (.5 * -quat[3]) * w[0] + (.5 * quat[0]) * w[1] + (.5 * quat[1]) * w[2];
+                fx[13] = (.5 * quat[2]) * w[0] + (.5 * -quat[1]) * w[1] + (.5 * quat[0]) * w[2];
+                o = 14;
+            }
+            if (P.time) fx[o] = x[P.n - 1];
+            c += lean_task_cost(P, tk, b, kp, fx, res);
+            double uRu = 0;
+            if (u)
+                for (int j = 0; j < P.m; j++) uRu += (u[j] * tk.r_diag[j]) * u[j];
+            c = c + uRu;
+        }
+        if (tk.limits_set) {
+            double qLq = 0;
+            for (int i = 0; i < P.n; i++) {
+                bool act;
+                double qi = limit_q(tk, i, x[i], act);
+                if (act) qLq += (qi * 1.0) * qi;
+            }
+            c += qLq;
+        }
+        total += c;
+    }
+    return total;
 }
 
 }  // namespace ilqrb

@@ -8,6 +8,7 @@
 //   k_final_fx       f(X) of the returned trajectory                 ILQRRecursive.cpp:37,51 (f_X)
 #pragma once
 #include "kin.cuh"
+#include "kin_lean.cuh"
 #include "wmat.cuh"
 
 namespace ilqrb {
@@ -251,7 +252,7 @@ __global__ void __launch_bounds__(128) k_linesearch(const DevProblem* __restrict
 __host__ __device__ inline int ls_affine_smem_doubles(int H, int ns, int ms) { return (H - 1) * ms + (MAX_KP_STEPS + 2) * ns + MAX_KP_STEPS * NCAND; }
 
 template <int N, int M>
-__global__ void __launch_bounds__(128, 4) k_linesearch_affine(const DevProblem* __restrict__ Pp, Work W, int line_search) {
+__global__ void __launch_bounds__(128, 3) k_linesearch_affine(const DevProblem* __restrict__ Pp, Work W, int line_search) {
     extern __shared__ double ls_smem[];
     constexpr unsigned FULL = 0xffffffffu;
     const DevProblem& P = *Pp;
@@ -270,83 +271,111 @@ __global__ void __launch_bounds__(128, 4) k_linesearch_affine(const DevProblem* 
     const double* Xb = W.X + (size_t)b * H * ns;
 
     // ---- phase A: deviation rollout; limits checked on the fly at both ends of every segment --------------------------
+    // lane (g, t) = (control row g, quarter t of the state columns): 4 lanes form one dot product, lane (i, 0) owns joint i
+    // (its deviation, its limits).  Gains, d and X rows run through 4-deep register rings so that no global load sits on
+    // the serial chain.
+    constexpr int PER = N / 4, PF = 4;
+    const int g = lane >> 2, t = lane & 3;
+    const bool rowl = g < m, owner = rowl && t == 0 && g < dof;
     for (int j = lane; j < 2 * ns; j += 32) sX2[j] = 0.0;
-    double dq = 0.0, dv = 0.0, dsum = 0.0;  // lane i < dof: deviation of joint i
+    double dq = 0.0, dv = 0.0;
     bool viol = false;
-    auto check = [&](int k) {  // lane i < dof: state entries i and dof + i of step k
-        if (!P.any_limits || lane >= dof) return;
-        for (int t = 0; t < P.n_tasks; t++) {
-            const DevTask& tk = P.tasks[t];
-            if (!tk.limits_set) continue;
-            bool a0, a1;
-            const double xq = Xb[(size_t)k * ns + lane];
-            limit_q(tk, lane, xq, a0);
-            limit_q(tk, lane, xq + dq, a1);
-            viol = viol || a0 || a1;
-            if (P.nb_deriv == 2) {
-                const double xv = Xb[(size_t)k * ns + dof + lane];
-                limit_q(tk, dof + lane, xv, a0);
-                limit_q(tk, dof + lane, xv + dv, a1);
-                viol = viol || a0 || a1;
+    // limits of the first limit-carrying task in registers (weight 0 -> +-inf); more than one such task: slow loop
+    int l0 = -1, l1 = -1;
+    if (P.any_limits)
+        for (int ti = P.n_tasks - 1; ti >= 0; ti--)
+            if (P.tasks[ti].limits_set) {
+                l1 = l0;
+                l0 = ti;
             }
-        }
-    };
-    double kcur[N], knext[N];
-    if (lane < m) {
-#pragma unroll
-        for (int j = 0; j < N; j++) kcur[j] = (j < n) ? __ldcs(Kb + (size_t)lane * ns + j) : 0.0;
+    double qmx = INFINITY, qmn = -INFINITY, vmx = INFINITY, vmn = -INFINITY;
+    if (l0 >= 0 && owner) {
+        const DevTask& tk = P.tasks[l0];
+        if (tk.limit_weight[g] != 0) qmx = tk.state_max[g], qmn = tk.state_min[g];
+        if (P.nb_deriv == 2 && tk.limit_weight[dof + g] != 0) vmx = tk.state_max[dof + g], vmn = tk.state_min[dof + g];
     }
+    auto check = [&](int k, double xq, double xv) {  // owner lanes: state entries g and dof + g of step k
+        if (l0 < 0 || !owner) return;
+        viol = viol || xq > qmx || xq < qmn || xq + dq > qmx || xq + dq < qmn;
+        if (P.nb_deriv == 2) viol = viol || xv > vmx || xv < vmn || xv + dv > vmx || xv + dv < vmn;
+        if (l1 >= 0)
+            for (int ti = l1; ti < P.n_tasks; ti++) {
+                const DevTask& tk = P.tasks[ti];
+                if (!tk.limits_set) continue;
+                bool a0, a1;
+                limit_q(tk, g, xq, a0);
+                limit_q(tk, g, xq + dq, a1);
+                viol = viol || a0 || a1;
+                if (P.nb_deriv == 2) {
+                    limit_q(tk, dof + g, xv, a0);
+                    limit_q(tk, dof + g, xv + dv, a1);
+                    viol = viol || a0 || a1;
+                }
+            }
+    };
+    double kr[PF][PER], dr[PF], xqr[PF], xvr[PF];
+    auto fetch = [&](int slot, int k) {  // operands of step k: gain row piece, d_g, X_{k+1} entries of the owner
+#pragma unroll
+        for (int j = 0; j < PER; j++) kr[slot][j] = (rowl && k < H - 1 && PER * t + j < n) ? __ldcs(Kb + ((size_t)k * m + g) * ns + PER * t + j) : 0.0;
+        dr[slot] = (rowl && t == 0 && k < H - 1) ? db[(size_t)k * ms + g] : 0.0;
+        xqr[slot] = (owner && l0 >= 0 && k < H - 1) ? Xb[(size_t)(k + 1) * ns + g] : 0.0;
+        xvr[slot] = (owner && l0 >= 0 && k < H - 1 && P.nb_deriv == 2) ? Xb[(size_t)(k + 1) * ns + dof + g] : 0.0;
+    };
+#pragma unroll
+    for (int r = 0; r < PF; r++) fetch(r, r);
     int sq = 0;  // next keypoint step index
     if (S > 0 && P.kp_steps[0] == 0) {
         for (int j = lane; j < ns; j += 32) sKX[j] = 0.0;
         sq = 1;
     }
-    check(0);
+    if (owner && l0 >= 0) check(0, Xb[g], P.nb_deriv == 2 ? Xb[dof + g] : 0.0);
     __syncwarp();
-    for (int k = 0; k < H - 1; k++) {
-        const double* cur = sX2 + (k & 1) * ns;
-        double* nxt = sX2 + ((k + 1) & 1) * ns;
-        double du = 0.0;
-        if (lane < m) {
-            if (k + 1 < H - 1) {  // next step's gain row is in flight while this one is used
-                const double* Kn = Kb + ((size_t)(k + 1) * m + lane) * ns;
+    for (int k0 = 0; k0 < H - 1; k0 += PF) {
 #pragma unroll
-                for (int j = 0; j < N; j++) knext[j] = (j < n) ? __ldcs(Kn + j) : 0.0;
-                if (k + 9 < H - 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(Kb + ((size_t)(k + 9) * m + lane) * ns));
+        for (int r = 0; r < PF; r++) {
+            const int k = k0 + r;
+            if (k < H - 1) {  // warp-uniform
+                const double* cur = sX2 + (k & 1) * ns;
+                double* nxt = sX2 + ((k + 1) & 1) * ns;
+                double acc = 0.0;
+#pragma unroll
+                for (int j = 0; j < PER; j++) acc += kr[r][j] * ((PER * t + j < n) ? cur[PER * t + j] : 0.0);
+                acc += __shfl_xor_sync(FULL, acc, 1);
+                acc += __shfl_xor_sync(FULL, acc, 2);
+                const double du = acc + dr[r];
+                const double xq = xqr[r], xv = xvr[r];
+                if (k + 8 < H - 1 && rowl) asm volatile("prefetch.global.L2 [%0];" ::"l"(Kb + ((size_t)(k + 8) * m + g) * ns + PER * t));
+                fetch(r, k + PF);
+                if (t == 0 && g < ms) sDU[(size_t)k * ms + g] = rowl ? du : 0.0;
+                if (owner) {
+                    if (P.nb_deriv == 1) {
+                        dq = __dadd_rn(dq, __dmul_rn(dt, du));
+                        nxt[g] = dq;
+                    } else {
+                        dq = __dadd_rn(dq, __dadd_rn(__dmul_rn(dt, dv), __dmul_rn(hdt2, du)));
+                        dv = __dadd_rn(dv, __dmul_rn(dt, du));
+                        nxt[g] = dq;
+                        nxt[dof + g] = dv;
+                    }
+                    check(k + 1, xq, xv);
+                }
+                __syncwarp();
+                if (sq < S && P.kp_steps[sq] == k + 1) {
+                    for (int j = lane; j < ns; j += 32) sKX[(size_t)sq * ns + j] = nxt[j];
+                    sq++;
+                }
             }
-            double acc = 0.0;
-#pragma unroll
-            for (int j = 0; j < N; j++)
-                if (j < n) acc += kcur[j] * cur[j];
-            du = acc + db[(size_t)k * ms + lane];
-            sDU[(size_t)k * ms + lane] = du;
-#pragma unroll
-            for (int j = 0; j < N; j++) kcur[j] = knext[j];
-        } else if (lane < ms) {
-            sDU[(size_t)k * ms + lane] = 0.0;
-        }
-        double nrm2 = du * du;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) nrm2 += __shfl_xor_sync(FULL, nrm2, o);
-        dsum += sqrt(nrm2);
-        if (lane < dof) {
-            if (P.nb_deriv == 1) {
-                dq = __dadd_rn(dq, __dmul_rn(dt, du));
-                nxt[lane] = dq;
-            } else {
-                dq = __dadd_rn(dq, __dadd_rn(__dmul_rn(dt, dv), __dmul_rn(hdt2, du)));
-                dv = __dadd_rn(dv, __dmul_rn(dt, du));
-                nxt[lane] = dq;
-                nxt[dof + lane] = dv;
-            }
-        }
-        check(k + 1);
-        __syncwarp();
-        if (sq < S && P.kp_steps[sq] == k + 1) {
-            for (int j = lane; j < ns; j += 32) sKX[(size_t)sq * ns + j] = nxt[j];
-            sq++;
         }
     }
+    // sum_k |du_k| of the alpha = 1 candidate (early-stop test of k_accept)
+    double dsum = 0.0;
+    for (int k = lane; k < H - 1; k += 32) {
+        double nrm2 = 0.0;
+        for (int i = 0; i < m; i++) nrm2 += sDU[(size_t)k * ms + i] * sDU[(size_t)k * ms + i];
+        dsum += sqrt(nrm2);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dsum += __shfl_xor_sync(FULL, dsum, o);
     viol = __any_sync(FULL, viol);
     __syncwarp();
     // ---- phase B: candidate costs -----------------------------------------------------------------------------------------
@@ -364,7 +393,7 @@ __global__ void __launch_bounds__(128, 4) k_linesearch_affine(const DevProblem* 
 #pragma unroll
             for (int i = 0; i < M; i++) u[i] = (i < m) ? __dadd_rn(Uk[i], __dmul_rn(alpha, sDU[(size_t)k * ms + i])) : 0.0;
         }
-        return stage_cost<N>(P, b, x, k < H - 1 ? u : nullptr, k);
+        return lean_stage_cost<N>(P, b, x, k < H - 1 ? u : nullptr, k);
     };
     double cost = 0.0;
     if (!viol) {
