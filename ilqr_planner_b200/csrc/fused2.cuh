@@ -64,8 +64,8 @@ __device__ __forceinline__ void st_w(double* M, const double (&e)[2][2], int g, 
     for (int c = 0; c < 2; c++) *reinterpret_cast<double2*>(M + g * BwdN2Smem::LDW + 8 * c + 2 * t) = make_double2(e[c][0], e[c][1]);
 }
 
-template <int DOF>
-__device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work& W, int b, int lane, double* wsmem) {
+template <int DOF, bool AL>
+__device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work& W, int b, int lane, double* wsmem, double penalty_frozen) {
     using S = BwdN2Smem;
     const int g = lane >> 2, t = lane & 3;
     const int dof = DOF > 0 ? DOF : P.dof, n = 2 * dof, m = dof, H = P.H;
@@ -168,6 +168,54 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
             Qx[0][1][h] = __dadd_rn(__dmul_rn(Pa[0][0][h], dt), Pa[0][1][h]);
             Qx[1][1][h] = __dadd_rn(__dmul_rn(n20, dt), n21);
         }
+        if (AL) {
+            // AL terms (AL-ILQR.cpp:116-134): rows r of the active set add Ik_r a_r a_r^T to the Hessian blocks and a_r (lambda_r + Ik_r c_r)
+            // to the gradients, a_r = [ckx_r cku_r], Ik_r = penalty.  Inactive rows contribute exact zeros (lambda = 0 there), so the
+            // sums run over the set bits only; each sum is formed on its own and then added, as the reference's products are.
+            const size_t bk = (size_t)b * (H - 1) + k;
+            const int nc = W.nc, nsu = n + m;
+            const double* Ac = W.alA + (size_t)(W.al_per_step ? k : 0) * nc * nsu;
+            unsigned bits = W.mask[bk];
+            if (bits) {
+                double Gxx[2][2][2] = {{{0, 0}, {0, 0}}, {{0, 0}, {0, 0}}}, Gux[2][2] = {{0, 0}, {0, 0}}, Guu[2] = {0, 0}, Gxu[2][2] = {{0, 0}, {0, 0}};
+                while (bits) {
+                    const int r = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    const double* a = Ac + (size_t)r * nsu;
+                    const double lic = W.lam[bk * nc + r] + penalty_frozen * W.Cs[bk * nc + r];
+                    const double aur = rowv ? a[n + g] : 0.0;
+                    const double axr[2] = {rowv ? a[g] : 0.0, rowv ? a[dof + g] : 0.0};
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        const int jl = 2 * t + h;
+                        const bool cv = jl < dof;
+                        const double ac0 = cv ? a[jl] : 0.0, ac1 = cv ? a[dof + jl] : 0.0, auc = cv ? a[n + jl] : 0.0;
+                        Gux[0][h] += (aur * penalty_frozen) * ac0;
+                        Gux[1][h] += (jl == 7) ? aur * lic : (aur * penalty_frozen) * ac1;
+                        Guu[h] += (aur * penalty_frozen) * auc;
+#pragma unroll
+                        for (int rr = 0; rr < 2; rr++) {
+                            Gxx[rr][0][h] += (axr[rr] * penalty_frozen) * ac0;
+                            Gxx[rr][1][h] += (jl == 7) ? axr[rr] * lic : (axr[rr] * penalty_frozen) * ac1;
+                            Gxu[rr][h] += (axr[rr] * penalty_frozen) * auc;
+                        }
+                    }
+                }
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    Qa[0][h] += Gux[0][h];
+                    Qa[1][h] += Gux[1][h];
+                    Quu[h] += Guu[h];
+                    Lr[h] = (2 * t + h == g) ? (rowv ? Quu[h] + 1e-6 * 1.0 : 1.0) : Quu[h];
+#pragma unroll
+                    for (int rr = 0; rr < 2; rr++) {
+                        Qx[rr][0][h] += Gxx[rr][0][h];
+                        Qx[rr][1][h] += Gxx[rr][1][h];
+                        Qxu[rr][h] += Gxu[rr][h];
+                    }
+                }
+            }
+        }
         if (k == next_kp) {
             add_kp(Qx, sp);
             sp--;
@@ -247,15 +295,15 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
     if (!spd && lane == 0) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
 }
 
-template <int DOF, int WARPS, int MINB>
-__global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n2(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
+template <int DOF, bool AL, int WARPS, int MINB>
+__global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n2(const DevProblem* __restrict__ Pp, Work W, int b0, int nB, double penalty_frozen) {
     extern __shared__ double smem[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int bl = blockIdx.x * WARPS + wid;
     if (bl >= nB) return;
     const int b = b0 + bl;
     if (W.done[b]) return;
-    backward_n2_body<DOF>(*Pp, W, b, lane, smem + (size_t)wid * BwdN2Smem::PER_WARP);
+    backward_n2_body<DOF, AL>(*Pp, W, b, lane, smem + (size_t)wid * BwdN2Smem::PER_WARP, penalty_frozen);
 }
 
 }  // namespace ilqrb

@@ -239,25 +239,29 @@ int launch_backward_ta(ilqrb_handle h, double pf) {
 bool fast_n2_applies(ilqrb_handle h, bool al) {
     static const bool force_generic = getenv("ILQRB_GENERIC") != nullptr;
     const DevProblem& P = h->hp;
-    return !force_generic && !al && !P.time && P.nb_deriv == 2 && P.dof <= 7 && P.n == 2 * P.dof && P.m == P.dof;
+    (void)al;
+    return !force_generic && !P.time && P.nb_deriv == 2 && P.dof <= 7 && P.n == 2 * P.dof && P.m == P.dof && h->W.nc <= 32;
 }
-template <int DOF, int WARPS, int MINB>
-int launch_backward_n2_t(ilqrb_handle h) {
+template <int DOF, bool AL, int WARPS, int MINB>
+int launch_backward_n2_t(ilqrb_handle h, double pf) {
     const size_t smem = (size_t)WARPS * BwdN2Smem::PER_WARP * sizeof(double);
-    auto kern = k_backward_n2<DOF, WARPS, MINB>;
+    auto kern = k_backward_n2<DOF, AL, WARPS, MINB>;
     static bool attr_set = false;
     if (!attr_set) {
         CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
     const int B = h->hp.B;
-    kern<<<(B + WARPS - 1) / WARPS, 32 * WARPS, smem, h->stream>>>(h->dp, h->W, 0, B);
+    kern<<<(B + WARPS - 1) / WARPS, 32 * WARPS, smem, h->stream>>>(h->dp, h->W, 0, B, pf);
     return 0;
 }
 int launch_backward(ilqrb_handle h, bool al, double pf) {
     h->begin(PS_BACKWARD);
     int rc;
-    if (fast_n2_applies(h, al)) rc = h->hp.dof == 7 ? launch_backward_n2_t<7, 4, 4>(h) : launch_backward_n2_t<0, 4, 4>(h);
+    if (fast_n2_applies(h, al)) {
+        if (al) rc = h->hp.dof == 7 ? launch_backward_n2_t<7, true, 4, 4>(h, pf) : launch_backward_n2_t<0, true, 4, 4>(h, pf);
+        else rc = h->hp.dof == 7 ? launch_backward_n2_t<7, false, 4, 4>(h, pf) : launch_backward_n2_t<0, false, 4, 4>(h, pf);
+    }
     else if (h->hp.time) rc = al ? launch_backward_ta<true, true>(h, pf) : launch_backward_ta<true, false>(h, pf);
     else rc = al ? launch_backward_ta<false, true>(h, pf) : launch_backward_ta<false, false>(h, pf);
     h->end();
@@ -462,7 +466,7 @@ int launch_linesearch(ilqrb_handle h, int line_search, bool al) {
     h->begin(PS_LINESEARCH);
     static const bool force_generic = getenv("ILQRB_GENERIC") != nullptr;
     const size_t need = 4 * (size_t)ls_affine_smem_doubles(h->hp.H, h->W.ns, h->W.ms) * sizeof(double);
-    if (!force_generic && !al && !h->hp.time && h->hp.m <= 8 && need <= 200 * 1024) {
+    if (!force_generic && !h->hp.time && h->hp.m <= 8 && need <= 200 * 1024) {  // AL line searches on the plain cost too
         int rc = 0;
 #define CALL(N, M) rc = launch_linesearch_affine_t<N, M>(h, line_search)
         DISPATCH_NM(size_class(h->hp.n, h->hp.m), CALL)
