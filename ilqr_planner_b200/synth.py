@@ -195,3 +195,26 @@ def config1(batch=1, horizon=50, dt=0.1, offset=0):
     R = np.ones(3) * 1e-5
     task = TaskSpec(kp_timestep=[horizon - 1], kp_target=tg, kp_precision=np.array([[Q]]), r_diag=R)
     return ProblemBatch(cabi.SYS_POSITION, 1, horizon, dt, 3, [RobotSpec(cabi.ROBOT_2D, 3, None, lengths)], [task], R, q0, np.zeros_like(q0))
+
+
+def config3_short(batch=16, horizon=60, dt=0.05, dof=5, offset=0, tight_limits=True):
+    """parity-test shape: the first `dof` joints of the chain, nb_deriv=2, soft joint limits tight enough to be violated
+    along the way (exercises the runtime-size double-integrator kernels and the exact limit path of the line search)"""
+    full = panda_chain()
+    segs, nj = [], 0
+    for sg in full:
+        segs.append(sg)
+        nj += int(sg["joint_type"] != cabi.JOINT_FIXED)
+        if nj == dof:
+            break
+    d = _draws(7, offset, offset + batch, [("q0", -0.4, 0.4, dof), ("t1", -0.6, 0.6, dof), ("t2", -0.6, 0.6, dof)])
+    q0 = PANDA_Q0[:dof] + d["q0"]
+    tg = _posorn_targets(segs, q0, [d["t1"], d["t2"]])
+    Q = np.diag([1, 1, 1, .1, .1, .1, 1, 1, 1, .1, .1, .1])
+    R = np.ones(dof) * 1e-4
+    span = 0.35 if tight_limits else 30.0
+    smax = np.concatenate([PANDA_Q0[:dof] + 0.4 + span, np.ones(dof) * (0.6 if tight_limits else 50.0)])
+    smin = np.concatenate([PANDA_Q0[:dof] - 0.4 - span, -np.ones(dof) * (0.6 if tight_limits else 50.0)])
+    task = TaskSpec(kp_timestep=[horizon // 2 - 1, horizon - 1], kp_target=tg, kp_precision=np.array([[Q, Q]]), r_diag=R, state_max=smax,
+                    state_min=smin, limit_weight=np.ones(2 * dof, dtype=np.int32))
+    return ProblemBatch(cabi.SYS_POS_ORN, 2, horizon, dt, dof, [RobotSpec(cabi.ROBOT_KDL, dof, segs)], [task], R, q0, np.zeros_like(q0))

@@ -315,3 +315,11 @@ def test_batch_ilqr_dual_task_vs_oracle(oracle_lib):
     from ilqr_planner_b200 import synth
     pb = synth.config5(batch=4, horizon=30)
     _check_batch(pb, None, 4, oracle_lib)
+
+
+def test_double_integrator_runtime_dof_and_active_limits(oracle_lib):
+    """5-joint chain, nb_deriv = 2: runtime-size kernels of the double-integrator path; with tight soft limits the line search
+    takes its exact per-step branch and the backward pass carries the limit terms"""
+    from ilqr_planner_b200 import synth
+    _check_recursive(synth.config3_short(batch=16, tight_limits=False), None, 6, oracle_lib)
+    _check_recursive(synth.config3_short(batch=16, tight_limits=True), None, 4, oracle_lib)
