@@ -60,17 +60,26 @@ __device__ __forceinline__ double fast_rcp(double x) {
     return y;
 }
 
+// exact power of two 2^(1022 - E) for x = f * 2^(E - 1023): x * pow2_unscale(x) lies in [0.5, 1)
+__device__ __forceinline__ double pow2_unscale(double x) { return __hiloint2double(0x7fd00000 - (__double2hiint(x) & 0x7ff00000), 0); }
+
 // Solve (L) X = Rr in registers, both (8NT)^2 matrices in accumulator layout: Gauss-Jordan elimination of the augmented
-// matrix [L | Rr] without pivoting and without row scaling (rows are divided by their diagonal once, at the end).
-// L = Quu + 1e-6 I in its leading m x m block (symmetric positive definite in normal operation) and identity outside;
-// replaces the PartialPivLU inverse and the two products of ILQRRecursive.cpp:89-91.  Pivot row / column / element
+// matrix [L | Rr] without pivoting.  L = Quu + 1e-6 I in its leading m x m block (symmetric positive definite in normal
+// operation) and identity outside; replaces the PartialPivLU inverse and the two products of ILQRRecursive.cpp:89-91.
+// Division-free form: stage k replaces row i by  s (p_kk row_i - l_ik row_k)  with s an exact power of two near 1/p_kk
+// (any row scaling leaves the solution unchanged; rows are divided by their diagonal once, at the end), so no reciprocal
+// sits on the pivot-to-pivot dependency chain: shuffle -> 2 multiplies -> fma per stage.  Pivot row / column / element
 // travel by warp shuffles; no shared memory, no barrier.  M > 0: m known at compile time.  On return Rr = L^-1 Rr.
-// Returns false if a pivot was <= 0, infinite or NaN.
+// Returns false if a pivot was <= 0, infinite or NaN (the scaling is positive, so pivot signs are those of the
+// unscaled elimination).
 template <int NT, int M>
 __device__ __forceinline__ bool gj_solve_regs(double (&L)[NT][NT][2], double (&Rr)[NT][NT][2], int m_rt, int g, int t) {
     constexpr unsigned FULL = 0xffffffffu;
     const int m = M > 0 ? M : m_rt;
     bool ok = true;
+    double rs[NT];  // scaling a row has received since its diagonal tile went dead (column tiles left of the pivot tile)
+#pragma unroll
+    for (int rt = 0; rt < NT; rt++) rs[rt] = 1.0;
 #pragma unroll
     for (int k = 0; k < 8 * NT; k++) {
         if (k < m) {  // warp-uniform (compile-time when M > 0)
@@ -90,17 +99,20 @@ __device__ __forceinline__ bool gj_solve_regs(double (&L)[NT][NT][2], double (&R
             for (int rt = 0; rt < NT; rt++) colk[rt] = __shfl_sync(FULL, L[rt][kt][kh], 4 * g + (kg >> 1));
             const int hi = __double2hiint(pkk);
             ok = ok && (hi > 0) && (hi < 0x7ff00000);
-            const double piv = fast_rcp(pkk);
+            const double sc = pow2_unscale(pkk);
+            const double a_all = pkk * sc;
 #pragma unroll
             for (int rt = 0; rt < NT; rt++) {
                 const bool prow = (rt == kt) && (g == kg);  // this lane owns row k: left as it is
-                const double f = prow ? 0.0 : colk[rt] * piv;
+                const double a = prow ? 1.0 : a_all;
+                const double c = prow ? 0.0 : colk[rt] * sc;
+                if (rt < kt) rs[rt] *= a;
 #pragma unroll
                 for (int ct = 0; ct < NT; ct++)
 #pragma unroll
                     for (int h = 0; h < 2; h++) {
-                        if (ct >= kt) L[rt][ct][h] = fma(-f, rl[ct][h], L[rt][ct][h]);
-                        Rr[rt][ct][h] = fma(-f, rr[ct][h], Rr[rt][ct][h]);
+                        if (ct >= kt) L[rt][ct][h] = fma(-c, rl[ct][h], a * L[rt][ct][h]);
+                        Rr[rt][ct][h] = fma(-c, rr[ct][h], a * Rr[rt][ct][h]);
                     }
             }
         }
@@ -109,12 +121,81 @@ __device__ __forceinline__ bool gj_solve_regs(double (&L)[NT][NT][2], double (&R
 #pragma unroll
     for (int rt = 0; rt < NT; rt++) {
         const double mine = (g & 1) ? L[rt][rt][1] : L[rt][rt][0];
-        const double dgi = __shfl_sync(FULL, mine, 4 * g + ((g >> 1) & 3));
+        const double dgi = __shfl_sync(FULL, mine, 4 * g + ((g >> 1) & 3)) * rs[rt];
         const double inv = fast_rcp(dgi);
 #pragma unroll
         for (int ct = 0; ct < NT; ct++) {
             Rr[rt][ct][0] *= inv;
             Rr[rt][ct][1] *= inv;
+        }
+    }
+    return ok;
+}
+
+// (L)^-1 in registers, in place: division-free Gauss-Jordan on [L | I] without pivoting, (8NT)^2 in accumulator layout.
+// L = Quu + 1e-6 I in its leading m x m block and identity outside; this is the explicit inverse the reference takes
+// (ILQRRecursive.cpp:89).  In-place storage: after stage k, column k of L is dead and its slots hold column k of the
+// right-hand block.  Stage k replaces row i by s (p_kk row_i - l_ik row_k), s an exact power of two near 1/p_kk, so every
+// row carries a scale: d_i (its diagonal, tracked per lane) for pivoted rows, the warp-uniform S for the others; rows are
+// divided by d_i at the end.  The shuffle/LSU data pipe bounds the backward kernels (ncu: l1tex__data_pipe_lsu_wavefronts
+// 83 %), so the pivot row travels through shared memory as one predicated 16-byte store per owner lane and one broadcast
+// 16-byte load per lane (1 wavefront each, against 4 for the shuffles), the pivot as a broadcast 8-byte load; only the
+// pivot-column element (quad-local) is shuffled.  sRow: (8NT) x LD scratch, row k used by stage k only.
+// Returns false if a pivot was <= 0, infinite or NaN.
+template <int NT, int M, int LD>
+__device__ __forceinline__ bool gj_inverse_regs(double (&Wm)[NT][NT][2], double* sRow, int m_rt, int g, int t) {
+    constexpr unsigned FULL = 0xffffffffu;
+    const int m = M > 0 ? M : m_rt;
+    bool ok = true;
+    double dg[NT], S = 1.0;
+#pragma unroll
+    for (int rt = 0; rt < NT; rt++) dg[rt] = 1.0;
+#pragma unroll
+    for (int k = 0; k < 8 * NT; k++) {
+        if (k < m) {  // warp-uniform (compile-time when M > 0)
+            const int kt = k >> 3, kg = k & 7, kh = k & 1;
+            if (g == kg) {
+#pragma unroll
+                for (int ct = 0; ct < NT; ct++) *reinterpret_cast<double2*>(sRow + k * LD + 8 * ct + 2 * t) = make_double2(Wm[kt][ct][0], Wm[kt][ct][1]);
+            }
+            __syncwarp();
+            double rk[NT][2], colk[NT];
+#pragma unroll
+            for (int ct = 0; ct < NT; ct++) {
+                const double2 v = *reinterpret_cast<const double2*>(sRow + k * LD + 8 * ct + 2 * t);
+                rk[ct][0] = v.x;
+                rk[ct][1] = v.y;
+            }
+            const double pkk = sRow[k * LD + k];
+#pragma unroll
+            for (int rt = 0; rt < NT; rt++) colk[rt] = __shfl_sync(FULL, Wm[rt][kt][kh], 4 * g + (kg >> 1));
+            const int hi = __double2hiint(pkk);
+            ok = ok && (hi > 0) && (hi < 0x7ff00000);
+            const double sc = pow2_unscale(pkk);
+            const double a_all = pkk * sc;
+            const bool kcol = (t == (kg >> 1));
+#pragma unroll
+            for (int rt = 0; rt < NT; rt++) {
+                const bool prow = (rt == kt) && (g == kg);  // this lane owns row k: left as it is
+                const double a = prow ? 1.0 : a_all;
+                const double c = prow ? 0.0 : colk[rt] * sc;
+                dg[rt] = prow ? pkk : dg[rt] * a_all;
+#pragma unroll
+                for (int ct = 0; ct < NT; ct++)
+#pragma unroll
+                    for (int h = 0; h < 2; h++) Wm[rt][ct][h] = fma(-c, rk[ct][h], a * Wm[rt][ct][h]);
+                if (kcol) Wm[rt][kt][kh] = prow ? S : -(c * S);  // column k of the right-hand block (its row k entry is the unpivoted-row scale)
+            }
+            S *= a_all;
+        }
+    }
+#pragma unroll
+    for (int rt = 0; rt < NT; rt++) {
+        const double inv = fast_rcp(dg[rt]);
+#pragma unroll
+        for (int ct = 0; ct < NT; ct++) {
+            Wm[rt][ct][0] *= inv;
+            Wm[rt][ct][1] *= inv;
         }
     }
     return ok;
@@ -296,16 +377,23 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
 
         st_c<NT, LD>(sQux, Qa, g, t);
         st_c<NT, LD>(sQuu, Qu2, g, t);
-        // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]                                            ILQRRecursive.cpp:89-91
+        // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]: explicit inverse, then the product on DMMA             ILQRRecursive.cpp:89-91
+        spd = gj_inverse_regs<NT, DOF, LD>(Inv, sKd, m, g, t) && spd;
+        st_c<NT, LD>(sM, Inv, g, t);
+        __syncwarp();
         double Kd[NT][NT][2];
 #pragma unroll
         for (int rt = 0; rt < NT; rt++)
 #pragma unroll
             for (int ct = 0; ct < NT; ct++) {
-                Kd[rt][ct][0] = -Qa[rt][ct][0];
-                Kd[rt][ct][1] = -Qa[rt][ct][1];
+                double c0 = 0.0, c1 = 0.0;
+#pragma unroll
+                for (int kt = 0; kt < NT; kt++)
+#pragma unroll
+                    for (int s = 0; s < 2; s++) dmma884(c0, c1, ld_a<LD>(sM, rt, kt, s, g, t), ld_b<LD>(sQux, kt, s, ct, g, t));
+                Kd[rt][ct][0] = -c0;
+                Kd[rt][ct][1] = -c1;
             }
-        spd = gj_solve_regs<NT, DOF>(Inv, Kd, m, g, t) && spd;
         st_c<NT, LD>(sKd, Kd, g, t);
         // stream K, d to global (time-forward index)
 #pragma unroll

@@ -16,7 +16,7 @@
 namespace ilqrb {
 
 // (L) X = [R0 R1] in registers: L one 8x8 tile (leading m x m block, identity outside), R two tiles side by side.
-// Gauss-Jordan without pivoting, rows divided by their diagonal at the end (see gj_solve_regs).
+// Division-free Gauss-Jordan without pivoting, rows divided by their diagonal at the end (see gj_solve_regs).
 template <int M>
 __device__ __forceinline__ bool gj_solve_1x2(double (&L)[2], double (&R)[2][2], int m_rt, int g, int t) {
     constexpr unsigned FULL = 0xffffffffu;
@@ -33,13 +33,15 @@ __device__ __forceinline__ bool gj_solve_1x2(double (&L)[2], double (&R)[2][2], 
             const double colk = __shfl_sync(FULL, L[kh], 4 * g + (k >> 1));
             const int hi = __double2hiint(pkk);
             ok = ok && (hi > 0) && (hi < 0x7ff00000);
-            const double f = (g == k) ? 0.0 : colk * fast_rcp(pkk);
-            L[0] = fma(-f, l0, L[0]);
-            L[1] = fma(-f, l1, L[1]);
-            R[0][0] = fma(-f, r00, R[0][0]);
-            R[0][1] = fma(-f, r01, R[0][1]);
-            R[1][0] = fma(-f, r10, R[1][0]);
-            R[1][1] = fma(-f, r11, R[1][1]);
+            const double sc = pow2_unscale(pkk);  // division-free stage: row_i <- sc (p_kk row_i - l_ik row_k)
+            const double a = (g == k) ? 1.0 : pkk * sc;
+            const double c = (g == k) ? 0.0 : colk * sc;
+            L[0] = fma(-c, l0, a * L[0]);
+            L[1] = fma(-c, l1, a * L[1]);
+            R[0][0] = fma(-c, r00, a * R[0][0]);
+            R[0][1] = fma(-c, r01, a * R[0][1]);
+            R[1][0] = fma(-c, r10, a * R[1][0]);
+            R[1][1] = fma(-c, r11, a * R[1][1]);
         }
     }
     const double mine = (g & 1) ? L[1] : L[0];
