@@ -92,7 +92,7 @@ def iptr(a):
 # every symbol include/ilqrb.h declares (tests/test_cabi_symbols.py checks the built library exports them all)
 SYMBOLS = [
     "ilqrb_abi_version", "ilqrb_last_error", "ilqrb_get_dims", "ilqrb_create", "ilqrb_destroy", "ilqrb_set_stream",
-    "ilqrb_synchronize", "ilqrb_update_problems", "ilqrb_solve_recursive", "ilqrb_solve_al", "ilqrb_solve_batch",
+    "ilqrb_synchronize", "ilqrb_update_problems", "ilqrb_solve_recursive", "ilqrb_solve_recursive_async", "ilqrb_solve_al", "ilqrb_solve_batch",
     "ilqrb_upload_u0", "ilqrb_run_recursive", "ilqrb_run_al", "ilqrb_run_batch", "ilqrb_download", "ilqrb_rollout",
     "ilqrb_kinematics", "ilqrb_set_profiling", "ilqrb_get_profile", "ilqrb_reset_profile", "ilqrb_launch_count",
     "ilqrb_chain_from_urdf", "ilqrb_build_psi",
@@ -122,6 +122,7 @@ def load():
     lib.ilqrb_synchronize.argtypes = [H]
     lib.ilqrb_update_problems.argtypes = [H, c_double_p, c_double_p, C.c_int, c_double_p]
     lib.ilqrb_solve_recursive.argtypes = [H, c_double_p, C.POINTER(SolveOpts), C.POINTER(Result)]
+    lib.ilqrb_solve_recursive_async.argtypes = [H, c_double_p, C.POINTER(SolveOpts), C.POINTER(Result)]
     lib.ilqrb_solve_al.argtypes = [H, c_double_p, C.POINTER(ALDesc), C.POINTER(SolveOpts), C.POINTER(Result)]
     lib.ilqrb_solve_batch.argtypes = [H, c_double_p, C.POINTER(BatchDesc), C.POINTER(SolveOpts), C.POINTER(Result)]
     lib.ilqrb_upload_u0.argtypes = [H, c_double_p]

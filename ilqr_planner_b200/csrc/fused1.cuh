@@ -63,76 +63,8 @@ __device__ __forceinline__ double fast_rcp(double x) {
 // exact power of two 2^(1022 - E) for x = f * 2^(E - 1023): x * pow2_unscale(x) lies in [0.5, 1)
 __device__ __forceinline__ double pow2_unscale(double x) { return __hiloint2double(0x7fd00000 - (__double2hiint(x) & 0x7ff00000), 0); }
 
-// Solve (L) X = Rr in registers, both (8NT)^2 matrices in accumulator layout: Gauss-Jordan elimination of the augmented
-// matrix [L | Rr] without pivoting.  L = Quu + 1e-6 I in its leading m x m block (symmetric positive definite in normal
-// operation) and identity outside; replaces the PartialPivLU inverse and the two products of ILQRRecursive.cpp:89-91.
-// Division-free form: stage k replaces row i by  s (p_kk row_i - l_ik row_k)  with s an exact power of two near 1/p_kk
-// (any row scaling leaves the solution unchanged; rows are divided by their diagonal once, at the end), so no reciprocal
-// sits on the pivot-to-pivot dependency chain: shuffle -> 2 multiplies -> fma per stage.  Pivot row / column / element
-// travel by warp shuffles; no shared memory, no barrier.  M > 0: m known at compile time.  On return Rr = L^-1 Rr.
-// Returns false if a pivot was <= 0, infinite or NaN (the scaling is positive, so pivot signs are those of the
-// unscaled elimination).
-template <int NT, int M>
-__device__ __forceinline__ bool gj_solve_regs(double (&L)[NT][NT][2], double (&Rr)[NT][NT][2], int m_rt, int g, int t) {
-    constexpr unsigned FULL = 0xffffffffu;
-    const int m = M > 0 ? M : m_rt;
-    bool ok = true;
-    double rs[NT];  // scaling a row has received since its diagonal tile went dead (column tiles left of the pivot tile)
-#pragma unroll
-    for (int rt = 0; rt < NT; rt++) rs[rt] = 1.0;
-#pragma unroll
-    for (int k = 0; k < 8 * NT; k++) {
-        if (k < m) {  // warp-uniform (compile-time when M > 0)
-            const int kt = k >> 3, kg = k & 7, kh = k & 1;
-            const double pkk = __shfl_sync(FULL, L[kt][kt][kh], 4 * kg + (kg >> 1));
-            double rl[NT][2], rr[NT][2], colk[NT];
-#pragma unroll
-            for (int ct = 0; ct < NT; ct++) {
-                if (ct >= kt) {  // columns left of the pivot tile are dead
-                    rl[ct][0] = __shfl_sync(FULL, L[kt][ct][0], 4 * kg + t);
-                    rl[ct][1] = __shfl_sync(FULL, L[kt][ct][1], 4 * kg + t);
-                }
-                rr[ct][0] = __shfl_sync(FULL, Rr[kt][ct][0], 4 * kg + t);
-                rr[ct][1] = __shfl_sync(FULL, Rr[kt][ct][1], 4 * kg + t);
-            }
-#pragma unroll
-            for (int rt = 0; rt < NT; rt++) colk[rt] = __shfl_sync(FULL, L[rt][kt][kh], 4 * g + (kg >> 1));
-            const int hi = __double2hiint(pkk);
-            ok = ok && (hi > 0) && (hi < 0x7ff00000);
-            const double sc = pow2_unscale(pkk);
-            const double a_all = pkk * sc;
-#pragma unroll
-            for (int rt = 0; rt < NT; rt++) {
-                const bool prow = (rt == kt) && (g == kg);  // this lane owns row k: left as it is
-                const double a = prow ? 1.0 : a_all;
-                const double c = prow ? 0.0 : colk[rt] * sc;
-                if (rt < kt) rs[rt] *= a;
-#pragma unroll
-                for (int ct = 0; ct < NT; ct++)
-#pragma unroll
-                    for (int h = 0; h < 2; h++) {
-                        if (ct >= kt) L[rt][ct][h] = fma(-c, rl[ct][h], a * L[rt][ct][h]);
-                        Rr[rt][ct][h] = fma(-c, rr[ct][h], a * Rr[rt][ct][h]);
-                    }
-            }
-        }
-    }
-    // divide every row by its diagonal entry: (i, i) lives in lane (g, g>>1), slot g&1 of tile [rt][rt]
-#pragma unroll
-    for (int rt = 0; rt < NT; rt++) {
-        const double mine = (g & 1) ? L[rt][rt][1] : L[rt][rt][0];
-        const double dgi = __shfl_sync(FULL, mine, 4 * g + ((g >> 1) & 3)) * rs[rt];
-        const double inv = fast_rcp(dgi);
-#pragma unroll
-        for (int ct = 0; ct < NT; ct++) {
-            Rr[rt][ct][0] *= inv;
-            Rr[rt][ct][1] *= inv;
-        }
-    }
-    return ok;
-}
-
-// (L)^-1 in registers, in place: division-free Gauss-Jordan on [L | I] without pivoting, (8NT)^2 in accumulator layout.
+// (L)^-1 in registers, in place: division-free Gauss-Jordan on [L | I] without pivoting, (8NT)^2 in accumulator layout
+// (any row scaling leaves the solution unchanged, so no reciprocal sits on the pivot-to-pivot dependency chain).
 // L = Quu + 1e-6 I in its leading m x m block and identity outside; this is the explicit inverse the reference takes
 // (ILQRRecursive.cpp:89).  In-place storage: after stage k, column k of L is dead and its slots hold column k of the
 // right-hand block.  Stage k replaces row i by s (p_kk row_i - l_ik row_k), s an exact power of two near 1/p_kk, so every
@@ -141,12 +73,11 @@ __device__ __forceinline__ bool gj_solve_regs(double (&L)[NT][NT][2], double (&R
 // 83 %), so the pivot row travels through shared memory as one predicated 16-byte store per owner lane and one broadcast
 // 16-byte load per lane (1 wavefront each, against 4 for the shuffles), the pivot as a broadcast 8-byte load; only the
 // pivot-column element (quad-local) is shuffled.  sRow: (8NT) x LD scratch, row k used by stage k only.
-// Returns false if a pivot was <= 0, infinite or NaN.
+// Returns (per lane, for its own rows) false if a pivot was <= 0, infinite or NaN.
 template <int NT, int M, int LD>
 __device__ __forceinline__ bool gj_inverse_regs(double (&Wm)[NT][NT][2], double* sRow, int m_rt, int g, int t) {
     constexpr unsigned FULL = 0xffffffffu;
     const int m = M > 0 ? M : m_rt;
-    bool ok = true;
     double dg[NT], S = 1.0;
 #pragma unroll
     for (int rt = 0; rt < NT; rt++) dg[rt] = 1.0;
@@ -169,33 +100,97 @@ __device__ __forceinline__ bool gj_inverse_regs(double (&Wm)[NT][NT][2], double*
             const double pkk = sRow[k * LD + k];
 #pragma unroll
             for (int rt = 0; rt < NT; rt++) colk[rt] = __shfl_sync(FULL, Wm[rt][kt][kh], 4 * g + (kg >> 1));
-            const int hi = __double2hiint(pkk);
-            ok = ok && (hi > 0) && (hi < 0x7ff00000);
             const double sc = pow2_unscale(pkk);
-            const double a_all = pkk * sc;
+            const double a = pkk * sc;  // every row, the pivot row included, is scaled by a
+            const double Sn = S * a;
             const bool kcol = (t == (kg >> 1));
 #pragma unroll
             for (int rt = 0; rt < NT; rt++) {
-                const bool prow = (rt == kt) && (g == kg);  // this lane owns row k: left as it is
-                const double a = prow ? 1.0 : a_all;
+                const bool prow = (rt == kt) && (g == kg);  // this lane owns row k: scaled only
                 const double c = prow ? 0.0 : colk[rt] * sc;
-                dg[rt] = prow ? pkk : dg[rt] * a_all;
+                dg[rt] = (prow ? pkk : dg[rt]) * a;
 #pragma unroll
                 for (int ct = 0; ct < NT; ct++)
 #pragma unroll
                     for (int h = 0; h < 2; h++) Wm[rt][ct][h] = fma(-c, rk[ct][h], a * Wm[rt][ct][h]);
-                if (kcol) Wm[rt][kt][kh] = prow ? S : -(c * S);  // column k of the right-hand block (its row k entry is the unpivoted-row scale)
+                if (kcol) Wm[rt][kt][kh] = prow ? Sn : -(c * S);  // column k of the right-hand block (row k: the scale of the unpivoted rows)
             }
-            S *= a_all;
+            S = Sn;
         }
     }
+    // every scaling factor is positive when the pivots are, and the last non-positive pivot leaves its own row's diagonal
+    // non-positive (zero and NaN propagate): the pivot test of the elimination is the sign test of the final diagonals
+    bool ok = true;
 #pragma unroll
     for (int rt = 0; rt < NT; rt++) {
+        const int hi = __double2hiint(dg[rt]);
+        ok = ok && (hi > 0) && (hi < 0x7ff00000);
         const double inv = fast_rcp(dg[rt]);
 #pragma unroll
         for (int ct = 0; ct < NT; ct++) {
             Wm[rt][ct][0] *= inv;
             Wm[rt][ct][1] *= inv;
+        }
+    }
+    return ok;  // per lane: combine with a vote where it is consumed
+}
+
+// Solve (L) X = Rr in registers for the larger systems (NT = 2).  There the elimination of the augmented matrix [L | Rr]
+// touches 14 elements per lane and stage and the kernel holds 2 warps per scheduler (255 registers), so it is bound by the
+// latency of the pivot-to-pivot chain: one reciprocal per stage and pivot rows by shuffle (26 cycles) measured faster on
+// B200 than the division-free form (a second multiply per element), than the shared-memory broadcast (store -> barrier
+// -> load per stage) and than the explicit inverse (16 more DMMA): C5 backward pass 38.9 / 40.8 / 40.9 / 43.0 ms.
+// Gauss-Jordan without pivoting and without row scaling (rows are divided by their diagonal once, at the end).
+// Returns false if a pivot was <= 0, infinite or NaN.
+template <int NT, int M>
+__device__ __forceinline__ bool gj_solve_regs(double (&L)[NT][NT][2], double (&Rr)[NT][NT][2], int m_rt, int g, int t) {
+    constexpr unsigned FULL = 0xffffffffu;
+    const int m = M > 0 ? M : m_rt;
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 8 * NT; k++) {
+        if (k < m) {  // warp-uniform (compile-time when M > 0)
+            const int kt = k >> 3, kg = k & 7, kh = k & 1;
+            const double pkk = __shfl_sync(FULL, L[kt][kt][kh], 4 * kg + (kg >> 1));
+            double rl[NT][2], rr[NT][2], colk[NT];
+#pragma unroll
+            for (int ct = 0; ct < NT; ct++) {
+                if (ct >= kt) {  // columns left of the pivot tile are dead
+                    rl[ct][0] = __shfl_sync(FULL, L[kt][ct][0], 4 * kg + t);
+                    rl[ct][1] = __shfl_sync(FULL, L[kt][ct][1], 4 * kg + t);
+                }
+                rr[ct][0] = __shfl_sync(FULL, Rr[kt][ct][0], 4 * kg + t);
+                rr[ct][1] = __shfl_sync(FULL, Rr[kt][ct][1], 4 * kg + t);
+            }
+#pragma unroll
+            for (int rt = 0; rt < NT; rt++) colk[rt] = __shfl_sync(FULL, L[rt][kt][kh], 4 * g + (kg >> 1));
+            const int hi = __double2hiint(pkk);
+            ok = ok && (hi > 0) && (hi < 0x7ff00000);
+            const double piv = fast_rcp(pkk);
+#pragma unroll
+            for (int rt = 0; rt < NT; rt++) {
+                const bool prow = (rt == kt) && (g == kg);  // this lane owns row k: left as it is
+                const double f = prow ? 0.0 : colk[rt] * piv;
+#pragma unroll
+                for (int ct = 0; ct < NT; ct++)
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        if (ct >= kt) L[rt][ct][h] = fma(-f, rl[ct][h], L[rt][ct][h]);
+                        Rr[rt][ct][h] = fma(-f, rr[ct][h], Rr[rt][ct][h]);
+                    }
+            }
+        }
+    }
+    // divide every row by its diagonal entry: (i, i) lives in lane (g, g>>1), slot g&1 of tile [rt][rt]
+#pragma unroll
+    for (int rt = 0; rt < NT; rt++) {
+        const double mine = (g & 1) ? L[rt][rt][1] : L[rt][rt][0];
+        const double dgi = __shfl_sync(FULL, mine, 4 * g + ((g >> 1) & 3));
+        const double inv = fast_rcp(dgi);
+#pragma unroll
+        for (int ct = 0; ct < NT; ct++) {
+            Rr[rt][ct][0] *= inv;
+            Rr[rt][ct][1] *= inv;
         }
     }
     return ok;
@@ -377,23 +372,27 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
 
         st_c<NT, LD>(sQux, Qa, g, t);
         st_c<NT, LD>(sQuu, Qu2, g, t);
-        // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]: explicit inverse, then the product on DMMA             ILQRRecursive.cpp:89-91
-        spd = gj_inverse_regs<NT, DOF, LD>(Inv, sKd, m, g, t) && spd;
-        st_c<NT, LD>(sM, Inv, g, t);
-        __syncwarp();
+        // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]                                            ILQRRecursive.cpp:89-91
         double Kd[NT][NT][2];
+        if constexpr (NT == 1) {  // explicit inverse, then the product on DMMA
+            spd = gj_inverse_regs<NT, DOF, LD>(Inv, sKd, m, g, t) && spd;
+            st_c<NT, LD>(sM, Inv, g, t);
+            __syncwarp();
+            double c0 = 0.0, c1 = 0.0;
 #pragma unroll
-        for (int rt = 0; rt < NT; rt++)
+            for (int s = 0; s < 2; s++) dmma884(c0, c1, ld_a<LD>(sM, 0, 0, s, g, t), ld_b<LD>(sQux, 0, s, 0, g, t));
+            Kd[0][0][0] = -c0;
+            Kd[0][0][1] = -c1;
+        } else {  // elimination of the augmented matrix
 #pragma unroll
-            for (int ct = 0; ct < NT; ct++) {
-                double c0 = 0.0, c1 = 0.0;
+            for (int rt = 0; rt < NT; rt++)
 #pragma unroll
-                for (int kt = 0; kt < NT; kt++)
-#pragma unroll
-                    for (int s = 0; s < 2; s++) dmma884(c0, c1, ld_a<LD>(sM, rt, kt, s, g, t), ld_b<LD>(sQux, kt, s, ct, g, t));
-                Kd[rt][ct][0] = -c0;
-                Kd[rt][ct][1] = -c1;
-            }
+                for (int ct = 0; ct < NT; ct++) {
+                    Kd[rt][ct][0] = -Qa[rt][ct][0];
+                    Kd[rt][ct][1] = -Qa[rt][ct][1];
+                }
+            spd = gj_solve_regs<NT, DOF>(Inv, Kd, m, g, t) && spd;
+        }
         st_c<NT, LD>(sKd, Kd, g, t);
         // stream K, d to global (time-forward index)
 #pragma unroll
@@ -455,7 +454,7 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
             }
         __syncwarp();  // shared operands are rewritten by the next step
     }
-    if (!spd && lane == 0) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
+    if (!__all_sync(0xffffffffu, spd) && lane == 0) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
 }
 
 template <int NT, int DOF, int WARPS, int MINB>

@@ -15,48 +15,10 @@
 
 namespace ilqrb {
 
-// (L) X = [R0 R1] in registers: L one 8x8 tile (leading m x m block, identity outside), R two tiles side by side.
-// Division-free Gauss-Jordan without pivoting, rows divided by their diagonal at the end (see gj_solve_regs).
-template <int M>
-__device__ __forceinline__ bool gj_solve_1x2(double (&L)[2], double (&R)[2][2], int m_rt, int g, int t) {
-    constexpr unsigned FULL = 0xffffffffu;
-    const int m = M > 0 ? M : m_rt;
-    bool ok = true;
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-        if (k < m) {
-            const int kh = k & 1;
-            const double pkk = __shfl_sync(FULL, L[kh], 4 * k + (k >> 1));
-            const double l0 = __shfl_sync(FULL, L[0], 4 * k + t), l1 = __shfl_sync(FULL, L[1], 4 * k + t);
-            const double r00 = __shfl_sync(FULL, R[0][0], 4 * k + t), r01 = __shfl_sync(FULL, R[0][1], 4 * k + t);
-            const double r10 = __shfl_sync(FULL, R[1][0], 4 * k + t), r11 = __shfl_sync(FULL, R[1][1], 4 * k + t);
-            const double colk = __shfl_sync(FULL, L[kh], 4 * g + (k >> 1));
-            const int hi = __double2hiint(pkk);
-            ok = ok && (hi > 0) && (hi < 0x7ff00000);
-            const double sc = pow2_unscale(pkk);  // division-free stage: row_i <- sc (p_kk row_i - l_ik row_k)
-            const double a = (g == k) ? 1.0 : pkk * sc;
-            const double c = (g == k) ? 0.0 : colk * sc;
-            L[0] = fma(-c, l0, a * L[0]);
-            L[1] = fma(-c, l1, a * L[1]);
-            R[0][0] = fma(-c, r00, a * R[0][0]);
-            R[0][1] = fma(-c, r01, a * R[0][1]);
-            R[1][0] = fma(-c, r10, a * R[1][0]);
-            R[1][1] = fma(-c, r11, a * R[1][1]);
-        }
-    }
-    const double mine = (g & 1) ? L[1] : L[0];
-    const double inv = fast_rcp(__shfl_sync(FULL, mine, 4 * g + ((g >> 1) & 3)));
-    R[0][0] *= inv;
-    R[0][1] *= inv;
-    R[1][0] *= inv;
-    R[1][1] *= inv;
-    return ok;
-}
-
 struct BwdN2Smem {
     static constexpr int LDW = 20, LDQ = 12;                 // 8 x 16 matrices / the 8 x 8 Quu
     static constexpr int SZW = 8 * LDW, SZQ = 8 * LDQ;
-    static constexpr int PER_WARP = 2 * SZW + 3 * SZQ;       // [K|d], Quu [K|d] + [Qux|Qu], Quu, Qxu (16 x 8)
+    static constexpr int PER_WARP = 2 * SZW + 4 * SZQ;       // [K|d], Quu [K|d] + [Qux|Qu], Quu, Qxu (16 x 8), (Quu + 1e-6 I)^-1
 };
 
 // fragment loads of the 8 x 16 matrices (row-major, leading dimension LDW)
@@ -77,6 +39,7 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
     double* sM = sKd + S::SZW;
     double* sQuu = sM + S::SZW;
     double* sQxu = sQuu + S::SZQ;  // 16 x 8
+    double* sInv = sQxu + 2 * S::SZQ;
     const bool rowv = g < dof;  // this lane's row is a real control / state row of its tile
     const double Rg = rowv ? P.r_diag[g] : 0.0;
     const double* Xb = W.X + (size_t)b * H * ns;
@@ -228,9 +191,25 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
         *reinterpret_cast<double2*>(sQuu + g * S::LDQ + 2 * t) = make_double2(Quu[0], Quu[1]);
 #pragma unroll
         for (int r = 0; r < 2; r++) *reinterpret_cast<double2*>(sQxu + (8 * r + g) * S::LDQ + 2 * t) = make_double2(Qxu[r][0], Qxu[r][1]);
-        // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]                                            ILQRRecursive.cpp:89-91
-        double Kd[2][2] = {{-Qa[0][0], -Qa[0][1]}, {-Qa[1][0], -Qa[1][1]}};
-        spd = gj_solve_1x2<DOF>(Lr, Kd, m, g, t) && spd;
+        // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]: explicit inverse (gj_inverse_regs; pivot rows travel through the sKd
+        // area), then the product on DMMA                                                ILQRRecursive.cpp:89-91
+        st_w(sM, Qa, g, t);
+        double Iv[1][1][2] = {{{Lr[0], Lr[1]}}};
+        spd = gj_inverse_regs<1, DOF, S::LDW>(Iv, sKd, m, g, t) && spd;
+        *reinterpret_cast<double2*>(sInv + g * S::LDQ + 2 * t) = make_double2(Iv[0][0][0], Iv[0][0][1]);
+        __syncwarp();
+        double Kd[2][2];
+        {
+            const double ia0 = sInv[g * S::LDQ + t], ia1 = sInv[g * S::LDQ + 4 + t];
+#pragma unroll
+            for (int c = 0; c < 2; c++) {
+                double c0 = 0.0, c1 = 0.0;
+                dmma884(c0, c1, ia0, ld_bw(sM, 0, c, g, t));
+                dmma884(c0, c1, ia1, ld_bw(sM, 1, c, g, t));
+                Kd[c][0] = -c0;
+                Kd[c][1] = -c1;
+            }
+        }
 #pragma unroll
         for (int c = 0; c < 2; c++)
 #pragma unroll
@@ -294,7 +273,7 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
             }
         __syncwarp();
     }
-    if (!spd && lane == 0) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
+    if (!__all_sync(0xffffffffu, spd) && lane == 0) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
 }
 
 template <int DOF, bool AL, int WARPS, int MINB>

@@ -966,6 +966,15 @@ int ilqrb_solve_recursive(ilqrb_handle h, const double* U0, const ilqrb_solve_op
     }
     return ilqrb_download(h, out);
 }
+int ilqrb_solve_recursive_async(ilqrb_handle h, const double* U0, const ilqrb_solve_opts* opts, ilqrb_result* out) {
+    int rc;
+    if (!h || !out) return fail(ILQRB_EINVAL, "null argument");
+    if ((rc = ilqrb_upload_u0(h, U0))) return rc;
+    h->downloaded = false;
+    if ((rc = run_recursive_like(h, nullptr, opts, out))) return rc;
+    if (h->downloaded) return 0;  // every group has queued its own device-to-host copies; ilqrb_synchronize waits for them
+    return ilqrb_download(h, out);
+}
 int ilqrb_solve_al(ilqrb_handle h, const double* U0, const ilqrb_al_desc* al, const ilqrb_solve_opts* opts, ilqrb_result* out) {
     int rc;
     if ((rc = ilqrb_upload_u0(h, U0))) return rc;

@@ -69,6 +69,15 @@ class Handle:
         cabi.check(self.lib.ilqrb_solve_recursive(self.h, cabi.dptr(U0), C.byref(o), C.byref(out.res)))
         return out
 
+    def solve_recursive_async(self, U0, nb_iter, line_search=True, early_stop=False, out=None):
+        """queues H2D + solve + D2H and returns; U0 and `out` (pinned) must stay untouched until synchronize()"""
+        out = out or ResultBuffers(self.pb, nb_iter, "recursive", pinned=True)
+        self._u0_keep = self._u(U0)
+        self._out_keep = out
+        o = opts(nb_iter, line_search, early_stop)
+        cabi.check(self.lib.ilqrb_solve_recursive_async(self.h, cabi.dptr(self._u0_keep), C.byref(o), C.byref(out.res)))
+        return out
+
     def solve_al(self, U0, A, b, lambda0, nb_iter, lag_update_step, penalty, scaling_factor, line_search=True, early_stop=False, out=None):
         al = make_al_desc(A, b, lambda0, lag_update_step, penalty, scaling_factor)
         out = out or ResultBuffers(self.pb, nb_iter, "al", nc=al.nc)

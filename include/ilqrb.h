@@ -201,6 +201,11 @@ int ilqrb_update_problems(ilqrb_handle h, const double* q0, const double* dq0, i
 /* ---- solvers: host-buffer entry points (H2D + solve + D2H) -------------------------------- */
 /* ILQRRecursive::solve (ILQRRecursive.cpp:21-181).  U0: [B][H-1][m] host. */
 int ilqrb_solve_recursive(ilqrb_handle h, const double* U0, const ilqrb_solve_opts* opts, ilqrb_result* out);
+/* The same call, returning as soon as the H2D copy of U0, the solve and the D2H copies into `out` are queued.  U0 and the
+ * buffers of `out` must be page-locked and stay untouched until ilqrb_synchronize(h) returns.  A caller that streams
+ * batches through two handles alternately overlaps one batch's result transfer (PCIe) with the next batch's solve.
+ * Systems on the generic path (time state, AL) complete synchronously. */
+int ilqrb_solve_recursive_async(ilqrb_handle h, const double* U0, const ilqrb_solve_opts* opts, ilqrb_result* out);
 /* AL_ILQR::solve (AL-ILQR.cpp:50-232). */
 int ilqrb_solve_al(ilqrb_handle h, const double* U0, const ilqrb_al_desc* al, const ilqrb_solve_opts* opts, ilqrb_result* out);
 /* BatchILQR::solve (BatchILQR.cpp:110-173) and BatchILQRCP::solve (BatchILQRCP.cpp:109-174): u0 [B][N]. */
