@@ -6,10 +6,9 @@
 //
 //   k_backward_n1   Riccati recursion (ILQRRecursive.cpp:69-97).  [P|p] lives in registers in the DMMA accumulator
 //                   layout; the products with A and B are exact scalings (x*1 and +0 are exact in IEEE, so
-//                   (B^T P) A == dt*P bit for bit), Quu^-1 is an in-register Gauss-Jordan driven by shuffles, and the
-//                   five dense products that remain per step (K = -Inv Qux, K^T Quu, and the three terms of the P
-//                   update) run on the FP64 tensor pipe (mma.sync m8n8k4.f64), operands re-laid-out through shared
-//                   memory.
+//                   (B^T P) A == dt*P bit for bit), (Quu + 1e-6 I)^-1 is an in-register division-free Gauss-Jordan, and the
+//                   three dense products that remain per step (K = -Inv Qux, -1e-6 K^T K and Qxu K of the P update)
+//                   run on the FP64 tensor pipe (mma.sync m8n8k4.f64), operands re-laid-out through shared memory.
 //
 //   k_forward_n1    line search + accept (ILQRRecursive.cpp:101-176).  With linear dynamics the candidate rollout is
 //                   affine in alpha:  x'(alpha) = x + alpha*dx,  u'(alpha) = u + alpha*du  where (dx,du) is the
@@ -199,7 +198,7 @@ __device__ __forceinline__ bool gj_solve_regs(double (&L)[NT][NT][2], double (&R
 template <int NT>
 struct BwdN1Smem {
     static constexpr int NX = 8 * NT, LD = NX + 4, SZ = NX * LD;
-    static constexpr int PER_WARP = 4 * SZ;  // [Qux|Qu], Quu, [K|d], Quu [K|d] + [Qux|Qu]
+    static constexpr int PER_WARP = 3 * SZ;  // [Qux|Qu], [K|d] (pivot rows of the elimination before that), (Quu + 1e-6 I)^-1
 };
 
 // ------------------------------------------------------------------------------------------------------------
@@ -215,8 +214,7 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
     const int ns = (n + 1) & ~1, ms = ns;
     const double dt = 1.0 * P.dt;  // B = Identity * dt
     double* sQux = wsmem;
-    double* sQuu = sQux + SZ;
-    double* sKd = sQuu + SZ;
+    double* sKd = sQux + SZ;
     double* sM = sKd + SZ;
 
     double Rrow[NT];
@@ -343,7 +341,7 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
         }
         // [Qux|Qu] = [0 | R u] + (B^T [P|p]) A_aug ;  Quu = R + (B^T P) B ;  [Qxx|Qx] = [l_xx|l_x] + (A^T [P|p]) A_aug
         // Qxu = (A^T P) B = P*dt has the same entries as Qux = dt*P                     ILQRRecursive.cpp:82-87
-        double Qa[NT][NT][2], Qu2[NT][NT][2], Qx[NT][NT][2], Inv[NT][NT][2];
+        double Qa[NT][NT][2], Qx[NT][NT][2], Inv[NT][NT][2];
 #pragma unroll
         for (int rt = 0; rt < NT; rt++) {
             const int i = 8 * rt + g;
@@ -357,7 +355,6 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
                     double quu = bp * dt;
                     if (i == j) quu = Rrow[rt] + quu;
                     quu = (j < m) ? quu : 0.0;  // rows >= m of [P|p] are zero already
-                    Qu2[rt][ct][h] = quu;
                     // Quu + 1e-6 I, identity outside the leading block                    ILQRRecursive.cpp:89
                     Inv[rt][ct][h] = (i == j) ? ((i < m) ? quu + 1e-6 * 1.0 : 1.0) : quu;
                     Qx[rt][ct][h] = Pa[rt][ct][h];
@@ -371,7 +368,6 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
         if (l0 >= 0) add_limits(Qx, x);
 
         st_c<NT, LD>(sQux, Qa, g, t);
-        st_c<NT, LD>(sQuu, Qu2, g, t);
         // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]                                            ILQRRecursive.cpp:89-91
         double Kd[NT][NT][2];
         if constexpr (NT == 1) {  // explicit inverse, then the product on DMMA
@@ -410,31 +406,20 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
         }
         __syncwarp();
 
-        // [M|mv] = Quu [K|d] + [Qux|Qu]   (= K^T-free half of ILQRRecursive.cpp:93-94: K^T Quu K + K^T Qux = K^T M)
-        double kb[NT][2][NT];
+        // [P|p] = [Qxx|Qx] + K^T (Quu [K|d] + [Qux|Qu]) + Qxu [K|d]                       ILQRRecursive.cpp:93-94
+        // With [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu] the bracket is -1e-6 [K|d] identically (for any P, symmetric or not), so the
+        // three-term form of the reference collapses to  [Qxx|Qx] - 1e-6 K^T [K|d] + Qxu [K|d]  — the same quantity without
+        // the cancellation of Quu K against Qux, and two products fewer.  (Row n = d^T [..] is produced too and masked out.)
+        double kb[NT][2][NT], ke[NT][2][NT];
 #pragma unroll
         for (int kt = 0; kt < NT; kt++)
 #pragma unroll
             for (int s = 0; s < 2; s++)
 #pragma unroll
-                for (int ct = 0; ct < NT; ct++) kb[kt][s][ct] = ld_b<LD>(sKd, kt, s, ct, g, t);  // B fragment of [K|d] == A fragment of [K|d]^T
-        double Mm[NT][NT][2];
-#pragma unroll
-        for (int rt = 0; rt < NT; rt++)
-#pragma unroll
-            for (int ct = 0; ct < NT; ct++) {
-                double c0 = Qa[rt][ct][0], c1 = Qa[rt][ct][1];
-#pragma unroll
-                for (int kt = 0; kt < NT; kt++)
-#pragma unroll
-                    for (int s = 0; s < 2; s++) dmma884(c0, c1, ld_a<LD>(sQuu, rt, kt, s, g, t), kb[kt][s][ct]);
-                Mm[rt][ct][0] = c0;
-                Mm[rt][ct][1] = c1;
-            }
-        st_c<NT, LD>(sM, Mm, g, t);
-        __syncwarp();
-
-        // [P|p] = [Qxx|Qx] + K^T [M|mv] + Qxu [K|d]     (row n = d^T [M|mv] is produced too and masked out)
+                for (int ct = 0; ct < NT; ct++) {
+                    kb[kt][s][ct] = ld_b<LD>(sKd, kt, s, ct, g, t);  // B fragment of [K|d] == A fragment of [K|d]^T
+                    ke[kt][s][ct] = -1e-6 * kb[kt][s][ct];
+                }
 #pragma unroll
         for (int rt = 0; rt < NT; rt++)
 #pragma unroll
@@ -443,7 +428,7 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
 #pragma unroll
                 for (int kt = 0; kt < NT; kt++)
 #pragma unroll
-                    for (int s = 0; s < 2; s++) dmma884(c0, c1, kb[kt][s][rt], ld_b<LD>(sM, kt, s, ct, g, t));
+                    for (int s = 0; s < 2; s++) dmma884(c0, c1, ke[kt][s][rt], kb[kt][s][ct]);
 #pragma unroll
                 for (int kt = 0; kt < NT; kt++)
 #pragma unroll

@@ -8,8 +8,9 @@
 //   B^T [P|p] = [M1 M2],  M1 = c2 P11 + dt P21,  M2 = c2 P12 + dt P22          (c2 = dt^2/2)
 //   [Qux|Qu]  = [M1, dt M1 + M2] + [0 | R u]        Quu = R + c2 M1 + dt M2
 //   A^T [P|p] = N,  N1c = P1c,  N2c = dt P1c + P2c ;   [Qxx|Qx] = [l_xx|l_x] + [Nr1, dt Nr1 + Nr2] ;   Qxu = c2 Nr1 + dt Nr2
-// Only [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu] (in-register Gauss-Jordan) and P' = Qxx + K^T (Quu K + Qux) + Qxu K
-// (20 DMMA m8n8k4.f64 per step) remain as dense work (ILQRRecursive.cpp:69-97).
+// Only [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu] (in-register Gauss-Jordan inverse, 4 DMMA for the product) and
+// P' = Qxx + K^T (Quu K + Qux) + Qxu K = Qxx - 1e-6 K^T K + Qxu K (16 DMMA m8n8k4.f64) remain as dense work per step
+// (ILQRRecursive.cpp:69-97).
 #pragma once
 #include "fused1.cuh"
 
@@ -18,7 +19,7 @@ namespace ilqrb {
 struct BwdN2Smem {
     static constexpr int LDW = 20, LDQ = 12;                 // 8 x 16 matrices / the 8 x 8 Quu
     static constexpr int SZW = 8 * LDW, SZQ = 8 * LDQ;
-    static constexpr int PER_WARP = 2 * SZW + 4 * SZQ;       // [K|d], Quu [K|d] + [Qux|Qu], Quu, Qxu (16 x 8), (Quu + 1e-6 I)^-1
+    static constexpr int PER_WARP = 2 * SZW + 3 * SZQ;       // [K|d], [Qux|Qu], Qxu (16 x 8), (Quu + 1e-6 I)^-1
 };
 
 // fragment loads of the 8 x 16 matrices (row-major, leading dimension LDW)
@@ -37,8 +38,7 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
     const double dt = 1.0 * P.dt, c2 = 1.0 * P.dt * P.dt / 2;
     double* sKd = wsmem;
     double* sM = sKd + S::SZW;
-    double* sQuu = sM + S::SZW;
-    double* sQxu = sQuu + S::SZQ;  // 16 x 8
+    double* sQxu = sM + S::SZW;  // 16 x 8
     double* sInv = sQxu + 2 * S::SZQ;
     const bool rowv = g < dof;  // this lane's row is a real control / state row of its tile
     const double Rg = rowv ? P.r_diag[g] : 0.0;
@@ -188,7 +188,6 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
         }
         add_limits(Qx, k);
 
-        *reinterpret_cast<double2*>(sQuu + g * S::LDQ + 2 * t) = make_double2(Quu[0], Quu[1]);
 #pragma unroll
         for (int r = 0; r < 2; r++) *reinterpret_cast<double2*>(sQxu + (8 * r + g) * S::LDQ + 2 * t) = make_double2(Qxu[r][0], Qxu[r][1]);
         // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]: explicit inverse (gj_inverse_regs; pivot rows travel through the sKd
@@ -228,33 +227,15 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
         }
         __syncwarp();
 
-        // [M|mv] = Quu [K|d] + [Qux|Qu]   (K^T Quu K + K^T Qux = K^T M, ILQRRecursive.cpp:93-94)
-        double kb[2][2], qa[2];  // B fragments of [K|d] (= A fragments of [K|d]^T), A fragments of Quu
-#pragma unroll
-        for (int s = 0; s < 2; s++) {
-            qa[s] = sQuu[g * S::LDQ + 4 * s + t];
-#pragma unroll
-            for (int c = 0; c < 2; c++) kb[s][c] = ld_bw(sKd, s, c, g, t);
-        }
-        double Mm[2][2];
-#pragma unroll
-        for (int c = 0; c < 2; c++) {
-            double c0 = Qa[c][0], c1 = Qa[c][1];
-#pragma unroll
-            for (int s = 0; s < 2; s++) dmma884(c0, c1, qa[s], kb[s][c]);
-            Mm[c][0] = c0;
-            Mm[c][1] = c1;
-        }
-        st_w(sM, Mm, g, t);
-        __syncwarp();
-
-        // [P|p] = [Qxx|Qx] + K^T [M|mv] + Qxu [K|d]
-        double mb[2][2], xa[2][2];  // B fragments of [M|mv]; A fragments of Qxu
+        // [P|p] = [Qxx|Qx] + K^T (Quu [K|d] + [Qux|Qu]) + Qxu [K|d]   (ILQRRecursive.cpp:93-94); the bracket is -1e-6 [K|d]
+        // identically because [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu] (see backward_n1_body)
+        double kb[2][2], ke[2][2], xa[2][2];  // B fragments of [K|d] (= A fragments of [K|d]^T), -1e-6 times them; A fragments of Qxu
 #pragma unroll
         for (int s = 0; s < 2; s++)
 #pragma unroll
             for (int c = 0; c < 2; c++) {
-                mb[s][c] = ld_bw(sM, s, c, g, t);
+                kb[s][c] = ld_bw(sKd, s, c, g, t);
+                ke[s][c] = -1e-6 * kb[s][c];
                 xa[s][c] = sQxu[(8 * c + g) * S::LDQ + 4 * s + t];
             }
 #pragma unroll
@@ -263,7 +244,7 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
             for (int c = 0; c < 2; c++) {
                 double c0 = Qx[r][c][0], c1 = Qx[r][c][1];
 #pragma unroll
-                for (int s = 0; s < 2; s++) dmma884(c0, c1, kb[s][r], mb[s][c]);
+                for (int s = 0; s < 2; s++) dmma884(c0, c1, kb[s][r], ke[s][c]);
 #pragma unroll
                 for (int s = 0; s < 2; s++) dmma884(c0, c1, xa[s][r], kb[s][c]);
                 // keep rows >= dof (incl. the d row the transposed fragment drags in) and unused columns at exact zero
