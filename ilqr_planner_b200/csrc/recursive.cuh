@@ -449,28 +449,126 @@ __global__ void __launch_bounds__(128, 3) k_linesearch_affine(const DevProblem* 
 __device__ __forceinline__ void al_constraints(const DevProblem& P, const Work& W, int b, int lane, bool upd, double penalty_next) {
     const int H = P.H, n = P.n, m = P.m, ns = W.ns, ms = W.ms;
     const int nc = W.nc, nsu = n + m;
-    for (int k = 0; k < H - 1; k++) {
-        const size_t bk = (size_t)b * (H - 1) + k;
-        const double* Ac = W.alA + (size_t)(W.al_per_step ? k : 0) * nc * nsu;
-        const double* bc = W.alb + (size_t)(W.al_per_step ? k : 0) * nc;
-        const double* Xk = W.X + ((size_t)b * H + k) * ns;
-        const double* Uk = W.U + bk * ms;
-        bool act = false;
-        if (lane < nc) {
-            double g = 0.0;
-            for (int j = 0; j < n; j++) g += Ac[lane * nsu + j] * Xk[j];
-            for (int j = 0; j < m; j++) g += Ac[lane * nsu + n + j] * Uk[j];
-            g = g - bc[lane];
-            const double lam = W.lam[bk * nc + lane];
-            act = !(g < 0 && lam == 0);
-            W.Cs[bk * nc + lane] = g;
-            if (upd) {
-                const double v = lam + penalty_next * g;
-                W.lam[bk * nc + lane] = (v < 0.0) ? 0.0 : v;  // cwiseMax(0)
+    // lanes 0-15 take the even step of a pair, lanes 16-31 the odd one (nc <= 16), four pairs in flight: the loads of a
+    // group are issued before its first store, so the L2 latency is paid once per 8 steps instead of once per step
+    constexpr int G = 4;
+    const int half = lane >> 4, r = lane & 15;
+    if (nc > 16) {  // wide constraint sets: one step at a time
+        for (int k = 0; k < H - 1; k++) {
+            const size_t bk = (size_t)b * (H - 1) + k;
+            const double* Ac = W.alA + (size_t)(W.al_per_step ? k : 0) * nc * nsu;
+            const double* bc = W.alb + (size_t)(W.al_per_step ? k : 0) * nc;
+            const double* Xk = W.X + ((size_t)b * H + k) * ns;
+            const double* Uk = W.U + bk * ms;
+            bool act = false;
+            if (lane < nc) {
+                double g = 0.0;
+                for (int j = 0; j < n; j++) g += Ac[lane * nsu + j] * Xk[j];
+                for (int j = 0; j < m; j++) g += Ac[lane * nsu + n + j] * Uk[j];
+                g = g - bc[lane];
+                const double lam = W.lam[bk * nc + lane];
+                act = !(g < 0 && lam == 0);
+                W.Cs[bk * nc + lane] = g;
+                if (upd) {
+                    const double v = lam + penalty_next * g;
+                    W.lam[bk * nc + lane] = (v < 0.0) ? 0.0 : v;  // cwiseMax(0)
+                }
+            }
+            const unsigned bits = __ballot_sync(0xffffffffu, act);
+            if (lane == 0) W.mask[bk] = bits;
+        }
+        return;
+    }
+    for (int k0 = 0; k0 < H - 1; k0 += 2 * G) {
+        double g[G], lam[G];
+        bool in[G];
+#pragma unroll
+        for (int q = 0; q < G; q++) {
+            const int k = k0 + 2 * q + half;
+            in[q] = (k < H - 1) && (r < nc);
+            g[q] = 0.0;
+            lam[q] = 0.0;
+            if (in[q]) {
+                const size_t bk = (size_t)b * (H - 1) + k;
+                const double* Ac = W.alA + (size_t)(W.al_per_step ? k : 0) * nc * nsu + (size_t)r * nsu;
+                const double* Xk = W.X + ((size_t)b * H + k) * ns;
+                const double* Uk = W.U + bk * ms;
+                double acc = 0.0;
+                for (int j = 0; j < n; j++) acc += Ac[j] * Xk[j];
+                for (int j = 0; j < m; j++) acc += Ac[n + j] * Uk[j];
+                g[q] = acc - W.alb[(size_t)(W.al_per_step ? k : 0) * nc + r];
+                lam[q] = W.lam[bk * nc + r];
             }
         }
-        const unsigned bits = __ballot_sync(0xffffffffu, act);
-        if (lane == 0) W.mask[bk] = bits;
+#pragma unroll
+        for (int q = 0; q < G; q++) {
+            const int k = k0 + 2 * q + half;
+            const size_t bk = (size_t)b * (H - 1) + k;
+            const bool act = in[q] && !(g[q] < 0 && lam[q] == 0);
+            if (in[q]) {
+                W.Cs[bk * nc + r] = g[q];
+                if (upd) {
+                    const double v = lam[q] + penalty_next * g[q];
+                    W.lam[bk * nc + r] = (v < 0.0) ? 0.0 : v;  // cwiseMax(0)
+                }
+            }
+            const unsigned bits = __ballot_sync(0xffffffffu, act);
+            if (r == 0 && k < H - 1) W.mask[bk] = (bits >> (16 * half)) & 0xffffu;
+        }
+    }
+}
+// the same for constraint sets shared by all steps with nc <= 16 (the C3 shape): lane (half, r) keeps row r of A in
+// registers, the trip counts are compile-time bounds, so the loads of 8 steps are in flight together (the runtime-bounded
+// loop above leaves 2-4: ncu shows 70 % of k_accept waiting on them).  Same summation order as al_constraints.
+template <int N, int M>
+__device__ __forceinline__ void al_constraints_t(const DevProblem& P, const Work& W, int b, int lane, bool upd, double penalty_next) {
+    const int H = P.H, n = P.n, m = P.m, ns = W.ns, ms = W.ms;
+    const int nc = W.nc, nsu = n + m;
+    constexpr int G = 4;
+    const int half = lane >> 4, r = lane & 15;
+    const bool row = r < nc;
+    double Ax[N], Au[M];
+#pragma unroll
+    for (int j = 0; j < N; j++) Ax[j] = (row && j < n) ? W.alA[(size_t)r * nsu + j] : 0.0;
+#pragma unroll
+    for (int j = 0; j < M; j++) Au[j] = (row && j < m) ? W.alA[(size_t)r * nsu + n + j] : 0.0;
+    const double br = row ? W.alb[r] : 0.0;
+    for (int k0 = 0; k0 < H - 1; k0 += 2 * G) {
+        double g[G], lam[G];
+        bool in[G];
+#pragma unroll
+        for (int q = 0; q < G; q++) {
+            const int k = k0 + 2 * q + half;
+            in[q] = (k < H - 1) && row;
+            const int kc = k < H - 1 ? k : H - 2;  // clamped: the loads stay unconditional and independent
+            const size_t bk = (size_t)b * (H - 1) + kc;
+            const double* Xk = W.X + ((size_t)b * H + kc) * ns;
+            const double* Uk = W.U + bk * ms;
+            double acc = 0.0;
+#pragma unroll
+            for (int j = 0; j < N; j++)
+                if (j < n) acc = fma(Ax[j], Xk[j], acc);
+#pragma unroll
+            for (int j = 0; j < M; j++)
+                if (j < m) acc = fma(Au[j], Uk[j], acc);
+            g[q] = acc - br;
+            lam[q] = row ? W.lam[bk * nc + r] : 0.0;
+        }
+#pragma unroll
+        for (int q = 0; q < G; q++) {
+            const int k = k0 + 2 * q + half;
+            const size_t bk = (size_t)b * (H - 1) + k;
+            const bool act = in[q] && !(g[q] < 0 && lam[q] == 0);
+            if (in[q]) {
+                W.Cs[bk * nc + r] = g[q];
+                if (upd) {
+                    const double v = lam[q] + penalty_next * g[q];
+                    W.lam[bk * nc + r] = (v < 0.0) ? 0.0 : v;  // cwiseMax(0)
+                }
+            }
+            const unsigned bits = __ballot_sync(0xffffffffu, act);
+            if (r == 0 && k < H - 1) W.mask[bk] = (bits >> (16 * half)) & 0xffffu;
+        }
     }
 }
 __global__ void __launch_bounds__(128) k_al_init(const DevProblem* __restrict__ Pp, Work W) {
@@ -517,38 +615,51 @@ __global__ void __launch_bounds__(128) k_accept(const DevProblem* __restrict__ P
         xq = P.q0[(size_t)b * dof + lane];
         if (P.nb_deriv == 2) xv = P.dq0[(size_t)b * dof + lane];
     }
-    for (int k = 0; k < H - 1; k++) {
-        const size_t bk = (size_t)b * (H - 1) + k;
-        const double* Uo = W.Uc + (bk * NCAND + sel) * ms;
-        double uu = 0.0;
-        if (lane < ms) {
-            uu = Uo[lane];
-            W.U[bk * ms + lane] = uu;
+    constexpr int PFK = 8;  // the controls of 8 steps are loaded ahead of the serial state recurrence
+    for (int k0 = 0; k0 < H - 1; k0 += PFK) {
+        double ub[PFK];
+#pragma unroll
+        for (int q = 0; q < PFK; q++) {
+            const int k = k0 + q;
+            ub[q] = (k < H - 1 && lane < ms) ? W.Uc[(((size_t)b * (H - 1) + k) * NCAND + sel) * ms + lane] : 0.0;
         }
-        double dt = P.dt;
-        if (P.time) {
-            const double s = __shfl_sync(0xffffffffu, uu, m - 1);
-            dt = __dmul_rn(s, s);
-        }
-        const double hdt2 = __dmul_rn(dt, dt) / 2;
-        if (lane < dof) {
-            if (P.nb_deriv == 1) {
-                xq = __dadd_rn(xq, __dadd_rn(__dmul_rn(dt, uu), __dmul_rn(hdt2, 0.0)));
-            } else {
-                xq = __dadd_rn(xq, __dadd_rn(__dmul_rn(dt, xv), __dmul_rn(hdt2, uu)));
-                xv = __dadd_rn(xv, __dmul_rn(dt, uu));
+#pragma unroll
+        for (int q = 0; q < PFK; q++) {
+            const int k = k0 + q;
+            if (k < H - 1) {
+                const size_t bk = (size_t)b * (H - 1) + k;
+                const double uu = ub[q];
+                if (lane < ms) W.U[bk * ms + lane] = uu;
+                double dt = P.dt;
+                if (P.time) {
+                    const double s = __shfl_sync(0xffffffffu, uu, m - 1);
+                    dt = __dmul_rn(s, s);
+                }
+                const double hdt2 = __dmul_rn(dt, dt) / 2;
+                if (lane < dof) {
+                    if (P.nb_deriv == 1) {
+                        xq = __dadd_rn(xq, __dadd_rn(__dmul_rn(dt, uu), __dmul_rn(hdt2, 0.0)));
+                    } else {
+                        xq = __dadd_rn(xq, __dadd_rn(__dmul_rn(dt, xv), __dmul_rn(hdt2, uu)));
+                        xv = __dadd_rn(xv, __dmul_rn(dt, uu));
+                    }
+                }
+                xt = __dadd_rn(xt, dt);
+                double* Xn = W.X + ((size_t)b * H + k + 1) * ns;
+                if (lane < dof) {
+                    Xn[lane] = xq;
+                    if (P.nb_deriv == 2) Xn[dof + lane] = xv;
+                }
+                if (P.time && lane == 0) Xn[n - 1] = xt;
             }
         }
-        xt = __dadd_rn(xt, dt);
-        double* Xn = W.X + ((size_t)b * H + k + 1) * ns;
-        if (lane < dof) {
-            Xn[lane] = xq;
-            if (P.nb_deriv == 2) Xn[dof + lane] = xv;
-        }
-        if (P.time && lane == 0) Xn[n - 1] = xt;
     }
     __syncwarp();
-    if (al) al_constraints(P, W, b, lane, ((it + 1) % lag_update_step) == 0, penalty_next);
+    if (al) {
+        const bool upd = ((it + 1) % lag_update_step) == 0;
+        if (W.nc <= 16 && !W.al_per_step) al_constraints_t<N, M>(P, W, b, lane, upd, penalty_next);
+        else al_constraints(P, W, b, lane, upd, penalty_next);
+    }
     if (lane == 0) {
         W.cost0[b] = newCost;
         W.cost_hist[(size_t)b * nb_iter + it] = newCost;
@@ -599,7 +710,7 @@ struct BwdSmem {
     static constexpr int NX = 8 * NXT, NU = 8 * NUT, LDX = NX + 4, LDU = NU + 4;
     static constexpr int SZ_XX = NX * LDX, SZ_UX = NU * LDX, SZ_XU = NX * LDU, SZ_UU = NU * LDU;
     // per warp: Paug, AtP, QxxQx (XX) ; BtP, QuxQu, Kd (UX) ; Qxu (XU) ; Quu (UU).
-    // KtQuu reuses AtP and Inv reuses BtP (both dead by then; XX >= XU and UX >= UU because NX >= NU).
+    // Inv reuses BtP (dead by then; UX >= UU because NX >= NU).
     static_assert(NXT >= NUT, "state tiles must cover control tiles");
     static constexpr int PER_WARP = 3 * SZ_XX + 3 * SZ_UX + 1 * SZ_XU + 1 * SZ_UU;
     static constexpr int DYN = SZ_XX + SZ_XU;  // A_aug, B
@@ -626,7 +737,6 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward(const DevProblem*
     double* Kd = QuxQu + S::SZ_UX;
     double* Qxu = Kd + S::SZ_UX;
     double* Quu = Qxu + S::SZ_XU;
-    double* KtQuu = AtP;  // alias (AtP is dead once Qxu is formed)
     double* Inv = BtP;    // alias (BtP is dead once Quu is formed)
 
     // ---- A_aug = blockdiag(A, 1), B  (PosOrnPlannerSys.cpp:115-128) ----
@@ -820,23 +930,22 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward(const DevProblem*
             }
             if (lane < ms) W.d[bk * ms + lane] = (lane < m) ? Kd[lane * LDX + n] : 0.0;
         }
-        // KtQuu = K^T Quu   (row n carries d^T Quu and is discarded below)
-        wm_gemm<NXT, NUT, NUT, true, false, false, false>(KtQuu, LDU, Kd, LDX, Quu, LDU, lane);
-        // [P|p] = (([Qxx|Qx] + KtQuu [K|d]) + K^T [Qux|Qu]) + Qxu [K|d]      ILQRRecursive.cpp:93-94
+        __syncwarp();
+        // [P|p] = [Qxx|Qx] + K^T (Quu [K|d] + [Qux|Qu]) + Qxu [K|d]      ILQRRecursive.cpp:93-94
+        // the bracket is -1e-6 [K|d] identically, because [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu] (see backward_n1_body)
         {
             const int g = lane >> 2, t = lane & 3;
 #pragma unroll
             for (int rt = 0; rt < NXT; rt++)
 #pragma unroll
                 for (int ct = 0; ct < NXT; ct++) {
-                    double a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0, c0 = 0.0, c1 = 0.0;
-                    wm_tile_acc<NUT, false, false>(a0, a1, KtQuu, LDU, Kd, LDX, rt, ct, g, t);
-                    wm_tile_acc<NUT, true, false>(b0, b1, Kd, LDX, QuxQu, LDX, rt, ct, g, t);
+                    double a0 = 0.0, a1 = 0.0, c0 = 0.0, c1 = 0.0;
+                    wm_tile_acc<NUT, true, false>(a0, a1, Kd, LDX, Kd, LDX, rt, ct, g, t);
                     wm_tile_acc<NUT, false, false>(c0, c1, Qxu, LDU, Kd, LDX, rt, ct, g, t);
                     const int i = 8 * rt + g, j = 8 * ct + 2 * t;
                     const double2 q = *reinterpret_cast<const double2*>(QxxQx + i * LDX + j);
-                    double v0 = ((q.x + a0) + b0) + c0;
-                    double v1 = ((q.y + a1) + b1) + c1;
+                    double v0 = fma(-1e-6, a0, q.x) + c0;
+                    double v1 = fma(-1e-6, a1, q.y) + c1;
                     if (i >= n || j > n) v0 = 0.0;
                     if (i >= n || j + 1 > n) v1 = 0.0;
                     *reinterpret_cast<double2*>(Paug + i * LDX + j) = make_double2(v0, v1);

@@ -1,13 +1,17 @@
-"""Small fixed workload for ncu: config 2 (B=4096, T=100), a few iterations of the Recursive solver."""
+"""Small fixed workload for ncu: a few iterations of the Recursive solver (c2, c3, c5) or of AL-iLQR (c3al)."""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from ilqr_planner_b200 import synth
-from ilqr_planner_b200.solver import Handle
+from ilqr_planner_b200.solver import Handle, make_al_desc
 nb_iter = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 which = sys.argv[2] if len(sys.argv) > 2 else "c2"
-pb = {"c2": lambda: synth.config2(batch=4096), "c3": lambda: synth.config3(batch=4096), "c5": lambda: synth.config5(batch=4096)}[which]()
+batch = int(sys.argv[3]) if len(sys.argv) > 3 else (16384 if which == "c3al" else 4096)
+pb = {"c2": synth.config2, "c3": synth.config3, "c3al": synth.config3, "c5": synth.config5}[which](batch=batch)
 with Handle(pb) as h:
     h.upload_u0(None)
-    h.run_recursive(nb_iter, True, False)
+    if which == "c3al":
+        h.run_al(make_al_desc(**synth.al_config3()), nb_iter, True, False)
+    else:
+        h.run_recursive(nb_iter, True, False)
     h.synchronize()
     print("launches", h.launch_count())
