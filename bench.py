@@ -267,7 +267,7 @@ def main():
     barrier()
     wall_ms = 1e3 * (time.perf_counter() - t0)
     ms_e2e = e0.elapsed_time(e1)
-    assert np.array_equal(out.cost, out2.cost), "the two pipelined handles disagree"
+    assert args.steps < 2 or np.array_equal(out.cost, out2.cost), "the two pipelined handles disagree"
     t = torch.tensor([ms_e2e, ms_sync], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -320,7 +320,7 @@ def main():
                 "roofline": {"kernel": "riccati_backward (k_backward_n1: DMMA m8n8k4.f64 + DFMA)", "bound": "tensor",
                              "achieved": alg_flops / bw_avg_s / 1e12 if bw_avg_s > 0 else None, "peak": fp64_peak, "unit": "TFLOP/s",
                              "frac": (alg_flops / bw_avg_s / 1e12 / fp64_peak) if (bw_avg_s > 0 and fp64_peak) else None,
-                             "traffic": 212e6 if B == BATCH_PER_GPU else None,
+                             "traffic": 213e6 if B == BATCH_PER_GPU else None,
                              "traffic_note": "dram__bytes_read+write per launch from profiles/ (ncu --set full, B=4096)",
                              "peak_source": "FP64 tensor peak measured in this run: cuBLAS DGEMM 4096^3 via torch.matmul (MEASURED_PEAKS.json has no FP64 entry; "
                                             "the bf16 figure there does not apply to an FP64 path)",
@@ -337,7 +337,9 @@ def main():
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": "first %d problems of the workload, all %d iterations, CPU oracle on %d threads, %.1f s" % (sample, NB_ITER, threads, dt)}
             # same problems -> same answers (sanity, not a timing)
-            line["cpu_gpu_cost_max_rel_diff"] = float(np.nanmax(np.abs(ref.cost - out.cost[:sample]) / np.maximum(np.abs(ref.cost), 1e-300)))
+            rel = np.abs(ref.cost - out.cost[:sample]) / np.maximum(np.abs(ref.cost), 1e-300)
+            line["cpu_gpu_cost_max_rel_diff"] = float(np.nanmax(rel))  # after all 20 iterations, worst of the sample
+            line["cpu_gpu_cost_median_rel_diff"] = float(np.nanmedian(rel))
         print(json.dumps(line), flush=True)
     h.close()
     if world > 1:
