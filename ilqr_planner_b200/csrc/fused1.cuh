@@ -205,13 +205,18 @@ struct BwdN1Smem {
 // backward Riccati pass, A = I, B = dt I.  Augmented layout: column n of the state-indexed matrices carries the
 // vector ([P|p], [Qux|Qu], [Qxx|Qx], [K|d]); rows >= n and columns > n are kept at exact zero.
 // DOF > 0: n = m = DOF at compile time; DOF == 0: read from the problem.
+// nsub > 0: the warp handles the diagonal block [off, off + nsub) of a problem whose tasks touch disjoint joint ranges
+// (composite robots, C5): l_xx, R and the dynamics are block diagonal there, so P, Quu and K are — in the reference's dense
+// arithmetic too, where the off-diagonal blocks are sums and products of exact zeros — and the pass splits into
+// independent passes per block; strides stay those of the full state.
 template <int NT, int DOF>
-__device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work& W, int b, int lane, double* wsmem) {
+__device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work& W, int b, int lane, double* wsmem, const int off = 0, const int nsub = 0) {
     using S = BwdN1Smem<NT>;
     constexpr int LD = S::LD, SZ = S::SZ;
     const int g = lane >> 2, t = lane & 3;
-    const int n = DOF > 0 ? DOF : P.n, m = n, H = P.H;
-    const int ns = (n + 1) & ~1, ms = ns;
+    const int nf = P.n;  // full state size: strides of LX, LXX, K
+    const int n = DOF > 0 ? DOF : (nsub > 0 ? nsub : P.n), m = n, H = P.H;
+    const int ns = (nf + 1) & ~1, ms = ns;
     const double dt = 1.0 * P.dt;  // B = Identity * dt
     double* sQux = wsmem;
     double* sKd = sQux + SZ;
@@ -219,10 +224,10 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
 
     double Rrow[NT];
 #pragma unroll
-    for (int rt = 0; rt < NT; rt++) Rrow[rt] = (8 * rt + g < m) ? P.r_diag[8 * rt + g] : 0.0;
+    for (int rt = 0; rt < NT; rt++) Rrow[rt] = (8 * rt + g < m) ? P.r_diag[off + 8 * rt + g] : 0.0;
 
-    const double* Xb = W.X + (size_t)b * H * ns;
-    const double* Ub = W.U + (size_t)b * (H - 1) * ms;
+    const double* Xb = W.X + (size_t)b * H * ns + off;
+    const double* Ub = W.U + (size_t)b * (H - 1) * ms + off;
     const int S_kp = P.n_kp_steps;
 
     // joint limits of the first limit-carrying task live in registers (weight 0 -> +-inf); further tasks: slow loop
@@ -239,16 +244,16 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
         const int i = 8 * rt + g;
         lmx[rt] = INFINITY;
         lmn[rt] = -INFINITY;
-        if (l0 >= 0 && i < n && P.tasks[l0].limit_weight[i] != 0) {
-            lmx[rt] = P.tasks[l0].state_max[i];
-            lmn[rt] = P.tasks[l0].state_min[i];
+        if (l0 >= 0 && i < n && P.tasks[l0].limit_weight[off + i] != 0) {
+            lmx[rt] = P.tasks[l0].state_max[off + i];
+            lmn[rt] = P.tasks[l0].state_min[off + i];
         }
     }
 
     // e += [l_xx | l_x] of keypoint step index s (k_kp_derivs / k_forward_n1 wrote them)    System.cpp:252-260,290-296
     auto add_kp = [&](double (&e)[NT][NT][2], int s) {
-        const double* lx = W.LX + ((size_t)b * S_kp + s) * n;
-        const double* lxx = W.LXX + ((size_t)b * S_kp + s) * n * n;
+        const double* lx = W.LX + ((size_t)b * S_kp + s) * nf + off;
+        const double* lxx = W.LXX + ((size_t)b * S_kp + s) * nf * nf + (size_t)off * nf + off;
 #pragma unroll
         for (int rt = 0; rt < NT; rt++) {
             const int i = 8 * rt + g;
@@ -258,7 +263,7 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
                 for (int h = 0; h < 2; h++) {
                     const int j = 8 * ct + 2 * t + h;
                     if (i < n) {
-                        if (j < n) e[rt][ct][h] += lxx[i * n + j];
+                        if (j < n) e[rt][ct][h] += lxx[i * nf + j];
                         else if (j == n) e[rt][ct][h] += lx[i];
                     }
                 }
@@ -291,7 +296,7 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
                     const int i = 8 * rt + g;
                     if (i < n) {
                         bool act;
-                        const double q = limit_q(tk, i, xr[rt], act);
+                        const double q = limit_q(tk, off + i, xr[rt], act);
                         if (act) add_lq(e, rt, q);
                     }
                 }
@@ -325,10 +330,10 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
     load_rows(Ub, ms, H - 2, m, un);
     load_rows(Xb, ns, H - 2, n, xn);
     bool spd = true;
-    double* Kg = W.K + ((size_t)b * (H - 1) + (H - 2)) * m * ns;  // walks backwards with k
-    double* dg = W.d + ((size_t)b * (H - 1) + (H - 2)) * ms;
+    double* Kg = W.K + ((size_t)b * (H - 1) + (H - 2)) * nf * ns + (size_t)off * ns + off;  // walks backwards with k
+    double* dg = W.d + ((size_t)b * (H - 1) + (H - 2)) * ms + off;
 
-    for (int k = H - 2; k >= 0; k--, Kg -= m * ns, dg -= ms) {
+    for (int k = H - 2; k >= 0; k--, Kg -= nf * ns, dg -= ms) {
         double u[NT], x[NT];
 #pragma unroll
         for (int rt = 0; rt < NT; rt++) {
@@ -398,7 +403,10 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
 #pragma unroll
                 for (int ct = 0; ct < NT; ct++) {
                     const int j = 8 * ct + 2 * t;
-                    if (j < ns) *reinterpret_cast<double2*>(Kg + i * ns + j) = make_double2(Kd[rt][ct][0], j + 1 < n ? Kd[rt][ct][1] : 0.0);
+                    if (nsub > 0) {  // a diagonal block: its own columns only (the offset may be odd: scalar stores)
+                        if (j < n) Kg[i * ns + j] = Kd[rt][ct][0];
+                        if (j + 1 < n) Kg[i * ns + j + 1] = Kd[rt][ct][1];
+                    } else if (j < ns) *reinterpret_cast<double2*>(Kg + i * ns + j) = make_double2(Kd[rt][ct][0], j + 1 < n ? Kd[rt][ct][1] : 0.0);
                     if (j == n) dg[i] = Kd[rt][ct][0];
                     else if (j + 1 == n) dg[i] = Kd[rt][ct][1];
                 }
@@ -439,7 +447,25 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
             }
         __syncwarp();  // shared operands are rewritten by the next step
     }
-    if (!__all_sync(0xffffffffu, spd) && lane == 0) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
+    if (!__all_sync(0xffffffffu, spd) && lane == 0) atomicOr(W.status + b, ILQRB_ST_QUU_NOT_SPD);
+}
+
+// diagonal blocks of the state that no task couples (ilqrb_api.cu: find_state_blocks)
+struct StateBlocks {
+    int nblk, off[4], size[4];
+};
+
+// one warp per (problem, diagonal block): see backward_n1_body
+template <int DOF, int WARPS, int MINB>
+__global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1_blocks(const DevProblem* __restrict__ Pp, Work W, int b0, int nB, StateBlocks sb) {
+    extern __shared__ double smem[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int w = blockIdx.x * WARPS + wid;
+    const int bl = w / sb.nblk, blk = w - bl * sb.nblk;
+    if (bl >= nB) return;
+    const int b = b0 + bl;
+    if (W.done[b]) return;
+    backward_n1_body<1, DOF>(*Pp, W, b, lane, smem + (size_t)wid * BwdN1Smem<1>::PER_WARP, sb.off[blk], sb.size[blk]);
 }
 
 template <int NT, int DOF, int WARPS, int MINB>

@@ -182,6 +182,40 @@ def config5(batch=65536, horizon=100, dt=0.1, offset=0):
     return ProblemBatch(cabi.SYS_POS_ORN, 1, horizon, dt, 14, robots, tasks, R, q0, np.zeros_like(q0))
 
 
+def _truncated_chain(dof):
+    segs, nj = [], 0
+    for sg in panda_chain():
+        segs.append(sg)
+        nj += int(sg["joint_type"] != cabi.JOINT_FIXED)
+        if nj == dof:
+            break
+    return segs
+
+
+def config5_uneven(batch=16, horizon=60, dt=0.1, offset=0, dofs=(5, 4), limits=True):
+    """parity-test shape: composite of two truncated chains of different size (odd block offset, runtime block sizes of
+    the block-diagonal backward pass), soft joint limits tight enough to be violated on the first arm"""
+    n = sum(dofs)
+    d = _draws(9, offset, offset + batch, [("q0", -0.4, 0.4, n), ("t1", -0.6, 0.6, n)])
+    q0 = np.concatenate([PANDA_Q0[:k] for k in dofs]) + d["q0"]
+    Q = np.diag([1, 1, 1, .1, .1, .1])
+    R = np.ones(n) * 1e-5
+    tasks, robots, at = [], [], 0
+    for a, k in enumerate(dofs):
+        segs = _truncated_chain(k)
+        sl = slice(at, at + k)
+        tg = _posorn_targets(segs, q0[:, sl], [d["t1"][:, sl]])
+        kw = {}
+        if limits and a == 0:
+            center = np.concatenate([PANDA_Q0[:j] for j in dofs])
+            kw = dict(state_max=center + 0.55, state_min=center - 0.55, limit_weight=np.ones(n, dtype=np.int32))
+        tasks.append(TaskSpec(kp_timestep=[horizon // 2 - 1 if a == 0 else horizon - 1], kp_target=tg, kp_precision=np.array([[Q]]), r_diag=R,
+                              robot=a, joint_offset=at, **kw))
+        robots.append(RobotSpec(cabi.ROBOT_KDL, k, segs))
+        at += k
+    return ProblemBatch(cabi.SYS_POS_ORN, 1, horizon, dt, n, robots, tasks, R, q0, np.zeros_like(q0))
+
+
 def config1(batch=1, horizon=50, dt=0.1, offset=0):
     """C1: Robot2D 3-link, position task, single integrator"""
     lengths = np.array([0.4, 0.3, 0.2])

@@ -143,6 +143,23 @@ def test_config5_dual_arm(oracle_lib):
     _check_recursive(synth.config5(batch=16), None, 6, oracle_lib)
 
 
+def test_composite_uneven_blocks(oracle_lib):
+    """block-diagonal backward pass (one warp per problem and per group of joints no task couples) with runtime block
+    sizes and an odd block offset; then with soft joint limits that the initial controls violate over most of the horizon.
+    The limit cases run 2 iterations: a quadratic limit penalty puts the next iterate on the limit itself, after which
+    `x > limit` is decided by rounding in any implementation (the reference's too)."""
+    from ilqr_planner_b200 import synth
+    _check_recursive(synth.config5_uneven(batch=16, limits=False), None, 6, oracle_lib)
+    _check_recursive(synth.config5_uneven(batch=8, dofs=(3, 2, 4), limits=False), None, 5, oracle_lib)
+    for pb in (synth.config5_uneven(batch=16, limits=True), synth.config5_uneven(batch=8, dofs=(5,), limits=True)):
+        u0 = np.full((pb.batch, pb.horizon - 1, pb.m), 0.3)
+        u0[:, :, ::2] *= -1
+        for nit in (1, 2):
+            out, ref = _check_recursive(pb, u0, nit, oracle_lib)
+        X = ref.X.reshape(pb.batch, pb.horizon, -1)
+        assert ((X > pb.tasks[0].state_max) | (X < pb.tasks[0].state_min)).any(), "the limits of this test must be active"
+
+
 def test_time_system_recursive(oracle_lib):
     from ilqr_planner_b200 import synth
     pb = synth.config4(batch=8, horizon=60)
