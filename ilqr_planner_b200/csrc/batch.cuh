@@ -473,6 +473,104 @@ __global__ void __launch_bounds__(256) k_batch_chol(Work W, BatchDev BW, int b0)
     if (tid == 0 && s_bad) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
 }
 
+// Left-looking variant of the same factorisation (default).  The right-looking kernel above reads and rewrites every
+// trailing 64x64 block once per panel (96 KB of traffic per 0.5 Mflop block product; at C4, N = 1592, that is 250 MB per
+// problem and iteration with 6 GB of matrices in flight, i.e. HBM traffic, next to the DMMA work).  Here block (I, J)
+// accumulates  A(I,J) - sum_k L(I,k) L(J,k)^T  in registers over all finished panels k < J (two 32 KB operand loads per
+// block product, the row panel L(J,k) shared by all I of the column), is read and written once, then the column is
+// finished: diagonal block factored in shared memory, its inverse kept there, L(I,J) = C Linv^T for the blocks below.
+__global__ void __launch_bounds__(256, 2) k_batch_chol_ll(Work W, BatchDev BW, int b0) {
+    extern __shared__ double sm[];
+    double* sD = sm;                    // diagonal block, its factor, then the factor's inverse for the rest of the column
+    double* sX = sD + 64 * CH_LD;       // L(I,k) ; then the updated block C
+    double* sY = sX + 64 * CH_LD;       // L(J,k)
+    const int bl = blockIdx.x, b = b0 + bl;
+    if (W.done[b]) return;
+    const int Np = BW.Np, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, t = lane & 3;
+    double* A = BW.A + (size_t)bl * Np * Np;
+    __shared__ int s_bad;
+    if (tid == 0) s_bad = 0;
+    for (int J0 = 0; J0 < Np; J0 += CH_NB) {
+        for (int I0 = J0; I0 < Np; I0 += 64) {
+            const bool diag = (I0 == J0);
+            double c[8][2];
+#pragma unroll
+            for (int ct = 0; ct < 8; ct++) c[ct][0] = c[ct][1] = 0.0;
+            for (int k0 = 0; k0 < J0; k0 += CH_NB) {
+                __syncthreads();  // the previous product is done with sX, sY
+                ch_load64(sX, A + (size_t)I0 * Np + k0, Np, tid);
+                if (!diag) ch_load64(sY, A + (size_t)J0 * Np + k0, Np, tid);
+                __syncthreads();
+                const double* sB = diag ? sX : sY;
+                double a[16];
+#pragma unroll
+                for (int ks = 0; ks < 16; ks++) a[ks] = sX[(8 * warp + g) * CH_LD + 4 * ks + t];
+#pragma unroll
+                for (int ct = 0; ct < 8; ct++) {
+                    if (diag && ct > warp) continue;  // lower triangle only
+#pragma unroll
+                    for (int ks = 0; ks < 16; ks++) dmma884(c[ct][0], c[ct][1], a[ks], sB[(8 * ct + g) * CH_LD + 4 * ks + t]);
+                }
+            }
+            __syncthreads();
+            // C = A(I,J) - sum, into shared memory (the diagonal block into sD, the others into sX)
+            double* sC = diag ? sD : sX;
+#pragma unroll
+            for (int ct = 0; ct < 8; ct++) {
+                const double2 o = *reinterpret_cast<const double2*>(A + (size_t)(I0 + 8 * warp + g) * Np + J0 + 8 * ct + 2 * t);
+                sC[(8 * warp + g) * CH_LD + 8 * ct + 2 * t] = o.x - c[ct][0];
+                sC[(8 * warp + g) * CH_LD + 8 * ct + 2 * t + 1] = o.y - c[ct][1];
+            }
+            __syncthreads();
+            if (diag) {
+                // factor the diagonal block (lower part)
+                for (int j = 0; j < 64; j++) {
+                    __syncthreads();  // rank-1 update of step j-1 complete
+                    const double djj = sD[j * CH_LD + j];
+                    __syncthreads();  // everybody holds the pivot before it is overwritten
+                    const double d = sqrt(djj);
+                    if (tid == 0) {
+                        if (!(djj > 0.0)) s_bad = 1;
+                        sD[j * CH_LD + j] = d;
+                    }
+                    if (tid > j && tid < 64) sD[tid * CH_LD + j] /= d;
+                    __syncthreads();
+                    for (int e = tid; e < 64 * 64; e += 256) {
+                        const int i = e >> 6, k = e & 63;
+                        if (k > j && k <= i) sD[i * CH_LD + k] -= sD[i * CH_LD + j] * sD[k * CH_LD + j];
+                    }
+                }
+                __syncthreads();
+                // write the factor back (upper part of the block zeroed) ; Linv into sY by forward substitution, one column per thread
+                for (int e = tid; e < 64 * 64; e += 256) {
+                    const int i = e >> 6, k = e & 63;
+                    const double v = (k <= i) ? sD[i * CH_LD + k] : 0.0;
+                    sD[i * CH_LD + k] = v;
+                    A[(size_t)(J0 + i) * Np + J0 + k] = v;
+                }
+                __syncthreads();
+                if (tid < 64) {
+                    const int j = tid;  // column j of the inverse: L x = e_j
+                    for (int i = 0; i < 64; i++) {
+                        double acc = (i == j) ? 1.0 : 0.0;
+                        for (int k = j; k < i; k++) acc -= sD[i * CH_LD + k] * sY[k * CH_LD + j];
+                        sY[i * CH_LD + j] = (i < j) ? 0.0 : acc / sD[i * CH_LD + i];
+                    }
+                }
+                __syncthreads();
+                for (int e = tid; e < 64 * 64; e += 256) sD[(e >> 6) * CH_LD + (e & 63)] = sY[(e >> 6) * CH_LD + (e & 63)];
+                __syncthreads();
+            } else {
+                // L(I,J) = C Linv^T
+                ch_xyT<false>(A + (size_t)I0 * Np + J0, Np, sX, sD, 1.0, false, warp, lane);
+            }
+        }
+    }
+    __syncthreads();
+    if (tid == 0 && s_bad) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // du = (L L^T)^-1 rhs : forward then backward substitution, one CTA (256 threads) per problem, 64-wide blocks.
 __global__ void __launch_bounds__(256) k_batch_trsv(Work W, BatchDev BW, int b0) {
@@ -767,8 +865,10 @@ inline int batch_run(cudaStream_t st, const DevProblem& P, const DevProblem* dp,
     static bool attr_set = false;
     const size_t smem_chol = 3 * 64 * CH_LD * sizeof(double), smem_trsv = (64 * CH_LD + Np) * sizeof(double);
     const size_t smem_asm = ((size_t)Sn * Sr + (size_t)Sn * Sn + Sn + H) * sizeof(double), smem_cp = (2 * (size_t)Sn * std::max(nw, 1) + (size_t)nw * (nw + 1)) * sizeof(double);
+    static const bool chol_right_looking = getenv("ILQRB_CHOL_RL") != nullptr;  // A/B switch: the first (right-looking) kernel
     if (!attr_set) {
         BCU(cudaFuncSetAttribute(k_batch_chol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_chol));
+        BCU(cudaFuncSetAttribute(k_batch_chol_ll, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_chol));
         attr_set = true;
     }
     if (smem_trsv > 48 * 1024) BCU(cudaFuncSetAttribute(k_batch_trsv, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_trsv));
@@ -789,7 +889,8 @@ inline int batch_run(cudaStream_t st, const DevProblem& P, const DevProblem* dp,
                 k_batch_syrk<<<dim3((unsigned)((Np / 8) * (Np / 64) + 3) / 4, nB), 128, 0, st>>>(dp, W, K, b0);
                 end();
                 begin(3);
-                k_batch_chol<<<nB, 256, smem_chol, st>>>(W, K, b0);
+                if (chol_right_looking) k_batch_chol<<<nB, 256, smem_chol, st>>>(W, K, b0);
+                else k_batch_chol_ll<<<nB, 256, smem_chol, st>>>(W, K, b0);
                 end();
                 begin(3);
                 k_batch_trsv<<<nB, 256, smem_trsv, st>>>(W, K, b0);
