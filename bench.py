@@ -329,6 +329,15 @@ def main():
                 "roofline_hbm": {"kernel": "riccati_backward", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                                  "frac": (achieved / hbm_peak) if achieved else None, "peak_source": peak_src,
                                  "algorithmic_bytes_per_launch": alg_bytes},
+                # second kernel of the iteration: line search + accept (k_forward_n1).  It streams K, d (written by the backward pass), X, U
+                # once and writes X, U once: the byte view against the measured copy peak; it is bound by the latency of its serial 99-step
+                # deviation rollout and the FK chains of the candidates (ncu: 51 % of stall samples on the long scoreboard), not by HBM
+                "roofline_forward": (lambda fms, fn: {"kernel": "linesearch_rollout (k_forward_n1)", "bound": "hbm",
+                                     "achieved": (B * 8.0 * ((H - 1) * (m * n + m) + 2 * (H * n + (H - 1) * m)) / (fms / max(fn, 1) * 1e-3) / 1e9) if fms > 0 else None,
+                                     "peak": hbm_peak, "unit": "GB/s", "peak_source": peak_src,
+                                     "algorithmic_bytes_per_launch": B * 8.0 * ((H - 1) * (m * n + m) + 2 * (H * n + (H - 1) * m)),
+                                     "avg_launch_ms": fms / max(fn, 1), "traffic": 337e6 if B == BATCH_PER_GPU else None,
+                                     "traffic_note": "cold-cache ncu capture (profiles/r1_c2_ncu_full_summary.txt)"})(*prof.get("linesearch_rollout", (0.0, 1))),
                 "kernel_ms_per_solve": {k: v[0] for k, v in prof.items()},
                 "final_cost_mean": float(np.nanmean(all_cost)), "problems_with_nan": int(np.isnan(all_cost).sum())}
         if world == 1 and not args.no_cpu_baseline:
@@ -340,6 +349,9 @@ def main():
             rel = np.abs(ref.cost - out.cost[:sample]) / np.maximum(np.abs(ref.cost), 1e-300)
             line["cpu_gpu_cost_max_rel_diff"] = float(np.nanmax(rel))  # after all 20 iterations, worst of the sample
             line["cpu_gpu_cost_median_rel_diff"] = float(np.nanmedian(rel))
+        rf = line["roofline_forward"]
+        if rf.get("achieved"):
+            rf["frac"] = rf["achieved"] / hbm_peak
         print(json.dumps(line), flush=True)
     h.close()
     if world > 1:
