@@ -340,3 +340,35 @@ def test_double_integrator_runtime_dof_and_active_limits(oracle_lib):
     from ilqr_planner_b200 import synth
     _check_recursive(synth.config3_short(batch=16, tight_limits=False), None, 6, oracle_lib)
     _check_recursive(synth.config3_short(batch=16, tight_limits=True), None, 4, oracle_lib)
+
+
+def test_async_solve_on_two_handles_matches_blocking_call():
+    """ilqrb_solve_recursive_async: batches streamed through two handles (one batch's download overlapping the next
+    batch's solve) return bit for bit what the blocking call returns, for every output buffer"""
+    from ilqr_planner_b200 import synth
+    from ilqr_planner_b200.problem import ResultBuffers
+    pbs = [synth.config2(batch=512, offset=512 * i) for i in range(4)]
+    want = []
+    for pb in pbs:
+        with _handle(pb) as h:
+            want.append(h.solve_recursive(None, 5, True, False))
+    hs = [_handle(pbs[0]), _handle(pbs[1])]
+    try:
+        outs = [ResultBuffers(pbs[0], 5, "recursive", pinned=True), ResultBuffers(pbs[1], 5, "recursive", pinned=True)]
+        u0 = np.zeros((512, 99 * 7))
+        # batches 0 and 1 in flight together; results must equal the blocking ones
+        for k in range(2):
+            hs[k].solve_recursive_async(u0, 5, True, False, out=outs[k])
+        for k in range(2):
+            hs[k].synchronize()
+            for f in ("X", "fX", "U", "K", "d", "cost", "cost_hist", "alpha_hist", "iters", "status"):
+                assert np.array_equal(getattr(outs[k], f), getattr(want[k], f), equal_nan=True), (k, f)
+        # the same handle and buffers reused for a second round after synchronize()
+        for k in range(2):
+            hs[k].solve_recursive_async(u0, 5, True, False, out=outs[k])
+        for k in range(2):
+            hs[k].synchronize()
+            assert np.array_equal(outs[k].K, want[k].K) and np.array_equal(outs[k].cost_hist, want[k].cost_hist)
+    finally:
+        for h in hs:
+            h.close()
