@@ -593,12 +593,22 @@ __global__ void __launch_bounds__(256) k_batch_trsv(Work W, BatchDev BW, int b0)
             if (tid > j && tid < 64) y[k0 + tid] -= sD[tid * CH_LD + j] * y[k0 + j];
             __syncthreads();
         }
-        for (int i = k0 + 64 + tid; i < Np; i += 256) {
-            const double* row = A + (size_t)i * Np + k0;
-            double acc = 0.0;
-#pragma unroll 8
-            for (int k = 0; k < 64; k++) acc += row[k] * y[k0 + k];
-            y[i] -= acc;
+        // rows below the block: 8 lanes per row, 64 contiguous bytes each (whole 128-byte lines per row), reduced by shuffles
+        {
+            const int l8 = tid & 7;
+            double yk[8];
+#pragma unroll
+            for (int q = 0; q < 8; q++) yk[q] = y[k0 + 8 * l8 + q];
+            for (int i0 = k0 + 64; i0 < Np; i0 += 32) {  // Np is a multiple of 64: all 32 rows of a pass exist
+                const int i = i0 + (tid >> 3);
+                const double2* row = reinterpret_cast<const double2*>(A + (size_t)i * Np + k0 + 8 * l8);
+                const double2 v0 = row[0], v1 = row[1], v2 = row[2], v3 = row[3];
+                double acc = v0.x * yk[0] + v0.y * yk[1] + v1.x * yk[2] + v1.y * yk[3] + v2.x * yk[4] + v2.y * yk[5] + v3.x * yk[6] + v3.y * yk[7];
+                acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+                acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+                acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+                if (l8 == 0) y[i] -= acc;
+            }
         }
     }
     // L^T x = z
