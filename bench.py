@@ -361,6 +361,26 @@ def main():
             rel = np.abs(ref.cost - out.cost[:sample]) / np.maximum(np.abs(ref.cost), 1e-300)
             line["cpu_gpu_cost_max_rel_diff"] = float(np.nanmax(rel))  # after all 20 iterations, worst of the sample
             line["cpu_gpu_cost_median_rel_diff"] = float(np.nanmedian(rel))
+            # the parity tests' measure: per-iteration cost traces against the scale of the trace, and the accepted step sequences
+            gh, rh = out.cost_hist[:sample], ref.cost_hist
+            line["cpu_gpu_trace_max_diff_over_trace_scale"] = float(np.nanmax(np.abs(gh - rh) / np.nanmax(np.abs(rh), axis=1, keepdims=True)))
+            # the oracle reports each iteration's line-search decision margin; below the 1e-9 cost tolerance a decision is a
+            # tie made by rounding (tests/test_gpu_parity.py: decisive_prefix), after which two runs may take different branches
+            ga, ra = out.alpha_hist[:sample], ref.alpha_hist
+            tie = ~(ref.margin_hist >= 1e-9) | np.isnan(ref.cost_hist)
+            first_tie = np.where(tie.any(axis=1), tie.argmax(axis=1), NB_ITER)
+            upto = np.array([np.array_equal(ga[i, :first_tie[i]], ra[i, :first_tie[i]]) for i in range(sample)])
+            full = np.all((ga == ra) | (np.isnan(ga) & np.isnan(ra)), axis=1)
+            line["cpu_gpu_step_sequences"] = {"problems": sample, "identical_up_to_first_tie": int(upto.sum()), "identical_all_%d_iterations" % NB_ITER: int(full.sum()),
+                                              "problems_with_a_tie": int(tie.any(axis=1).sum())}
+            # where a sequence parts before a declared tie: how far the cost has fallen by then (a cost 1e-6 of its start is a sum of
+            # squared residuals whose 1e-12 trajectory differences move it by more than the 1e-9 margin)
+            early = np.nonzero(~upto)[0]
+            if early.size:
+                it_d = [int(np.argmax(~((ga[i] == ra[i]) | (np.isnan(ga[i]) & np.isnan(ra[i]))))) for i in early]
+                fall = [float(ref.cost_hist[i, max(k - 1, 0)] / np.nanmax(ref.cost_hist[i])) for i, k in zip(early, it_d)]
+                line["cpu_gpu_step_sequences"]["parting_before_a_tie"] = {"count": int(early.size), "earliest_iteration": int(min(it_d)) + 1,
+                                                                           "largest_cost_over_trace_scale_when_parting": max(fall)}
         rf = line["roofline_forward"]
         if rf.get("achieved"):
             rf["frac"] = rf["achieved"] / hbm_peak
