@@ -372,3 +372,28 @@ def test_async_solve_on_two_handles_matches_blocking_call():
     finally:
         for h in hs:
             h.close()
+
+
+def test_dense_two_tile_backward_pass_still_matches():
+    """ILQRB_NO_BLOCKS=1 (read once per process, hence the subprocess): the dense 16x16 backward kernel that the
+    block-diagonal pass replaces for composite robots stays correct and gives the same answer as the block pass"""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r)\n"
+        "from ilqr_planner_b200 import synth\n"
+        "from ilqr_planner_b200.solver import Handle\n"
+        "from oracle import oracle\n"
+        "pb = synth.config5(batch=8)\n"
+        "with Handle(pb, device=0) as h: out = h.solve_recursive(None, 5, True, False)\n"
+        "ref = oracle.solve_recursive(pb, None, 5, True, False, threads=8)\n"
+        "sc = np.abs(ref.cost_hist).max()\n"
+        "assert np.abs(out.cost_hist - ref.cost_hist).max() / sc < 1e-9, np.abs(out.cost_hist - ref.cost_hist).max() / sc\n"
+        "assert np.array_equal(out.alpha_hist, ref.alpha_hist)\n"
+        "assert np.abs(out.K - ref.K).max() / np.abs(ref.K).max() < 1e-8\n"
+        "print('dense ok')\n" % root)
+    env = dict(os.environ, ILQRB_NO_BLOCKS="1")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "dense ok" in r.stdout, r.stdout + r.stderr
