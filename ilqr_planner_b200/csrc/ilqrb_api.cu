@@ -69,6 +69,7 @@ struct ilqrb_handle_s {
     int64_t prof_n[ILQRB_PROF_SLOTS] = {0};
     int64_t launches = 0;
     bool downloaded = false;  // the last run already sent its results to the host (per group)
+    bool streaming = false;   // the current solve came through ilqrb_solve_recursive_async
     // problem groups of the fast path (one stream each)
     static constexpr int MAX_GROUPS = 8;
     int n_groups = 0;
@@ -671,7 +672,10 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
         // The batch is split into G groups of problems, each on its own stream, the first backward pass of group g+1
         // held back until group g has finished its own: from then on the FP64-bound backward pass of one group shares
         // the SMs with the latency-bound forward pass of another.  (Profiling mode: one group, per-kernel event pairs.)
-        int G = h->prof ? 1 : (int)env_uint("ILQRB_GROUPS", out_async ? 8 : 3);
+        // measured on B200 (C2, B = 4096; ILQRB_GROUPS sweeps in DESIGN.md): 3 groups for device-resident results, 8 when one blocking call
+        // must hide its own downloads, 5 when the caller streams batches through two handles (the other handle's solve covers the
+        // downloads, and fewer, larger groups keep the kernels closer to a full wave)
+        int G = h->prof ? 1 : (int)env_uint("ILQRB_GROUPS", out_async ? (h->streaming ? 5 : 8) : 3);
         if (G > ilqrb_handle_s::MAX_GROUPS) G = ilqrb_handle_s::MAX_GROUPS;
         if (G < 1 || B < 64 * G) G = 1;
         if (G == 1) {
@@ -1045,7 +1049,10 @@ int ilqrb_solve_recursive_async(ilqrb_handle h, const double* U0, const ilqrb_so
     if (!h || !out) return fail(ILQRB_EINVAL, "null argument");
     if ((rc = ilqrb_upload_u0(h, U0))) return rc;
     h->downloaded = false;
-    if ((rc = run_recursive_like(h, nullptr, opts, out))) return rc;
+    h->streaming = true;
+    rc = run_recursive_like(h, nullptr, opts, out);
+    h->streaming = false;
+    if (rc) return rc;
     if (h->downloaded) return 0;  // every group has queued its own device-to-host copies; ilqrb_synchronize waits for them
     return ilqrb_download(h, out);
 }
