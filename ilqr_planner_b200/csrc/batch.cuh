@@ -29,44 +29,13 @@
 #include <string>
 #include <vector>
 
+#include "batch_types.hpp"
+#include "handle.hpp"
 #include "kin.cuh"
-#include "recursive.cuh"
+#include "wmat.cuh"
+#include "work.cuh"
 
 namespace ilqrb {
-
-constexpr int BNC = NCAND + 1;  // candidate 0 = current controls (alpha = 0), 1..11 = alpha 1, 1/2, .., 2^-10
-
-struct BatchDev {  // POD view passed to the kernels
-    // sizes
-    int N = 0, Np = 0, S = 0, Sn = 0, SnP = 0, Sr = 0, nw = 0, cp = 0, chunk = 0;  // Np = N padded to 64, SnP = Sn padded to 4
-    // S = distinct keypoint timesteps (row blocks of J, L, Su: Sn = S n); nk = keypoints incl. duplicates (slots of e, Q: Sr = nk r)
-    int nk = 0;
-    int vp[MAX_KP_STEPS];   // slot -> timestep (sorted, duplicates kept)
-    int vds[MAX_KP_STEPS];  // slot -> index of that timestep in P.kp_steps
-    // whole batch
-    double* u = nullptr;      // [B][N]
-    double* du = nullptr;     // [B][N]
-    double* cc = nullptr;     // [B][BNC] candidate costs (0: cost0)
-    double* Qfull = nullptr;  // [Sr][Sr] shared precision override, or nullptr
-    double* psi = nullptr;    // [N][nw]
-    double* psiRpsi = nullptr;  // [nw][nw]  Psi^T R Psi
-    // per chunk of problems
-    double* X = nullptr;    // [C][H][n]  states of the current controls (double-integrator time systems: B needs the post-step velocity)
-    double* Jt = nullptr;   // [C][S][r][n]
-    double* e = nullptr;    // [C][Sr]
-    double* Ld = nullptr;   // [C][S][n]  diagonal of L (0 / penalty)
-    double* ql = nullptr;   // [C][S][n]
-    double* Wm = nullptr;   // [C][Sn][Sn]
-    double* g = nullptr;    // [C][Sn]
-    double* Su = nullptr;   // [C][SnP][Np]  (rows >= Sn and columns >= N are zero)
-    double* T = nullptr;    // [C][SnP][Np]
-    double* A = nullptr;    // [C][Np][Np]
-    double* rhs = nullptr;  // [C][Np]
-};
-struct BatchWork : BatchDev {
-    bool allocated = false;
-    std::vector<void*> allocs;
-};
 
 __device__ __forceinline__ double batch_alpha(int c) { return c == 0 ? 0.0 : 1.0 / (double)(1 << (c - 1)); }
 
@@ -787,14 +756,14 @@ inline int batch_alloc(BatchWork& BW, T** p, size_t count, std::string& err) {
     *p = (T*)q;
     return 0;
 }
-inline void batch_free(BatchWork& BW) {
+inline void batch_free_impl(BatchWork& BW) {
     for (void* p : BW.allocs) cudaFree(p);
     BW = BatchWork();
 }
 
 // solver::BatchILQR::solve / BatchILQRCP::solve for the whole batch, chunk by chunk (the dense N x N workspaces of a
 // chunk must fit the workspace budget, ILQRB_BATCH_WS_GB, default 24 GB).  `begin(slot)` / `end()` bracket every launch.
-inline int batch_run(cudaStream_t st, const DevProblem& P, const DevProblem* dp, Work& W, BatchWork& BW, const ilqrb_batch_desc* bd,
+inline int batch_run(cudaStream_t st, int device, const DevProblem& P, const DevProblem* dp, Work& W, BatchWork& BW, const ilqrb_batch_desc* bd,
                      const ilqrb_solve_opts* opts, std::string& err, std::function<void(int)> begin, std::function<void()> end) {
     // keypoint slots (time-sorted, duplicates kept) and their distinct-step index
     std::vector<int> vp;
@@ -817,7 +786,7 @@ inline int batch_run(cudaStream_t st, const DevProblem& P, const DevProblem* dp,
         err = "Batch solvers: too many keypoint rows";
         return ILQRB_EUNSUPPORTED;
     }
-    if (BW.allocated && (BW.N != N || BW.nw != nw || BW.S != S || BW.nk != nk)) batch_free(BW);
+    if (BW.allocated && (BW.N != N || BW.nw != nw || BW.S != S || BW.nk != nk)) batch_free_impl(BW);
     int rc;
     if (!BW.allocated) {
         BW.N = N; BW.Np = Np; BW.S = S; BW.Sn = Sn; BW.SnP = SnP; BW.Sr = Sr; BW.nw = nw; BW.cp = cp; BW.nk = nk;
@@ -872,18 +841,24 @@ inline int batch_run(cudaStream_t st, const DevProblem& P, const DevProblem* dp,
         BCU(cudaMemsetAsync(W.status, 0, B * sizeof(int), st));
         BCU(cudaMemsetAsync(W.cost0, 0, B * sizeof(double), st));
     }
-    static bool attr_set = false;
     const size_t smem_chol = 3 * 64 * CH_LD * sizeof(double), smem_trsv = (64 * CH_LD + Np) * sizeof(double);
     const size_t smem_asm = ((size_t)Sn * Sr + (size_t)Sn * Sn + Sn + H) * sizeof(double), smem_cp = (2 * (size_t)Sn * std::max(nw, 1) + (size_t)nw * (nw + 1)) * sizeof(double);
     static const bool chol_right_looking = getenv("ILQRB_CHOL_RL") != nullptr;  // A/B switch: the first (right-looking) kernel
-    if (!attr_set) {
-        BCU(cudaFuncSetAttribute(k_batch_chol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_chol));
-        BCU(cudaFuncSetAttribute(k_batch_chol_ll, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_chol));
-        attr_set = true;
+    {
+        static DynSmem a_chol, a_chol_ll, a_trsv, a_asm, a_cp;  // per-device "raised to" values
+        auto ens = [&](DynSmem& a, auto kern, size_t smem) -> int {
+            if (smem <= 48 * 1024) return 0;
+            const bool tracked = device >= 0 && device < MAX_DEVICES;
+            if (!tracked || smem > a.raised[device].load(std::memory_order_relaxed)) {
+                BCU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                if (tracked) a.raised[device].store(smem, std::memory_order_relaxed);
+            }
+            return 0;
+        };
+        if ((rc = ens(a_chol, k_batch_chol, smem_chol)) || (rc = ens(a_chol_ll, k_batch_chol_ll, smem_chol)) || (rc = ens(a_trsv, k_batch_trsv, smem_trsv)) ||
+            (rc = ens(a_asm, k_batch_assemble, smem_asm)) || (rc = ens(a_cp, k_batch_cp, smem_cp)))
+            return rc;
     }
-    if (smem_trsv > 48 * 1024) BCU(cudaFuncSetAttribute(k_batch_trsv, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_trsv));
-    if (smem_asm > 48 * 1024) BCU(cudaFuncSetAttribute(k_batch_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_asm));
-    if (smem_cp > 48 * 1024) BCU(cudaFuncSetAttribute(k_batch_cp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cp));
     for (int b0 = 0; b0 < B; b0 += BW.chunk) {
         const int nB = std::min(BW.chunk, B - b0);
         const unsigned fp_grid = (unsigned)(((size_t)nB * BNC + 63) / 64);

@@ -21,7 +21,8 @@
 //                   steps of the accepted trajectory are produced for the next backward pass.
 #pragma once
 #include "kin_lean.cuh"
-#include "recursive.cuh"
+#include "wmat.cuh"
+#include "work.cuh"
 
 namespace ilqrb {
 

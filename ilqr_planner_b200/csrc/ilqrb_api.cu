@@ -1,6 +1,6 @@
 // ilqrb_api.cu — C ABI of libilqrb.so (include/ilqrb.h): handle management, descriptor flattening, kernel
 // launch sequences of the four solvers, result download.  Host logic only orchestrates; all arithmetic of the
-// solve path runs in the CUDA kernels of recursive.cuh / batch.cuh.  There is no CPU fallback.
+// solve path runs in the CUDA kernels behind the launchers of handle.hpp.  There is no CPU fallback.
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -11,126 +11,37 @@
 #include <string>
 #include <vector>
 
-#include "batch.cuh"
-#include "fused1.cuh"
-#include "fused2.cuh"
-#include "recursive.cuh"
+#include "handle.hpp"
 
 using namespace ilqrb;
 
 namespace {
-
 thread_local std::string g_err;
+const char* kProfNames[ILQRB_PROF_SLOTS] = {"rollout_init", "kp_derivs",  "riccati_backward", "linesearch_rollout", "accept",     "final_fx",
+                                            "batch_fp",     "batch_assemble", "batch_syrk",    "batch_cholesky",     "batch_linesearch", "misc"};
+}  // namespace
 
+namespace ilqrb {
 int fail(int code, const std::string& msg) {
     g_err = msg;
     return code;
 }
+}  // namespace ilqrb
 
-#define CU(call)                                                                                              \
-    do {                                                                                                      \
-        cudaError_t e_ = (call);                                                                              \
-        if (e_ != cudaSuccess) return fail(ILQRB_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
-    } while (0)
-
-enum ProfSlot { PS_ROLLOUT_INIT = 0, PS_KP_DERIVS, PS_BACKWARD, PS_LINESEARCH, PS_ACCEPT, PS_FINAL, PS_BATCH_FP, PS_BATCH_ASM, PS_BATCH_SYRK, PS_BATCH_CHOL, PS_BATCH_LS, PS_MISC };
-const char* kProfNames[ILQRB_PROF_SLOTS] = {"rollout_init", "kp_derivs",  "riccati_backward", "linesearch_rollout", "accept",     "final_fx",
-                                            "batch_fp",     "batch_assemble", "batch_syrk",    "batch_cholesky",     "batch_linesearch", "misc"};
-
-}  // namespace
-
-struct ilqrb_handle_s {
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    bool own_stream = false;
-    DevProblem hp;          // host copy holding device pointers
-    DevProblem* dp = nullptr;
-    ilqrb_dims dims;
-    Work W;
-    std::vector<void*> allocs;
-    int cap_iter = 0;
-    int last_nb_iter = 0;
-    int last_solver = 0;  // 1 recursive, 2 al, 3 batch
-    double* d_fX = nullptr;
-    double* d_pack = nullptr;  // staging for packed downloads
-    size_t pack_elems = 0;
-    double* d_alA = nullptr;
-    double* d_alb = nullptr;
-    size_t alA_elems = 0, alb_elems = 0;
-    std::vector<double> h_lam0;
-    BatchWork BW;
-    // profiling
-    bool prof = false;
-    std::vector<cudaEvent_t> ev_pool;
-    struct Rec { int slot; cudaEvent_t a, b; };
-    std::vector<Rec> recs;
-    size_t ev_used = 0;
-    double prof_ms[ILQRB_PROF_SLOTS] = {0};
-    int64_t prof_n[ILQRB_PROF_SLOTS] = {0};
-    int64_t launches = 0;
-    bool downloaded = false;  // the last run already sent its results to the host (per group)
-    bool streaming = false;   // the current solve came through ilqrb_solve_recursive_async
-    // problem groups of the fast path (one stream each)
-    static constexpr int MAX_GROUPS = 8;
-    int n_groups = 0;
-    cudaStream_t gstream[MAX_GROUPS] = {nullptr};
-    cudaEvent_t ev_start = nullptr, ev_stagger[MAX_GROUPS] = {nullptr}, ev_done[MAX_GROUPS] = {nullptr};
-    int ensure_groups(int G) {
-        if (!ev_start && cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming) != cudaSuccess) return fail(ILQRB_ECUDA, "cudaEventCreate");
-        int least = 0, greatest = 0;
-        cudaDeviceGetStreamPriorityRange(&least, &greatest);  // numerically lower = higher priority
-        for (; n_groups < G; n_groups++) {
-            // earlier groups get higher priority: they finish first and their results travel while later groups compute
-            const int prio = std::min(least, greatest + n_groups);
-            if (cudaStreamCreateWithPriority(&gstream[n_groups], cudaStreamNonBlocking, prio) != cudaSuccess ||
-                cudaEventCreateWithFlags(&ev_stagger[n_groups], cudaEventDisableTiming) != cudaSuccess ||
-                cudaEventCreateWithFlags(&ev_done[n_groups], cudaEventDisableTiming) != cudaSuccess)
-                return fail(ILQRB_ECUDA, "could not create the group streams");
-        }
-        return 0;
+int ilqrb_handle_s::ensure_groups(int G) {
+    if (!ev_start && cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming) != cudaSuccess) return fail(ILQRB_ECUDA, "cudaEventCreate");
+    int least = 0, greatest = 0;
+    cudaDeviceGetStreamPriorityRange(&least, &greatest);  // numerically lower = higher priority
+    for (; n_groups < G; n_groups++) {
+        // earlier groups get higher priority: they finish first and their results travel while later groups compute
+        const int prio = std::min(least, greatest + n_groups);
+        if (cudaStreamCreateWithPriority(&gstream[n_groups], cudaStreamNonBlocking, prio) != cudaSuccess ||
+            cudaEventCreateWithFlags(&ev_stagger[n_groups], cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&ev_done[n_groups], cudaEventDisableTiming) != cudaSuccess)
+            return fail(ILQRB_ECUDA, "could not create the group streams");
     }
-
-    template <class T>
-    int alloc(T** p, size_t count) {
-        void* q = nullptr;
-        cudaError_t e = cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T));
-        if (e != cudaSuccess) return fail(ILQRB_ENOMEM, std::string("cudaMalloc: ") + cudaGetErrorString(e));
-        allocs.push_back(q);
-        *p = (T*)q;
-        return 0;
-    }
-    cudaEvent_t ev() {
-        if (ev_used == ev_pool.size()) {
-            cudaEvent_t e;
-            cudaEventCreate(&e);
-            ev_pool.push_back(e);
-        }
-        return ev_pool[ev_used++];
-    }
-    void begin(int slot) {
-        launches++;
-        if (!prof) return;
-        Rec r{slot, ev(), ev()};
-        cudaEventRecord(r.a, stream);
-        recs.push_back(r);
-    }
-    void end() {
-        if (!prof) return;
-        cudaEventRecord(recs.back().b, stream);
-    }
-    void resolve() {
-        if (recs.empty()) return;
-        cudaStreamSynchronize(stream);
-        for (auto& r : recs) {
-            float ms = 0;
-            cudaEventElapsedTime(&ms, r.a, r.b);
-            prof_ms[r.slot] += ms;
-            prof_n[r.slot]++;
-        }
-        recs.clear();
-        ev_used = 0;
-    }
-};
+    return 0;
+}
 
 namespace {
 
@@ -191,218 +102,6 @@ int upload(ilqrb_handle h, T** dst, const T* src, size_t count) {
     return 0;
 }
 
-// ---- dispatch over the compiled size classes -------------------------------------------------------------
-int size_class(int n, int m) {  // thread kernels <N, M>
-    if (n <= 8 && m <= 8) return 0;
-    if (n <= 16 && m <= 8) return 1;
-    if (n <= 16 && m <= 16) return 2;
-    return 3;
-}
-#define DISPATCH_NM(cls, CALL)          \
-    switch (cls) {                      \
-        case 0: { CALL(8, 8); } break;  \
-        case 1: { CALL(16, 8); } break; \
-        case 2: { CALL(16, 16); } break;\
-        default: { CALL(32, 16); } break;\
-    }
-
-int tile_class(int n, int m) {  // backward kernel <NXT, NUT>: 8*NXT >= n+1, 8*NUT >= m
-    if (n + 1 <= 8 && m <= 8) return 0;
-    if (n + 1 <= 16 && m <= 8) return 1;
-    if (n + 1 <= 16 && m <= 16) return 2;
-    return 3;
-}
-
-template <int NXT, int NUT, bool TIME, bool AL, int WARPS, int MINB>
-int launch_backward_t(ilqrb_handle h, double penalty_frozen) {
-    using S = BwdSmem<NXT, NUT>;
-    const size_t smem = ((TIME ? WARPS : 1) * S::DYN + (size_t)WARPS * S::PER_WARP) * sizeof(double);
-    auto kern = k_backward<NXT, NUT, TIME, AL, WARPS, MINB>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
-    }
-    const int B = h->hp.B;
-    kern<<<(B + WARPS - 1) / WARPS, 32 * WARPS, smem, h->stream>>>(h->dp, h->W, penalty_frozen);
-    return 0;
-}
-template <bool TIME, bool AL>
-int launch_backward_ta(ilqrb_handle h, double pf) {
-    switch (tile_class(h->hp.n, h->hp.m)) {
-        case 0: return launch_backward_t<1, 1, TIME, AL, 4, 7>(h, pf);
-        case 1: return launch_backward_t<2, 1, TIME, AL, 4, 3>(h, pf);
-        case 2: return launch_backward_t<2, 2, TIME, AL, 4, 2>(h, pf);
-        default: return launch_backward_t<4, 2, TIME, AL, 2, 1>(h, pf);
-    }
-}
-// double-integrator fast backward pass (fused2.cuh): nb_deriv = 2, no time state, no AL terms, dof <= 7
-bool fast_n2_applies(ilqrb_handle h, bool al) {
-    static const bool force_generic = getenv("ILQRB_GENERIC") != nullptr;
-    const DevProblem& P = h->hp;
-    (void)al;
-    return !force_generic && !P.time && P.nb_deriv == 2 && P.dof <= 7 && P.n == 2 * P.dof && P.m == P.dof && h->W.nc <= 32;
-}
-template <int DOF, bool AL, int WARPS, int MINB>
-int launch_backward_n2_t(ilqrb_handle h, double pf) {
-    const size_t smem = (size_t)WARPS * BwdN2Smem::PER_WARP * sizeof(double);
-    auto kern = k_backward_n2<DOF, AL, WARPS, MINB>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
-    }
-    const int B = h->hp.B;
-    kern<<<(B + WARPS - 1) / WARPS, 32 * WARPS, smem, h->stream>>>(h->dp, h->W, 0, B, pf);
-    return 0;
-}
-int launch_backward(ilqrb_handle h, bool al, double pf) {
-    h->begin(PS_BACKWARD);
-    int rc;
-    if (fast_n2_applies(h, al)) {
-        if (al) rc = h->hp.dof == 7 ? launch_backward_n2_t<7, true, 4, 4>(h, pf) : launch_backward_n2_t<0, true, 4, 4>(h, pf);
-        else rc = h->hp.dof == 7 ? launch_backward_n2_t<7, false, 4, 4>(h, pf) : launch_backward_n2_t<0, false, 4, 4>(h, pf);
-    }
-    else if (h->hp.time) rc = al ? launch_backward_ta<true, true>(h, pf) : launch_backward_ta<true, false>(h, pf);
-    else rc = al ? launch_backward_ta<false, true>(h, pf) : launch_backward_ta<false, false>(h, pf);
-    h->end();
-    if (rc) return rc;
-    CU(cudaGetLastError());
-    return 0;
-}
-
-// ---- fast path (fused1.cuh): single integrator, no time state, no AL ---------------------------------------
-bool fast_n1_applies(ilqrb_handle h, bool al) {
-    static const bool forced_generic = getenv("ILQRB_GENERIC") != nullptr;  // A/B switch for tests and profiling
-    const DevProblem& P = h->hp;
-    return !forced_generic && !al && P.nb_deriv == 1 && !P.time && P.n == P.m && P.n + 1 <= 16 &&
-           (size_t)fwd_n1_smem_doubles(P.H, h->W.ns, P.n_kp_steps) * sizeof(double) <= 200 * 1024;
-}
-template <int NT, int DOF, int WARPS, int MINB>
-int launch_backward_n1_t(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
-    const size_t smem = (size_t)WARPS * BwdN1Smem<NT>::PER_WARP * sizeof(double);
-    auto kern = k_backward_n1<NT, DOF, WARPS, MINB>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
-    }
-    kern<<<(nB + WARPS - 1) / WARPS, 32 * WARPS, smem, st>>>(h->dp, h->W, b0, nB);
-    return 0;
-}
-// Diagonal blocks of the state that no task couples: every task reads the joints [joint_offset, joint_offset + dof of its
-// robot) only, so l_x / l_xx (and with R diagonal, A = I, B = dt I the whole Riccati recursion) are block diagonal over
-// the connected groups of those ranges.  Returns nblk >= 2 only if the groups tile [0, n) and fit one 8x8 tile each.
-StateBlocks find_state_blocks(const DevProblem& P) {
-    StateBlocks sb{};
-    sb.nblk = 0;
-    static const bool off_switch = getenv("ILQRB_NO_BLOCKS") != nullptr;  // A/B switch for tests and profiling
-    if (off_switch || P.nb_deriv != 1 || P.time || P.n != P.m || P.n_tasks < 2) return sb;
-    int lo[ILQRB_MAX_TASKS], hi[ILQRB_MAX_TASKS], cnt = 0;
-    for (int ti = 0; ti < P.n_tasks; ti++) {
-        const int a = P.tasks[ti].joint_offset, e = a + P.robots[P.tasks[ti].robot].dof;
-        int k = 0;
-        for (; k < cnt; k++)
-            if (a < hi[k] && lo[k] < e) break;  // overlaps group k
-        if (k == cnt) {
-            lo[cnt] = a;
-            hi[cnt] = e;
-            cnt++;
-        } else {
-            lo[k] = std::min(lo[k], a);
-            hi[k] = std::max(hi[k], e);
-        }
-    }
-    for (bool merged = true; merged;) {  // groups that grew into one another
-        merged = false;
-        for (int i = 0; i < cnt && !merged; i++)
-            for (int j = i + 1; j < cnt && !merged; j++)
-                if (lo[i] < hi[j] && lo[j] < hi[i]) {
-                    lo[i] = std::min(lo[i], lo[j]);
-                    hi[i] = std::max(hi[i], hi[j]);
-                    lo[j] = lo[cnt - 1];
-                    hi[j] = hi[cnt - 1];
-                    cnt--;
-                    merged = true;
-                }
-    }
-    if (cnt < 2 || cnt > 4) return sb;
-    for (int i = 0; i < cnt; i++)  // sort by offset
-        for (int j = i + 1; j < cnt; j++)
-            if (lo[j] < lo[i]) {
-                std::swap(lo[i], lo[j]);
-                std::swap(hi[i], hi[j]);
-            }
-    int at = 0;
-    for (int i = 0; i < cnt; i++) {
-        if (lo[i] != at || hi[i] - lo[i] > 7) return sb;
-        at = hi[i];
-    }
-    if (at != P.n) return sb;
-    sb.nblk = cnt;
-    for (int i = 0; i < cnt; i++) {
-        sb.off[i] = lo[i];
-        sb.size[i] = hi[i] - lo[i];
-    }
-    return sb;
-}
-template <int DOF, int WARPS, int MINB>
-int launch_backward_n1_blocks_t(ilqrb_handle h, int b0, int nB, cudaStream_t st, const StateBlocks& sb) {
-    const size_t smem = (size_t)WARPS * BwdN1Smem<1>::PER_WARP * sizeof(double);
-    auto kern = k_backward_n1_blocks<DOF, WARPS, MINB>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
-    }
-    const int warps = nB * sb.nblk;
-    kern<<<(warps + WARPS - 1) / WARPS, 32 * WARPS, smem, st>>>(h->dp, h->W, b0, nB, sb);
-    return 0;
-}
-int launch_backward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
-    h->begin(PS_BACKWARD);
-    const int n = h->hp.n;
-    int rc;
-    const StateBlocks sb = find_state_blocks(h->hp);
-    if (sb.nblk >= 2) {
-        bool all7 = true;
-        for (int i = 0; i < sb.nblk; i++) all7 = all7 && sb.size[i] == 7;
-        rc = all7 ? launch_backward_n1_blocks_t<7, 4, 7>(h, b0, nB, st, sb) : launch_backward_n1_blocks_t<0, 4, 7>(h, b0, nB, st, sb);
-    } else if (n == 7) rc = launch_backward_n1_t<1, 7, 4, 7>(h, b0, nB, st);
-    else if (n == 14) rc = launch_backward_n1_t<2, 14, 4, 2>(h, b0, nB, st);
-    else if (n + 1 <= 8) rc = launch_backward_n1_t<1, 0, 4, 7>(h, b0, nB, st);
-    else rc = launch_backward_n1_t<2, 0, 4, 2>(h, b0, nB, st);
-    h->end();
-    if (rc) return rc;
-    CU(cudaGetLastError());
-    return 0;
-}
-template <int NT, int DOF, int MINB>
-int launch_forward_n1_t(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop) {
-    const DevProblem& P = h->hp;
-    const size_t smem = (size_t)fwd_n1_smem_doubles(P.H, h->W.ns, P.n_kp_steps) * sizeof(double);
-    auto kern = k_forward_n1<NT, DOF, MINB>;
-    static size_t attr_smem = 0;
-    if (smem > attr_smem) {
-        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_smem = smem;
-    }
-    kern<<<nB, 32, smem, st>>>(h->dp, h->W, b0, it, nb_iter, line_search, early_stop);
-    return 0;
-}
-int launch_forward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop) {
-    const int n = h->hp.n;
-    int rc;
-    h->begin(PS_LINESEARCH);
-    if (n == 7) rc = launch_forward_n1_t<1, 7, 28>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
-    else if (n == 14) rc = launch_forward_n1_t<2, 14, 12>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
-    else if (n + 1 <= 8) rc = launch_forward_n1_t<1, 0, 28>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
-    else rc = launch_forward_n1_t<2, 0, 12>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
-    h->end();
-    if (rc) return rc;
-    CU(cudaGetLastError());
-    return 0;
-}
 unsigned env_uint(const char* name, unsigned dflt) {
     const char* v = getenv(name);
     return v ? (unsigned)strtoul(v, nullptr, 10) : dflt;
@@ -430,6 +129,11 @@ __global__ void k_pack(double* __restrict__ dst, const double* __restrict__ src,
     double v = src[row * stride + c];
     if (scale) v *= scale[row / rows_per_problem];
     dst[i] = v;
+}
+// dst[i] = src[(i mod per_problem) mod src_len]: one small array replicated over the batch (and over the steps of a problem)
+__global__ void k_bcast_rows(double* __restrict__ dst, const double* __restrict__ src, size_t tot, size_t per_problem, size_t src_len) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < tot) dst[i] = src[(i % per_problem) % src_len];
 }
 __global__ void k_unpack(double* __restrict__ dst, const double* __restrict__ src, size_t rows, int w, int stride) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -459,119 +163,9 @@ int download_packed(ilqrb_handle h, double* dst_host, const double* src_dev, siz
     return 0;
 }
 
-// one thread per (problem, timestep): stacked task Jacobian (test hook)
-__global__ void k_rollout_jac(const DevProblem* __restrict__ Pp, Work W, double* __restrict__ Jout) {
-    const DevProblem& P = *Pp;
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P.B * P.H) return;
-    const int b = idx / P.H, k = idx % P.H, n = P.n, dof = P.dof;
-    const double* x = W.X + ((size_t)b * P.H + k) * W.ns;
-    double xs[MAXN], dqs[MAXM];
-    for (int i = 0; i < n; i++) xs[i] = x[i];
-    for (int i = 0; i < dof; i++) dqs[i] = (P.nb_deriv == 2) ? xs[dof + i] : 0.0;
-    double* out = Jout + (size_t)idx * P.r * n;
-    for (int t = 0; t < P.n_tasks; t++) {
-        const DevTask& tk = P.tasks[t];
-        EEState e;
-        task_ee(P, tk, xs, dqs, e);
-        task_jacobian(P, tk, e, out + (size_t)tk.r_off * n, n);
-    }
-}
-__global__ void k_kinematics(const DevProblem* __restrict__ Pp, int robot, int nq, const double* __restrict__ q, const double* __restrict__ dq, double* x, double* quat,
-                             double* J, double* dx, double* w) {
-    const DevProblem& P = *Pp;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nq) return;
-    const DevRobot& rb = P.robots[robot];
-    double qs[RDOF], dqs[RDOF];
-    for (int c = 0; c < RDOF; c++) {
-        qs[c] = c < rb.dof ? q[(size_t)i * rb.dof + c] : 0.0;
-        dqs[c] = c < rb.dof ? dq[(size_t)i * rb.dof + c] : 0.0;
-    }
-    EEState e;
-    if (rb.kind == ILQRB_ROBOT_2D) robot2d_update_kinematics(rb.lengths, rb.dof, qs, dqs, e);
-    else kdl_update_kinematics(rb.segs, rb.n_segments, rb.dof, qs, dqs, e);
-    for (int a = 0; a < 3; a++) {
-        x[(size_t)i * 3 + a] = e.x[a];
-        dx[(size_t)i * 3 + a] = e.dx[a];
-        w[(size_t)i * 3 + a] = e.w[a];
-    }
-    for (int a = 0; a < 4; a++) quat[(size_t)i * 4 + a] = e.quat[a];
-    for (int a = 0; a < 6; a++)
-        for (int c = 0; c < rb.dof; c++) J[((size_t)i * 6 + a) * rb.dof + c] = a < 3 ? e.Jv[c][a] : e.Jw[c][a - 3];
-}
-
-int launch_init(ilqrb_handle h, int b0 = 0, int nB = -1, cudaStream_t st = nullptr) {
-    if (nB < 0) nB = h->hp.B;
-    if (!st) st = h->stream;
-    h->begin(PS_ROLLOUT_INIT);
-#define CALL(N, M) k_rollout_init<N, M><<<(nB + 127) / 128, 128, 0, st>>>(h->dp, h->W, b0, nB)
-    DISPATCH_NM(size_class(h->hp.n, h->hp.m), CALL)
-#undef CALL
-    h->end();
-    CU(cudaGetLastError());
-    return 0;
-}
-int launch_derivs(ilqrb_handle h, int b0 = 0, int nB = -1, cudaStream_t st = nullptr) {
-    if (nB < 0) nB = h->hp.B;
-    if (!st) st = h->stream;
-    const int tot = nB * h->hp.n_kp_steps;
-    h->begin(PS_KP_DERIVS);
-    k_kp_derivs<<<(tot + 63) / 64, 64, 0, st>>>(h->dp, h->W, b0, nB);
-    h->end();
-    CU(cudaGetLastError());
-    return 0;
-}
-// affine line search (k_linesearch_affine): linear dynamics, no AL terms
-template <int N, int M>
-int launch_linesearch_affine_t(ilqrb_handle h, int line_search) {
-    const DevProblem& P = h->hp;
-    const size_t smem = 4 * (size_t)ls_affine_smem_doubles(P.H, h->W.ns, h->W.ms) * sizeof(double);
-    auto kern = k_linesearch_affine<N, M>;
-    static size_t attr = 0;
-    if (smem > attr) {
-        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr = smem;
-    }
-    kern<<<(P.B + 3) / 4, 128, smem, h->stream>>>(h->dp, h->W, line_search);
-    return 0;
-}
-int launch_linesearch(ilqrb_handle h, int line_search, bool al) {
-    const int tot = h->hp.B * CAND_LANES;
-    h->begin(PS_LINESEARCH);
-    static const bool force_generic = getenv("ILQRB_GENERIC") != nullptr;
-    const size_t need = 4 * (size_t)ls_affine_smem_doubles(h->hp.H, h->W.ns, h->W.ms) * sizeof(double);
-    if (!force_generic && !h->hp.time && h->hp.m <= 8 && need <= 200 * 1024) {  // AL line searches on the plain cost too
-        int rc = 0;
-#define CALL(N, M) rc = launch_linesearch_affine_t<N, M>(h, line_search)
-        DISPATCH_NM(size_class(h->hp.n, h->hp.m), CALL)
-#undef CALL
-        h->end();
-        if (rc) return rc;
-        CU(cudaGetLastError());
-        return 0;
-    }
-#define CALL(N, M) k_linesearch<N, M><<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, line_search)
-    DISPATCH_NM(size_class(h->hp.n, h->hp.m), CALL)
-#undef CALL
-    h->end();
-    CU(cudaGetLastError());
-    return 0;
-}
-int launch_accept(ilqrb_handle h, int it, int nb_iter, int line_search, int early_stop, int al, int lag, double pen_next) {
-    const int tot = h->hp.B * 32;
-    h->begin(PS_ACCEPT);
-#define CALL(N, M) k_accept<N, M><<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, it, nb_iter, line_search, early_stop, al, lag, pen_next)
-    DISPATCH_NM(size_class(h->hp.n, h->hp.m), CALL)
-#undef CALL
-    h->end();
-    CU(cudaGetLastError());
-    return 0;
-}
-
 // Results of problems [b0, b0+nB) packed and sent to the caller's buffers, all asynchronous on `st`.  Every output has
 // its own slice of one staging buffer (problem-major), so ranges never wait for one another.
-int enqueue_download_range(ilqrb_handle h, const ilqrb_result* out, int b0, int nB, int nit, cudaStream_t st) {
+int enqueue_download_range(ilqrb_handle h, const ilqrb_result* out, int b0, int nB, int nit, cudaStream_t st, bool gains = true) {
     const DevProblem& P = h->hp;
     const size_t B = P.B;
     const int H = P.H, n = P.n, m = P.m;
@@ -593,13 +187,11 @@ int enqueue_download_range(ilqrb_handle h, const ilqrb_result* out, int b0, int 
     };
     if ((rc = pack(out->X, sX, h->W.X, H, n, h->W.ns, nullptr, 1))) return rc;
     if ((rc = pack(out->U, sU, h->W.U, H - 1, m, h->W.ms, nullptr, 1))) return rc;
-    if ((rc = pack(out->K, sK, h->W.K, (size_t)(H - 1) * m, n, h->W.ns, nullptr, 1))) return rc;
+    if (gains && (rc = pack(out->K, sK, h->W.K, (size_t)(H - 1) * m, n, h->W.ns, nullptr, 1))) return rc;
     // ds are returned multiplied by the accepted alpha (ILQRRecursive.cpp:128,144,162)
-    if ((rc = pack(out->d, sD, h->W.d, H - 1, m, h->W.ms, h->last_nb_iter > 0 ? h->W.alpha_last : nullptr, H - 1))) return rc;
+    if (gains && (rc = pack(out->d, sD, h->W.d, H - 1, m, h->W.ms, h->last_nb_iter > 0 ? h->W.alpha_last : nullptr, H - 1))) return rc;
     if (out->fX) {
-        const int tot = nB * H;
-        k_final_fx<<<(tot + 127) / 128, 128, 0, st>>>(h->dp, h->W, h->d_fX, b0, nB);
-        CU(cudaGetLastError());
+        if ((rc = launch_final_fx(h, b0, nB, st))) return rc;
         const size_t off = (size_t)b0 * H * P.nt;
         CU(cudaMemcpyAsync(out->fX + off, h->d_fX + off, (size_t)nB * H * P.nt * sizeof(double), cudaMemcpyDeviceToHost, st));
     }
@@ -650,23 +242,22 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
         h->W.al_per_step = al->per_step;
         h->W.alA = h->d_alA;
         h->W.alb = h->d_alb;
-        // initial multipliers replicated over the batch (and over steps when given once)
-        h->h_lam0.resize((size_t)B * (H - 1) * nc);
-        for (int b = 0; b < B; b++)
-            for (int k = 0; k < H - 1; k++)
-                std::memcpy(&h->h_lam0[((size_t)b * (H - 1) + k) * nc], al->lambda0 + (size_t)(al->per_step ? k : 0) * nc, nc * sizeof(double));
-        CU(cudaMemcpyAsync(h->W.lam, h->h_lam0.data(), h->h_lam0.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-        CU(cudaStreamSynchronize(h->stream));
+        // initial multipliers: one copy to the device, replicated over the batch (and over steps when given once) by a kernel
+        if (eb > h->lam0_elems) {
+            if ((rc = h->alloc(&h->d_lam0, eb))) return rc;
+            h->lam0_elems = eb;
+        }
+        CU(cudaMemcpyAsync(h->d_lam0, al->lambda0, eb * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        {
+            const size_t tot = (size_t)B * (H - 1) * nc;
+            k_bcast_rows<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(h->W.lam, h->d_lam0, tot, (size_t)(H - 1) * nc, al->per_step ? (size_t)(H - 1) * nc : (size_t)nc);
+            CU(cudaGetLastError());
+        }
         pen = al->penalty;
         pen_frozen = pen;
     }
     if ((rc = launch_init(h))) return rc;
-    if (al) {
-        h->begin(PS_MISC);
-        k_al_init<<<(B * 32 + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W);
-        h->end();
-        CU(cudaGetLastError());
-    }
+    if (al && (rc = launch_al_init(h))) return rc;
     if (fast_n1_applies(h, al != nullptr)) {
         if (opts->nb_iter > 0 && (rc = launch_derivs(h))) return rc;  // later iterations: phase F of the forward pass
         // The batch is split into G groups of problems, each on its own stream, the first backward pass of group g+1
@@ -677,7 +268,7 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
         // downloads, and fewer, larger groups keep the kernels closer to a full wave)
         // device-resident results: about three groups per two waves of the forward kernel (28 resident warps per SM with one state
         // tile, 12 with two), at least 3: C2 B = 4096 / 8192 / 16384 -> 3 / 3 / 6, C5 B = 8192 -> 7 (sweeps in DESIGN.md)
-        const int wave = 148 * (n + 1 <= 8 ? 28 : 12);
+        const int wave = fast_n1_wave(h);
         const int g_dev = std::min(8, std::max(3, (3 * B + 2 * wave - 1) / (2 * wave)));
         int G = h->prof ? 1 : (int)env_uint("ILQRB_GROUPS", out_async ? (h->streaming ? 5 : 8) : g_dev);
         if (G > ilqrb_handle_s::MAX_GROUPS) G = ilqrb_handle_s::MAX_GROUPS;
@@ -724,7 +315,7 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
     }
     for (int it = 0; it < opts->nb_iter; it++) {
         if ((rc = launch_derivs(h))) return rc;
-        if ((rc = launch_backward(h, al != nullptr, pen_frozen))) return rc;
+        if ((rc = fast_n2_applies(h, al != nullptr) ? launch_backward_n2(h, al != nullptr, pen_frozen) : launch_backward_generic(h, al != nullptr, pen_frozen))) return rc;
         if ((rc = launch_linesearch(h, opts->line_search, al != nullptr))) return rc;
         double pen_next = pen;
         bool upd = false;
@@ -1006,33 +597,13 @@ int ilqrb_download(ilqrb_handle h, ilqrb_result* out) {
     const size_t B = P.B;
     const int H = P.H, n = P.n, m = P.m, nit = std::max(h->last_nb_iter, 1);
     int rc;
-    if (h->last_solver == 3) {
-        std::string err;
-        rc = batch_download(h->stream, P, h->BW, out, h->W, nit, err);
-        return rc ? fail(rc, err) : 0;
-    }
-    if ((rc = download_packed(h, out->X, h->W.X, B * H, n, h->W.ns, nullptr, 1))) return rc;
-    if ((rc = download_packed(h, out->U, h->W.U, B * (H - 1), m, h->W.ms, nullptr, 1))) return rc;
-    if (h->last_solver == 1) {
-        if ((rc = download_packed(h, out->K, h->W.K, B * (H - 1) * m, n, h->W.ns, nullptr, 1))) return rc;
-        // ds are returned multiplied by the accepted alpha (ILQRRecursive.cpp:128,144,162)
-        if ((rc = download_packed(h, out->d, h->W.d, B * (H - 1), m, h->W.ms, h->last_nb_iter > 0 ? h->W.alpha_last : nullptr, H - 1))) return rc;
-    }
-    if (out->fX) {
-        const int tot = (int)(B * H);
-        h->begin(PS_FINAL);
-        k_final_fx<<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, h->d_fX, 0, (int)B);
-        h->end();
-        CU(cudaGetLastError());
-        CU(cudaMemcpyAsync(out->fX, h->d_fX, B * H * P.nt * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-    }
-    if (out->cost) CU(cudaMemcpyAsync(out->cost, h->W.cost0, B * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-    if (out->cost_hist) CU(cudaMemcpyAsync(out->cost_hist, h->W.cost_hist, B * nit * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-    if (out->alpha_hist) CU(cudaMemcpyAsync(out->alpha_hist, h->W.alpha_hist, B * nit * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-    if (out->iters) CU(cudaMemcpyAsync(out->iters, h->W.iters, B * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-    if (out->status) CU(cudaMemcpyAsync(out->status, h->W.status, B * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    if (h->last_solver == 3) return batch_download_h(h, out, nit);
+    // every output has its own slice of the staging buffer: all packs and copies are queued, one synchronisation at the end
+    if ((rc = enqueue_download_range(h, out, 0, (int)B, nit, h->stream, h->last_solver == 1))) return rc;
     if (out->lambda && h->last_solver == 2) CU(cudaMemcpyAsync(out->lambda, h->W.lam, B * (H - 1) * h->W.nc * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
+    (void)n;
+    (void)m;
     return 0;
 }
 
@@ -1070,11 +641,9 @@ int ilqrb_solve_al(ilqrb_handle h, const double* U0, const ilqrb_al_desc* al, co
 int ilqrb_run_batch(ilqrb_handle h, const ilqrb_batch_desc* bd, const ilqrb_solve_opts* opts) {
     if (!h || !opts) return fail(ILQRB_EINVAL, "null argument");
     CU(cudaSetDevice(h->device));
-    std::string err;
     int rc = ensure_iter_capacity(h, std::max(opts->nb_iter, 1));
     if (rc) return rc;
-    rc = batch_run(h->stream, h->hp, h->dp, h->W, h->BW, bd, opts, err, [h](int slot) { h->begin(PS_BATCH_FP + slot); }, [h]() { h->end(); });
-    if (rc) return fail(rc, err);
+    if ((rc = batch_run_h(h, bd, opts))) return rc;
     h->last_nb_iter = opts->nb_iter;
     h->last_solver = 3;
     return 0;
@@ -1096,17 +665,14 @@ int ilqrb_rollout(ilqrb_handle h, const double* U, double* X, double* fX, double
     const size_t B = P.B;
     const int H = P.H;
     if ((rc = download_packed(h, X, h->W.X, B * H, P.n, h->W.ns, nullptr, 1))) return rc;
-    const int tot = (int)(B * H);
     if (fX) {
-        k_final_fx<<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, h->d_fX, 0, (int)B);
-        CU(cudaGetLastError());
+        if ((rc = launch_final_fx(h, 0, (int)B, h->stream))) return rc;
         CU(cudaMemcpyAsync(fX, h->d_fX, B * H * P.nt * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     }
     if (J) {
         const size_t el = B * H * P.r * P.n;
         if ((rc = ensure_pack(h, el))) return rc;
-        k_rollout_jac<<<(tot + 127) / 128, 128, 0, h->stream>>>(h->dp, h->W, h->d_pack);
-        CU(cudaGetLastError());
+        if ((rc = launch_rollout_jac(h, h->d_pack))) return rc;
         CU(cudaMemcpyAsync(J, h->d_pack, el * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     }
     if (cost) CU(cudaMemcpyAsync(cost, h->W.cost0, B * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
@@ -1127,9 +693,7 @@ int ilqrb_kinematics(ilqrb_handle h, int robot, int nq, const double* q, const d
     cudaMemcpyAsync(buf, q, in * sizeof(double), cudaMemcpyHostToDevice, h->stream);
     if (dq) cudaMemcpyAsync(dq_d, dq, in * sizeof(double), cudaMemcpyHostToDevice, h->stream);
     else cudaMemsetAsync(dq_d, 0, in * sizeof(double), h->stream);
-    h->begin(PS_MISC);
-    k_kinematics<<<(nq + 127) / 128, 128, 0, h->stream>>>(h->dp, robot, nq, buf, dq_d, ox, oq, oJ, odx, ow);
-    h->end();
+    launch_kinematics(h, robot, nq, buf, dq_d, ox, oq, oJ, odx, ow);
     if (x) cudaMemcpyAsync(x, ox, (size_t)nq * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
     if (quat) cudaMemcpyAsync(quat, oq, (size_t)nq * 4 * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
     if (J) cudaMemcpyAsync(J, oJ, (size_t)nq * 6 * dof * sizeof(double), cudaMemcpyDeviceToHost, h->stream);

@@ -1,0 +1,142 @@
+// launch_fused1.cu — launchers of the single-integrator fast path (fused1.cuh): k_backward_n1 / k_backward_n1_blocks / k_forward_n1.
+#include <cstdlib>
+
+#include "fused1.cuh"
+#include "handle.hpp"
+
+namespace ilqrb {
+
+bool fast_n1_applies(ilqrb_handle h, bool al) {
+    const DevProblem& P = h->hp;
+    return !generic_forced() && !al && P.nb_deriv == 1 && !P.time && P.n == P.m && P.n + 1 <= 16 &&
+           (size_t)fwd_n1_smem_doubles(P.H, h->W.ns, P.n_kp_steps) * sizeof(double) <= 200 * 1024;
+}
+// resident problems of one full wave of the forward kernel: 28 warps per SM with one state tile, 12 with two
+int fast_n1_wave(ilqrb_handle h) { return 148 * (h->hp.n + 1 <= 8 ? 28 : 12); }
+
+namespace {
+
+template <int NT, int DOF, int WARPS, int MINB>
+int launch_backward_n1_t(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
+    const size_t smem = (size_t)WARPS * BwdN1Smem<NT>::PER_WARP * sizeof(double);
+    auto kern = k_backward_n1<NT, DOF, WARPS, MINB>;
+    static DynSmem attr;
+    int rc = attr.ensure(kern, smem, h->device);
+    if (rc) return rc;
+    kern<<<(nB + WARPS - 1) / WARPS, 32 * WARPS, smem, st>>>(h->dp, h->W, b0, nB);
+    return 0;
+}
+// Diagonal blocks of the state that no task couples: every task reads the joints [joint_offset, joint_offset + dof of its
+// robot) only, so l_x / l_xx (and with R diagonal, A = I, B = dt I the whole Riccati recursion) are block diagonal over
+// the connected groups of those ranges.  Returns nblk >= 2 only if the groups tile [0, n) and fit one 8x8 tile each.
+StateBlocks find_state_blocks(const DevProblem& P) {
+    StateBlocks sb{};
+    sb.nblk = 0;
+    static const bool off_switch = getenv("ILQRB_NO_BLOCKS") != nullptr;  // A/B switch for tests and profiling
+    if (off_switch || P.nb_deriv != 1 || P.time || P.n != P.m || P.n_tasks < 2) return sb;
+    int lo[ILQRB_MAX_TASKS], hi[ILQRB_MAX_TASKS], cnt = 0;
+    for (int ti = 0; ti < P.n_tasks; ti++) {
+        const int a = P.tasks[ti].joint_offset, e = a + P.robots[P.tasks[ti].robot].dof;
+        int k = 0;
+        for (; k < cnt; k++)
+            if (a < hi[k] && lo[k] < e) break;  // overlaps group k
+        if (k == cnt) {
+            lo[cnt] = a;
+            hi[cnt] = e;
+            cnt++;
+        } else {
+            lo[k] = std::min(lo[k], a);
+            hi[k] = std::max(hi[k], e);
+        }
+    }
+    for (bool merged = true; merged;) {  // groups that grew into one another
+        merged = false;
+        for (int i = 0; i < cnt && !merged; i++)
+            for (int j = i + 1; j < cnt && !merged; j++)
+                if (lo[i] < hi[j] && lo[j] < hi[i]) {
+                    lo[i] = std::min(lo[i], lo[j]);
+                    hi[i] = std::max(hi[i], hi[j]);
+                    lo[j] = lo[cnt - 1];
+                    hi[j] = hi[cnt - 1];
+                    cnt--;
+                    merged = true;
+                }
+    }
+    if (cnt < 2 || cnt > 4) return sb;
+    for (int i = 0; i < cnt; i++)  // sort by offset
+        for (int j = i + 1; j < cnt; j++)
+            if (lo[j] < lo[i]) {
+                std::swap(lo[i], lo[j]);
+                std::swap(hi[i], hi[j]);
+            }
+    int at = 0;
+    for (int i = 0; i < cnt; i++) {
+        if (lo[i] != at || hi[i] - lo[i] > 7) return sb;
+        at = hi[i];
+    }
+    if (at != P.n) return sb;
+    sb.nblk = cnt;
+    for (int i = 0; i < cnt; i++) {
+        sb.off[i] = lo[i];
+        sb.size[i] = hi[i] - lo[i];
+    }
+    return sb;
+}
+template <int DOF, int WARPS, int MINB>
+int launch_backward_n1_blocks_t(ilqrb_handle h, int b0, int nB, cudaStream_t st, const StateBlocks& sb) {
+    const size_t smem = (size_t)WARPS * BwdN1Smem<1>::PER_WARP * sizeof(double);
+    auto kern = k_backward_n1_blocks<DOF, WARPS, MINB>;
+    static DynSmem attr;
+    int rc = attr.ensure(kern, smem, h->device);
+    if (rc) return rc;
+    const int warps = nB * sb.nblk;
+    kern<<<(warps + WARPS - 1) / WARPS, 32 * WARPS, smem, st>>>(h->dp, h->W, b0, nB, sb);
+    return 0;
+}
+template <int NT, int DOF, int MINB>
+int launch_forward_n1_t(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop) {
+    const DevProblem& P = h->hp;
+    const size_t smem = (size_t)fwd_n1_smem_doubles(P.H, h->W.ns, P.n_kp_steps) * sizeof(double);
+    auto kern = k_forward_n1<NT, DOF, MINB>;
+    static DynSmem attr;
+    int rc = attr.ensure(kern, smem, h->device);
+    if (rc) return rc;
+    kern<<<nB, 32, smem, st>>>(h->dp, h->W, b0, it, nb_iter, line_search, early_stop);
+    return 0;
+}
+
+}  // namespace
+
+int launch_backward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
+    h->begin(PS_BACKWARD);
+    const int n = h->hp.n;
+    int rc;
+    const StateBlocks sb = find_state_blocks(h->hp);
+    if (sb.nblk >= 2) {
+        bool all7 = true;
+        for (int i = 0; i < sb.nblk; i++) all7 = all7 && sb.size[i] == 7;
+        rc = all7 ? launch_backward_n1_blocks_t<7, 4, 7>(h, b0, nB, st, sb) : launch_backward_n1_blocks_t<0, 4, 7>(h, b0, nB, st, sb);
+    } else if (n == 7) rc = launch_backward_n1_t<1, 7, 4, 7>(h, b0, nB, st);
+    else if (n == 14) rc = launch_backward_n1_t<2, 14, 4, 2>(h, b0, nB, st);
+    else if (n + 1 <= 8) rc = launch_backward_n1_t<1, 0, 4, 7>(h, b0, nB, st);
+    else rc = launch_backward_n1_t<2, 0, 4, 2>(h, b0, nB, st);
+    h->end();
+    if (rc) return rc;
+    CU(cudaGetLastError());
+    return 0;
+}
+int launch_forward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop) {
+    const int n = h->hp.n;
+    int rc;
+    h->begin(PS_LINESEARCH);
+    if (n == 7) rc = launch_forward_n1_t<1, 7, 28>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+    else if (n == 14) rc = launch_forward_n1_t<2, 14, 12>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+    else if (n + 1 <= 8) rc = launch_forward_n1_t<1, 0, 28>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+    else rc = launch_forward_n1_t<2, 0, 12>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+    h->end();
+    if (rc) return rc;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace ilqrb
