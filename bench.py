@@ -106,6 +106,24 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_figures():
+    """per-kernel DRAM traffic and executed FP64 flops per launch from the committed ncu capture (profiles/ncu_kernels.json,
+    written by tools/ncu_summary.py --json from the `ncu --set full` report of tools/profile_run.py)"""
+    p = os.path.join(ROOT, "profiles", "ncu_kernels.json")
+    try:
+        return json.load(open(p))
+    except Exception:
+        return {}
+
+
+def ncu_kernel(figs, key, batch):
+    """entry of kernel `key` if the capture was taken at this batch size (figures are per launch)"""
+    e = figs.get("kernels", {}).get(key)
+    if not e or e.get("batch") != batch:
+        return {}
+    return e
+
+
 def cpu_baseline_run(batch, threads=None):
     """the oracle over `batch` problems of the workload on all host threads -> (solves/s, threads, seconds)"""
     from ilqr_planner_b200 import synth
@@ -118,9 +136,18 @@ def cpu_baseline_run(batch, threads=None):
     return batch / dt, threads, dt, out
 
 
+def use_test_side_chain():
+    """the robot chain from the test-side URDF reader (oracle/urdf_chain.py) instead of the product's ilqrb_chain_from_urdf:
+    the reference arm's process then never maps libilqrb.so"""
+    from ilqr_planner_b200 import synth
+    from oracle import urdf_chain
+    synth._chain_cache["panda"] = urdf_chain.kdl_chain_from_urdf(open(synth.PANDA_URDF).read(), "panda_link0", "panda_tip")
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
+    use_test_side_chain()
     sample = 16 * max(1, (os.cpu_count() or 8) // 4)
     for _ in range(args.warmup):
         cpu_baseline_run(max(sample // 4, 8))
@@ -137,6 +164,107 @@ def run_reference(args, rank, world):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def w_bw(n, m):
+    """SURVEY 8d dense-generic flop count of one backward Riccati step"""
+    return 4 * m * n * n + 2 * m * n * n + 2 * m * m * n + 4 * n ** 3 + 2 * n ** 3 + 2 * n * n * m + 2 * m * n + 2 * n * n + 2 * m ** 3 + 2 * m * m * n + 2 * m * m \
+        + (2 * n * m * m + 6 * n * n * m + 3 * n * n) + 6 * n * m
+
+
+def other_configs(torch, device, fp64_peak, hbm_peak):
+    """The other BASELINE.json configs on one GPU (parity-test shapes; the bench line proper is configs[1]): device-resident
+    solves/s (CUDA events on the solve stream, U0 reset inside the timed region), the dominant kernel with its algorithmic
+    roofline fraction, and the same solve through the blocking host-buffer C-ABI call (e2e: H2D of U0 and D2H of every result
+    inside the timed region)."""
+    import numpy as np
+    from ilqr_planner_b200 import synth
+    from ilqr_planner_b200.problem import ResultBuffers
+    from ilqr_planner_b200.solver import Handle, build_psi, make_al_desc, make_batch_desc
+    res = {}
+
+    def run(name, pb, nit, kind="recursive", al=None, u0=None, psi=None, reps=3, flops_of=None, note=None):
+        stream = torch.cuda.Stream()
+        with Handle(pb, device=device, stream=stream.cuda_stream) as h:
+            ald = make_al_desc(**al) if al else None
+            bd = make_batch_desc(None, psi) if kind == "batch" else None
+
+            def go():
+                h.upload_u0(u0)
+                if kind == "al":
+                    h.run_al(ald, nit, True, False)
+                elif kind == "batch":
+                    h.run_batch(bd, nit, False)
+                else:
+                    h.run_recursive(nit, True, False)
+            go()
+            h.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(reps):
+                go()
+            e1.record(stream)
+            h.synchronize()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / reps
+            h.set_profiling(True)
+            h.reset_profile()
+            go()
+            prof = h.profile()
+            h.set_profiling(False)
+            # e2e: blocking host-buffer call
+            out = ResultBuffers(pb, nit, kind, nc=(ald.nc if ald else 0))
+            u0h = None if u0 is None else np.ascontiguousarray(u0)
+
+            def call():
+                if kind == "al":
+                    h.solve_al(u0h, al["A"], al["b"], al["lambda0"], nit, al["lag_update_step"], al["penalty"], al["scaling_factor"], True, False, out=out)
+                elif kind == "batch":
+                    h.solve_batch(u0h, nit, False, psi=psi, out=out)
+                else:
+                    h.solve_recursive(u0h, nit, True, False, out=out)
+            call()
+            t0 = time.perf_counter()
+            call()
+            e2e_s = time.perf_counter() - t0
+        dom = max(prof.items(), key=lambda kv: kv[1][0])
+        entry = {"batch": pb.batch, "nb_iter": nit, "solves_per_s": pb.batch / (ms * 1e-3), "ms_per_solve_batch": ms, "ms_per_iteration": ms / nit,
+                 "kernel_ms": {k: round(v[0], 3) for k, v in prof.items()}, "dominant_kernel": dom[0], "e2e_solves_per_s": pb.batch / e2e_s,
+                 "e2e_mode": "one blocking host-buffer C-ABI call (pageable numpy buffers), H2D + solve + D2H"}
+        if flops_of:
+            kname, flops, peak, unit = flops_of
+            t = prof.get(kname, (0.0, 0))
+            if t[1]:
+                ach = flops / (t[0] / t[1] * 1e-3) / (1e12 if unit == "TFLOP/s" else 1e9)
+                entry["roofline"] = {"kernel": kname, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak if peak else None, "avg_launch_ms": t[0] / t[1]}
+        if note:
+            entry["note"] = note
+        res[name] = entry
+
+    H = 100
+    pb = synth.config1(batch=4096)
+    run("C1 Robot2D position T=50 Recursive", pb, 20, flops_of=("riccati_backward", w_bw(3, 3) * 49.0 * 4096, fp64_peak, "TFLOP/s"))
+    pb = synth.config3_active(batch=16384)
+    al = synth.al_config3_active("qbox", lag_update_step=5)
+    run("C3 AL-iLQR nd=2 T=100, 14 joint-box rows ACTIVE (config3_active)", pb, 40, kind="al", al=al, reps=2,
+        flops_of=("riccati_backward", (w_bw(14, 7) + 2 * 14 * 21 * 21) * 99.0 * 16384, fp64_peak, "TFLOP/s"),
+        note="dense-generic algorithmic count (SURVEY 8d); the kernel exploits the integrator structure, so a fraction near or above 1 means "
+             "the counted work is not executed - see executed_pipe_utilisation of profiles/")
+    pb = synth.config3(batch=16384)
+    run("C3 AL-iLQR nd=2 T=100, rows = Panda joint limits (inert for these targets)", pb, 40, kind="al", al=synth.al_config3(), reps=2)
+    pb = synth.config5(batch=8192)
+    run("C5 dual arm n=m=14 T=100 Recursive", pb, 20, flops_of=("riccati_backward", w_bw(14, 14) * 99.0 * 8192, fp64_peak, "TFLOP/s"),
+        note="block-diagonal backward pass: two 7x7 recursions per problem instead of the dense 14x14 the algorithmic figure counts")
+    pb = synth.config4(batch=4096, horizon=H)
+    run("PosOrnTime Recursive T=100", pb, 20, u0=synth.u0_time(pb), flops_of=("riccati_backward", w_bw(8, 8) * 99.0 * 4096, fp64_peak, "TFLOP/s"))
+    pb = synth.config4(batch=1024, horizon=200)
+    N = 199 * 8
+    run("C4 BatchILQR PosOrnTime T=200 N=1592, one 1024-problem chunk", pb, 3, kind="batch", u0=synth.u0_time(pb), reps=1,
+        flops_of=("batch_cholesky", (N ** 3 / 3.0 + 2.0 * N * N) * 1024 * 3 / 3 * 1.0, fp64_peak, "TFLOP/s"),
+        note="batch_cholesky = blocked Cholesky + the two triangular solves, N^3/3 + 2 N^2 flop per problem and iteration")
+    psi = np.kron(build_psi("unitstep", 199, 2), np.identity(8))
+    run("C4 BatchILQRCP PosOrnTime T=200, Psi = 2 unit steps", pb, 20, kind="batch", u0=synth.u0_time(pb), psi=psi, reps=1)
+    return res
 
 
 def dfma_peak_tflops(torch):
@@ -165,6 +293,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH_PER_GPU, help="problems per GPU (default: the BASELINE config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the other BASELINE configs (N=1 line only)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -210,8 +339,9 @@ def main():
         torch.cuda.synchronize()
 
     # ---- device-resident throughput ("value") -----------------------------------------------------------------
-    h.upload_u0(None)
+    # every solve starts from U0 = 0: the reset (a cudaMemsetAsync on the solve stream) is part of the timed step
     for _ in range(args.warmup):
+        h.upload_u0(None)
         h.run_recursive(NB_ITER, True, False)
     h.synchronize()
     sampler = ClockSampler(local_rank)
@@ -223,6 +353,7 @@ def main():
     with torch.cuda.stream(stream):
         e0.record(stream)
         for _ in range(args.steps):
+            h.upload_u0(None)
             h.run_recursive(NB_ITER, True, False)
         e1.record(stream)
     barrier()
@@ -301,6 +432,7 @@ def main():
     # ---- per-kernel durations with event pairs (separate pass, not part of `value`) -------------------------------
     h.set_profiling(True)
     h.reset_profile()
+    h.upload_u0(None)
     h.run_recursive(NB_ITER, True, False)
     prof = h.profile()
     h.set_profiling(False)
@@ -317,6 +449,10 @@ def main():
         alg_flops = B * (H - 1) * float(flops_step)
         achieved = alg_bytes / bw_avg_s / 1e9 if bw_avg_s > 0 else None
         fp64_peak = dfma_peak_tflops(torch)
+        from ilqr_planner_b200.solver import fp64_peaks
+        dfma_peak, dmma_peak = fp64_peaks(local_rank)  # micro-benchmarks of the library itself (csrc/ubench.cu)
+        figs = ncu_figures()
+        nb, nf = ncu_kernel(figs, "k_backward_n1", B), ncu_kernel(figs, "k_forward_n1", B)
         tot_ms = sum(v[0] for v in prof.values())
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
                 "ms_per_iteration": ms_max / args.steps / NB_ITER, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -332,10 +468,15 @@ def main():
                 "roofline": {"kernel": "riccati_backward (k_backward_n1: DMMA m8n8k4.f64 + DFMA)", "bound": "tensor",
                              "achieved": alg_flops / bw_avg_s / 1e12 if bw_avg_s > 0 else None, "peak": fp64_peak, "unit": "TFLOP/s",
                              "frac": (alg_flops / bw_avg_s / 1e12 / fp64_peak) if (bw_avg_s > 0 and fp64_peak) else None,
-                             "traffic": 213e6 if B == BATCH_PER_GPU else None,
-                             "traffic_note": "dram__bytes_read+write per launch from profiles/ (ncu --set full, B=4096)",
+                             "traffic": nb.get("dram_bytes"),
+                             "traffic_note": "dram__bytes_read+write per launch, %s" % figs.get("source", "profiles/ncu_kernels.json absent"),
                              "peak_source": "FP64 tensor peak measured in this run: cuBLAS DGEMM 4096^3 via torch.matmul (MEASURED_PEAKS.json has no FP64 entry; "
                                             "the bf16 figure there does not apply to an FP64 path)",
+                             "peaks_measured_here_tflops": {"cublas_dgemm_4096": fp64_peak, "dfma_ubench": dfma_peak, "dmma_m8n8k4_ubench": dmma_peak},
+                             # what the kernel executes (ncu: DFMA x 2 + DADD + DMUL thread instructions + DMMA m8n8k4 x 512), against the DFMA peak:
+                             # the structure of A, B removes most of the dense-generic work the algorithmic figure counts
+                             "executed_flops_per_launch": nb.get("executed_flops"),
+                             "executed_pipe_utilisation": (nb["executed_flops"] / bw_avg_s / 1e12 / dfma_peak) if (nb.get("executed_flops") and bw_avg_s > 0 and dfma_peak) else None,
                              "algorithmic_flops_per_launch": alg_flops, "algorithmic_flops_per_problem_step": flops_step,
                              "avg_launch_ms": bw_avg_s * 1e3, "share_of_step": bw_ms / tot_ms if tot_ms else None},
                 "roofline_hbm": {"kernel": "riccati_backward", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
@@ -348,8 +489,9 @@ def main():
                                      "achieved": (B * 8.0 * ((H - 1) * (m * n + m) + 2 * (H * n + (H - 1) * m)) / (fms / max(fn, 1) * 1e-3) / 1e9) if fms > 0 else None,
                                      "peak": hbm_peak, "unit": "GB/s", "peak_source": peak_src,
                                      "algorithmic_bytes_per_launch": B * 8.0 * ((H - 1) * (m * n + m) + 2 * (H * n + (H - 1) * m)),
-                                     "avg_launch_ms": fms / max(fn, 1), "traffic": 337e6 if B == BATCH_PER_GPU else None,
-                                     "traffic_note": "cold-cache ncu capture (profiles/r1_c2_ncu_full_summary.txt)"})(*prof.get("linesearch_rollout", (0.0, 1))),
+                                     "avg_launch_ms": fms / max(fn, 1), "traffic": nf.get("dram_bytes"),
+                                     "executed_flops_per_launch": nf.get("executed_flops"),
+                                     "traffic_note": "dram__bytes_read+write per launch, cold-cache ncu capture, %s" % figs.get("source", "profiles/ncu_kernels.json absent")})(*prof.get("linesearch_rollout", (0.0, 1))),
                 "kernel_ms_per_solve": {k: v[0] for k, v in prof.items()},
                 "final_cost_mean": float(np.nanmean(all_cost)), "problems_with_nan": int(np.isnan(all_cost).sum())}
         if world == 1 and not args.no_cpu_baseline:
@@ -381,6 +523,11 @@ def main():
                 fall = [float(ref.cost_hist[i, max(k - 1, 0)] / np.nanmax(ref.cost_hist[i])) for i, k in zip(early, it_d)]
                 line["cpu_gpu_step_sequences"]["parting_before_a_tie"] = {"count": int(early.size), "earliest_iteration": int(min(it_d)) + 1,
                                                                            "largest_cost_over_trace_scale_when_parting": max(fall)}
+        if world == 1 and not args.no_configs and B == BATCH_PER_GPU:
+            try:
+                line["configs"] = other_configs(torch, local_rank, fp64_peak, hbm_peak)
+            except Exception as e:  # the headline line must survive a failure here
+                line["configs"] = {"error": repr(e)}
         rf = line["roofline_forward"]
         if rf.get("achieved"):
             rf["frac"] = rf["achieved"] / hbm_peak

@@ -95,7 +95,7 @@ SYMBOLS = [
     "ilqrb_synchronize", "ilqrb_update_problems", "ilqrb_solve_recursive", "ilqrb_solve_recursive_async", "ilqrb_solve_al", "ilqrb_solve_batch",
     "ilqrb_upload_u0", "ilqrb_run_recursive", "ilqrb_run_al", "ilqrb_run_batch", "ilqrb_download", "ilqrb_rollout",
     "ilqrb_kinematics", "ilqrb_set_profiling", "ilqrb_get_profile", "ilqrb_reset_profile", "ilqrb_launch_count",
-    "ilqrb_chain_from_urdf", "ilqrb_build_psi",
+    "ilqrb_chain_from_urdf", "ilqrb_build_psi", "ilqrb_fp64_peaks",
 ]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -140,6 +140,7 @@ def load():
     lib.ilqrb_chain_from_urdf.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.c_char_p, c_double_p, c_double_p,
                                           C.POINTER(Segment), C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.ilqrb_build_psi.argtypes = [C.c_char_p, C.c_int, C.c_int, c_double_p]
+    lib.ilqrb_fp64_peaks.argtypes = [C.c_int, c_double_p, c_double_p]
     if lib.ilqrb_abi_version() != ABI_VERSION:
         raise RuntimeError("libilqrb.so ABI version mismatch")
     _lib = lib

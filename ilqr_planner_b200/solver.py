@@ -176,3 +176,11 @@ def build_psi(kind, dim, K):
     out = np.zeros((dim, cols))
     cabi.check(lib.ilqrb_build_psi(kind.encode(), int(dim), int(K), cabi.dptr(out)))
     return out
+
+
+def fp64_peaks(device=0):
+    """(DFMA, DMMA m8n8k4) TFLOP/s of `device`, measured in place by the library (ilqrb_fp64_peaks)"""
+    lib = cabi.load()
+    a, b = C.c_double(0), C.c_double(0)
+    cabi.check(lib.ilqrb_fp64_peaks(int(device), C.cast(C.byref(a), cabi.c_double_p), C.cast(C.byref(b), cabi.c_double_p)))
+    return a.value, b.value

@@ -252,3 +252,58 @@ def config3_short(batch=16, horizon=60, dt=0.05, dof=5, offset=0, tight_limits=T
     task = TaskSpec(kp_timestep=[horizon // 2 - 1, horizon - 1], kp_target=tg, kp_precision=np.array([[Q, Q]]), r_diag=R, state_max=smax,
                     state_min=smin, limit_weight=np.ones(2 * dof, dtype=np.int32))
     return ProblemBatch(cabi.SYS_POS_ORN, 2, horizon, dt, dof, [RobotSpec(cabi.ROBOT_KDL, dof, segs)], [task], R, q0, np.zeros_like(q0))
+
+
+def config3_active(batch=64, horizon=100, dt=0.05, offset=0):
+    """C3 shape (7-DoF, nb_deriv=2) whose AL constraints bind: starts within 0.1 rad of the tutorial posture, targets 0.4-0.6 rad
+    away per joint, so the joint box / velocity / acceleration rows of `al_config3_active` are active over most of the solve."""
+    segs = panda_chain()
+    d = _draws(8, offset, offset + batch, [("q0", -0.1, 0.1, 7), ("t1", 0.4, 0.6, 7), ("s1", -1.0, 1.0, 7), ("t2", 0.4, 0.6, 7), ("s2", -1.0, 1.0, 7)])
+    q0 = PANDA_Q0 + d["q0"]
+    tg = _posorn_targets(segs, q0, [np.sign(d["s1"]) * d["t1"], np.sign(d["s2"]) * d["t2"]])
+    Q = np.diag([1, 1, 1, .1, .1, .1, 1, 1, 1, .1, .1, .1])
+    R = np.ones(7) * 1e-5
+    smax = np.concatenate([np.ones(7) * np.pi * 10, np.ones(7) * 10])  # System limits inactive: the AL rows are what is exercised
+    task = TaskSpec(kp_timestep=[horizon // 2 - 1, horizon - 1], kp_target=tg, kp_precision=np.array([[Q, Q]]), r_diag=R, state_max=smax,
+                    state_min=-smax, limit_weight=np.ones(14, dtype=np.int32))
+    return ProblemBatch(cabi.SYS_POS_ORN, 2, horizon, dt, 7, [RobotSpec(cabi.ROBOT_KDL, 7, segs)], [task], R, q0, np.zeros_like(q0))
+
+
+def al_config3_active(kind="qbox", horizon=100, lag_update_step=3):
+    """AL rows for `config3_active` on s = [q(7); v(7); u(7)]:
+      "qbox"   14 rows  |q - q_tutorial| <= 0.3                                   (shared by all steps; nc <= 16)
+      "mixed"  29 rows  the box, v <= 0.25 (7 rows), |u| <= 0.3 on joints 0..3 (8 rows): rows on the state, the velocity and the control
+      "steps"  16 rows per step: a box shrinking from 0.45 to 0.25 over the horizon and u_0 <= 0.3, -u_0 <= 0.3 (per_step = 1)"""
+    def box(w):
+        A = np.zeros((14, 21))
+        A[:7, :7] = np.eye(7)
+        A[7:, :7] = -np.eye(7)
+        return A, np.concatenate([PANDA_Q0 + w, -(PANDA_Q0 - w)])
+    if kind == "qbox":
+        A, b = box(0.3)
+        lam0 = np.zeros(14)
+    elif kind == "mixed":
+        Ab, bb = box(0.3)
+        Av = np.zeros((7, 21))
+        Av[:, 7:14] = np.eye(7)
+        Au = np.zeros((8, 21))
+        Au[:4, 14:18] = np.eye(4)
+        Au[4:, 14:18] = -np.eye(4)
+        A = np.concatenate([Ab, Av, Au])
+        b = np.concatenate([bb, np.ones(7) * 0.25, np.ones(8) * 0.3])
+        lam0 = np.zeros(29)
+        lam0[3] = 0.01  # a multiplier that starts positive (AL-ILQR.cpp:27: such a row is active whatever its constraint value)
+    elif kind == "steps":
+        As, bs = [], []
+        for k in range(horizon - 1):
+            Ab, bb = box(0.45 - 0.2 * k / (horizon - 2))
+            Au = np.zeros((2, 21))
+            Au[0, 14] = 1.0
+            Au[1, 14] = -1.0
+            As.append(np.concatenate([Ab, Au]))
+            bs.append(np.concatenate([bb, [0.3, 0.3]]))
+        A, b = np.array(As), np.array(bs)
+        lam0 = np.zeros((horizon - 1, 16))
+    else:
+        raise ValueError(kind)
+    return dict(A=A, b=b, lambda0=lam0, lag_update_step=lag_update_step, penalty=0.25, scaling_factor=1.1)

@@ -246,6 +246,9 @@ int ilqrb_set_profiling(ilqrb_handle h, int enabled); /* adds an event pair arou
 int ilqrb_get_profile(ilqrb_handle h, ilqrb_profile* out);
 int ilqrb_reset_profile(ilqrb_handle h);
 int64_t ilqrb_launch_count(ilqrb_handle h); /* kernels launched by this handle since creation */
+/* FP64 peak rates of `device` measured in place with CUDA events (every SM full, best of several passes): DFMA and DMMA
+ * m8n8k4 (the FP64 tensor shape), in TFLOP/s.  The denominators of the FP64 rooflines bench.py reports.                  */
+int ilqrb_fp64_peaks(int device, double* dfma_tflops, double* dmma_tflops);
 
 #ifdef __cplusplus
 }

@@ -38,6 +38,7 @@ def load():
     lib.oracle_solve_batch.argtypes = [P(cabi.ProblemDesc), cabi.c_double_p, P(cabi.BatchDesc), P(cabi.SolveOpts), P(cabi.Result), C.c_int]
     lib.oracle_rollout.argtypes = [P(cabi.ProblemDesc), cabi.c_double_p, cabi.c_double_p, cabi.c_double_p, cabi.c_double_p, cabi.c_double_p, C.c_int]
     lib.oracle_kinematics.argtypes = [P(cabi.ProblemDesc), C.c_int, C.c_int] + [cabi.c_double_p] * 7
+    lib.oracle_batch_step_truth.argtypes = [P(cabi.ProblemDesc), cabi.c_double_p, P(cabi.BatchDesc), cabi.c_double_p, cabi.c_double_p, C.c_int]
     lib.oracle_set_margin_out.argtypes = [cabi.c_double_p]
     lib.oracle_set_margin_out.restype = None
     _lib = lib
@@ -119,6 +120,17 @@ def solve_batch(pb, u0, nb_iter, early_stop=False, Q=None, psi=None, threads=1):
     with _margins(out, pb, nb_iter):
         _check(load().oracle_solve_batch(C.byref(d), cabi.dptr(u0), C.byref(bd), C.byref(opts), C.byref(out.res), threads))
     return out
+
+
+def batch_step_truth(pb, u0, Q=None, psi=None, threads=1):
+    """first-iteration step of BatchILQR / BatchILQRCP: (du as the reference computes it, du solved in __float128 from the same inputs)"""
+    d = pb.to_desc()
+    bd = make_batch_desc(Q, psi)
+    N = (pb.horizon - 1) * pb.m
+    u0 = None if u0 is None else np.ascontiguousarray(np.asarray(u0, dtype=np.float64).reshape(pb.batch, -1))
+    du_ref, du_q = np.empty((pb.batch, N)), np.empty((pb.batch, N))
+    _check(load().oracle_batch_step_truth(C.byref(d), cabi.dptr(u0), C.byref(bd), cabi.dptr(du_ref), cabi.dptr(du_q), threads))
+    return du_ref, du_q
 
 
 def rollout(pb, U, threads=1):

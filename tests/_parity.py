@@ -1,0 +1,154 @@
+"""Parity measures shared by the GPU tests.
+
+The bar (north_star): per iteration the same accepted step sequence; trajectories, gains and cost within 1e-9 relative.
+Two things decide whether a difference between two FP64 implementations of the same algorithm can meet that bar at all, and
+both are MEASURED here on the oracle itself instead of being guessed:
+
+  * `rel()` is element-wise: |a - b| / max(|b|, floor * max|b|) — an element is compared with its own magnitude, with an
+    absolute floor (a fraction of the array's largest magnitude) under entries that pass through zero.
+
+  * Self-sensitivity: the oracle is run again with every q0 moved by one ulp up and one ulp down.  A 1-ulp input change is the
+    smallest perturbation there is, so whatever the oracle's own outputs move by under it is rounding noise that no
+    implementation (the reference included, built with another compiler or on another CPU) can be held below.  From the two
+    perturbed runs come
+      - the instability set: problems whose accepted-step sequence changes;
+      - the tie threshold: the largest line-search decision margin (oracle `margin_hist`: smallest |candidate - incumbent| /
+        |incumbent| over the candidates of an iteration) at which such a change was observed, times 4.  A decision with a
+        margin below it is decided by rounding, not by the algorithm;
+      - the noise floor of every output array (its largest element-wise deviation over the problems whose sequence did
+        not change).
+    A GPU result passes if it is within max(1e-9, 4 x noise floor) of the oracle on the tie-free problems and its step
+    sequences agree with the oracle's up to each problem's first tie.
+"""
+import numpy as np
+
+RTOL = 1e-9
+TIE_FLOOR = 1e-12  # below this a margin is a tie whatever was measured
+NOISE_FACTOR = 4.0
+# Small batches see few or no flips of their own, so their measured threshold is floored by the one measured at full size
+# (tests/test_gpu_parity.py::test_full_size_parity_against_measured_instability re-measures and prints it on every run):
+# 4096 problems of configs[1], 20 iterations, q0 +- 1 ulp: largest decision margin at which the oracle's own step sequence
+# changed = 4.6e-9 (27 % of the problems change sequence), times NOISE_FACTOR.
+TIE_MEASURED_FULL_SIZE = 2e-8
+
+
+def rel(a, b, floor=1e-3, scale=None):
+    """largest element-wise relative difference; NaN patterns must agree.  `scale`: absolute floor of the denominators
+    (instead of floor * max|b|), for quantities that vanish at convergence and are meaningful against another array's size"""
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    assert a.shape == b.shape, (a.shape, b.shape)
+    nan_a, nan_b = np.isnan(a), np.isnan(b)
+    assert np.array_equal(nan_a, nan_b), "NaN pattern differs"
+    if nan_a.all() or a.size == 0:
+        return 0.0
+    if scale is not None:
+        return _scaled(a, b, floor, scale)
+    scale = float(np.nanmax(np.abs(b)))
+    if scale == 0.0:
+        return float(np.nanmax(np.abs(a)))
+    den = np.maximum(np.abs(b), floor * scale)
+    return float(np.nanmax(np.abs(a - b) / den))
+
+
+def _scaled(a, b, floor, scale):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    if a.size == 0:
+        return 0.0
+    return float(np.nanmax(np.abs(a - b) / np.maximum(np.abs(b), scale)))
+
+
+def ulp_shift(pb, ulps):
+    """the same problems with every q0 moved by `ulps` units in the last place (negative: down)"""
+    import copy
+    q = copy.copy(pb)
+    q0 = np.asarray(pb.q0, dtype=np.float64).copy()
+    for _ in range(abs(ulps)):
+        q0 = np.nextafter(q0, q0 + np.sign(ulps))
+    q.q0 = q0
+    return q
+
+
+def measure(solve, pb, fields, shifts=(+1, -1, +2, -2), **kw):
+    """oracle run + its neighbours a few ulps of q0 away -> Sensitivity.  solve(pb) -> result with margin_hist"""
+    ref = solve(pb)
+    return Sensitivity(ref, [solve(ulp_shift(pb, k)) for k in shifts], fields, **kw)
+
+
+def same_sequence(a, b):
+    """per problem: accepted-step sequences identical (NaN = not run = equal)"""
+    return np.all((a == b) | (np.isnan(a) & np.isnan(b)), axis=1)
+
+
+class Sensitivity:
+    """oracle vs oracle under +-1 ulp of q0: instability set, tie threshold, per-array noise floors"""
+
+    def __init__(self, ref, perturbed, fields, tie_min=TIE_MEASURED_FULL_SIZE):
+        self.ref = ref
+        self.perturbed = perturbed
+        B, nit = ref.alpha_hist.shape
+        self.stable = np.ones(B, dtype=bool)
+        flip_margins = []
+        for r in perturbed:
+            same = same_sequence(r.alpha_hist, ref.alpha_hist)
+            self.stable &= same
+            for b in np.nonzero(~same)[0]:
+                eq = (r.alpha_hist[b] == ref.alpha_hist[b]) | (np.isnan(r.alpha_hist[b]) & np.isnan(ref.alpha_hist[b]))
+                k = int(np.argmax(~eq))
+                mg = ref.margin_hist[b, k]
+                if np.isfinite(mg):
+                    flip_margins.append(float(mg))
+        self.flip_margins = np.array(flip_margins)
+        self.largest_flip_margin = float(self.flip_margins.max()) if self.flip_margins.size else 0.0
+        self.tie = max(TIE_FLOOR, tie_min, NOISE_FACTOR * self.largest_flip_margin)
+        # per-iteration relative cost noise, per problem (max over the perturbed runs)
+        with np.errstate(invalid="ignore", divide="ignore"):
+            self.cost_noise = np.max([np.abs(r.cost_hist - ref.cost_hist) / np.abs(ref.cost_hist) for r in perturbed], axis=0)
+        # noise floor of every compared quantity over the problems whose sequence did not change.
+        # fields: names of result arrays, or {name: (getter(result) -> array, rel-kwargs)}
+        self.measures = {f: ((lambda r, f=f: getattr(r, f)), {}) for f in fields} if not isinstance(fields, dict) else fields
+        self.noise = {}
+        st = self.stable
+        for f, (get, kw) in self.measures.items():
+            self.noise[f] = max(rel(get(r)[st], get(ref)[st], **kw) for r in perturbed) if st.any() else 0.0
+
+    def err(self, field, out, mask=None):
+        """element-wise relative difference of `out` from the oracle for one measure, over the problems of `mask`"""
+        get, kw = self.measures[field]
+        a, b = get(out), get(self.ref)
+        if mask is not None:
+            a, b = a[mask], b[mask]
+        return rel(a, b, **kw)
+
+    def tol(self, field):
+        return max(RTOL, NOISE_FACTOR * self.noise.get(field, 0.0))
+
+    def first_tie(self):
+        """per problem: index of the first iteration whose decision is a tie (margin below the measured threshold, or a NaN
+        cost), or the number of iterations run"""
+        ref = self.ref
+        tie = ~(ref.margin_hist >= self.tie) | np.isnan(ref.cost_hist)
+        n = np.asarray(ref.iters, dtype=int)
+        out = np.empty(len(n), dtype=int)
+        for b in range(len(n)):
+            t = np.nonzero(tie[b, :n[b]])[0]
+            out[b] = t[0] if t.size else n[b]
+        return out
+
+    def tie_free(self):
+        return self.first_tie() == np.asarray(self.ref.iters, dtype=int)
+
+    def summary(self):
+        return ("instability set %d of %d, largest margin at a flip %.2e -> tie threshold %.2e; noise floors %s" %
+                ((~self.stable).sum(), len(self.stable), self.largest_flip_margin, self.tie, {k: "%.1e" % v for k, v in self.noise.items()}))
+
+
+def check_sequences(out, sens):
+    """GPU step sequences agree with the oracle's up to each problem's first tie; returns the tie-free mask"""
+    ref = sens.ref
+    ft = sens.first_tie()
+    for b in range(len(ft)):
+        k = ft[b]
+        assert np.array_equal(out.alpha_hist[b, :k], ref.alpha_hist[b, :k]), \
+            "problem %d: step sequence parts from the oracle's at iteration %d, before its first tie (%d)" % (
+                b, int(np.argmax(out.alpha_hist[b, :k] != ref.alpha_hist[b, :k])), k)
+    return ft == np.asarray(ref.iters, dtype=int)
