@@ -231,12 +231,12 @@ def other_configs(torch, device, fp64_peak, hbm_peak):
         entry = {"batch": pb.batch, "nb_iter": nit, "solves_per_s": pb.batch / (ms * 1e-3), "ms_per_solve_batch": ms, "ms_per_iteration": ms / nit,
                  "kernel_ms": {k: round(v[0], 3) for k, v in prof.items()}, "dominant_kernel": dom[0], "e2e_solves_per_s": pb.batch / e2e_s,
                  "e2e_mode": "one blocking host-buffer C-ABI call (pageable numpy buffers), H2D + solve + D2H"}
-        if flops_of:
+        if flops_of:  # (kernel family, algorithmic flops of the whole batch per ITERATION, peak, unit)
             kname, flops, peak, unit = flops_of
             t = prof.get(kname, (0.0, 0))
             if t[1]:
-                ach = flops / (t[0] / t[1] * 1e-3) / (1e12 if unit == "TFLOP/s" else 1e9)
-                entry["roofline"] = {"kernel": kname, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak if peak else None, "avg_launch_ms": t[0] / t[1]}
+                ach = flops / (t[0] / nit * 1e-3) / (1e12 if unit == "TFLOP/s" else 1e9)
+                entry["roofline"] = {"kernel": kname, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak if peak else None, "ms_per_iteration": t[0] / nit}
         if note:
             entry["note"] = note
         res[name] = entry
@@ -260,7 +260,7 @@ def other_configs(torch, device, fp64_peak, hbm_peak):
     pb = synth.config4(batch=1024, horizon=200)
     N = 199 * 8
     run("C4 BatchILQR PosOrnTime T=200 N=1592, one 1024-problem chunk", pb, 3, kind="batch", u0=synth.u0_time(pb), reps=1,
-        flops_of=("batch_cholesky", (N ** 3 / 3.0 + 2.0 * N * N) * 1024 * 3 / 3 * 1.0, fp64_peak, "TFLOP/s"),
+        flops_of=("batch_cholesky", (N ** 3 / 3.0 + 2.0 * N * N) * 1024, fp64_peak, "TFLOP/s"),
         note="batch_cholesky = blocked Cholesky + the two triangular solves, N^3/3 + 2 N^2 flop per problem and iteration")
     psi = np.kron(build_psi("unitstep", 199, 2), np.identity(8))
     run("C4 BatchILQRCP PosOrnTime T=200, Psi = 2 unit steps", pb, 20, kind="batch", u0=synth.u0_time(pb), psi=psi, reps=1)

@@ -7,7 +7,7 @@
 //   k_backward_n1   Riccati recursion (ILQRRecursive.cpp:69-97).  [P|p] lives in registers in the DMMA accumulator
 //                   layout; the products with A and B are exact scalings (x*1 and +0 are exact in IEEE, so
 //                   (B^T P) A == dt*P bit for bit), (Quu + 1e-6 I)^-1 is an in-register division-free Gauss-Jordan, and the
-//                   three dense products that remain per step (K = -Inv Qux, -1e-6 K^T K and Qxu K of the P update)
+//                   four dense products that remain per step (K = -Inv Qux; M = Quu K + Qux, K^T M and Qxu K of the P update)
 //                   run on the FP64 tensor pipe (mma.sync m8n8k4.f64), operands re-laid-out through shared memory.
 //
 //   k_forward_n1    line search + accept (ILQRRecursive.cpp:101-176).  With linear dynamics the candidate rollout is
@@ -199,7 +199,8 @@ __device__ __forceinline__ bool gj_solve_regs(double (&L)[NT][NT][2], double (&R
 template <int NT>
 struct BwdN1Smem {
     static constexpr int NX = 8 * NT, LD = NX + 4, SZ = NX * LD;
-    static constexpr int PER_WARP = 3 * SZ;  // [Qux|Qu], [K|d] (pivot rows of the elimination before that), (Quu + 1e-6 I)^-1
+    // [Qux|Qu], [K|d] (pivot rows of the elimination before that), (Quu + 1e-6 I)^-1 then M = Quu [K|d] + [Qux|Qu], Quu
+    static constexpr int PER_WARP = 4 * SZ;
 };
 
 // ------------------------------------------------------------------------------------------------------------
@@ -222,6 +223,7 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
     double* sQux = wsmem;
     double* sKd = sQux + SZ;
     double* sM = sKd + SZ;
+    double* sQuu = sM + SZ;
 
     double Rrow[NT];
 #pragma unroll
@@ -347,7 +349,7 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
         }
         // [Qux|Qu] = [0 | R u] + (B^T [P|p]) A_aug ;  Quu = R + (B^T P) B ;  [Qxx|Qx] = [l_xx|l_x] + (A^T [P|p]) A_aug
         // Qxu = (A^T P) B = P*dt has the same entries as Qux = dt*P                     ILQRRecursive.cpp:82-87
-        double Qa[NT][NT][2], Qx[NT][NT][2], Inv[NT][NT][2];
+        double Qa[NT][NT][2], Qx[NT][NT][2], Inv[NT][NT][2], Quu[NT][NT][2];
 #pragma unroll
         for (int rt = 0; rt < NT; rt++) {
             const int i = 8 * rt + g;
@@ -363,6 +365,7 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
                     quu = (j < m) ? quu : 0.0;  // rows >= m of [P|p] are zero already
                     // Quu + 1e-6 I, identity outside the leading block                    ILQRRecursive.cpp:89
                     Inv[rt][ct][h] = (i == j) ? ((i < m) ? quu + 1e-6 * 1.0 : 1.0) : quu;
+                    Quu[rt][ct][h] = quu;  // the un-regularised Quu of the P update below
                     Qx[rt][ct][h] = Pa[rt][ct][h];
                 }
         }
@@ -374,6 +377,7 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
         if (l0 >= 0) add_limits(Qx, x);
 
         st_c<NT, LD>(sQux, Qa, g, t);
+        st_c<NT, LD>(sQuu, Quu, g, t);
         // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]                                            ILQRRecursive.cpp:89-91
         double Kd[NT][NT][2];
         if constexpr (NT == 1) {  // explicit inverse, then the product on DMMA
@@ -416,19 +420,43 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
         __syncwarp();
 
         // [P|p] = [Qxx|Qx] + K^T (Quu [K|d] + [Qux|Qu]) + Qxu [K|d]                       ILQRRecursive.cpp:93-94
-        // With [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu] the bracket is -1e-6 [K|d] identically (for any P, symmetric or not), so the
-        // three-term form of the reference collapses to  [Qxx|Qx] - 1e-6 K^T [K|d] + Qxu [K|d]  — the same quantity without
-        // the cancellation of Quu K against Qux, and two products fewer.  (Row n = d^T [..] is produced too and masked out.)
-        double kb[NT][2][NT], ke[NT][2][NT];
+        // The bracket M is formed as written, with the un-regularised Quu.  Analytically M = -1e-6 [K|d] (because
+        // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]), and round 1 used that identity to save two products — but the reference's form is
+        // stationary in K: an error dK in the computed gains (cond(Quu) eps) enters P through (K^T Quu + Qxu) dK = M^T dK ~ 0,
+        // whereas the collapsed form passes Qxu dK on at first order, step after step.  Measured against a long-double run of
+        // the oracle (tests/_parity.py): gains 1.1e-9 from the truth with the collapsed form, 2e-11 with this one, which is
+        // what the reference's own arithmetic gives.  (Row n = d^T [..] is produced too and masked out.)
+        double kb[NT][2][NT], mb[NT][2][NT];
 #pragma unroll
         for (int kt = 0; kt < NT; kt++)
 #pragma unroll
             for (int s = 0; s < 2; s++)
 #pragma unroll
+                for (int ct = 0; ct < NT; ct++) kb[kt][s][ct] = ld_b<LD>(sKd, kt, s, ct, g, t);  // B fragment of [K|d] == A fragment of [K|d]^T
+        {
+            double Mm[NT][NT][2];
+#pragma unroll
+            for (int rt = 0; rt < NT; rt++)
+#pragma unroll
                 for (int ct = 0; ct < NT; ct++) {
-                    kb[kt][s][ct] = ld_b<LD>(sKd, kt, s, ct, g, t);  // B fragment of [K|d] == A fragment of [K|d]^T
-                    ke[kt][s][ct] = -1e-6 * kb[kt][s][ct];
+                    double c0 = Qa[rt][ct][0], c1 = Qa[rt][ct][1];
+#pragma unroll
+                    for (int kt = 0; kt < NT; kt++)
+#pragma unroll
+                        for (int s = 0; s < 2; s++) dmma884(c0, c1, ld_a<LD>(sQuu, rt, kt, s, g, t), kb[kt][s][ct]);
+                    Mm[rt][ct][0] = c0;
+                    Mm[rt][ct][1] = c1;
                 }
+            __syncwarp();  // NT == 1: every lane has read the inverse in sM
+            st_c<NT, LD>(sM, Mm, g, t);
+            __syncwarp();
+        }
+#pragma unroll
+        for (int kt = 0; kt < NT; kt++)
+#pragma unroll
+            for (int s = 0; s < 2; s++)
+#pragma unroll
+                for (int ct = 0; ct < NT; ct++) mb[kt][s][ct] = ld_b<LD>(sM, kt, s, ct, g, t);
 #pragma unroll
         for (int rt = 0; rt < NT; rt++)
 #pragma unroll
@@ -437,7 +465,7 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
 #pragma unroll
                 for (int kt = 0; kt < NT; kt++)
 #pragma unroll
-                    for (int s = 0; s < 2; s++) dmma884(c0, c1, ke[kt][s][rt], kb[kt][s][ct]);
+                    for (int s = 0; s < 2; s++) dmma884(c0, c1, kb[kt][s][rt], mb[kt][s][ct]);
 #pragma unroll
                 for (int kt = 0; kt < NT; kt++)
 #pragma unroll

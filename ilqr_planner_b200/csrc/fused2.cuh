@@ -9,7 +9,7 @@
 //   [Qux|Qu]  = [M1, dt M1 + M2] + [0 | R u]        Quu = R + c2 M1 + dt M2
 //   A^T [P|p] = N,  N1c = P1c,  N2c = dt P1c + P2c ;   [Qxx|Qx] = [l_xx|l_x] + [Nr1, dt Nr1 + Nr2] ;   Qxu = c2 Nr1 + dt Nr2
 // Only [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu] (in-register Gauss-Jordan inverse, 4 DMMA for the product) and
-// P' = Qxx + K^T (Quu K + Qux) + Qxu K = Qxx - 1e-6 K^T K + Qxu K (16 DMMA m8n8k4.f64) remain as dense work per step
+// M = Quu [K|d] + [Qux|Qu] (4 DMMA), P' = Qxx + K^T M + Qxu K (16 DMMA m8n8k4.f64) remain as dense work per step
 // (ILQRRecursive.cpp:69-97).
 #pragma once
 #include "fused1.cuh"
@@ -19,7 +19,7 @@ namespace ilqrb {
 struct BwdN2Smem {
     static constexpr int LDW = 20, LDQ = 12;                 // 8 x 16 matrices / the 8 x 8 Quu
     static constexpr int SZW = 8 * LDW, SZQ = 8 * LDQ;
-    static constexpr int PER_WARP = 2 * SZW + 3 * SZQ;       // [K|d], [Qux|Qu], Qxu (16 x 8), (Quu + 1e-6 I)^-1
+    static constexpr int PER_WARP = 2 * SZW + 4 * SZQ;       // [K|d], [Qux|Qu] then M, Qxu (16 x 8), (Quu + 1e-6 I)^-1, Quu
 };
 
 // fragment loads of the 8 x 16 matrices (row-major, leading dimension LDW)
@@ -40,6 +40,7 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
     double* sM = sKd + S::SZW;
     double* sQxu = sM + S::SZW;  // 16 x 8
     double* sInv = sQxu + 2 * S::SZQ;
+    double* sQuu = sInv + S::SZQ;
     const bool rowv = g < dof;  // this lane's row is a real control / state row of its tile
     const double Rg = rowv ? P.r_diag[g] : 0.0;
     const double* Xb = W.X + (size_t)b * H * ns;
@@ -196,6 +197,7 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
         double Iv[1][1][2] = {{{Lr[0], Lr[1]}}};
         spd = gj_inverse_regs<1, DOF, S::LDW>(Iv, sKd, m, g, t) && spd;
         *reinterpret_cast<double2*>(sInv + g * S::LDQ + 2 * t) = make_double2(Iv[0][0][0], Iv[0][0][1]);
+        *reinterpret_cast<double2*>(sQuu + g * S::LDQ + 2 * t) = make_double2(Quu[0], Quu[1]);  // un-regularised, for the P update
         __syncwarp();
         double Kd[2][2];
         {
@@ -227,24 +229,43 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
         }
         __syncwarp();
 
-        // [P|p] = [Qxx|Qx] + K^T (Quu [K|d] + [Qux|Qu]) + Qxu [K|d]   (ILQRRecursive.cpp:93-94); the bracket is -1e-6 [K|d]
-        // identically because [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu] (see backward_n1_body)
-        double kb[2][2], ke[2][2], xa[2][2];  // B fragments of [K|d] (= A fragments of [K|d]^T), -1e-6 times them; A fragments of Qxu
+        // [P|p] = [Qxx|Qx] + K^T (Quu [K|d] + [Qux|Qu]) + Qxu [K|d]   (ILQRRecursive.cpp:93-94).  The bracket M is formed as
+        // written, with the un-regularised Quu: this form is stationary in K, so the rounding error of the computed gains does not
+        // enter P at first order (see backward_n1_body; the collapsed form M = -1e-6 [K|d] of round 1 lost that)
+        double kb[2][2], mb[2][2], xa[2][2];  // B fragments of [K|d] (= A fragments of [K|d]^T) and of M; A fragments of Qxu
 #pragma unroll
         for (int s = 0; s < 2; s++)
 #pragma unroll
             for (int c = 0; c < 2; c++) {
                 kb[s][c] = ld_bw(sKd, s, c, g, t);
-                ke[s][c] = -1e-6 * kb[s][c];
                 xa[s][c] = sQxu[(8 * c + g) * S::LDQ + 4 * s + t];
             }
+        {
+            const double qa0 = sQuu[g * S::LDQ + t], qa1 = sQuu[g * S::LDQ + 4 + t];
+            double Mm[2][2];
+#pragma unroll
+            for (int c = 0; c < 2; c++) {
+                double c0 = Qa[c][0], c1 = Qa[c][1];
+                dmma884(c0, c1, qa0, kb[0][c]);
+                dmma884(c0, c1, qa1, kb[1][c]);
+                Mm[c][0] = c0;
+                Mm[c][1] = c1;
+            }
+            __syncwarp();  // every lane has read [Qux|Qu] in sM
+            st_w(sM, Mm, g, t);
+            __syncwarp();
+        }
+#pragma unroll
+        for (int s = 0; s < 2; s++)
+#pragma unroll
+            for (int c = 0; c < 2; c++) mb[s][c] = ld_bw(sM, s, c, g, t);
 #pragma unroll
         for (int r = 0; r < 2; r++)
 #pragma unroll
             for (int c = 0; c < 2; c++) {
                 double c0 = Qx[r][c][0], c1 = Qx[r][c][1];
 #pragma unroll
-                for (int s = 0; s < 2; s++) dmma884(c0, c1, kb[s][r], ke[s][c]);
+                for (int s = 0; s < 2; s++) dmma884(c0, c1, kb[s][r], mb[s][c]);
 #pragma unroll
                 for (int s = 0; s < 2; s++) dmma884(c0, c1, xa[s][r], kb[s][c]);
                 // keep rows >= dof (incl. the d row the transposed fragment drags in) and unused columns at exact zero

@@ -847,7 +847,8 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward(const DevProblem*
         }
         __syncwarp();
         // [P|p] = [Qxx|Qx] + K^T (Quu [K|d] + [Qux|Qu]) + Qxu [K|d]      ILQRRecursive.cpp:93-94
-        // the bracket is -1e-6 [K|d] identically, because [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu] (see backward_n1_body)
+        // the bracket M (un-regularised Quu) is formed as written, in place over [Qux|Qu]: stationary in K (see backward_n1_body)
+        wm_gemm<NUT, NXT, NUT, false, false, true, false>(QuxQu, LDX, Quu, LDU, Kd, LDX, lane);
         {
             const int g = lane >> 2, t = lane & 3;
 #pragma unroll
@@ -855,12 +856,12 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward(const DevProblem*
 #pragma unroll
                 for (int ct = 0; ct < NXT; ct++) {
                     double a0 = 0.0, a1 = 0.0, c0 = 0.0, c1 = 0.0;
-                    wm_tile_acc<NUT, true, false>(a0, a1, Kd, LDX, Kd, LDX, rt, ct, g, t);
+                    wm_tile_acc<NUT, true, false>(a0, a1, Kd, LDX, QuxQu, LDX, rt, ct, g, t);
                     wm_tile_acc<NUT, false, false>(c0, c1, Qxu, LDU, Kd, LDX, rt, ct, g, t);
                     const int i = 8 * rt + g, j = 8 * ct + 2 * t;
                     const double2 q = *reinterpret_cast<const double2*>(QxxQx + i * LDX + j);
-                    double v0 = fma(-1e-6, a0, q.x) + c0;
-                    double v1 = fma(-1e-6, a1, q.y) + c1;
+                    double v0 = (q.x + a0) + c0;
+                    double v1 = (q.y + a1) + c1;
                     if (i >= n || j > n) v0 = 0.0;
                     if (i >= n || j + 1 > n) v1 = 0.0;
                     *reinterpret_cast<double2*>(Paug + i * LDX + j) = make_double2(v0, v1);

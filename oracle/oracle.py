@@ -12,24 +12,27 @@ from ilqr_planner_b200 import cabi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_build", "liboracle.so")
-_lib = None
+# same source, other arithmetic (oracle/Makefile): "fma" = -ffp-contract=fast, "ld" = long double internally
+VARIANTS = {None: LIB_PATH, "fma": os.path.join(_HERE, "_build", "liboracle_fma.so"), "ld": os.path.join(_HERE, "_build", "liboracle_ld.so")}
+_libs = {}
 
 
 def build(force=False):
     src = os.path.join(_HERE, "ilqr_oracle.cpp")
     hdr = os.path.join(_HERE, "..", "include", "ilqrb.h")
-    if (not force and os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= max(os.path.getmtime(src), os.path.getmtime(hdr))):
+    newest = max(os.path.getmtime(src), os.path.getmtime(hdr), os.path.getmtime(os.path.join(_HERE, "Makefile")))
+    if (not force and all(os.path.exists(p) and os.path.getmtime(p) >= newest for p in VARIANTS.values())):
         return LIB_PATH
-    subprocess.check_call(["make", "-C", _HERE, "-B"], stdout=subprocess.DEVNULL)
+    subprocess.check_call(["make", "-C", _HERE, "-B", "-j3", "all"], stdout=subprocess.DEVNULL)
     return LIB_PATH
 
 
-def load():
-    global _lib
-    if _lib is not None:
-        return _lib
+def load(variant=None):
+    """variant None: the oracle proper (FP64, -ffp-contract=off); "fma" / "ld": see VARIANTS"""
+    if variant in _libs:
+        return _libs[variant]
     build()
-    lib = C.CDLL(LIB_PATH)
+    lib = C.CDLL(VARIANTS[variant])
     P = C.POINTER
     lib.oracle_last_error.restype = C.c_char_p
     lib.oracle_get_dims.argtypes = [P(cabi.ProblemDesc), P(cabi.Dims)]
@@ -41,7 +44,7 @@ def load():
     lib.oracle_batch_step_truth.argtypes = [P(cabi.ProblemDesc), cabi.c_double_p, P(cabi.BatchDesc), cabi.c_double_p, cabi.c_double_p, C.c_int]
     lib.oracle_set_margin_out.argtypes = [cabi.c_double_p]
     lib.oracle_set_margin_out.restype = None
-    _lib = lib
+    _libs[variant] = lib
     return lib
 
 
@@ -57,25 +60,26 @@ def hardware_threads():
 class _margins:
     """attach a [B][nb_iter] `margin_hist` (line-search decision margins, a test aid) to the result of a solve"""
 
-    def __init__(self, out, pb, nb_iter):
+    def __init__(self, out, pb, nb_iter, variant=None):
         self.out = out
+        self.variant = variant
         out.margin_hist = np.full((pb.batch, max(nb_iter, 1)), np.nan)
 
     def __enter__(self):
-        load().oracle_set_margin_out(cabi.dptr(self.out.margin_hist))
+        load(self.variant).oracle_set_margin_out(cabi.dptr(self.out.margin_hist))
 
     def __exit__(self, *a):
-        load().oracle_set_margin_out(cabi.dptr(None))
+        load(self.variant).oracle_set_margin_out(cabi.dptr(None))
 
 
-def solve_recursive(pb, U0, nb_iter, line_search=True, early_stop=False, threads=1):
+def solve_recursive(pb, U0, nb_iter, line_search=True, early_stop=False, threads=1, variant=None):
     from ilqr_planner_b200.problem import ResultBuffers
     d = pb.to_desc()
     out = ResultBuffers(pb, nb_iter, "recursive")
     opts = cabi.SolveOpts(nb_iter, int(line_search), int(early_stop), 0)
     U0 = None if U0 is None else np.ascontiguousarray(np.asarray(U0, dtype=np.float64).reshape(pb.batch, pb.horizon - 1, pb.m))
-    with _margins(out, pb, nb_iter):
-        _check(load().oracle_solve_recursive(C.byref(d), cabi.dptr(U0), C.byref(opts), C.byref(out.res), threads))
+    with _margins(out, pb, nb_iter, variant):
+        _check(load(variant).oracle_solve_recursive(C.byref(d), cabi.dptr(U0), C.byref(opts), C.byref(out.res), threads))
     return out
 
 
@@ -90,15 +94,15 @@ def make_al_desc(pb, A, b, lambda0, lag_update_step, penalty, scaling_factor):
     return al
 
 
-def solve_al(pb, U0, A, b, lambda0, nb_iter, lag_update_step, penalty, scaling_factor, line_search=True, early_stop=False, threads=1):
+def solve_al(pb, U0, A, b, lambda0, nb_iter, lag_update_step, penalty, scaling_factor, line_search=True, early_stop=False, threads=1, variant=None):
     from ilqr_planner_b200.problem import ResultBuffers
     d = pb.to_desc()
     al = make_al_desc(pb, A, b, lambda0, lag_update_step, penalty, scaling_factor)
     out = ResultBuffers(pb, nb_iter, "al", nc=al.nc)
     opts = cabi.SolveOpts(nb_iter, int(line_search), int(early_stop), 0)
     U0 = None if U0 is None else np.ascontiguousarray(np.asarray(U0, dtype=np.float64).reshape(pb.batch, pb.horizon - 1, pb.m))
-    with _margins(out, pb, nb_iter):
-        _check(load().oracle_solve_al(C.byref(d), cabi.dptr(U0), C.byref(al), C.byref(opts), C.byref(out.res), threads))
+    with _margins(out, pb, nb_iter, variant):
+        _check(load(variant).oracle_solve_al(C.byref(d), cabi.dptr(U0), C.byref(al), C.byref(opts), C.byref(out.res), threads))
     return out
 
 
@@ -110,15 +114,15 @@ def make_batch_desc(Q=None, psi=None):
     return bd
 
 
-def solve_batch(pb, u0, nb_iter, early_stop=False, Q=None, psi=None, threads=1):
+def solve_batch(pb, u0, nb_iter, early_stop=False, Q=None, psi=None, threads=1, variant=None):
     from ilqr_planner_b200.problem import ResultBuffers
     d = pb.to_desc()
     bd = make_batch_desc(Q, psi)
     out = ResultBuffers(pb, nb_iter, "batch")
     opts = cabi.SolveOpts(nb_iter, 1, int(early_stop), 0)
     u0 = None if u0 is None else np.ascontiguousarray(np.asarray(u0, dtype=np.float64).reshape(pb.batch, -1))
-    with _margins(out, pb, nb_iter):
-        _check(load().oracle_solve_batch(C.byref(d), cabi.dptr(u0), C.byref(bd), C.byref(opts), C.byref(out.res), threads))
+    with _margins(out, pb, nb_iter, variant):
+        _check(load(variant).oracle_solve_batch(C.byref(d), cabi.dptr(u0), C.byref(bd), C.byref(opts), C.byref(out.res), threads))
     return out
 
 

@@ -7,18 +7,24 @@ both are MEASURED here on the oracle itself instead of being guessed:
   * `rel()` is element-wise: |a - b| / max(|b|, floor * max|b|) — an element is compared with its own magnitude, with an
     absolute floor (a fraction of the array's largest magnitude) under entries that pass through zero.
 
-  * Self-sensitivity: the oracle is run again with every q0 moved by one ulp up and one ulp down.  A 1-ulp input change is the
-    smallest perturbation there is, so whatever the oracle's own outputs move by under it is rounding noise that no
-    implementation (the reference included, built with another compiler or on another CPU) can be held below.  From the two
-    perturbed runs come
+  * Self-sensitivity: the oracle is run again (a) with every q0 moved by one ulp up and one ulp down — the smallest input
+    perturbation there is — and (b) built with fused multiply-adds allowed (liboracle_fma.so: -ffp-contract=fast, GCC's default
+    and what the reference's own build gets on an FMA machine: every operation rounds differently).  Whatever the oracle's
+    own outputs move by between these equally valid runs is rounding noise that no implementation (the reference included,
+    built with another compiler or on another CPU) can be held below.  From these neighbour runs come
       - the instability set: problems whose accepted-step sequence changes;
       - the tie threshold: the largest line-search decision margin (oracle `margin_hist`: smallest |candidate - incumbent| /
         |incumbent| over the candidates of an iteration) at which such a change was observed, times 4.  A decision with a
         margin below it is decided by rounding, not by the algorithm;
       - the noise floor of every output array (its largest element-wise deviation over the problems whose sequence did
         not change).
-    A GPU result passes if it is within max(1e-9, 4 x noise floor) of the oracle on the tie-free problems and its step
-    sequences agree with the oracle's up to each problem's first tie.
+  * Truth: the same oracle source built with every internal double widened to long double (liboracle_ld.so, 64-bit
+    mantissa): the identical algorithm 2048 times finer.  The FP64 oracle's distance from it is how far the reference's own
+    arithmetic sits from the exact answer; it joins the noise floor, and `check_truth` holds the GPU to being as close to the
+    truth as the FP64 runs are (within NOISE_FACTOR).  This is what showed that the collapsed P update of round 1
+    (-1e-6 K^T K for K^T (Quu K + Qux)) put the gains 60 times further from the truth than the reference's form.
+    A GPU result passes if it is within max(1e-9, 4 x noise floor) of the oracle on the tie-free problems, as close to the truth
+    as the FP64 oracle builds are (x 4), and its step sequences agree with the oracle's up to each problem's first tie.
 """
 import numpy as np
 
@@ -68,10 +74,14 @@ def ulp_shift(pb, ulps):
     return q
 
 
-def measure(solve, pb, fields, shifts=(+1, -1, +2, -2), **kw):
-    """oracle run + its neighbours a few ulps of q0 away -> Sensitivity.  solve(pb) -> result with margin_hist"""
-    ref = solve(pb)
-    return Sensitivity(ref, [solve(ulp_shift(pb, k)) for k in shifts], fields, **kw)
+NEIGHBOURS = ((0, "fma"), (+1, None), (-1, None), (+1, "fma"), (-1, "fma"))
+
+
+def measure(solve, pb, fields, neighbours=NEIGHBOURS, truth=True, **kw):
+    """oracle run + its neighbours (+ the long-double truth) -> Sensitivity.  solve(pb, variant) -> result with margin_hist;
+    a neighbour is (ulps of q0, oracle build)"""
+    ref = solve(pb, None)
+    return Sensitivity(ref, [solve(ulp_shift(pb, k) if k else pb, v) for k, v in neighbours], fields, truth=solve(pb, "ld") if truth else None, **kw)
 
 
 def same_sequence(a, b):
@@ -82,9 +92,10 @@ def same_sequence(a, b):
 class Sensitivity:
     """oracle vs oracle under +-1 ulp of q0: instability set, tie threshold, per-array noise floors"""
 
-    def __init__(self, ref, perturbed, fields, tie_min=TIE_MEASURED_FULL_SIZE):
+    def __init__(self, ref, perturbed, fields, tie_min=TIE_MEASURED_FULL_SIZE, truth=None):
         self.ref = ref
         self.perturbed = perturbed
+        self.truth = truth
         B, nit = ref.alpha_hist.shape
         self.stable = np.ones(B, dtype=bool)
         flip_margins = []
@@ -110,6 +121,14 @@ class Sensitivity:
         st = self.stable
         for f, (get, kw) in self.measures.items():
             self.noise[f] = max(rel(get(r)[st], get(ref)[st], **kw) for r in perturbed) if st.any() else 0.0
+        # distance of the FP64 runs from the long-double truth, over the problems where all of them take the truth's steps
+        self.truth_err = {}
+        if truth is not None:
+            self.with_truth = st & same_sequence(truth.alpha_hist, ref.alpha_hist)
+            wt = self.with_truth
+            for f, (get, kw) in self.measures.items():
+                self.truth_err[f] = max(rel(get(r)[wt], get(truth)[wt], **kw) for r in [ref, perturbed[0]]) if wt.any() else 0.0
+                self.noise[f] = max(self.noise[f], self.truth_err[f])
 
     def err(self, field, out, mask=None):
         """element-wise relative difference of `out` from the oracle for one measure, over the problems of `mask`"""
@@ -137,9 +156,22 @@ class Sensitivity:
     def tie_free(self):
         return self.first_tie() == np.asarray(self.ref.iters, dtype=int)
 
+    def check_truth(self, out, mask=None):
+        """`out` is as close to the long-double truth as the FP64 oracle builds are (x NOISE_FACTOR, floor RTOL), per measure"""
+        if self.truth is None:
+            return {}
+        m = self.with_truth if mask is None else (self.with_truth & mask)
+        got = {}
+        for f, (get, kw) in self.measures.items():
+            e = rel(get(out)[m], get(self.truth)[m], **kw) if m.any() else 0.0
+            got[f] = e
+            assert e < max(RTOL, NOISE_FACTOR * self.truth_err[f]), "%s: %.2e from the long-double truth, the FP64 oracle %.2e" % (f, e, self.truth_err[f])
+        return got
+
     def summary(self):
-        return ("instability set %d of %d, largest margin at a flip %.2e -> tie threshold %.2e; noise floors %s" %
-                ((~self.stable).sum(), len(self.stable), self.largest_flip_margin, self.tie, {k: "%.1e" % v for k, v in self.noise.items()}))
+        return ("instability set %d of %d, largest margin at a flip %.2e -> tie threshold %.2e; noise floors %s; FP64 oracle from the long-double truth %s" %
+                ((~self.stable).sum(), len(self.stable), self.largest_flip_margin, self.tie, {k: "%.1e" % v for k, v in self.noise.items()},
+                 {k: "%.1e" % v for k, v in self.truth_err.items()}))
 
 
 def check_sequences(out, sens):

@@ -74,8 +74,8 @@ def _check_recursive(pb, u0, nb_iter, oracle, early_stop=False, min_tie_free=0.5
     fields = dict(REC_FIELDS)
     dscale = None
 
-    def solve(p):
-        return oracle.solve_recursive(p, u0, nb_iter, True, early_stop, threads=8)
+    def solve(p, v=None):
+        return oracle.solve_recursive(p, u0, nb_iter, True, early_stop, threads=8, variant=v)
     sens = pt.measure(solve, pb, fields)
     ref = sens.ref
     free = pt.check_sequences(out, sens)  # exact step sequences up to each problem's first tie
@@ -94,6 +94,7 @@ def _check_recursive(pb, u0, nb_iter, oracle, early_stop=False, min_tie_free=0.5
     dn = max(rel(r.d[sens.stable], ref.d[sens.stable], scale=dscale) for r in sens.perturbed) if sens.stable.any() else 0.0
     assert rel(out.d[free], ref.d[free], scale=dscale) < max(RTOL, pt.NOISE_FACTOR * dn)
     assert rel(out.cost[free], ref.cost[free], floor=0.0) < sens.tol("cost_hist")
+    sens.check_truth(out, free)
     return out, ref
 
 
@@ -182,9 +183,9 @@ def _check_al(pb, al, nb_iter, oracle, line_search=True, want_active=True):
     with _handle(pb) as h:
         out = h.solve_al(None, al["A"], al["b"], al["lambda0"], nb_iter, al["lag_update_step"], al["penalty"], al["scaling_factor"], line_search, False)
 
-    def solve(p):
+    def solve(p, v=None):
         return oracle.solve_al(p, None, al["A"], al["b"], al["lambda0"], nb_iter, al["lag_update_step"], al["penalty"], al["scaling_factor"], line_search, False,
-                               threads=8)
+                               threads=8, variant=v)
     sens = pt.measure(solve, pb, AL_FIELDS)
     ref = sens.ref
     if want_active:
@@ -205,6 +206,7 @@ def _check_al(pb, al, nb_iter, oracle, line_search=True, want_active=True):
     for f in ("X", "U", "lam"):
         e = sens.err(f, out, free)
         assert e < sens.tol(f), "%s %.2e (bound %.2e; %s)" % (f, e, sens.tol(f), sens.summary())
+    sens.check_truth(out, free)
     return out, ref
 
 
@@ -265,7 +267,7 @@ def test_generic_recursive_path_vs_oracle(oracle_lib):
         "for pb, nit in ((synth.config2(batch=16), 6), (synth.config3(batch=8), 4)):\n"
         "    with Handle(pb, device=0) as h: out = h.solve_recursive(None, nit, True, False)\n"
         "    F = {'cost_hist': (lambda r: r.cost_hist, dict(floor=0.0)), 'X': (lambda r: r.X, {}), 'U': (lambda r: r.U, {}), 'K': (lambda r: r.K, {})}\n"
-        "    sens = pt.measure(lambda p: oracle.solve_recursive(p, None, nit, True, False, threads=8), pb, F)\n"
+        "    sens = pt.measure(lambda p, v=None: oracle.solve_recursive(p, None, nit, True, False, threads=8, variant=v), pb, F)\n"
         "    free = pt.check_sequences(out, sens)\n"
         "    assert free.sum() >= pb.batch // 2\n"
         "    for f in F:\n"
@@ -366,7 +368,7 @@ def _check_batch(pb, u0, nb_iter, oracle, psi=None, early_stop=False):
     __float128 solution."""
     with _handle(pb) as h:
         out = h.solve_batch(u0, nb_iter, early_stop, psi=psi)
-    sens = pt.measure(lambda p: oracle.solve_batch(p, u0, nb_iter, early_stop, psi=psi, threads=8), pb, BATCH_FIELDS)
+    sens = pt.measure(lambda p, v=None: oracle.solve_batch(p, u0, nb_iter, early_stop, psi=psi, threads=8, variant=v), pb, BATCH_FIELDS)
     ref = sens.ref
     free = pt.check_sequences(out, sens)
     assert free.sum() >= pb.batch // 2, sens.summary()
@@ -498,9 +500,9 @@ def test_c4_at_its_own_size(oracle_lib):
     pb = synth.config4(batch=2, horizon=200)
     u0 = synth.u0_time(pb)
     assert (pb.horizon - 1) * pb.m == 1592
-    out, ref = _check_batch_shifts(pb, u0, 2, oracle_lib, shifts=(+1, -1))
+    out, ref = _check_batch_shifts(pb, u0, 2, oracle_lib)
     psi = np.kron(build_psi("unitstep", pb.horizon - 1, 2), np.identity(pb.m))
-    _check_batch_shifts(pb, u0, 3, oracle_lib, psi=psi, shifts=(+1, -1))
+    _check_batch_shifts(pb, u0, 3, oracle_lib, psi=psi)
     old = os.environ.get("ILQRB_BATCH_WS_GB")
     os.environ["ILQRB_BATCH_WS_GB"] = "0.03"  # one problem needs 21 MB of N x N matrix plus the rest: chunks of one problem
     try:
@@ -514,11 +516,12 @@ def test_c4_at_its_own_size(oracle_lib):
     assert np.array_equal(o2.U, out.U) and np.array_equal(o2.cost_hist, out.cost_hist) and np.array_equal(o2.alpha_hist, out.alpha_hist)
 
 
-def _check_batch_shifts(pb, u0, nb_iter, oracle, psi=None, shifts=(+1, -1)):
+def _check_batch_shifts(pb, u0, nb_iter, oracle, psi=None):
     """_check_batch with fewer oracle neighbours (the N = 1592 inverse of the oracle takes tens of seconds per iteration)"""
     with _handle(pb) as h:
         out = h.solve_batch(u0, nb_iter, False, psi=psi)
-    sens = pt.measure(lambda p: oracle.solve_batch(p, u0, nb_iter, False, psi=psi, threads=8), pb, BATCH_FIELDS, shifts=shifts)
+    sens = pt.measure(lambda p, v=None: oracle.solve_batch(p, u0, nb_iter, False, psi=psi, threads=8, variant=v), pb, BATCH_FIELDS,
+                      neighbours=((0, "fma"), (+1, None), (-1, None)), truth=False)
     ref = sens.ref
     pt.check_sequences(out, sens)
     keep = ~np.isnan(ref.cost_hist) & (np.arange(ref.cost_hist.shape[1])[None, :] <= sens.first_tie()[:, None])
@@ -590,16 +593,17 @@ def test_full_size_parity_against_measured_instability(oracle_lib):
         out = h.solve_recursive(None, nit, True, False)
     threads = os.cpu_count() or 8
     fields = dict(REC_FIELDS)
-    sens = pt.measure(lambda p: oracle_lib.solve_recursive(p, None, nit, True, False, threads=threads), pb, fields, shifts=(+1, -1), tie_min=0.0)
+    sens = pt.measure(lambda p, v=None: oracle_lib.solve_recursive(p, None, nit, True, False, threads=threads, variant=v), pb, fields,
+                      neighbours=((0, "fma"), (+1, None), (-1, None)), tie_min=0.0)
     ref = sens.ref
     print("oracle vs itself:", sens.summary())
     gpu_diff = ~pt.same_sequence(out.alpha_hist, ref.alpha_hist)
-    self_diff = [(~pt.same_sequence(r.alpha_hist, ref.alpha_hist)).sum() for r in sens.perturbed]
+    self_diff = [int((~pt.same_sequence(r.alpha_hist, ref.alpha_hist)).sum()) for r in sens.perturbed]
     free = sens.tie_free()
     with np.errstate(invalid="ignore", divide="ignore"):
         dev = np.abs(out.cost_hist - ref.cost_hist) / np.abs(ref.cost_hist)
     med_gpu, med_self = np.nanmedian(dev, axis=0), np.nanmedian(sens.cost_noise, axis=0)
-    print("GPU sequences differing from the oracle's: %d ; oracle (+1 ulp, -1 ulp) from itself: %s ; tie-free problems %d" % (gpu_diff.sum(), self_diff, free.sum()))
+    print("GPU sequences differing from the oracle's: %d ; oracle neighbours (FMA build, +1 ulp, -1 ulp) from the oracle: %s ; tie-free problems %d" % (gpu_diff.sum(), self_diff, free.sum()))
     print("per-iteration relative cost difference, median over problems: GPU %s\n   oracle noise %s" % (np.array2string(med_gpu, precision=1), np.array2string(med_self, precision=1)))
     print("worst over tie-free problems: GPU %.2e, oracle noise %.2e" % (np.nanmax(dev[free]), np.nanmax(sens.cost_noise[free & sens.stable])))
     # (iii) and (i): sequences
@@ -610,6 +614,7 @@ def test_full_size_parity_against_measured_instability(oracle_lib):
     for f in ("cost_hist", "X", "U", "fX", "K"):
         e = sens.err(f, out, free)
         assert e < sens.tol(f), "%s %.2e (bound %.2e)" % (f, e, sens.tol(f))
+    print("from the long-double truth (GPU):", {k: "%.1e" % v for k, v in sens.check_truth(out, free).items()})
     # (ii)
     assert gpu_diff.sum() <= 1.1 * max(self_diff) + 8, (gpu_diff.sum(), self_diff)
     # (iv)
