@@ -15,6 +15,7 @@ JOINT_FIXED, JOINT_ROT, JOINT_TRANS = 0, 1, 2
 KP_STRIDE = 15
 N_ALPHA = 11
 MAX_SEGMENTS = 24
+KIN_STATIC_MAX_NQ = 4096
 ST_NAN_COST, ST_QUU_NOT_SPD, ST_EARLY_STOP = 1, 2, 4
 PROF_SLOTS = 12
 
@@ -95,7 +96,7 @@ SYMBOLS = [
     "ilqrb_synchronize", "ilqrb_update_problems", "ilqrb_solve_recursive", "ilqrb_solve_recursive_async", "ilqrb_solve_al", "ilqrb_solve_batch",
     "ilqrb_upload_u0", "ilqrb_run_recursive", "ilqrb_run_al", "ilqrb_run_batch", "ilqrb_download", "ilqrb_rollout",
     "ilqrb_kinematics", "ilqrb_set_profiling", "ilqrb_get_profile", "ilqrb_reset_profile", "ilqrb_launch_count",
-    "ilqrb_chain_from_urdf", "ilqrb_build_psi", "ilqrb_fp64_peaks",
+    "ilqrb_chain_from_urdf", "ilqrb_build_psi", "ilqrb_fp64_peaks", "ilqrb_kinematics_static",
 ]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -132,6 +133,7 @@ def load():
     lib.ilqrb_download.argtypes = [H, C.POINTER(Result)]
     lib.ilqrb_rollout.argtypes = [H, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p]
     lib.ilqrb_kinematics.argtypes = [H, C.c_int, C.c_int, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p]
+    lib.ilqrb_kinematics_static.argtypes = lib.ilqrb_kinematics.argtypes
     lib.ilqrb_set_profiling.argtypes = [H, C.c_int]
     lib.ilqrb_get_profile.argtypes = [H, C.POINTER(Profile)]
     lib.ilqrb_reset_profile.argtypes = [H]

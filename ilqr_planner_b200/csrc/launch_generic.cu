@@ -205,4 +205,60 @@ int launch_kinematics(ilqrb_handle h, int robot, int nq, const double* q, const 
     return 0;
 }
 
+
+// ---- kinematics hook without any allocation -------------------------------------------------------------------------
+// ilqrb_kinematics stages its inputs and outputs in a cudaMalloc'ed buffer per call.  Callers that cannot allocate (code under
+// CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) get the same kernel with its staging area in a
+// file-scope device array: every GPU that loads the library holds these ILQRB_KIN_STATIC_MAX_NQ * 69 doubles (2.26 MB) until
+// exit.  The array is shared by all handles and calls of the process on that device and keeps the last call's contents: the
+// velocity slots are cleared when dq is NULL, everything else is overwritten before it is read; two calls that overlap on the
+// GPU (different streams or handles, no synchronisation between them) race on it.
+static __device__ __align__(256) double g_kin_scratch[(size_t)ILQRB_KIN_STATIC_MAX_NQ * (2 * RDOF + 3 + 4 + 6 * RDOF + 3 + 3)];
+
+namespace {
+// In host code `g_kin_scratch` is a host-side stand-in, not a device address: the address a kernel may be given comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+int kin_scratch_ptr(int device, double** out) {
+    static double* ptr[MAX_DEVICES];
+    static std::atomic<bool> have[MAX_DEVICES];
+    if (device < 0 || device >= MAX_DEVICES) return fail(ILQRB_EINVAL, "device index beyond the per-device table");
+    if (!have[device].load(std::memory_order_acquire)) {
+        double* p = nullptr;
+        CU(cudaGetSymbolAddress((void**)&p, g_kin_scratch));
+        ptr[device] = p;
+        have[device].store(true, std::memory_order_release);
+    }
+    *out = ptr[device];
+    return 0;
+}
+}  // namespace
+
 }  // namespace ilqrb
+
+extern "C" int ilqrb_kinematics_static(ilqrb_handle h, int robot, int nq, const double* q, const double* dq, double* x, double* quat, double* J, double* dx, double* w) {
+    using namespace ilqrb;
+    if (!h) return fail(ILQRB_EINVAL, "null handle");
+    if (robot < 0 || robot >= h->hp.n_robots) return fail(ILQRB_EINVAL, "robot out of range");
+    if (nq < 1 || !q) return fail(ILQRB_EINVAL, "no configurations");
+    if (nq > ILQRB_KIN_STATIC_MAX_NQ)
+        return fail(ILQRB_EINVAL, "ilqrb_kinematics_static: nq = " + std::to_string(nq) + " exceeds the static scratch area (ILQRB_KIN_STATIC_MAX_NQ = " +
+                                      std::to_string(ILQRB_KIN_STATIC_MAX_NQ) + " configurations); split the call or use ilqrb_kinematics");
+    CU(cudaSetDevice(h->device));
+    double* buf = nullptr;
+    int rc = kin_scratch_ptr(h->device, &buf);
+    if (rc) return rc;
+    const int dof = h->hp.robots[robot].dof;
+    const size_t in = (size_t)nq * dof;
+    double *dq_d = buf + in, *ox = buf + 2 * in, *oq = ox + (size_t)nq * 3, *oJ = oq + (size_t)nq * 4, *odx = oJ + (size_t)nq * 6 * dof, *ow = odx + (size_t)nq * 3;
+    CU(cudaMemcpyAsync(buf, q, in * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    if (dq) CU(cudaMemcpyAsync(dq_d, dq, in * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    else CU(cudaMemsetAsync(dq_d, 0, in * sizeof(double), h->stream));  // the array keeps the last call's contents
+    if ((rc = launch_kinematics(h, robot, nq, buf, dq_d, ox, oq, oJ, odx, ow))) return rc;
+    if (x) CU(cudaMemcpyAsync(x, ox, (size_t)nq * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (quat) CU(cudaMemcpyAsync(quat, oq, (size_t)nq * 4 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (J) CU(cudaMemcpyAsync(J, oJ, (size_t)nq * 6 * dof * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (dx) CU(cudaMemcpyAsync(dx, odx, (size_t)nq * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (w) CU(cudaMemcpyAsync(w, ow, (size_t)nq * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}

@@ -229,6 +229,16 @@ int ilqrb_kinematics(ilqrb_handle h, int robot, int nq, const double* q, const d
                      double* x, double* quat, double* J, double* dx, double* w);
 
 
+/* The same as ilqrb_kinematics, but allocating nothing: the device staging area for q, dq and the five outputs is a
+ * file-scope static array inside the library instead of a cudaMalloc per call.  No counterpart in the reference; added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Limit: nq <= ILQRB_KIN_STATIC_MAX_NQ configurations per call (larger nq -> ILQRB_EINVAL with a
+ * message); every GPU that loads the library holds the 2.26 MB array until exit.  All calls and handles on one device share the
+ * array, which keeps the last call's contents: calls that overlap on the GPU race; serialise them.                          */
+#define ILQRB_KIN_STATIC_MAX_NQ 4096
+int ilqrb_kinematics_static(ilqrb_handle h, int robot, int nq, const double* q, const double* dq,
+                            double* x, double* quat, double* J, double* dx, double* w);
+
 /* ---- host-side builders (run once per robot / solver; no GPU work) -------------------------- */
 /* URDF -> chain descriptor.  Replaces tup::TinyURDFParser (TinyURDFParser.cpp:35-160) + the chain part of the
  * sim::KDLRobot constructor (KDLRobot.cpp:17-70), including the trailing "robot_custom_tip" segment built from
