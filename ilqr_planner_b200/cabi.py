@@ -17,7 +17,7 @@ N_ALPHA = 11
 MAX_SEGMENTS = 24
 KIN_STATIC_MAX_NQ = 4096
 ST_NAN_COST, ST_QUU_NOT_SPD, ST_EARLY_STOP = 1, 2, 4
-PROF_SLOTS = 12
+PROF_SLOTS = 13
 
 c_double_p = C.POINTER(C.c_double)
 c_int32_p = C.POINTER(C.c_int32)

@@ -524,8 +524,11 @@ __host__ __device__ inline int fwd_n1_smem_doubles(int H, int ns, int S) {
 
 // forward pass: line search over all candidates, accept, derivatives of the accepted trajectory.  One warp per block.
 // returns true when the early-stop rule fired for this problem
-template <int NT, int DOF>
-__device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work& W, int b, int lane, double* smem, int it, int nb_iter, int line_search, int early_stop) {
+// SPLIT: phase A has run in its own kernel (k_fwd_rollout_n1, fused1_fwd.cuh) and left du, dx at the keypoint steps and the limit
+// flag in global memory; this body then does phases B-F only, with `smem` = [32][6] Jacobian columns + [NCAND][S] costs.
+template <int NT, int DOF, bool SPLIT = false>
+__device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work& W, int b, int lane, double* smem, int it, int nb_iter, int line_search, int early_stop,
+                                                double* s_cc_split = nullptr) {
     constexpr int NX = 8 * NT;
     constexpr unsigned FULL = 0xffffffffu;
     constexpr int PF = (NT == 1) ? 4 : 3;  // register ring of gain fragments, in steps (L2 prefetch runs further ahead)
@@ -533,10 +536,10 @@ __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work&
     const int n = DOF > 0 ? DOF : P.n, m = n, dof = n, H = P.H, S = P.n_kp_steps;
     const int ns = (n + 1) & ~1, ms = ns;
     const double dt = P.dt;
-    double* sDU = smem;                   // [H-1][ms]  alpha = 1 control deviation
-    double* sDXk = sDU + (H - 1) * ms;    // [S][ns]    alpha = 1 state deviation at the keypoint steps
-    double* s_cc = sDXk + S * ns;         // [NCAND][S]
-    double* s_J = sDU;                    // [32][6]    phase F only, when sDU is dead
+    double* sDU = SPLIT ? W.DU + (size_t)b * (H - 1) * ms : smem;        // [H-1][ms]  alpha = 1 control deviation
+    double* sDXk = SPLIT ? W.DXk + (size_t)b * S * ns : sDU + (H - 1) * ms;  // [S][ns]    alpha = 1 state deviation at the keypoint steps
+    double* s_cc = SPLIT ? (s_cc_split ? s_cc_split : smem + 32 * 6) : sDXk + S * ns;  // [NCAND][S]
+    double* s_J = SPLIT ? smem : sDU;                                      // [32][6]    phase F only (not SPLIT: when sDU is dead)
     double* Xb = W.X + (size_t)b * H * ns;
     double* Ub = W.U + (size_t)b * (H - 1) * ms;
     const double* Kb = W.K + (size_t)b * (H - 1) * m * ns;
@@ -568,7 +571,8 @@ __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work&
     //      columns equal), so every lane of row group g ends up with du_g.  Along the way: is any joint limit violated
     //      at either end of the candidate segment [x, x + dx]?  (if not, no candidate pays a limit penalty)
     bool viol = (l1 >= 0);  // several limit-carrying sub-systems: always take the exact path below
-    if (l0 >= 0) {          // the initial state is common to all candidates but still pays its penalty
+    if constexpr (SPLIT) viol = viol || (W.viol[b] != 0);
+    if (!SPLIT && l0 >= 0) {  // the initial state is common to all candidates but still pays its penalty
 #pragma unroll
         for (int rt = 0; rt < NT; rt++) {
             const int i = 8 * rt + g;
@@ -576,7 +580,7 @@ __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work&
             viol = viol || (x00 > lmx[rt]) || (x00 < lmn[rt]);
         }
     }
-    {
+    if constexpr (!SPLIT) {
         // L2 prefetch stream, PFD steps ahead of the register ring: lanes 0-3 cover the 4 cache lines a gain matrix can
         // straddle, lane 4 the feed-forward row, lane 5 the control row (phases C, E), lane 6 the state row
         constexpr int PFD = 24;
@@ -741,11 +745,18 @@ __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work&
             lean_task_eval(P, tk, [&](int j) { return xk[off + j] + alpha * dxk[off + j]; }, -1, fx, Jc);
             double cst = lean_task_cost(P, tk, b, kp, fx, res);
             if (k < H - 1) {
-                double uRu = 0.0;
-                for (int j = 0; j < m; j++) {
-                    const double uj = Ub[(size_t)k * ms + j] + alpha * sDU[k * ms + j];
-                    uRu += (uj * tk.r_diag[j]) * uj;
+                double uRu = 0.0, uo[NX], ud[NX];  // compile-time bounds: the loads of a row are in flight together
+#pragma unroll
+                for (int j = 0; j < NX; j++) {
+                    uo[j] = j < m ? Ub[(size_t)k * ms + j] : 0.0;
+                    ud[j] = j < m ? sDU[k * ms + j] : 0.0;
                 }
+#pragma unroll
+                for (int j = 0; j < NX; j++)
+                    if (j < m) {
+                        const double uj = uo[j] + alpha * ud[j];
+                        uRu += (uj * tk.r_diag[j]) * uj;
+                    }
                 cst += uRu;
             }
             cost += cst;
@@ -774,13 +785,16 @@ __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work&
         double xq = P.q0[(size_t)b * dof + lane];
         const double hdt2 = __dmul_rn(dt, dt) / 2;
         for (int k0 = 0; k0 < H - 1; k0 += 8) {
-            double uu[8];
+            double uu[8], dd[8];  // both operand streams loaded ahead of the serial chain (SPLIT: the deviation lives in global memory)
 #pragma unroll
-            for (int j = 0; j < 8; j++) uu[j] = (k0 + j < H - 1) ? Ub[(size_t)(k0 + j) * ms + lane] : 0.0;
+            for (int j = 0; j < 8; j++) {
+                uu[j] = (k0 + j < H - 1) ? Ub[(size_t)(k0 + j) * ms + lane] : 0.0;
+                dd[j] = (k0 + j < H - 1) ? sDU[(k0 + j) * ms + lane] : 0.0;
+            }
 #pragma unroll
             for (int j = 0; j < 8; j++)
                 if (k0 + j < H - 1) {
-                    const double un = uu[j] + alpha * sDU[(k0 + j) * ms + lane];
+                    const double un = uu[j] + alpha * dd[j];
                     Ub[(size_t)(k0 + j) * ms + lane] = un;
                     xq = __dadd_rn(xq, __dadd_rn(__dmul_rn(dt, un), __dmul_rn(hdt2, 0.0)));
                     Xb[(size_t)(k0 + j + 1) * ns + lane] = xq;

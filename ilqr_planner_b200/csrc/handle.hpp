@@ -28,7 +28,7 @@ int fail(int code, const std::string& msg);  // sets the thread-local message of
         if (e_ != cudaSuccess) return ::ilqrb::fail(ILQRB_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
-enum ProfSlot { PS_ROLLOUT_INIT = 0, PS_KP_DERIVS, PS_BACKWARD, PS_LINESEARCH, PS_ACCEPT, PS_FINAL, PS_BATCH_FP, PS_BATCH_ASM, PS_BATCH_SYRK, PS_BATCH_CHOL, PS_BATCH_LS, PS_MISC };
+enum ProfSlot { PS_ROLLOUT_INIT = 0, PS_KP_DERIVS, PS_BACKWARD, PS_LINESEARCH, PS_ACCEPT, PS_FINAL, PS_BATCH_FP, PS_BATCH_ASM, PS_BATCH_SYRK, PS_BATCH_CHOL, PS_BATCH_LS, PS_MISC, PS_FWD_ROLLOUT };
 
 constexpr int MAX_DEVICES = 64;
 

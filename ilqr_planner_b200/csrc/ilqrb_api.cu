@@ -18,7 +18,8 @@ using namespace ilqrb;
 namespace {
 thread_local std::string g_err;
 const char* kProfNames[ILQRB_PROF_SLOTS] = {"rollout_init", "kp_derivs",  "riccati_backward", "linesearch_rollout", "accept",     "final_fx",
-                                            "batch_fp",     "batch_assemble", "batch_syrk",    "batch_cholesky",     "batch_linesearch", "misc"};
+                                            "batch_fp",     "batch_assemble", "batch_syrk",    "batch_cholesky",     "batch_linesearch", "misc",
+                                            "deviation_rollout"};
 }  // namespace
 
 namespace ilqrb {
@@ -495,7 +496,8 @@ int ilqrb_create(const ilqrb_problem_desc* d, int device, ilqrb_handle* out) {
         (rc = h->alloc(&W.d, B * (H - 1) * W.ms)) || (rc = h->alloc(&W.Uc, B * (H - 1) * NCAND * W.ms)) || (rc = h->alloc(&W.cost_c, B * NCAND)) ||
         (rc = h->alloc(&W.dun_c, B * NCAND)) || (rc = h->alloc(&W.cost0, B)) || (rc = h->alloc(&W.LX, B * S * n)) || (rc = h->alloc(&W.LXX, B * S * n * n)) ||
         (rc = h->alloc(&W.alpha_last, B)) || (rc = h->alloc(&W.done, B)) || (rc = h->alloc(&W.iters, B)) || (rc = h->alloc(&W.status, B)) ||
-        (rc = h->alloc(&h->d_fX, B * H * dm.nt))) {
+        (rc = h->alloc(&h->d_fX, B * H * dm.nt)) || (rc = h->alloc(&W.DU, n == m ? B * (H - 1) * W.ms : 1)) || (rc = h->alloc(&W.DXk, n == m ? B * S * W.ns : 1)) ||
+        (rc = h->alloc(&W.viol, B))) {
         ilqrb_destroy(h);
         return rc;
     }

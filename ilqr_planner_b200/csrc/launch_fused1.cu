@@ -1,7 +1,7 @@
 // launch_fused1.cu — launchers of the single-integrator fast path (fused1.cuh): k_backward_n1 / k_backward_n1_blocks / k_forward_n1.
 #include <cstdlib>
 
-#include "fused1.cuh"
+#include "fused1_fwd.cuh"
 #include "handle.hpp"
 
 namespace ilqrb {
@@ -105,6 +105,40 @@ int launch_forward_n1_t(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it,
     return 0;
 }
 
+// two-kernel forward pass (fused1_fwd.cuh)
+template <int NT, int DOF, int RING, int SPS, int WARPS, int MINB>
+int launch_fwd_rollout_t(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
+    const size_t smem = fwd_ring_smem_bytes<RING, SPS>(h->hp.m, h->W.ns, WARPS);
+    auto kern = k_fwd_rollout_n1<NT, DOF, RING, SPS, WARPS, MINB>;
+    static DynSmem attr;
+    int rc = attr.ensure(kern, smem, h->device);
+    if (rc) return rc;
+    kern<<<(nB + WARPS - 1) / WARPS, 32 * WARPS, smem, st>>>(h->dp, h->W, b0, nB);
+    return 0;
+}
+template <int NT, int DOF, int MINB>
+int launch_fwd_select_t(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop) {
+    const size_t smem = (size_t)fwd_select_smem_doubles(h->hp.n_kp_steps) * sizeof(double);
+    k_fwd_select_n1<NT, DOF, MINB><<<nB, 32, smem, st>>>(h->dp, h->W, b0, it, nb_iter, line_search, early_stop);
+    return 0;
+}
+template <int NT, int DOF, int RING, int SPS, int WARPS, int MINB>
+int launch_forward_ring_t(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop) {
+    const size_t smem = (size_t)WARPS * fwd_fused_warp_bytes<RING, SPS>(h->hp.m, h->W.ns, h->hp.n_kp_steps);
+    auto kern = k_forward_ring_n1<NT, DOF, RING, SPS, WARPS, MINB>;
+    static DynSmem attr;
+    int rc = attr.ensure(kern, smem, h->device);
+    if (rc) return rc;
+    kern<<<(nB + WARPS - 1) / WARPS, 32 * WARPS, smem, st>>>(h->dp, h->W, b0, nB, it, nb_iter, line_search, early_stop);
+    return 0;
+}
+// A/B switches: ILQRB_FWD_V1 = the single-kernel forward pass of round 1 (gains through a register ring), ILQRB_FWD_SPLIT = the
+// bulk-copy rollout and phases B-F as two launches; default = both in one kernel (k_forward_ring_n1)
+int fwd_mode() {
+    static const int mode = getenv("ILQRB_FWD_V1") ? 1 : (getenv("ILQRB_FWD_SPLIT") ? 2 : 0);
+    return mode;
+}
+
 }  // namespace
 
 int launch_backward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
@@ -128,6 +162,42 @@ int launch_backward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
 int launch_forward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop) {
     const int n = h->hp.n;
     int rc;
+    if (fwd_mode() == 0) {
+        h->begin(PS_LINESEARCH);
+        // (RING, SPS, WARPS per block, blocks per SM) measured on B200 at C2 (tools/sweep_fwd.sh, profiles/r2_sweep_forward.txt), us per
+        // launch of 4096 problems: (2,4,1,28) 121 | (3,4,1,28) 127 | (2,6,1,28) 127 | (2,6,4,7) 138 | (3,4,4,7) 144 | round-1 kernel 133 |
+        // rollout and phases B-F as two launches 55 + 96
+        static const int variant = getenv("ILQRB_FWD_VARIANT") ? atoi(getenv("ILQRB_FWD_VARIANT")) : 0;
+        if (n == 7 && variant == 1) rc = launch_forward_ring_t<1, 7, 3, 4, 4, 7>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+        else if (n == 7 && variant == 2) rc = launch_forward_ring_t<1, 7, 3, 4, 1, 28>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+        else if (n == 7) rc = launch_forward_ring_t<1, 7, 2, 4, 1, 28>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+        else if (n == 14) rc = launch_forward_ring_t<2, 14, 3, 2, 4, 3>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+        else if (n + 1 <= 8) rc = launch_forward_ring_t<1, 0, 2, 4, 1, 28>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+        else rc = launch_forward_ring_t<2, 0, 3, 2, 4, 3>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+        h->end();
+        if (rc) return rc;
+        CU(cudaGetLastError());
+        return 0;
+    }
+    if (fwd_mode() == 2) {
+        h->begin(PS_FWD_ROLLOUT);
+        if (n == 7) rc = launch_fwd_rollout_t<1, 7, 3, 4, 4, 7>(h, b0, nB, st);
+        else if (n == 14) rc = launch_fwd_rollout_t<2, 14, 3, 2, 4, 3>(h, b0, nB, st);
+        else if (n + 1 <= 8) rc = launch_fwd_rollout_t<1, 0, 3, 4, 4, 7>(h, b0, nB, st);
+        else rc = launch_fwd_rollout_t<2, 0, 3, 2, 4, 3>(h, b0, nB, st);
+        h->end();
+        if (rc) return rc;
+        CU(cudaGetLastError());
+        h->begin(PS_LINESEARCH);
+        if (n == 7) rc = launch_fwd_select_t<1, 7, 16>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+        else if (n == 14) rc = launch_fwd_select_t<2, 14, 12>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+        else if (n + 1 <= 8) rc = launch_fwd_select_t<1, 0, 16>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+        else rc = launch_fwd_select_t<2, 0, 12>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+        h->end();
+        if (rc) return rc;
+        CU(cudaGetLastError());
+        return 0;
+    }
     h->begin(PS_LINESEARCH);
     if (n == 7) rc = launch_forward_n1_t<1, 7, 28>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
     else if (n == 14) rc = launch_forward_n1_t<2, 14, 12>(h, b0, nB, st, it, nb_iter, line_search, early_stop);

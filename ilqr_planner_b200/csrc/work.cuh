@@ -26,6 +26,9 @@ struct Work {
     double* cost_hist;     // [B][nb_iter]
     double* alpha_hist;    // [B][nb_iter]
     double* alpha_last;    // [B]
+    double* DU;            // [B][H-1][ms]     alpha = 1 control deviation of the forward pass (fused1_fwd.cuh)
+    double* DXk;           // [B][S][ns]       alpha = 1 state deviation at the keypoint steps
+    int* viol;             // [B]              a joint limit is violated at an end of some candidate segment
     int* done;             // [B]
     int* iters;            // [B]
     int* status;           // [B]

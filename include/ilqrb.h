@@ -175,7 +175,7 @@ typedef struct ilqrb_result {
 } ilqrb_result;
 
 /* accumulated device time per kernel family, measured with CUDA events on the solve stream */
-#define ILQRB_PROF_SLOTS 12
+#define ILQRB_PROF_SLOTS 13
 typedef struct ilqrb_profile {
     double ms[ILQRB_PROF_SLOTS];
     int64_t launches[ILQRB_PROF_SLOTS];
