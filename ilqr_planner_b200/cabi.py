@@ -97,6 +97,8 @@ SYMBOLS = [
     "ilqrb_upload_u0", "ilqrb_run_recursive", "ilqrb_run_al", "ilqrb_run_batch", "ilqrb_download", "ilqrb_rollout",
     "ilqrb_kinematics", "ilqrb_set_profiling", "ilqrb_get_profile", "ilqrb_reset_profile", "ilqrb_launch_count",
     "ilqrb_chain_from_urdf", "ilqrb_build_psi", "ilqrb_fp64_peaks", "ilqrb_kinematics_static",
+    "ilqrb_multi_plan", "ilqrb_create_multi", "ilqrb_multi_destroy", "ilqrb_multi_count", "ilqrb_multi_slice", "ilqrb_multi_solve_recursive",
+    "ilqrb_multi_solve_al", "ilqrb_multi_solve_batch", "ilqrb_multi_upload_u0", "ilqrb_multi_run_recursive", "ilqrb_multi_synchronize", "ilqrb_multi_download",
 ]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -134,6 +136,19 @@ def load():
     lib.ilqrb_rollout.argtypes = [H, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p]
     lib.ilqrb_kinematics.argtypes = [H, C.c_int, C.c_int, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p]
     lib.ilqrb_kinematics_static.argtypes = lib.ilqrb_kinematics.argtypes
+    IP = C.POINTER(C.c_int)
+    lib.ilqrb_multi_plan.argtypes = [C.c_int, C.c_int, IP, IP]
+    lib.ilqrb_create_multi.argtypes = [C.POINTER(ProblemDesc), C.c_int, IP, C.POINTER(H)]
+    lib.ilqrb_multi_destroy.argtypes = [H]
+    lib.ilqrb_multi_count.argtypes = [H]
+    lib.ilqrb_multi_slice.argtypes = [H, C.c_int, IP, IP, IP, C.POINTER(H)]
+    lib.ilqrb_multi_solve_recursive.argtypes = [H, c_double_p, C.POINTER(SolveOpts), C.POINTER(Result)]
+    lib.ilqrb_multi_solve_al.argtypes = [H, c_double_p, C.POINTER(ALDesc), C.POINTER(SolveOpts), C.POINTER(Result)]
+    lib.ilqrb_multi_solve_batch.argtypes = [H, c_double_p, C.POINTER(BatchDesc), C.POINTER(SolveOpts), C.POINTER(Result)]
+    lib.ilqrb_multi_upload_u0.argtypes = [H, c_double_p]
+    lib.ilqrb_multi_run_recursive.argtypes = [H, C.POINTER(SolveOpts)]
+    lib.ilqrb_multi_synchronize.argtypes = [H]
+    lib.ilqrb_multi_download.argtypes = [H, C.POINTER(Result), C.c_int]
     lib.ilqrb_set_profiling.argtypes = [H, C.c_int]
     lib.ilqrb_get_profile.argtypes = [H, C.POINTER(Profile)]
     lib.ilqrb_reset_profile.argtypes = [H]

@@ -899,12 +899,12 @@ inline int batch_run(cudaStream_t st, int device, const DevProblem& P, const Dev
 
 inline int batch_download(cudaStream_t st, const DevProblem& P, BatchWork& BW, ilqrb_result* out, const Work& W, int nit, std::string& err) {
     const size_t B = P.B;
-    if (out->U) BCU(cudaMemcpyAsync(out->U, BW.u, B * BW.N * sizeof(double), cudaMemcpyDeviceToHost, st));
-    if (out->cost) BCU(cudaMemcpyAsync(out->cost, W.cost0, B * sizeof(double), cudaMemcpyDeviceToHost, st));
-    if (out->cost_hist) BCU(cudaMemcpyAsync(out->cost_hist, W.cost_hist, B * nit * sizeof(double), cudaMemcpyDeviceToHost, st));
-    if (out->alpha_hist) BCU(cudaMemcpyAsync(out->alpha_hist, W.alpha_hist, B * nit * sizeof(double), cudaMemcpyDeviceToHost, st));
-    if (out->iters) BCU(cudaMemcpyAsync(out->iters, W.iters, B * sizeof(int), cudaMemcpyDeviceToHost, st));
-    if (out->status) BCU(cudaMemcpyAsync(out->status, W.status, B * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (out->U) BCU(cudaMemcpyAsync(out->U, BW.u, B * BW.N * sizeof(double), cudaMemcpyDefault, st));
+    if (out->cost) BCU(cudaMemcpyAsync(out->cost, W.cost0, B * sizeof(double), cudaMemcpyDefault, st));
+    if (out->cost_hist) BCU(cudaMemcpyAsync(out->cost_hist, W.cost_hist, B * nit * sizeof(double), cudaMemcpyDefault, st));
+    if (out->alpha_hist) BCU(cudaMemcpyAsync(out->alpha_hist, W.alpha_hist, B * nit * sizeof(double), cudaMemcpyDefault, st));
+    if (out->iters) BCU(cudaMemcpyAsync(out->iters, W.iters, B * sizeof(int), cudaMemcpyDefault, st));
+    if (out->status) BCU(cudaMemcpyAsync(out->status, W.status, B * sizeof(int), cudaMemcpyDefault, st));
     BCU(cudaStreamSynchronize(st));
     return 0;
 }

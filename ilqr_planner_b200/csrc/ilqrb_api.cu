@@ -159,7 +159,7 @@ int download_packed(ilqrb_handle h, double* dst_host, const double* src_dev, siz
     const size_t tot = rows * w;
     k_pack<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(h->d_pack, src_dev, rows, w, stride, scale, rpp);
     CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(dst_host, h->d_pack, tot * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(dst_host, h->d_pack, tot * sizeof(double), cudaMemcpyDefault, h->stream));
     CU(cudaStreamSynchronize(h->stream));  // staging buffer is reused
     return 0;
 }
@@ -183,7 +183,7 @@ int enqueue_download_range(ilqrb_handle h, const ilqrb_result* out, int b0, int 
         double* dst = stage + (size_t)b0 * per_problem_rows * w;
         k_pack<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(dst, src + (size_t)b0 * per_problem_rows * stride, rows, w, stride, scale ? scale + b0 : nullptr, rpp);
         CU(cudaGetLastError());
-        CU(cudaMemcpyAsync(host + (size_t)b0 * per_problem_rows * w, dst, tot * sizeof(double), cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(host + (size_t)b0 * per_problem_rows * w, dst, tot * sizeof(double), cudaMemcpyDefault, st));
         return 0;
     };
     if ((rc = pack(out->X, sX, h->W.X, H, n, h->W.ns, nullptr, 1))) return rc;
@@ -194,13 +194,13 @@ int enqueue_download_range(ilqrb_handle h, const ilqrb_result* out, int b0, int 
     if (out->fX) {
         if ((rc = launch_final_fx(h, b0, nB, st))) return rc;
         const size_t off = (size_t)b0 * H * P.nt;
-        CU(cudaMemcpyAsync(out->fX + off, h->d_fX + off, (size_t)nB * H * P.nt * sizeof(double), cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(out->fX + off, h->d_fX + off, (size_t)nB * H * P.nt * sizeof(double), cudaMemcpyDefault, st));
     }
-    if (out->cost) CU(cudaMemcpyAsync(out->cost + b0, h->W.cost0 + b0, nB * sizeof(double), cudaMemcpyDeviceToHost, st));
-    if (out->cost_hist) CU(cudaMemcpyAsync(out->cost_hist + (size_t)b0 * nit, h->W.cost_hist + (size_t)b0 * nit, (size_t)nB * nit * sizeof(double), cudaMemcpyDeviceToHost, st));
-    if (out->alpha_hist) CU(cudaMemcpyAsync(out->alpha_hist + (size_t)b0 * nit, h->W.alpha_hist + (size_t)b0 * nit, (size_t)nB * nit * sizeof(double), cudaMemcpyDeviceToHost, st));
-    if (out->iters) CU(cudaMemcpyAsync(out->iters + b0, h->W.iters + b0, nB * sizeof(int), cudaMemcpyDeviceToHost, st));
-    if (out->status) CU(cudaMemcpyAsync(out->status + b0, h->W.status + b0, nB * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (out->cost) CU(cudaMemcpyAsync(out->cost + b0, h->W.cost0 + b0, nB * sizeof(double), cudaMemcpyDefault, st));
+    if (out->cost_hist) CU(cudaMemcpyAsync(out->cost_hist + (size_t)b0 * nit, h->W.cost_hist + (size_t)b0 * nit, (size_t)nB * nit * sizeof(double), cudaMemcpyDefault, st));
+    if (out->alpha_hist) CU(cudaMemcpyAsync(out->alpha_hist + (size_t)b0 * nit, h->W.alpha_hist + (size_t)b0 * nit, (size_t)nB * nit * sizeof(double), cudaMemcpyDefault, st));
+    if (out->iters) CU(cudaMemcpyAsync(out->iters + b0, h->W.iters + b0, nB * sizeof(int), cudaMemcpyDefault, st));
+    if (out->status) CU(cudaMemcpyAsync(out->status + b0, h->W.status + b0, nB * sizeof(int), cudaMemcpyDefault, st));
     return 0;
 }
 
@@ -602,7 +602,7 @@ int ilqrb_download(ilqrb_handle h, ilqrb_result* out) {
     if (h->last_solver == 3) return batch_download_h(h, out, nit);
     // every output has its own slice of the staging buffer: all packs and copies are queued, one synchronisation at the end
     if ((rc = enqueue_download_range(h, out, 0, (int)B, nit, h->stream, h->last_solver == 1))) return rc;
-    if (out->lambda && h->last_solver == 2) CU(cudaMemcpyAsync(out->lambda, h->W.lam, B * (H - 1) * h->W.nc * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (out->lambda && h->last_solver == 2) CU(cudaMemcpyAsync(out->lambda, h->W.lam, B * (H - 1) * h->W.nc * sizeof(double), cudaMemcpyDefault, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     (void)n;
     (void)m;
@@ -669,15 +669,15 @@ int ilqrb_rollout(ilqrb_handle h, const double* U, double* X, double* fX, double
     if ((rc = download_packed(h, X, h->W.X, B * H, P.n, h->W.ns, nullptr, 1))) return rc;
     if (fX) {
         if ((rc = launch_final_fx(h, 0, (int)B, h->stream))) return rc;
-        CU(cudaMemcpyAsync(fX, h->d_fX, B * H * P.nt * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaMemcpyAsync(fX, h->d_fX, B * H * P.nt * sizeof(double), cudaMemcpyDefault, h->stream));
     }
     if (J) {
         const size_t el = B * H * P.r * P.n;
         if ((rc = ensure_pack(h, el))) return rc;
         if ((rc = launch_rollout_jac(h, h->d_pack))) return rc;
-        CU(cudaMemcpyAsync(J, h->d_pack, el * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaMemcpyAsync(J, h->d_pack, el * sizeof(double), cudaMemcpyDefault, h->stream));
     }
-    if (cost) CU(cudaMemcpyAsync(cost, h->W.cost0, B * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (cost) CU(cudaMemcpyAsync(cost, h->W.cost0, B * sizeof(double), cudaMemcpyDefault, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     return 0;
 }

@@ -184,3 +184,88 @@ def fp64_peaks(device=0):
     a, b = C.c_double(0), C.c_double(0)
     cabi.check(lib.ilqrb_fp64_peaks(int(device), C.cast(C.byref(a), cabi.c_double_p), C.cast(C.byref(b), cabi.c_double_p)))
     return a.value, b.value
+
+
+def multi_plan(batch, n_slices):
+    """contiguous slices of `batch` problems over n_slices devices (ilqrb_multi_plan; no GPU work)"""
+    lib = cabi.load()
+    lo, hi = (C.c_int * n_slices)(), (C.c_int * n_slices)()
+    cabi.check(lib.ilqrb_multi_plan(int(batch), int(n_slices), lo, hi))
+    return list(zip(lo[:], hi[:]))
+
+
+class MultiHandle:
+    """one batch sharded over several GPUs of one box (ilqrb_create_multi): same solve calls as Handle, whole-batch buffers"""
+
+    def __init__(self, pb: ProblemBatch, devices):
+        self.pb = pb
+        self.lib = cabi.load()
+        self.desc = pb.to_desc()
+        self.h = C.c_void_p()
+        devs = (C.c_int * len(devices))(*[int(d) for d in devices])
+        cabi.check(self.lib.ilqrb_create_multi(C.byref(self.desc), len(devices), devs, C.byref(self.h)))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.ilqrb_multi_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    _u = Handle._u
+
+    def slices(self):
+        out = []
+        for i in range(self.lib.ilqrb_multi_count(self.h)):
+            d, lo, hi = C.c_int(), C.c_int(), C.c_int()
+            cabi.check(self.lib.ilqrb_multi_slice(self.h, i, C.byref(d), C.byref(lo), C.byref(hi), None))
+            out.append((d.value, lo.value, hi.value))
+        return out
+
+    def solve_recursive(self, U0, nb_iter, line_search=True, early_stop=False, out=None):
+        out = out or ResultBuffers(self.pb, nb_iter, "recursive")
+        U0 = self._u(U0)
+        o = opts(nb_iter, line_search, early_stop)
+        cabi.check(self.lib.ilqrb_multi_solve_recursive(self.h, cabi.dptr(U0), C.byref(o), C.byref(out.res)))
+        return out
+
+    def solve_al(self, U0, A, b, lambda0, nb_iter, lag_update_step, penalty, scaling_factor, line_search=True, early_stop=False, out=None):
+        al = make_al_desc(A, b, lambda0, lag_update_step, penalty, scaling_factor)
+        out = out or ResultBuffers(self.pb, nb_iter, "al", nc=al.nc)
+        U0 = self._u(U0)
+        o = opts(nb_iter, line_search, early_stop)
+        cabi.check(self.lib.ilqrb_multi_solve_al(self.h, cabi.dptr(U0), C.byref(al), C.byref(o), C.byref(out.res)))
+        return out
+
+    def solve_batch(self, u0, nb_iter, early_stop=False, Q=None, psi=None, out=None):
+        bd = make_batch_desc(Q, psi)
+        out = out or ResultBuffers(self.pb, nb_iter, "batch")
+        u0 = self._u(u0)
+        o = opts(nb_iter, True, early_stop)
+        cabi.check(self.lib.ilqrb_multi_solve_batch(self.h, cabi.dptr(u0), C.byref(bd), C.byref(o), C.byref(out.res)))
+        return out
+
+    def upload_u0(self, U0):
+        self._u0_keep = self._u(U0)
+        cabi.check(self.lib.ilqrb_multi_upload_u0(self.h, cabi.dptr(self._u0_keep)))
+
+    def run_recursive(self, nb_iter, line_search=True, early_stop=False):
+        o = opts(nb_iter, line_search, early_stop)
+        cabi.check(self.lib.ilqrb_multi_run_recursive(self.h, C.byref(o)))
+
+    def synchronize(self):
+        cabi.check(self.lib.ilqrb_multi_synchronize(self.h))
+
+    def download(self, out, nb_iter):
+        cabi.check(self.lib.ilqrb_multi_download(self.h, C.byref(out.res), int(nb_iter)))
+        return out

@@ -191,7 +191,7 @@ int ilqrb_get_dims(const ilqrb_problem_desc* desc, ilqrb_dims* out);
 
 /* Copies the descriptor to device `device`.  Replaces the construction of
  * KDLRobot/System objects (KDLRobot.cpp:17-70, System.cpp:18-86) for a batch.            */
-int ilqrb_create(const ilqrb_problem_desc* desc, int device, ilqrb_handle* out);
+int ilqrb_create(const ilqrb_problem_desc* desc, int device, ilqrb_handle* out); /* several devices: ilqrb_create_multi */
 int ilqrb_destroy(ilqrb_handle h);
 int ilqrb_set_stream(ilqrb_handle h, void* cuda_stream); /* default: a private stream */
 int ilqrb_synchronize(ilqrb_handle h);
@@ -216,7 +216,32 @@ int ilqrb_upload_u0(ilqrb_handle h, const double* U0); /* NULL = zeros */
 int ilqrb_run_recursive(ilqrb_handle h, const ilqrb_solve_opts* opts); /* async on the stream */
 int ilqrb_run_al(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solve_opts* opts);
 int ilqrb_run_batch(ilqrb_handle h, const ilqrb_batch_desc* bd, const ilqrb_solve_opts* opts);
-int ilqrb_download(ilqrb_handle h, ilqrb_result* out); /* synchronizes */
+int ilqrb_download(ilqrb_handle h, ilqrb_result* out); /* synchronizes; buffers: host, or device memory of any GPU (see below) */
+
+/* ---- one batch over several GPUs of one box ------------------------------------------------------
+ * The reference has no counterpart (single thread, one problem); SURVEY 8e: the problem batch shards contiguously over the
+ * devices, every device runs all iterations on its slice, no exchange during the solve, one final gather.  A multi handle
+ * owns one ilqrb_handle per device (devices may repeat: two slices on one GPU); the blocking calls drive the devices from one
+ * host thread each and every device writes its slice of the caller's whole-batch buffers itself.  Result buffers of
+ * ilqrb_download / ilqrb_multi_download may be host memory or device memory of any GPU of the process (unified addressing;
+ * between the devices of a set peer access is enabled, so a device-resident gather travels over NVLink).                      */
+typedef struct ilqrb_multi_s* ilqrb_multi;
+/* contiguous slices [lo[i], hi[i]) of `batch` problems over n_slices devices, sizes differing by at most one (no GPU work) */
+int ilqrb_multi_plan(int batch, int n_slices, int* lo, int* hi);
+/* devices: [n_devices] CUDA device indices, NULL = 0 .. n_devices-1.  desc describes the WHOLE batch (host pointers). */
+int ilqrb_create_multi(const ilqrb_problem_desc* desc, int n_devices, const int* devices, ilqrb_multi* out);
+int ilqrb_multi_destroy(ilqrb_multi m);
+int ilqrb_multi_count(ilqrb_multi m);
+int ilqrb_multi_slice(ilqrb_multi m, int i, int* device, int* lo, int* hi, ilqrb_handle* h); /* any output may be NULL */
+/* ILQRRecursive / AL_ILQR / BatchILQR(CP)::solve over the whole batch: U0 and the buffers of `out` span all B problems */
+int ilqrb_multi_solve_recursive(ilqrb_multi m, const double* U0, const ilqrb_solve_opts* opts, ilqrb_result* out);
+int ilqrb_multi_solve_al(ilqrb_multi m, const double* U0, const ilqrb_al_desc* al, const ilqrb_solve_opts* opts, ilqrb_result* out);
+int ilqrb_multi_solve_batch(ilqrb_multi m, const double* u0, const ilqrb_batch_desc* bd, const ilqrb_solve_opts* opts, ilqrb_result* out);
+/* split form: upload once, run (returns once the launches are queued on every device), synchronize, gather */
+int ilqrb_multi_upload_u0(ilqrb_multi m, const double* U0);
+int ilqrb_multi_run_recursive(ilqrb_multi m, const ilqrb_solve_opts* opts);
+int ilqrb_multi_synchronize(ilqrb_multi m);
+int ilqrb_multi_download(ilqrb_multi m, ilqrb_result* out, int nb_iter); /* nb_iter of the run (row length of the traces) */
 
 /* ---- kernel-level test hooks --------------------------------------------------------------- */
 /* System::forwardPass over the horizon for given controls (PosOrnPlannerSys.cpp:114-138 etc.):

@@ -107,3 +107,25 @@ def test_no_cpu_fallback():
         pytest.skip("a GPU is present")
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         Handle(synth.config2(batch=2))
+
+
+def test_multi_plan_slices_tile_the_batch():
+    """ilqrb_multi_plan (the slicing of ilqrb_create_multi): contiguous, complete, sizes within one of each other"""
+    from ilqr_planner_b200.solver import multi_plan
+    for B, G in ((65536, 8), (4096, 3), (7, 7), (10, 4), (1, 1), (4097, 8)):
+        sl = multi_plan(B, G)
+        assert sl[0][0] == 0 and sl[-1][1] == B and len(sl) == G
+        assert all(a[1] == b[0] for a, b in zip(sl, sl[1:]))
+        sizes = [hi - lo for lo, hi in sl]
+        assert max(sizes) - min(sizes) <= 1 and min(sizes) >= 1
+    with pytest.raises(RuntimeError, match="more slices than problems"):
+        multi_plan(3, 4)
+
+
+def test_create_multi_refuses_without_a_gpu_or_with_bad_devices():
+    import torch
+    from ilqr_planner_b200.solver import MultiHandle
+    pb = synth.config2(batch=8)
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError, match="no CUDA device"):
+            MultiHandle(pb, [0, 1])
