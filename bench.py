@@ -267,6 +267,47 @@ def other_configs(torch, device, fp64_peak, hbm_peak):
     return res
 
 
+def stream_e2e(torch, hs, outs, u0s, steps, nb_iter, streams, barrier):
+    """the streaming host-buffer form: batches alternate between two handles, batch i's D2H overlapping batch i+1's solve -> ms"""
+    for i in range(4):
+        hs[i % 2].synchronize()
+        hs[i % 2].solve_recursive_async(u0s[i % 2], nb_iter, True, False, out=outs[i % 2])
+    hs[0].synchronize()
+    hs[1].synchronize()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(streams[0])
+    streams[1].wait_event(e0)
+    for i in range(steps):
+        k = i % 2
+        hs[k].synchronize()
+        hs[k].solve_recursive_async(u0s[k], nb_iter, True, False, out=outs[k])
+    streams[0].wait_stream(streams[1])
+    e1.record(streams[0])
+    barrier()
+    return e0.elapsed_time(e1)
+
+
+def d2h_ceiling_gbs(torch, dist, world, barrier, mbytes=256, reps=4):
+    """aggregate device-to-host bandwidth of this box with all `world` GPUs copying into pinned host memory at the same time
+    (plain cudaMemcpyAsync, one copy per call): the ceiling of every host-buffer e2e number at this N"""
+    n = mbytes * (1 << 20) // 8
+    src = torch.zeros(n, dtype=torch.float64, device="cuda")
+    dst = torch.empty(n, dtype=torch.float64).pin_memory()
+    dst.copy_(src, non_blocking=True)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        dst.copy_(src, non_blocking=True)
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return world * reps * n * 8 / (float(t.item()) * 1e-3) / 1e9
+
+
 def dfma_peak_tflops(torch):
     """FP64 peak proxy measured here: torch fp64 matmul 4096^3 (cuBLAS DGEMM), best of 5 — MEASURED_PEAKS.json has no FP64 entry"""
     try:
@@ -419,7 +460,50 @@ def main():
     e2e_sync_value = world * B * args.steps / (ms_sync * 1e-3)
     h2d = u0.nbytes
     d2h = sum(a.nbytes for a in (out.X, out.fX, out.U, out.K, out.d, out.cost, out.cost_hist, out.alpha_hist, out.iters, out.status))
+    # the same streaming form for a caller that does not take the gains back (out->K = out->d = NULL: 4x fewer bytes), and the
+    # box's aggregate D2H ceiling with all ranks copying at once: the host-buffer numbers at N >= 4 are bounded by it
+    outs_ng = (ResultBuffers(pb, NB_ITER, "recursive", pinned=True, gains=False), ResultBuffers(pb, NB_ITER, "recursive", pinned=True, gains=False))
+    ms_ng = stream_e2e(torch, hs, outs_ng, u0s, args.steps, NB_ITER, (stream, stream2), barrier)
+    t = torch.tensor([ms_ng], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ng_value = world * B * args.steps / (float(t.item()) * 1e-3)
+    d2h_ng = sum(a.nbytes for a in (outs_ng[0].X, outs_ng[0].fX, outs_ng[0].U, outs_ng[0].cost, outs_ng[0].cost_hist, outs_ng[0].alpha_hist, outs_ng[0].iters, outs_ng[0].status))
+    d2h_ceiling = d2h_ceiling_gbs(torch, dist, world, barrier)
     h2.close()
+    del outs_ng
+
+    # ---- north_star target workloads (device-resident, max over ranks): 8192 problems of C2 per GPU (65,536 on 8 GPUs) and the
+    # 65,536-problem dual-arm batch of configs[4] split evenly over the ranks
+    def target_run(pbt, reps=2):
+        st = torch.cuda.Stream()
+        with Handle(pbt, device=local_rank, stream=st.cuda_stream) as ht:
+            ht.upload_u0(None)
+            ht.run_recursive(NB_ITER, True, False)
+            ht.synchronize()
+            barrier()
+            a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(st)
+            for _ in range(reps):
+                ht.upload_u0(None)
+                ht.run_recursive(NB_ITER, True, False)
+            b_.record(st)
+            ht.synchronize()
+            barrier()
+            tt = torch.tensor([a.elapsed_time(b_) / reps], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt.item())
+    north_star = None
+    if not args.no_configs and B == BATCH_PER_GPU:
+        ms_c2 = target_run(synth.config2(batch=8192, horizon=HORIZON, offset=rank * 8192))
+        per = 65536 // world
+        ms_c5 = target_run(synth.config5(batch=per, horizon=HORIZON, offset=rank * per))
+        north_star = {"c2_8192_per_gpu": {"global_batch": 8192 * world, "solves_per_s": 8192 * world / (ms_c2 * 1e-3), "ms_per_solve_batch": ms_c2},
+                      "configs4_dual_arm_65536_total": {"global_batch": per * world, "batch_per_gpu": per, "solves_per_s": per * world / (ms_c5 * 1e-3), "ms_per_solve_batch": ms_c5,
+                                                         "scaling": "strong (65,536 problems split over the ranks)"},
+                      "note": "device-resident, CUDA events on the solve stream, U0 reset inside the timed region, max over ranks; the north_star batch "
+                              "(65,536 C2 problems on 8 GPUs) is the c2 entry at n_gpus = 8"}
 
     # ---- final gather of the per-problem costs (the only collective; outside the data path) -----------------------
     cost_t = torch.from_numpy(out.cost.copy()).cuda()
@@ -462,7 +546,13 @@ def main():
                         "mode": "ilqrb_solve_recursive_async on two handles used alternately: batch i's D2H overlaps batch i+1's solve; every batch's "
                                 "U0 H2D and full result D2H (pinned host memory) inside the timed region, which ends with the last batch on the host",
                         "sync_call": {"value": e2e_sync_value, "unit": UNIT, "ms_per_step": ms_sync / args.steps,
-                                      "mode": "one blocking ilqrb_solve_recursive per batch (H2D -> solve -> D2H, no overlap across batches)"}},
+                                      "mode": "one blocking ilqrb_solve_recursive per batch (H2D -> solve -> D2H, no overlap across batches)"},
+                        "no_gains": {"value": e2e_ng_value, "unit": UNIT, "d2h_bytes_per_step": int(d2h_ng),
+                                     "mode": "the streaming form with out->K = out->d = NULL (the caller keeps X, f(X), U, cost and the traces only)"},
+                        # what bounds the host-buffer numbers: all ranks' result copies converge on one host
+                        "d2h_ceiling_gbs": d2h_ceiling, "d2h_gbs": e2e_value * d2h / B / 1e9, "frac_of_d2h_ceiling": e2e_value * d2h / B / 1e9 / d2h_ceiling,
+                        "d2h_ceiling_note": "aggregate D2H rate of this box with all %d GPUs copying 256 MB blocks into pinned host memory at once" % world},
+                "north_star_target": north_star,
                 "gpu_launches": int(launches),
                 # dominant kernel = the backward Riccati pass; SURVEY 8d: it is bound by the FP64 (tensor/DMMA + DFMA) pipe
                 "roofline": {"kernel": "riccati_backward (k_backward_n1: DMMA m8n8k4.f64 + DFMA)", "bound": "tensor",

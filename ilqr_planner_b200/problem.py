@@ -201,7 +201,7 @@ def limit_weights(nb_deriv, dof, time, dq_max=None, dq_min=None):
 class ResultBuffers:
     """numpy outputs + the ctypes ilqrb_result pointing at them"""
 
-    def __init__(self, pb: ProblemBatch, nb_iter, solver="recursive", nc=0, pinned=False):
+    def __init__(self, pb: ProblemBatch, nb_iter, solver="recursive", nc=0, pinned=False, gains=True):
         B, H, n, m, nt = pb.batch, pb.horizon, pb.n, pb.m, pb.nt
         self.res = cabi.Result()
         nan = np.nan
@@ -232,7 +232,7 @@ class ResultBuffers:
             self.fX = alloc((B, H, nt))
             self.U = alloc((B, H - 1, m))
             self.res.X, self.res.fX, self.res.U = cabi.dptr(self.X), cabi.dptr(self.fX), cabi.dptr(self.U)
-        if solver == "recursive":
+        if solver == "recursive" and gains:  # gains=False: out->K = out->d = NULL, the caller does not want Ks / ds back
             self.K = alloc((B, H - 1, m, n))
             self.d = alloc((B, H - 1, m))
             self.res.K, self.res.d = cabi.dptr(self.K), cabi.dptr(self.d)
