@@ -8,9 +8,10 @@ import os
 
 import numpy as np
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 SYS_POS_ORN, SYS_POS_ORN_TIME, SYS_POSITION = 0, 1, 2
 ROBOT_KDL, ROBOT_2D = 0, 1
+TASK_POSE, TASK_JOINT = 0, 1
 JOINT_FIXED, JOINT_ROT, JOINT_TRANS = 0, 1, 2
 KP_STRIDE = 15
 N_ALPHA = 11
@@ -37,7 +38,8 @@ class Task(C.Structure):
     _fields_ = [("robot", C.c_int32), ("joint_offset", C.c_int32), ("has_transform", C.c_int32), ("n_keypoints", C.c_int32),
                 ("T", C.c_double * 16), ("kp_timestep", c_int32_p), ("kp_target", c_double_p), ("kp_precision", c_double_p),
                 ("precision_per_problem", C.c_int32), ("limits_set", C.c_int32), ("r_diag", c_double_p),
-                ("state_max", c_double_p), ("state_min", c_double_p), ("limit_weight", c_int32_p)]
+                ("state_max", c_double_p), ("state_min", c_double_p), ("limit_weight", c_int32_p),
+                ("task_kind", C.c_int32), ("pad_", C.c_int32), ("kp_deadzone", c_double_p)]
 
 
 class ProblemDesc(C.Structure):

@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(64) k_batch_fp(const DevProblem* __restrict__ 
                 for (int a = 0; a < tk.r_t; a++) res[a] = 0.0;
                 if (kp >= 0) {
                     const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
-                    task_residual(P, tk, fx, tg, res);
+                    task_residual(P, tk, fx, tg, res, task_deadzone(tk, kp));
                 }
                 for (int a = 0; a < tk.r_t; a++) evec[s * P.r + tk.r_off + a] = res[a];
                 if (c == 0) {

@@ -831,7 +831,7 @@ __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work&
                 lean_task_eval(P, tk, [&](int j) { return xk[off + j]; }, cj, fx, Jc);
                 if (kp >= 0) {
                     const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
-                    task_residual(P, tk, fx, tg, res);
+                    task_residual(P, tk, fx, tg, res, task_deadzone(tk, kp));
                 }
                 const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + (kp >= 0 ? kp : 0)) * r * r;
                 double gsum = 0.0;

@@ -70,7 +70,19 @@ int derive_dims(const ilqrb_problem_desc* d, ilqrb_dims* o, int* task_nt, int* t
         if (rb.dof < 1 || rb.dof > ILQRB_MAX_ROBOT_DOF) return fail(ILQRB_EUNSUPPORTED, "robot dof must be 1..7 (KDLRobot.cpp:112 limit)");
         if (tk.joint_offset < 0 || tk.joint_offset + rb.dof > d->dof) return fail(ILQRB_EINVAL, "task joint range outside the state");
         int nt, r;
-        if (d->sys_kind == ILQRB_SYS_POSITION) {
+        if (tk.task_kind != ILQRB_TASK_POSE && tk.task_kind != ILQRB_TASK_JOINT) return fail(ILQRB_EINVAL, "unknown task_kind");
+        if (tk.kp_deadzone && (tk.task_kind != ILQRB_TASK_POSE || d->sys_kind != ILQRB_SYS_POS_ORN))
+            return fail(ILQRB_EINVAL, "kp_deadzone (PosOrnKeypointDistFunct) applies to the end-effector tasks of PosOrnPlannerSys only (the reference has no time variant)");
+        if (tk.task_kind == ILQRB_TASK_JOINT) {
+            if (d->sys_kind == ILQRB_SYS_POSITION) return fail(ILQRB_EUNSUPPORTED, "joint-space tasks need a PosOrn or PosOrnTime dynamics class (sys_kind)");
+            if (d->nb_deriv != 1)
+                return fail(ILQRB_EUNSUPPORTED, "JointSpacePlannerSys with nb_deriv = 2 is not built: the reference's Jacobian Identity(2 dof, dof) "
+                                                "(JointSpacePlannerSys.cpp:79) has the wrong shape for its own cost_x (undefined behaviour there)");
+            if (tk.has_transform) return fail(ILQRB_EINVAL, "joint-space tasks do not take a transform");
+            if (tk.joint_offset != 0 || rb.dof != d->dof) return fail(ILQRB_EUNSUPPORTED, "a joint-space task must span the whole joint vector");
+            if (rb.dof > 7) return fail(ILQRB_EUNSUPPORTED, "joint-space keypoint records hold 7 joints");
+            nt = r = d->nb_deriv * rb.dof + time;
+        } else if (d->sys_kind == ILQRB_SYS_POSITION) {
             if (tk.has_transform) return fail(ILQRB_EUNSUPPORTED, "POSITION tasks do not take a transform");
             const int car = rb.kind == ILQRB_ROBOT_2D ? 2 : 3;
             nt = car * d->nb_deriv;
@@ -446,6 +458,16 @@ int ilqrb_create(const ilqrb_problem_desc* d, int device, ilqrb_handle* out) {
             if (!seen) steps.push_back(tk.kp_timestep[i]);
         }
         o.precision_per_problem = tk.precision_per_problem;
+        o.kind = tk.task_kind;
+        o.kp_deadzone = nullptr;
+        if (tk.kp_deadzone) {
+            double* ddz = nullptr;
+            if ((rc = upload(h, &ddz, tk.kp_deadzone, (size_t)tk.n_keypoints * 4))) {
+                ilqrb_destroy(h);
+                return rc;
+            }
+            o.kp_deadzone = ddz;
+        }
         o.limits_set = tk.limits_set;
         o.nt_t = task_nt[t];
         o.r_t = task_r[t];

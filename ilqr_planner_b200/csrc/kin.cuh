@@ -49,6 +49,8 @@ struct DevTask {
     double r_diag[MAXM];
     double state_max[MAXN], state_min[MAXN];
     int limit_weight[MAXN];
+    int kind, pad_;              // ILQRB_TASK_POSE / ILQRB_TASK_JOINT
+    const double* kp_deadzone;   // [Kp][4] pos_radius, orn_thresh[3] (PosOrnKeypointDistFunct) or nullptr
 };
 struct DevProblem {
     int sys_kind, nb_deriv, H, B, dof, n_robots, n_tasks, time;
@@ -445,6 +447,14 @@ HD void minus2H_times(const double* q, const double* v, double* o) {
 // EE state of task `tk` at the joint state (q, dq) of the whole system (robot view + optional transform).
 HD void task_ee(const DevProblem& P, const DevTask& tk, const double* q, const double* dq, EEState& e) {
     const DevRobot& rb = P.robots[tk.robot];
+    if (tk.kind == ILQRB_TASK_JOINT) {  // joint-space tasks observe the state itself: e carries q (Jv slots unused)
+#pragma unroll
+        for (int c = 0; c < RDOF; c++) {
+            e.Jv[c][0] = c < rb.dof ? q[tk.joint_offset + c] : 0.0;
+            e.Jv[c][1] = c < rb.dof ? dq[tk.joint_offset + c] : 0.0;
+        }
+        return;
+    }
     if (rb.kind == ILQRB_ROBOT_2D) robot2d_update_kinematics(rb.lengths, rb.dof, q + tk.joint_offset, dq + tk.joint_offset, e);
     else kdl_update_kinematics(rb.segs, rb.n_segments, rb.dof, q + tk.joint_offset, dq + tk.joint_offset, e);
     if (tk.has_transform) apply_transform(tk.T, rb.dof, e);
@@ -453,6 +463,14 @@ HD void task_ee(const DevProblem& P, const DevTask& tk, const double* q, const d
 // task vector f(x) of one task: PosOrnPlannerSys::getFxJac (PosOrnPlannerSys.cpp:80-102), PosOrnTimePlannerSys::getFxJac
 // (PosOrnTimePlannerSys.cpp:85-112); layout [p, quat, (dp, dquat), (t)]; POSITION: [p, (dp)]
 HD void task_fx(const DevProblem& P, const DevTask& tk, const EEState& e, double t, double* fx) {
+    if (tk.kind == ILQRB_TASK_JOINT) {  // JointSpacePlannerSys::getFxJac: fx = getState() = [q, (dq), (t)]   JointSpacePlannerSys.cpp:77-91
+        const int dofr = P.robots[tk.robot].dof;
+        for (int i = 0; i < dofr; i++) fx[i] = e.Jv[i][0];
+        if (P.nb_deriv == 2)
+            for (int i = 0; i < dofr; i++) fx[dofr + i] = e.Jv[i][1];
+        if (P.time) fx[P.nb_deriv * dofr] = t;
+        return;
+    }
     if (P.sys_kind == ILQRB_SYS_POSITION) {
         const int car = tk.nt_t / P.nb_deriv;
         for (int i = 0; i < car; i++) fx[i] = e.x[i];
@@ -484,8 +502,17 @@ HD void task_fx(const DevProblem& P, const DevTask& tk, const EEState& e, double
 }
 
 // Keypoint::diff — PosOrnKeypoint.cpp:24-45, SpacetimeKeypoint.cpp:19-24; tg = one ILQRB_KP_STRIDE record
-HD void task_residual(const DevProblem& P, const DevTask& tk, const double* fx, const double* tg, double* res) {
+// dz: the keypoint's dead zone [pos_radius, orn_thresh[3]] (PosOrnKeypointDistFunct) or nullptr
+HD void task_residual(const DevProblem& P, const DevTask& tk, const double* fx, const double* tg, double* res, const double* dz = nullptr) {
     const int nd = P.nb_deriv;
+    if (tk.kind == ILQRB_TASK_JOINT) {  // AngularKeypoint::diff = target - state (AngularKeypoint.cpp:22-25); time: AngularTimeKeypoint.cpp:19-24
+        const int dofr = P.robots[tk.robot].dof;
+        for (int i = 0; i < dofr; i++) res[i] = tg[i] - fx[i];
+        if (nd == 2)
+            for (int i = 0; i < dofr; i++) res[dofr + i] = tg[7 + i] - fx[dofr + i];
+        if (P.time) res[nd * dofr] = tg[14] - fx[nd * dofr];
+        return;
+    }
     if (P.sys_kind == ILQRB_SYS_POSITION) {
         const int car = tk.nt_t / nd;
         bool zero = true;
@@ -522,8 +549,34 @@ HD void task_residual(const DevProblem& P, const DevTask& tk, const double* fx, 
             minus2H_times(tg + 3, dd, res + 9);
         }
     }
+    if (dz != nullptr && dz[0] >= 0.0) {
+        // PosOrnKeypointDistFunct::diff (PosOrnKeypointDistFunct.cpp:13-35): the position residual shrinks by pos_radius (zero inside
+        // the ball); each orientation component shrinks by its threshold.  The reference tests `abs(residual) <= thresh` with an
+        // UNQUALIFIED abs in a file without using-directives: with libstdc++ that is ::abs(int), so the comparison sees the residual
+        // truncated to an integer (SURVEY quirk list, Q18); restated as compiled.
+        const double nrm = sqrt(res[0] * res[0] + res[1] * res[1] + res[2] * res[2]);
+        if (nrm <= dz[0]) {
+            res[0] = res[1] = res[2] = 0.0;
+        } else {
+            const double k = nrm - dz[0];
+            res[0] = res[0] / nrm * k;
+            res[1] = res[1] / nrm * k;
+            res[2] = res[2] / nrm * k;
+        }
+        for (int i = 0; i < 3; i++) {
+            const int ia = abs((int)res[3 + i]);
+            if ((double)ia <= dz[1 + i]) {
+                res[3 + i] = 0.0;
+            } else {
+                const int sign = res[3 + i] < 0 ? -1 : 1;
+                res[3 + i] = res[3 + i] - sign * dz[1 + i];
+            }
+        }
+    }
     if (P.time) res[6 * nd] = tg[14] - fx[ns];
 }
+// dead zone record of keypoint kp of task tk, or nullptr
+HD const double* task_deadzone(const DevTask& tk, int kp) { return tk.kp_deadzone ? tk.kp_deadzone + 4 * kp : nullptr; }
 
 // Task Jacobian rows of one task (r_t x n, row-major into J with leading dimension ldj):
 // PosOrnPlannerSys::getFxJac J = Jkdl or blockdiag(J,J) (PosOrnPlannerSys.cpp:87-101); time: trailing 1
@@ -533,6 +586,10 @@ HD void task_jacobian(const DevProblem& P, const DevTask& tk, const EEState& e, 
     const int nd = P.nb_deriv, dof = P.dof;
     for (int i = 0; i < tk.r_t; i++)
         for (int j = 0; j < P.n; j++) J[i * ldj + j] = 0;
+    if (tk.kind == ILQRB_TASK_JOINT) {  // Identity(nb_Q_var, nb_ctrl_var)   JointSpacePlannerSys.cpp:79, JointSpaceTimePlannerSys.cpp:83
+        for (int i = 0; i < tk.r_t && i < P.m; i++) J[i * ldj + i] = 1;
+        return;
+    }
     const int rows = (P.sys_kind == ILQRB_SYS_POSITION) ? tk.nt_t / nd : 6;
     for (int blk = 0; blk < nd; blk++)
         for (int c = 0; c < rb.dof; c++) {
@@ -591,7 +648,7 @@ HD double stage_cost(const DevProblem& P, int b, const double* x, const double* 
             double fx[MAX_NTT], res[MAX_RT];
             task_fx(P, tk, e, P.time ? x[P.n - 1] : 0.0, fx);
             const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
-            task_residual(P, tk, fx, tg, res);
+            task_residual(P, tk, fx, tg, res, task_deadzone(tk, kp));
             const int r = tk.r_t;
             const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + kp) * r * r;
             double dQd = 0;

@@ -264,7 +264,7 @@ __device__ __forceinline__ void lean_kdl_fk_twist(const ilqrb_segment* __restric
 // d^T Q d of task tk at keypoint kp for task vector fx   (System.cpp:216-220)
 __device__ __forceinline__ double lean_task_cost(const DevProblem& P, const DevTask& tk, int b, int kp, const double* fx, double* res) {
     const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
-    task_residual(P, tk, fx, tg, res);
+    task_residual(P, tk, fx, tg, res, task_deadzone(tk, kp));
     const int r = tk.r_t;
     const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + kp) * r * r;
     double dQd = 0;
@@ -281,7 +281,7 @@ __device__ __forceinline__ double lean_task_cost(const DevProblem& P, const DevT
 template <int N>
 __device__ __forceinline__ double lean_stage_cost(const DevProblem& P, int b, const double* x, const double* u, int k) {
     bool lean_ok = P.sys_kind != ILQRB_SYS_POSITION;
-    for (int t = 0; t < P.n_tasks; t++) lean_ok = lean_ok && P.robots[P.tasks[t].robot].kind == ILQRB_ROBOT_KDL;
+    for (int t = 0; t < P.n_tasks; t++) lean_ok = lean_ok && P.robots[P.tasks[t].robot].kind == ILQRB_ROBOT_KDL && P.tasks[t].kind == ILQRB_TASK_POSE;
     if (!lean_ok) return stage_cost<N>(P, b, x, u, k);
     double total = 0;
     const int dof = P.dof;

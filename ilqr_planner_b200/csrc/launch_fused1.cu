@@ -8,6 +8,8 @@ namespace ilqrb {
 
 bool fast_n1_applies(ilqrb_handle h, bool al) {
     const DevProblem& P = h->hp;
+    for (int t = 0; t < P.n_tasks; t++)
+        if (P.tasks[t].kind != ILQRB_TASK_POSE) return false;  // joint-space tasks: generic kernels
     return !generic_forced() && !al && P.nb_deriv == 1 && !P.time && P.n == P.m && P.n + 1 <= 16 &&
            (size_t)fwd_n1_smem_doubles(P.H, h->W.ns, P.n_kp_steps) * sizeof(double) <= 200 * 1024;
 }

@@ -53,6 +53,7 @@ void slice_desc(const ilqrb_problem_desc& d, const int* task_r, int lo, int hi, 
 // residual size of one task (the arithmetic of ilqrb_get_dims, per task)
 int task_residual_size(const ilqrb_problem_desc& d, int t) {
     const int time = d.sys_kind == ILQRB_SYS_POS_ORN_TIME ? 1 : 0;
+    if (d.tasks[t].task_kind == ILQRB_TASK_JOINT) return d.nb_deriv * d.robots[d.tasks[t].robot].dof + time;
     if (d.sys_kind == ILQRB_SYS_POSITION) return (d.robots[d.tasks[t].robot].kind == ILQRB_ROBOT_2D ? 2 : 3) * d.nb_deriv;
     return 6 * d.nb_deriv + time;
 }

@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(64) k_kp_derivs(const DevProblem* __restrict__
         double fx[MAX_NTT], res[MAX_RT];
         task_fx(P, tk, e, P.time ? xs[n - 1] : 0.0, fx);
         const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
-        task_residual(P, tk, fx, tg, res);
+        task_residual(P, tk, fx, tg, res, task_deadzone(tk, kp));
         const int r = tk.r_t;
         const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + kp) * r * r;
         double J[MAX_RT * MAXN];

@@ -52,6 +52,8 @@ class TaskSpec:
     state_max: Optional[np.ndarray] = None
     state_min: Optional[np.ndarray] = None
     limit_weight: Optional[np.ndarray] = None
+    task_kind: int = cabi.TASK_POSE           # TASK_JOINT: JointSpace(Time)PlannerSys with Angular(Time)Keypoints
+    kp_deadzone: Optional[np.ndarray] = None  # [Kp][4] pos_radius, orn_thresh[3] (PosOrnKeypointDistFunct); None = plain keypoints
 
 
 @dataclass
@@ -85,6 +87,9 @@ class ProblemBatch:
         return self.dof + self.time
 
     def task_dims(self, t):
+        if self.tasks[t].task_kind == cabi.TASK_JOINT:
+            d = self.nb_deriv * self.robots[self.tasks[t].robot].dof + self.time
+            return d, d
         if self.sys_kind == cabi.SYS_POSITION:
             car = 2 if self.robots[self.tasks[t].robot].kind == cabi.ROBOT_2D else 3
             return car * self.nb_deriv, car * self.nb_deriv
@@ -110,7 +115,7 @@ class ProblemBatch:
             tasks.append(TaskSpec(kp_timestep=list(t.kp_timestep), kp_target=np.asarray(t.kp_target)[lo:hi],
                                   kp_precision=prec[lo:hi] if prec.shape[0] > 1 else prec, r_diag=t.r_diag, robot=t.robot,
                                   joint_offset=t.joint_offset, T=t.T, state_max=t.state_max, state_min=t.state_min,
-                                  limit_weight=t.limit_weight))
+                                  limit_weight=t.limit_weight, task_kind=t.task_kind, kp_deadzone=t.kp_deadzone))
         return ProblemBatch(self.sys_kind, self.nb_deriv, self.horizon, self.dt, self.dof, self.robots, tasks, self.r_diag,
                             np.asarray(self.q0)[lo:hi], np.asarray(self.dq0)[lo:hi])
 
@@ -150,6 +155,11 @@ class ProblemBatch:
             tasks[i].kp_target = cabi.dptr(tg)
             tasks[i].kp_precision = cabi.dptr(pr)
             tasks[i].precision_per_problem = per
+            tasks[i].task_kind = int(t.task_kind)
+            if t.kp_deadzone is not None:
+                dz = _f64(t.kp_deadzone, (Kp, 4))
+                keep.append(dz)
+                tasks[i].kp_deadzone = cabi.dptr(dz)
             tasks[i].r_diag = cabi.dptr(rd)
             if t.T is not None:
                 tasks[i].has_transform = 1

@@ -307,3 +307,69 @@ def al_config3_active(kind="qbox", horizon=100, lag_update_step=3):
     else:
         raise ValueError(kind)
     return dict(A=A, b=b, lambda0=lam0, lag_update_step=lag_update_step, penalty=0.25, scaling_factor=1.1)
+
+
+# ---- joint-space systems, angular keypoints, dead-zone keypoints (the HYBRID_* / JOINT_SPACE_* notebook structures;
+# the notebooks draw their joint targets with an unseeded np.random.uniform, so their stored traces cannot be reproduced) -------
+def _joint_targets(q0, dq_list, times=None):
+    tg = np.zeros((q0.shape[0], len(dq_list), cabi.KP_STRIDE))
+    for i, dq in enumerate(dq_list):
+        tg[:, i, 0:q0.shape[1]] = q0 + dq
+        if times is not None:
+            tg[:, i, 14] = times[i]
+    return tg
+
+
+def config_joint_space(batch=16, horizon=100, dt=0.1, offset=0, time=False):
+    """JOINT_SPACE_SYS(_TIME): JointSpace(Time)PlannerSys, two Angular(Time)Keypoints at H/2-1 and H-1, Q = I (time entry .1),
+    R = 1e-5, Panda joint limits as soft limits"""
+    segs = panda_chain()
+    d = _draws(10 + int(time), offset, offset + batch, [("q0", -0.3, 0.3, 7), ("t1", -0.8, 0.8, 7), ("t2", -0.8, 0.8, 7)])
+    q0 = np.clip(PANDA_Q0 + d["q0"], PANDA_LOWER + 0.1, PANDA_UPPER - 0.1)
+    tg = _joint_targets(q0, [d["t1"], d["t2"]], times=(2.5, 5.0) if time else None)
+    nq = 7 + int(time)
+    Q = np.identity(nq)
+    if time:
+        Q[-1, -1] = .1
+    R = np.ones(nq) * 1e-5
+    smax = np.concatenate([PANDA_UPPER, [0.0]]) if time else PANDA_UPPER
+    smin = np.concatenate([PANDA_LOWER, [0.0]]) if time else PANDA_LOWER
+    w = np.array([1] * 7 + ([0] if time else []), dtype=np.int32)
+    task = TaskSpec(kp_timestep=[horizon // 2 - 1, horizon - 1], kp_target=tg, kp_precision=np.array([[Q, Q]]), r_diag=R, state_max=smax, state_min=smin,
+                    limit_weight=w, task_kind=cabi.TASK_JOINT)
+    return ProblemBatch(cabi.SYS_POS_ORN_TIME if time else cabi.SYS_POS_ORN, 1, horizon, 0.0 if time else dt, 7, [RobotSpec(cabi.ROBOT_KDL, 7, segs)], [task], R, q0,
+                        np.zeros_like(q0))
+
+
+def config_hybrid(batch=16, horizon=120, dt=0.01, offset=0, time=False):
+    """HYBRID_SYS(_TIME): SequentialSystem(JointSpace(Time)PlannerSys with one angular keypoint at H/2-1, PosOrn(Time)PlannerSys with one
+    pose keypoint at H-1), sub-system R = 1e-3 (time: 1e-5), top-level R = 1e-6"""
+    segs = panda_chain()
+    d = _draws(12 + int(time), offset, offset + batch, [("q0", -0.3, 0.3, 7), ("t1", -0.5, 0.5, 7), ("t2", -0.5, 0.5, 7)])
+    q0 = np.clip(PANDA_Q0 + d["q0"], PANDA_LOWER + 0.1, PANDA_UPPER - 0.1)
+    nq = 7 + int(time)
+    tgj = _joint_targets(q0, [d["t1"]], times=(2.5,) if time else None)
+    tgp = _posorn_targets(segs, q0, [d["t2"]])
+    Qj = np.identity(nq)
+    Qp = np.diag([1, 1, 1, .1, .1, .1] + ([0.0] if time else []))
+    if time:
+        Qj[-1, -1] = 0.0
+        tgp[:, 0, 14] = 5.0
+    Rsub = np.ones(nq) * (1e-5 if time else 1e-3)
+    smax = np.concatenate([PANDA_UPPER, [0.0]]) if time else PANDA_UPPER
+    smin = np.concatenate([PANDA_LOWER, [0.0]]) if time else PANDA_LOWER
+    w = np.array([1] * 7 + ([0] if time else []), dtype=np.int32)
+    t1 = TaskSpec(kp_timestep=[horizon // 2 - 1], kp_target=tgj, kp_precision=np.array([[Qj]]), r_diag=Rsub, state_max=smax, state_min=smin, limit_weight=w,
+                  task_kind=cabi.TASK_JOINT)
+    t2 = TaskSpec(kp_timestep=[horizon - 1], kp_target=tgp, kp_precision=np.array([[Qp]]), r_diag=Rsub, state_max=smax, state_min=smin, limit_weight=w)
+    R = np.ones(nq) * 1e-6
+    return ProblemBatch(cabi.SYS_POS_ORN_TIME if time else cabi.SYS_POS_ORN, 1, horizon, 0.0 if time else dt, 7, [RobotSpec(cabi.ROBOT_KDL, 7, segs)], [t1, t2], R, q0,
+                        np.zeros_like(q0))
+
+
+def config2_deadzone(batch=16, horizon=100, dt=0.1, offset=0, nb_deriv=1):
+    """C2 shape with PosOrnKeypointDistFunct keypoints: the first keypoint has a 5 cm / (0.05, 0.1, 2.0) rad dead zone, the second is a
+    plain PosOrnKeypoint (negative radius)"""
+    pb = config2(batch=batch, horizon=horizon, dt=dt, offset=offset) if nb_deriv == 1 else config3(batch=batch, horizon=horizon, dt=dt, offset=offset)
+    pb.tasks[0].kp_deadzone = np.array([[0.05, 0.05, 0.1, 2.0], [-1.0, 0.0, 0.0, 0.0]])
+    return pb

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define ILQRB_ABI_VERSION 1
+#define ILQRB_ABI_VERSION 2 /* 2: ilqrb_task.task_kind, ilqrb_task.kp_deadzone */
 
 /* error codes */
 #define ILQRB_OK 0
@@ -42,6 +42,14 @@ extern "C" {
 #define ILQRB_SYS_POS_ORN 0      /* sys::PosOrnPlannerSys      PosOrnPlannerSys.cpp:54-142      */
 #define ILQRB_SYS_POS_ORN_TIME 1 /* sys::PosOrnTimePlannerSys  PosOrnTimePlannerSys.cpp:50-188  */
 #define ILQRB_SYS_POSITION 2     /* position-only task (README.md:15; SURVEY §8g note C1)       */
+
+/* task kinds: what one sub-system of the list observes (ilqrb_task.task_kind) */
+#define ILQRB_TASK_POSE 0  /* the end-effector task of desc->sys_kind (PosOrn / PosOrnTime / Position planner systems)        */
+#define ILQRB_TASK_JOINT 1 /* sys::JointSpacePlannerSys / JointSpaceTimePlannerSys (JointSpacePlannerSys.cpp:77-111,
+                              JointSpaceTimePlannerSys.cpp:81-140): f(x) = x, J = I, keypoints = sys::AngularKeypoint /
+                              AngularTimeKeypoint (AngularKeypoint.cpp:13-27, AngularTimeKeypoint.cpp:12-24): residual target - x.
+                              nb_deriv = 1 only (with nb_deriv = 2 the reference's J = Identity(2 dof, dof) has the wrong shape).
+                              desc->sys_kind still selects the dynamics (POS_ORN: fixed dt, POS_ORN_TIME: time state).            */
 
 /* robot kinds */
 #define ILQRB_ROBOT_KDL 0 /* sim::KDLRobot   KDLRobot.cpp:17-115 (serial chain, orocos_kdl semantics) */
@@ -56,7 +64,8 @@ extern "C" {
 #define ILQRB_MAX_ROBOT_DOF 7 /* KDLRobot.cpp:112 hard-codes getJacobianDerivative<7> */
 #define ILQRB_MAX_TASKS 4
 #define ILQRB_MAX_KEYPOINTS 8
-#define ILQRB_KP_STRIDE 15 /* per keypoint target record: pos[3] quat[4](w,x,y,z) dpos[3] dquat[4] time */
+#define ILQRB_KP_STRIDE 15 /* per keypoint target record: pos[3] quat[4](w,x,y,z) dpos[3] dquat[4] time ;
+                              ILQRB_TASK_JOINT: q*[7] dq*[7] time (entries beyond the robot's dof unused) */
 #define ILQRB_N_ALPHA 11   /* line-search candidates 1, 1/2, ..., 2^-10 (ILQRRecursive.cpp:101-155) */
 
 /* per-problem status bits in ilqrb_result.status */
@@ -106,6 +115,12 @@ typedef struct ilqrb_task {
     const double* state_max;   /* [n] (time systems: last entry ignored, weight 0)         */
     const double* state_min;   /* [n]                                                      */
     const int32_t* limit_weight;/* [n] joint_limits_weight_ (System.cpp:49-60)             */
+    int32_t task_kind;         /* ILQRB_TASK_* */
+    int32_t pad_;
+    /* sys::PosOrnKeypointDistFunct (PosOrnKeypointDistFunct.cpp:13-35): [Kp][4] = pos_radius, orn_thresh[3] per keypoint, shared by
+     * the batch; a keypoint with a negative pos_radius is a plain PosOrnKeypoint; NULL = no dead zones.  POSE tasks of
+     * PosOrnPlannerSys only (the reference has no time variant).                                                               */
+    const double* kp_deadzone;
 } ilqrb_task;
 
 typedef struct ilqrb_problem_desc {

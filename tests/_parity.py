@@ -21,16 +21,20 @@ both are MEASURED here on the oracle itself instead of being guessed:
   * Truth: the same oracle source built with every internal double widened to long double (liboracle_ld.so, 64-bit
     mantissa): the identical algorithm 2048 times finer.  The FP64 oracle's distance from it is how far the reference's own
     arithmetic sits from the exact answer; it joins the noise floor, and `check_truth` holds the GPU to being as close to the
-    truth as the FP64 runs are (within NOISE_FACTOR).  This is what showed that the collapsed P update of round 1
+    truth as the FP64 runs are (within TRUTH_FACTOR).  This is what showed that the collapsed P update of round 1
     (-1e-6 K^T K for K^T (Quu K + Qux)) put the gains 60 times further from the truth than the reference's form.
     A GPU result passes if it is within max(1e-9, 4 x noise floor) of the oracle on the tie-free problems, as close to the truth
-    as the FP64 oracle builds are (x 4), and its step sequences agree with the oracle's up to each problem's first tie.
+    as the FP64 oracle builds are (x 8), and its step sequences agree with the oracle's up to each problem's first tie.
 """
 import numpy as np
 
 RTOL = 1e-9
 TIE_FLOOR = 1e-12  # SURVEY 7.3 item 1: below this a margin is a tie whatever was measured
 NOISE_FACTOR = 4.0
+# check_truth compares two MAXIMA over ~1e5 elements of independent rounding errors (GPU vs truth, FP64 oracle vs truth), each
+# dominated by its own worst element: equally accurate implementations differ by a factor of a few in that statistic, so the
+# truth check allows 8 (measured: 0.2 .. 4.5 over the suite's cases) — the collapsed P update it was built to catch sat at 60.
+TRUTH_FACTOR = 8.0
 # Small batches see few or no flips of their own, so their measured threshold is floored by the one measured at full size
 # (tests/test_gpu_parity.py::test_full_size_parity_against_measured_instability re-measures and prints it on every run):
 # 4096 problems of configs[1], 20 iterations, q0 +- 1 ulp: largest decision margin at which the oracle's own step sequence
@@ -157,7 +161,7 @@ class Sensitivity:
         return self.first_tie() == np.asarray(self.ref.iters, dtype=int)
 
     def check_truth(self, out, mask=None):
-        """`out` is as close to the long-double truth as the FP64 oracle builds are (x NOISE_FACTOR, floor RTOL), per measure"""
+        """`out` is as close to the long-double truth as the FP64 oracle builds are (x TRUTH_FACTOR, floor RTOL), per measure"""
         if self.truth is None:
             return {}
         m = self.with_truth if mask is None else (self.with_truth & mask)
@@ -165,7 +169,7 @@ class Sensitivity:
         for f, (get, kw) in self.measures.items():
             e = rel(get(out)[m], get(self.truth)[m], **kw) if m.any() else 0.0
             got[f] = e
-            assert e < max(RTOL, NOISE_FACTOR * self.truth_err[f]), "%s: %.2e from the long-double truth, the FP64 oracle %.2e" % (f, e, self.truth_err[f])
+            assert e < max(RTOL, TRUTH_FACTOR * self.truth_err[f]), "%s: %.2e from the long-double truth, the FP64 oracle %.2e" % (f, e, self.truth_err[f])
         return got
 
     def summary(self):

@@ -57,3 +57,22 @@ def test_fk_matches_notebook_literal(oracle_lib):
     x, quat, J, dx, w = oracle_lib.kinematics(pb, 0, pb.q0)
     np.testing.assert_allclose(x[0], [0.38162676, 0.28572033, 0.57378428], atol=5e-9)
     np.testing.assert_allclose(quat[0], [-0.03647984, 0.94060485, 0.33742794, 0.00860923], atol=5e-9)
+
+
+def test_joint_space_notebook_trace_shape(oracle_lib):
+    """JOINT_SPACE_SYS.ipynb draws its two joint targets with an unseeded np.random.uniform, so its stored trace cannot be reproduced;
+    what the oracle's JointSpacePlannerSys / AngularKeypoint restatement can be held to is the trace's SHAPE (cell 15: iteration 1
+    accepts alpha = 1 and lands on a cost ~1e-5, iteration 2 finds no improving step, takes alpha = 2^-10 and the early stop fires;
+    cells 14 / 16: the batch solvers start from the same cost and the CP solver's second cost is orders of magnitude below the first)"""
+    import numpy as np
+    from ilqr_planner_b200 import synth
+    from ilqr_planner_b200.solver import build_psi
+    pb = synth.config_joint_space(batch=8)
+    r = oracle_lib.solve_recursive(pb, None, 10, True, True, threads=4)
+    assert np.all(r.iters == 2) and np.all(r.alpha_hist[:, 0] == 1.0) and np.all(r.alpha_hist[:, 1] == 2.0 ** -10)
+    assert np.all(r.cost_hist[:, 0] < 1e-4) and np.all(r.cost_hist[:, 1] >= r.cost_hist[:, 0])
+    psi = np.kron(build_psi("unitstep", pb.horizon - 1, 2), np.identity(pb.m))
+    cp = oracle_lib.solve_batch(pb, None, 4, True, psi=psi, threads=4)
+    ba = oracle_lib.solve_batch(pb, None, 2, True, threads=4)
+    assert np.array_equal(cp.cost_hist[:, 0], ba.cost_hist[:, 0]) and np.all(cp.alpha_hist[:, 0] == 1.0)
+    assert np.all(cp.cost_hist[:, 1] < 1e-2 * cp.cost_hist[:, 0])
