@@ -536,7 +536,7 @@ def main():
         from ilqr_planner_b200.solver import fp64_peaks
         dfma_peak, dmma_peak = fp64_peaks(local_rank)  # micro-benchmarks of the library itself (csrc/ubench.cu)
         figs = ncu_figures()
-        nb, nf = ncu_kernel(figs, "k_backward_n1", B), ncu_kernel(figs, "k_forward_n1", B)
+        nb, nf = ncu_kernel(figs, "k_backward_n1", B), (ncu_kernel(figs, "k_forward_ring_n1", B) or ncu_kernel(figs, "k_forward_n1", B))
         tot_ms = sum(v[0] for v in prof.values())
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
                 "ms_per_iteration": ms_max / args.steps / NB_ITER, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -575,7 +575,7 @@ def main():
                 # second kernel of the iteration: line search + accept (k_forward_n1).  It streams K, d (written by the backward pass), X, U
                 # once and writes X, U once: the byte view against the measured copy peak; it is bound by the latency of its serial 99-step
                 # deviation rollout and the FK chains of the candidates (ncu: 51 % of stall samples on the long scoreboard), not by HBM
-                "roofline_forward": (lambda fms, fn: {"kernel": "linesearch_rollout (k_forward_n1)", "bound": "hbm",
+                "roofline_forward": (lambda fms, fn: {"kernel": "linesearch_rollout (k_forward_ring_n1)", "bound": "hbm",
                                      "achieved": (B * 8.0 * ((H - 1) * (m * n + m) + 2 * (H * n + (H - 1) * m)) / (fms / max(fn, 1) * 1e-3) / 1e9) if fms > 0 else None,
                                      "peak": hbm_peak, "unit": "GB/s", "peak_source": peak_src,
                                      "algorithmic_bytes_per_launch": B * 8.0 * ((H - 1) * (m * n + m) + 2 * (H * n + (H - 1) * m)),

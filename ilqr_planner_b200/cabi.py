@@ -16,6 +16,7 @@ JOINT_FIXED, JOINT_ROT, JOINT_TRANS = 0, 1, 2
 KP_STRIDE = 15
 N_ALPHA = 11
 MAX_SEGMENTS = 24
+SD_LOGMAP, SD_EXPMAP, SD_DISTANCE, SD_TRANSPORT, SD_DQUAT_TO_W_JAC = range(5)
 KIN_STATIC_MAX_NQ = 4096
 ST_NAN_COST, ST_QUU_NOT_SPD, ST_EARLY_STOP = 1, 2, 4
 PROF_SLOTS = 13
@@ -98,7 +99,7 @@ SYMBOLS = [
     "ilqrb_synchronize", "ilqrb_update_problems", "ilqrb_solve_recursive", "ilqrb_solve_recursive_async", "ilqrb_solve_al", "ilqrb_solve_batch",
     "ilqrb_upload_u0", "ilqrb_run_recursive", "ilqrb_run_al", "ilqrb_run_batch", "ilqrb_download", "ilqrb_rollout",
     "ilqrb_kinematics", "ilqrb_set_profiling", "ilqrb_get_profile", "ilqrb_reset_profile", "ilqrb_launch_count",
-    "ilqrb_chain_from_urdf", "ilqrb_build_psi", "ilqrb_fp64_peaks", "ilqrb_kinematics_static",
+    "ilqrb_chain_from_urdf", "ilqrb_build_psi", "ilqrb_fp64_peaks", "ilqrb_kinematics_static", "ilqrb_eval_point", "ilqrb_keypoint_diff", "ilqrb_sd", "ilqrb_host_alloc", "ilqrb_host_free",
     "ilqrb_multi_plan", "ilqrb_create_multi", "ilqrb_multi_destroy", "ilqrb_multi_count", "ilqrb_multi_slice", "ilqrb_multi_solve_recursive",
     "ilqrb_multi_solve_al", "ilqrb_multi_solve_batch", "ilqrb_multi_upload_u0", "ilqrb_multi_run_recursive", "ilqrb_multi_synchronize", "ilqrb_multi_download",
 ]
@@ -139,6 +140,11 @@ def load():
     lib.ilqrb_kinematics.argtypes = [H, C.c_int, C.c_int, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p]
     lib.ilqrb_kinematics_static.argtypes = lib.ilqrb_kinematics.argtypes
     IP = C.POINTER(C.c_int)
+    lib.ilqrb_eval_point.argtypes = [H, C.c_int, IP, IP] + [c_double_p] * 9
+    lib.ilqrb_keypoint_diff.argtypes = [C.c_int] * 5 + [c_double_p, c_double_p, C.c_int, c_double_p, c_double_p]
+    lib.ilqrb_sd.argtypes = [C.c_int, C.c_int, C.c_int] + [c_double_p] * 4
+    lib.ilqrb_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
+    lib.ilqrb_host_free.argtypes = [C.c_void_p]
     lib.ilqrb_multi_plan.argtypes = [C.c_int, C.c_int, IP, IP]
     lib.ilqrb_create_multi.argtypes = [C.POINTER(ProblemDesc), C.c_int, IP, C.POINTER(H)]
     lib.ilqrb_multi_destroy.argtypes = [H]

@@ -137,6 +137,22 @@ class Handle:
                                              cabi.dptr(dx), cabi.dptr(w)))
         return x, quat, J, dx, w
 
+    def eval_point(self, x, k=None, u=None, problem=None, fx_in=None):
+        """System::getFxJac(xk), diff, cost, cost_x, cost_xx at nq points (ilqrb_eval_point): x [nq][n], k [nq] timesteps,
+        u [nq][m] (None = zeros), problem [nq] (None = problem 0), fx_in [nq][nt] (None = diff of f(x)).
+        Returns a dict of fx, J, diff, cost, cost_x, cost_xx."""
+        pb = self.pb
+        x = np.ascontiguousarray(np.asarray(x, dtype=np.float64).reshape(-1, pb.n))
+        nq = x.shape[0]
+        ia = lambda v: None if v is None else np.ascontiguousarray(np.broadcast_to(np.asarray(v, dtype=np.int32), (nq,)))
+        da = lambda v, w: None if v is None else np.ascontiguousarray(np.asarray(v, dtype=np.float64).reshape(nq, w))
+        k, problem, u, fx_in = ia(k), ia(problem), da(u, pb.m), da(fx_in, pb.nt)
+        o = dict(fx=np.empty((nq, pb.nt)), J=np.empty((nq, pb.r, pb.n)), diff=np.empty((nq, pb.r)), cost=np.empty(nq), cost_x=np.empty((nq, pb.n)),
+                 cost_xx=np.empty((nq, pb.n, pb.n)))
+        cabi.check(self.lib.ilqrb_eval_point(self.h, nq, cabi.iptr(problem), cabi.iptr(k), cabi.dptr(x), cabi.dptr(u), cabi.dptr(fx_in), cabi.dptr(o["fx"]),
+                                             cabi.dptr(o["J"]), cabi.dptr(o["diff"]), cabi.dptr(o["cost"]), cabi.dptr(o["cost_x"]), cabi.dptr(o["cost_xx"])))
+        return o
+
     # ---- profiling
     def set_profiling(self, on):
         cabi.check(self.lib.ilqrb_set_profiling(self.h, int(on)))
@@ -269,3 +285,33 @@ class MultiHandle:
     def download(self, out, nb_iter):
         cabi.check(self.lib.ilqrb_multi_download(self.h, C.byref(out.res), int(nb_iter)))
         return out
+
+
+def keypoint_diff(sys_kind, task_kind, nb_deriv, dof, target, fx, deadzone=None, device=0):
+    """Keypoint::diff without a system (ilqrb_keypoint_diff): target = one KP_STRIDE record, fx [nq][nt] -> [nq][r]"""
+    lib = cabi.load()
+    time = 1 if sys_kind == cabi.SYS_POS_ORN_TIME else 0
+    if task_kind == cabi.TASK_JOINT:
+        nt = r = nb_deriv * dof + time
+    elif sys_kind == cabi.SYS_POSITION:
+        nt = r = dof * nb_deriv
+    else:
+        nt, r = 7 * nb_deriv + time, 6 * nb_deriv + time
+    target = np.ascontiguousarray(np.asarray(target, dtype=np.float64).reshape(cabi.KP_STRIDE))
+    fx = np.ascontiguousarray(np.asarray(fx, dtype=np.float64).reshape(-1, nt))
+    dz = None if deadzone is None else np.ascontiguousarray(np.asarray(deadzone, dtype=np.float64).reshape(4))
+    out = np.empty((fx.shape[0], r))
+    cabi.check(lib.ilqrb_keypoint_diff(device, sys_kind, task_kind, nb_deriv, dof, cabi.dptr(target), cabi.dptr(dz), fx.shape[0], cabi.dptr(fx), cabi.dptr(out)))
+    return out
+
+
+def sd(op, a, b=None, c=None, device=0):
+    """utils::Sd on S^3 (ilqrb_sd): op = cabi.SD_*, operands [nq][4]"""
+    lib = cabi.load()
+    a = np.ascontiguousarray(np.asarray(a, dtype=np.float64).reshape(-1, 4))
+    nq = a.shape[0]
+    cv = lambda v: None if v is None else np.ascontiguousarray(np.asarray(v, dtype=np.float64).reshape(nq, 4))
+    b, c = cv(b), cv(c)
+    out = np.empty(nq) if op == cabi.SD_DISTANCE else np.empty((nq, 3, 4)) if op == cabi.SD_DQUAT_TO_W_JAC else np.empty((nq, 4))
+    cabi.check(lib.ilqrb_sd(device, op, nq, cabi.dptr(a), cabi.dptr(b), cabi.dptr(c), cabi.dptr(out)))
+    return out

@@ -3,6 +3,7 @@
 #pragma once
 #include "dense.hpp"
 #include "keypoint.hpp"
+#include "sd.hpp"
 #include "sim.hpp"
 #include "solver.hpp"
 #include "system.hpp"

@@ -1,4 +1,5 @@
 // planner_systems.hpp — sys::PosOrnPlannerSys (PosOrnPlannerSys.h:18-77), sys::PosOrnTimePlannerSys (PosOrnTimePlannerSys.h:18-72),
+// sys::JointSpacePlannerSys (JointSpacePlannerSys.h:17-66), sys::JointSpaceTimePlannerSys (JointSpaceTimePlannerSys.h),
 // sys::SequentialSystem (SequentialSystem.h:15-62) and the position-only planner of README.md:15 (SURVEY §8g note C1).
 // Included by system.hpp.
 #pragma once
@@ -43,6 +44,42 @@ inline VectorXd joint_state(sim::SimulationInterface& rb, int nb_deriv, bool tim
     return x;
 }
 
+// A, B of the fixed-dt integrators (PosOrnPlannerSys.cpp:114-128, JointSpacePlannerSys.cpp:93-107)
+inline void linearize_fixed_dt(int d, int nb_deriv, int n, int m, double dt, MatrixXd& A, MatrixXd& B) {
+    A = MatrixXd::Identity(n, n);
+    B = MatrixXd::Zero(n, m);
+    for (int i = 0; i < d; i++) {
+        if (nb_deriv == 1) {
+            B(i, i) = dt;
+        } else {
+            A(i, d + i) = dt;
+            B(i, i) = dt * dt / 2;
+            B(d + i, i) = dt;
+        }
+    }
+}
+// A, B of the time systems, dt = s^2 with s the last control (PosOrnTimePlannerSys.cpp:149-176, JointSpaceTimePlannerSys.cpp:116-146);
+// v = joint velocity AFTER the step (reference behaviour)
+inline void linearize_time(int d, int nb_deriv, int n, int m, const VectorXd& x_after, const VectorXd& uk, MatrixXd& A, MatrixXd& B) {
+    const int mc = m - 1;
+    const double s = uk(mc), dt = s * s;
+    A = MatrixXd::Identity(n, n);
+    B = MatrixXd::Zero(n, m);
+    for (int i = 0; i < d; i++) {
+        if (nb_deriv == 1) {
+            B(i, i) = dt;
+            B(i, mc) = 2 * s * uk(i);
+        } else {
+            A(i, d + i) = dt;
+            B(i, i) = dt * dt / 2;
+            B(d + i, i) = dt;
+            B(i, mc) = 2 * s * x_after(d + i) + 2 * s * s * s * uk(i);
+            B(d + i, mc) = 2 * s * uk(i);
+        }
+    }
+    B(n - 1, mc) = 2 * s;
+}
+
 }  // namespace detail_sys
 
 class PosOrnPlannerSys : public System {
@@ -63,22 +100,17 @@ public:
     }
     // PosOrnPlannerSys.cpp:114-138; the integration itself is SimulationInterface::sendVel / sendAcc
     std::tuple<VectorXd, VectorXd, MatrixXd, MatrixXd, MatrixXd> forwardPass(const VectorXd&, const VectorXd& uk, int) override {
-        const int d = r->getDOF();
-        MatrixXd A = MatrixXd::Identity(nb_state_var_, nb_state_var_), B = MatrixXd::Zero(nb_state_var_, nb_ctrl_var_);
-        for (int i = 0; i < d; i++) {
-            if (nb_deriv_ == 1) {
-                B(i, i) = dt_;
-            } else {
-                A(i, d + i) = dt_;
-                B(i, i) = dt_ * dt_ / 2;
-                B(d + i, i) = dt_;
-            }
-        }
+        MatrixXd A, B;
         if (nb_deriv_ == 1) r->sendVel(dt_, uk);
         else r->sendAcc(dt_, uk);
+        linearize(getState(), uk, A, B);
         auto fj = getFxJac();
         return std::make_tuple(getState(), std::get<0>(fj), A, B, std::get<1>(fj));
     }
+    void linearize(const VectorXd&, const VectorXd&, MatrixXd& A, MatrixXd& B) const override {
+        detail_sys::linearize_fixed_dt(r->getDOF(), nb_deriv_, nb_state_var_, nb_ctrl_var_, dt_, A, B);
+    }
+    using System::getFxJac;
     std::tuple<VectorXd, MatrixXd> getFxJac() override { return detail_sys::fx_jac(*r, nb_deriv_, false); }
     VectorXd getState() override { return detail_sys::joint_state(*r, nb_deriv_, false); }
     void reset() override { r->setConfiguration(q0_, dq0_); }
@@ -131,46 +163,20 @@ public:
     }
     // PosOrnTimePlannerSys.cpp:149-184: dt = s^2, the last control column of B is d x+/d s
     std::tuple<VectorXd, VectorXd, MatrixXd, MatrixXd, MatrixXd> forwardPass(const VectorXd&, const VectorXd& uk, int) override {
-        const int d = r->getDOF(), mc = nb_ctrl_var_ - 1;
+        const int mc = nb_ctrl_var_ - 1;
         const double s = uk(mc), dt = s * s;
-        MatrixXd A = MatrixXd::Identity(nb_state_var_, nb_state_var_), B = MatrixXd::Zero(nb_state_var_, nb_ctrl_var_);
-        const VectorXd c = uk.head(mc);
-        if (nb_deriv_ == 1) {
-            r->sendVel(dt, c);
-            for (int i = 0; i < d; i++) {
-                B(i, i) = dt;
-                B(i, mc) = 2 * s * c(i);
-            }
-        } else {
-            r->sendAcc(dt, c);
-            const VectorXd v = r->getJointsVel();  // velocity AFTER the step (reference behaviour)
-            for (int i = 0; i < d; i++) {
-                A(i, d + i) = dt;
-                B(i, i) = dt * dt / 2;
-                B(d + i, i) = dt;
-                B(i, mc) = 2 * s * v(i) + 2 * s * s * s * c(i);
-                B(d + i, mc) = 2 * s * c(i);
-            }
-        }
-        B(nb_state_var_ - 1, mc) = 2 * s;
+        if (nb_deriv_ == 1) r->sendVel(dt, uk.head(mc));
+        else r->sendAcc(dt, uk.head(mc));
+        MatrixXd A, B;
+        linearize(getState(), uk, A, B);
         auto fj = getFxJac();
         return std::make_tuple(getState(), std::get<0>(fj), A, B, std::get<1>(fj));
     }
-    std::tuple<VectorXd, MatrixXd> getFxJac() override { return detail_sys::fx_jac(*r, nb_deriv_, true); }
-    // PosOrnTimePlannerSys.cpp:114-137
-    std::tuple<VectorXd, MatrixXd> getFxJac(VectorXd xk) {
-        const int d = r->getDOF();
-        const VectorXd oq = r->getJointsPos(), odq = r->getJointsVel();
-        const double ot = r->getTime();
-        VectorXd dq = VectorXd::Zero(d);
-        if (nb_deriv_ == 2) dq = xk.segment(d, d);
-        r->setConfiguration(xk.head(d), dq);
-        r->setTime(xk(xk.size() - 1));
-        auto out = getFxJac();
-        r->setConfiguration(oq, odq);
-        r->setTime(ot);
-        return out;
+    void linearize(const VectorXd& x_after, const VectorXd& uk, MatrixXd& A, MatrixXd& B) const override {
+        detail_sys::linearize_time(r->getDOF(), nb_deriv_, nb_state_var_, nb_ctrl_var_, x_after, uk, A, B);
     }
+    std::tuple<VectorXd, MatrixXd> getFxJac() override { return detail_sys::fx_jac(*r, nb_deriv_, true); }
+    using System::getFxJac;  // getFxJac(xk), PosOrnTimePlannerSys.cpp:114-137: on the device (system_hooks.hpp)
     VectorXd getState() override { return detail_sys::joint_state(*r, nb_deriv_, true); }
     void reset() override { r->setConfiguration(q0_, dq0_); }
 
@@ -206,7 +212,141 @@ private:
     VectorXd q0_, dq0_;
 };
 
-// SequentialSystem.cpp:13-76: several planners of the same kind on one joint state; tasks stack, costs add
+// JointSpacePlannerSys.h:17-66, JointSpacePlannerSys.cpp:13-111: the task is the joint state itself (f(x) = x, J = Identity), keypoints
+// are AngularKeypoints; the integrator is PosOrnPlannerSys's
+class JointSpacePlannerSys : public System {
+public:
+    JointSpacePlannerSys(const std::shared_ptr<sim::SimulationInterface>& r_, const std::vector<std::shared_ptr<Keypoint>>& kps, const VectorXd& RtDiag, const VectorXd& qMax,
+                         const VectorXd& qMin, const VectorXd& dqMax, const VectorXd& dqMin, int horizon, int nbDeriv, double dt)
+        : System(r_, kps, RtDiag, qMax, qMin, dqMax, dqMin, horizon, nbDeriv, {"JNT"}) {
+        localInit(dt);
+    }
+    JointSpacePlannerSys(const std::shared_ptr<sim::SimulationInterface>& r_, const std::vector<std::shared_ptr<Keypoint>>& kps, const VectorXd& RtDiag, const VectorXd& qMax,
+                         const VectorXd& qMin, int horizon, int nbDeriv, double dt)
+        : System(r_, kps, RtDiag, qMax, qMin, horizon, nbDeriv, {"JNT"}) {
+        localInit(dt);
+    }
+    JointSpacePlannerSys(const std::shared_ptr<sim::SimulationInterface>& r_, const std::vector<std::shared_ptr<Keypoint>>& kps, const VectorXd& RtDiag, int horizon, int nbDeriv,
+                         double dt)
+        : System(r_, kps, RtDiag, horizon, nbDeriv, {"JNT"}) {
+        localInit(dt);
+    }
+    // JointSpacePlannerSys.cpp:93-111
+    std::tuple<VectorXd, VectorXd, MatrixXd, MatrixXd, MatrixXd> forwardPass(const VectorXd&, const VectorXd& uk, int) override {
+        MatrixXd A, B;
+        if (nb_deriv_ == 1) r->sendVel(dt_, uk);
+        else r->sendAcc(dt_, uk);
+        linearize(getState(), uk, A, B);
+        auto fj = getFxJac();
+        return std::make_tuple(getState(), std::get<0>(fj), A, B, std::get<1>(fj));
+    }
+    void linearize(const VectorXd&, const VectorXd&, MatrixXd& A, MatrixXd& B) const override {
+        detail_sys::linearize_fixed_dt(r->getDOF(), nb_deriv_, nb_state_var_, nb_ctrl_var_, dt_, A, B);
+    }
+    using System::getFxJac;
+    // JointSpacePlannerSys.cpp:77-81 (Identity(nb_Q_var, nb_ctrl_var): only nb_deriv = 1 has a shape the cost can use)
+    std::tuple<VectorXd, MatrixXd> getFxJac() override { return std::make_tuple(getState(), MatrixXd::Identity(nb_Q_var_, nb_ctrl_var_)); }
+    VectorXd getState() override { return detail_sys::joint_state(*r, nb_deriv_, false); }
+    void reset() override { r->setConfiguration(q0_, dq0_); }
+    double getDt() const { return dt_; }
+    void flatten(detail::Flat& f) const override {
+        f.sys_kind = ILQRB_SYS_POS_ORN;
+        f.nb_deriv = nb_deriv_;
+        f.horizon = horizon_;
+        f.dt = dt_;
+        f.dof = r->getDOF();
+        f.tasks.emplace_back();
+        flattenTask(f.tasks.back(), false, ILQRB_TASK_JOINT);
+        f.r_diag = f.tasks.back().r_diag;
+        f.q0 = detail::to_std(q0_);
+        f.dq0 = detail::to_std(dq0_);
+    }
+
+private:
+    // JointSpacePlannerSys.cpp:54-75
+    void localInit(double dt) {
+        dt_ = dt;
+        q0_ = r->getJointsPos();
+        dq0_ = r->getJointsVel();
+        x0_ = detail_sys::joint_state(*r, nb_deriv_, false);
+        nb_state_var_ = int(x0_.rows());
+        nb_ctrl_var_ = r->getDOF();
+        nb_target_var_ = nb_state_var_;
+        nb_Q_var_ = nb_target_var_;
+    }
+    double dt_ = 0;
+    VectorXd q0_, dq0_;
+};
+
+// JointSpaceTimePlannerSys.h, JointSpaceTimePlannerSys.cpp:13-150: joint-space task with the time state; keypoints are AngularTimeKeypoints
+class JointSpaceTimePlannerSys : public System {
+public:
+    JointSpaceTimePlannerSys(const std::shared_ptr<sim::SimulationInterface>& r_, const std::vector<std::shared_ptr<Keypoint>>& kps, const VectorXd& RtDiag, const VectorXd& qMax,
+                             const VectorXd& qMin, const VectorXd& dqMax, const VectorXd& dqMin, int horizon, int nbDeriv)
+        : System(r_, kps, RtDiag, qMax, qMin, dqMax, dqMin, horizon, nbDeriv, {"JNT_TIME"}) {
+        localInit();
+    }
+    JointSpaceTimePlannerSys(const std::shared_ptr<sim::SimulationInterface>& r_, const std::vector<std::shared_ptr<Keypoint>>& kps, const VectorXd& RtDiag, const VectorXd& qMax,
+                             const VectorXd& qMin, int horizon, int nbDeriv)
+        : System(r_, kps, RtDiag, qMax, qMin, horizon, nbDeriv, {"JNT_TIME"}) {
+        localInit();
+    }
+    JointSpaceTimePlannerSys(const std::shared_ptr<sim::SimulationInterface>& r_, const std::vector<std::shared_ptr<Keypoint>>& kps, const VectorXd& RtDiag, int horizon, int nbDeriv)
+        : System(r_, kps, RtDiag, horizon, nbDeriv, {"JNT_TIME"}) {
+        localInit();
+    }
+    // JointSpaceTimePlannerSys.cpp:116-150
+    std::tuple<VectorXd, VectorXd, MatrixXd, MatrixXd, MatrixXd> forwardPass(const VectorXd&, const VectorXd& uk, int) override {
+        const int mc = nb_ctrl_var_ - 1;
+        const double s = uk(mc), dt = s * s;
+        if (nb_deriv_ == 1) r->sendVel(dt, uk.head(mc));
+        else r->sendAcc(dt, uk.head(mc));
+        MatrixXd A, B;
+        linearize(getState(), uk, A, B);
+        auto fj = getFxJac();
+        return std::make_tuple(getState(), std::get<0>(fj), A, B, std::get<1>(fj));
+    }
+    void linearize(const VectorXd& x_after, const VectorXd& uk, MatrixXd& A, MatrixXd& B) const override {
+        detail_sys::linearize_time(r->getDOF(), nb_deriv_, nb_state_var_, nb_ctrl_var_, x_after, uk, A, B);
+    }
+    using System::getFxJac;
+    // JointSpaceTimePlannerSys.cpp:73-77
+    std::tuple<VectorXd, MatrixXd> getFxJac() override { return std::make_tuple(getState(), MatrixXd::Identity(nb_target_var_, nb_ctrl_var_)); }
+    VectorXd getState() override { return detail_sys::joint_state(*r, nb_deriv_, true); }
+    void reset() override { r->setConfiguration(q0_, dq0_); }
+    void flatten(detail::Flat& f) const override {
+        f.sys_kind = ILQRB_SYS_POS_ORN_TIME;
+        f.nb_deriv = nb_deriv_;
+        f.horizon = horizon_;
+        f.dt = 0;
+        f.dof = r->getDOF();
+        f.tasks.emplace_back();
+        flattenTask(f.tasks.back(), true, ILQRB_TASK_JOINT);
+        f.r_diag = f.tasks.back().r_diag;
+        f.q0 = detail::to_std(q0_);
+        f.dq0 = detail::to_std(dq0_);
+    }
+
+private:
+    // JointSpaceTimePlannerSys.cpp:41-59
+    void localInit() {
+        q0_ = r->getJointsPos();
+        dq0_ = r->getJointsVel();
+        const int d = r->getDOF();
+        x0_ = VectorXd::Zero(nb_deriv_ * d + 1);
+        for (int i = 0; i < d; i++) {
+            x0_(i) = q0_(i);
+            if (nb_deriv_ == 2) x0_(d + i) = dq0_(i);
+        }
+        nb_state_var_ = int(x0_.rows());
+        nb_ctrl_var_ = d + 1;
+        nb_target_var_ = nb_state_var_;
+        nb_Q_var_ = nb_target_var_;
+    }
+    VectorXd q0_, dq0_;
+};
+
+// SequentialSystem.cpp:13-76: several planners on one joint state (end-effector and joint-space sub-systems may mix); tasks stack, costs add
 class SequentialSystem : public System {
 public:
     SequentialSystem(const std::shared_ptr<sim::SimulationInterface>& r_, const std::vector<std::shared_ptr<System>>& systems, const VectorXd& RtDiag, int, int) : systems_(systems) {
@@ -242,6 +382,8 @@ public:
         auto fj = getFxJac();
         return std::make_tuple(std::get<0>(first), std::get<0>(fj), std::get<2>(first), std::get<3>(first), std::get<1>(fj));
     }
+    void linearize(const VectorXd& x_after, const VectorXd& uk, MatrixXd& A, MatrixXd& B) const override { systems_.at(0)->linearize(x_after, uk, A, B); }
+    using System::getFxJac;
     // SequentialSystem.cpp:93-113
     std::tuple<VectorXd, MatrixXd> getFxJac() override {
         VectorXd fx = VectorXd::Zero(nb_target_var_);

@@ -1,7 +1,9 @@
 // system.hpp — host mirror of sys::System and its concrete planners (System.h:27-205, PosOrnPlannerSys.h, PosOrnTimePlannerSys.h,
 // SequentialSystem.h).  Same constructors, size arithmetic (localInit), keypoint checks and error messages; the object is a
 // description that `flatten`s into detail::Flat, from which the solvers build `ilqrb_problem_desc` (include/ilqrb.h).
-// The cost model (System.cpp:213-312) and the rollout run on the device only.
+// The cost model (System.cpp:213-312) and the rollout run on the device only: the single-point methods of the reference's
+// debugging API (diff, diffBatch, cost*, cost_F*, getFxJac(xk), fpBatch) evaluate through a cached one-problem handle
+// (ilqrb_eval_point / ilqrb_rollout); their bodies are in system_hooks.hpp, after the descriptor builder they need.
 #pragma once
 #include <algorithm>
 #include <map>
@@ -23,7 +25,10 @@ struct TaskFlat {
     bool limits_set = false;
     std::vector<double> state_max, state_min;  // [n]
     std::vector<int32_t> weight;               // [n]
+    int task_kind = ILQRB_TASK_POSE;
+    std::vector<double> deadzone;              // [Kp][4] (PosOrnKeypointDistFunct; radius -1 = plain keypoint) or empty
 };
+struct HookHandle;  // one-problem device handle of a System (system_hooks.hpp)
 
 struct Flat {
     int sys_kind = ILQRB_SYS_POS_ORN, nb_deriv = 1, horizon = 0, dof = 0;
@@ -145,6 +150,38 @@ public:
         return idx;
     }
 
+    // ---- single-point debugging API, evaluated on the device (system_hooks.hpp) ----
+    // System.cpp:103-109 / SequentialSystem.cpp:167-184
+    virtual VectorXd diff(const VectorXd& actual_state, int k);
+    // System.cpp:111-119: x = the task vectors at the keypoints, stacked
+    VectorXd diffBatch(const VectorXd& x);
+    // System.cpp:163-179: f(x) and its Jacobian at a given state, the simulation left untouched
+    virtual std::tuple<VectorXd, MatrixXd> getFxJac(VectorXd xk);
+    // System.cpp:121-142
+    std::pair<MatrixXd, VectorXd> inspectJointLimit(const VectorXd& x_k);
+    // System.cpp:144-161
+    std::tuple<VectorXd, VectorXd, VectorXd, VectorXd, MatrixXd, MatrixXd, MatrixXd, MatrixXd> forwardPassWithLimits(const VectorXd& xk, const VectorXd& uk, int k);
+    // System.cpp:181-211: (fX, qL, [A, B, J, L] per timestep) of the rollout of u from the initial state
+    std::tuple<VectorXd, VectorXd, std::vector<std::tuple<MatrixXd, MatrixXd, MatrixXd, MatrixXd>>> fpBatch(const VectorXd& u);
+    // System.cpp:213-312
+    VectorXd cost(const VectorXd& xk, const VectorXd& uk, int k);
+    VectorXd cost_x(const VectorXd& xk, const VectorXd& uk, int k);
+    MatrixXd cost_xx(const VectorXd& xk, const VectorXd& uk, int k);
+    VectorXd cost_u(const VectorXd&, const VectorXd& uk, int) {  // R uk (System.cpp:274-276)
+        VectorXd o = VectorXd::Zero(R.rows());
+        for (long i = 0; i < R.rows(); i++)
+            for (long j = 0; j < R.cols(); j++) o(i) += R(i, j) * uk(j);
+        return o;
+    }
+    MatrixXd cost_uu(const VectorXd&, const VectorXd&, int) { return R; }
+    MatrixXd cost_ux(const VectorXd&, const VectorXd& uk, int) { return MatrixXd::Zero(uk.rows(), nb_state_var_); }
+    MatrixXd cost_xu(const VectorXd&, const VectorXd& uk, int) { return MatrixXd::Zero(nb_state_var_, uk.rows()); }
+    VectorXd cost_F(const VectorXd& xk) { return cost(xk, VectorXd::Zero(nb_ctrl_var_), horizon_ - 1); }
+    VectorXd cost_F_x(const VectorXd& xk) { return cost_x(xk, VectorXd::Zero(nb_ctrl_var_), horizon_ - 1); }
+    MatrixXd cost_F_xx(const VectorXd& xk) { return cost_xx(xk, VectorXd::Zero(nb_ctrl_var_), horizon_ - 1); }
+    // A, B of the step that took the state to x_after under uk (the time systems' B depends on both)
+    virtual void linearize(const VectorXd& x_after, const VectorXd& uk, MatrixXd& A, MatrixXd& B) const = 0;
+
     // descriptor side
     virtual void flatten(detail::Flat& f) const = 0;
 
@@ -159,10 +196,15 @@ protected:
         if (!EXPECTED_KP_TAGS_.empty()) checkKeypoints();
     }
     // one task of the descriptor from this system's own robot view, keypoints, R and limits; `time` appends the zero-weight entry
-    void flattenTask(detail::TaskFlat& t, bool time) const {
+    void flattenTask(detail::TaskFlat& t, bool time, int task_kind = ILQRB_TASK_POSE) const {
         r->describe(t.view);
+        t.task_kind = task_kind;
         const int rq = nb_Q_var_;
+        bool any_dz = false;
         for (auto const& kp : keypoints) {
+            double dz[4] = {-1, 0, 0, 0};
+            if (kp->deadzone(dz)) any_dz = true;
+            t.deadzone.insert(t.deadzone.end(), dz, dz + 4);
             t.timestep.push_back(kp->getTimestep());
             t.target.resize(t.target.size() + ILQRB_KP_STRIDE);
             kp->writeRecord(&t.target[t.target.size() - ILQRB_KP_STRIDE]);
@@ -171,6 +213,7 @@ protected:
             for (int a = 0; a < rq; a++)
                 for (int b = 0; b < rq; b++) t.precision.push_back(P(a, b));
         }
+        if (!any_dz) t.deadzone.clear();
         for (long i = 0; i < R.rows(); i++) t.r_diag.push_back(R(i, i));
         t.limits_set = limits_set_;
         if (limits_set_) {
@@ -184,6 +227,13 @@ protected:
             }
         }
     }
+
+    struct EvalOut {
+        std::vector<double> fx, J, diff, cost, cost_x, cost_xx;
+    };
+    // one query point through ilqrb_eval_point on the cached one-problem handle
+    EvalOut evalPoint(const VectorXd& xk, const VectorXd* uk, int k, const VectorXd* fx_in);
+    std::shared_ptr<detail::HookHandle> hook_;
 
     VectorXd x0_;
     int nb_state_var_ = 0, nb_target_var_ = 0, nb_ctrl_var_ = 0, nb_Q_var_ = 0, horizon_ = 0, nb_deriv_ = 1;

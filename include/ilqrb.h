@@ -23,6 +23,7 @@
 #ifndef ILQRB_H_
 #define ILQRB_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -278,6 +279,41 @@ int ilqrb_kinematics(ilqrb_handle h, int robot, int nq, const double* q, const d
 #define ILQRB_KIN_STATIC_MAX_NQ 4096
 int ilqrb_kinematics_static(ilqrb_handle h, int robot, int nq, const double* q, const double* dq,
                             double* x, double* quat, double* J, double* dx, double* w);
+
+/* Page-locked host memory for U0 / result buffers (cudaHostAlloc, portable across the devices of the process): the host-buffer
+ * entry points copy at the full PCIe rate only from / to such memory, and the *_async form requires it.  No reference counterpart
+ * (the reference has no device); used by the C++ / PyLQR batch entry points for their result arenas.                           */
+int ilqrb_host_alloc(size_t bytes, void** out);
+int ilqrb_host_free(void* p);
+
+/* ---- single-point hooks behind the reference's debugging API ------------------ */
+/* nq query points, one device thread each, evaluated by the device functions the solvers use.
+ *   problem [nq]   which problem's keypoint targets / precisions apply (NULL = problem 0)
+ *   k       [nq]   timestep of System::cost(xk, uk, k) / System::diff(state, k) (NULL = no keypoint anywhere)
+ *   x [nq][n], u [nq][m] (NULL = zeros: the cost_F* forms, System.cpp:236-246)
+ *   fx_in [nq][nt] task vectors for System::diff (NULL = diff of f(x))
+ * outputs (any may be NULL):
+ *   fx [nq][nt], J [nq][r][n]     System::getFxJac(xk)            System.cpp:163-179, SequentialSystem.cpp:93-113
+ *   diff [nq][r]                  System::diff(fx_in | f(x), k)   System.cpp:103-109, SequentialSystem.cpp:167-184
+ *   cost [nq]                     System::cost                    System.cpp:213-234
+ *   cost_x [nq][n]                System::cost_x                  System.cpp:248-272
+ *   cost_xx [nq][n][n]            System::cost_xx                 System.cpp:286-308                                     */
+int ilqrb_eval_point(ilqrb_handle h, int nq, const int32_t* problem, const int32_t* k, const double* x, const double* u, const double* fx_in,
+                     double* fx, double* J, double* diff, double* cost, double* cost_x, double* cost_xx);
+/* Keypoint::diff without a system (PosOrnKeypoint.cpp:24-45, SpacetimeKeypoint.cpp:19-24, PosOrnKeypointDistFunct.cpp:13-35,
+ * AngularKeypoint.cpp:22-25, AngularTimeKeypoint.cpp:19-24): target = one ILQRB_KP_STRIDE record, deadzone = [4] or NULL,
+ * fx [nq][nt] -> diff [nq][r].  dof: joints of a JOINT keypoint; cartesian axes (2|3) of a POSITION keypoint; unused for POSE. */
+int ilqrb_keypoint_diff(int device, int sys_kind, int task_kind, int nb_deriv, int dof, const double* target, const double* deadzone,
+                        int nq, const double* fx, double* diff);
+/* utils::Sd on S^3, the only sphere the path uses (sd.h:19-99).  a, b, c: [nq][4].
+ *   LOGMAP(base = a, y = b) -> [nq][4]      EXPMAP(base = a, u = b) -> [nq][4]      DISTANCE(x = a, y = b) -> [nq]
+ *   TRANSPORT(v = a, base1 = b, base2 = c) -> [nq][4]      DQUAT_TO_W_JAC(q = a) -> [nq][3][4]                              */
+#define ILQRB_SD_LOGMAP 0
+#define ILQRB_SD_EXPMAP 1
+#define ILQRB_SD_DISTANCE 2
+#define ILQRB_SD_TRANSPORT 3
+#define ILQRB_SD_DQUAT_TO_W_JAC 4
+int ilqrb_sd(int device, int op, int nq, const double* a, const double* b, const double* c, double* out);
 
 /* ---- host-side builders (run once per robot / solver; no GPU work) -------------------------- */
 /* URDF -> chain descriptor.  Replaces tup::TinyURDFParser (TinyURDFParser.cpp:35-160) + the chain part of the

@@ -43,6 +43,8 @@ def load(variant=None):
     lib.oracle_kinematics.argtypes = [P(cabi.ProblemDesc), C.c_int, C.c_int] + [cabi.c_double_p] * 7
     lib.oracle_batch_step_truth.argtypes = [P(cabi.ProblemDesc), cabi.c_double_p, P(cabi.BatchDesc), cabi.c_double_p, cabi.c_double_p, C.c_int]
     lib.oracle_set_margin_out.argtypes = [cabi.c_double_p]
+    lib.oracle_eval_point.argtypes = [P(cabi.ProblemDesc), C.c_int, cabi.c_int32_p, cabi.c_int32_p] + [cabi.c_double_p] * 9
+    lib.oracle_sd.argtypes = [C.c_int, C.c_int] + [cabi.c_double_p] * 4
     lib.oracle_set_margin_out.restype = None
     _libs[variant] = lib
     return lib
@@ -158,3 +160,29 @@ def kinematics(pb, robot, q, dq=None):
     x, quat, J, dx, w = np.zeros((nq, 3)), np.zeros((nq, 4)), np.zeros((nq, 6, dof)), np.zeros((nq, 3)), np.zeros((nq, 3))
     _check(load().oracle_kinematics(C.byref(d), robot, nq, cabi.dptr(q), cabi.dptr(dq), cabi.dptr(x), cabi.dptr(quat), cabi.dptr(J), cabi.dptr(dx), cabi.dptr(w)))
     return x, quat, J, dx, w
+
+
+def eval_point(pb, x, k=None, u=None, problem=None, fx_in=None):
+    """twin of solver.Handle.eval_point"""
+    d = pb.to_desc()
+    x = np.ascontiguousarray(np.asarray(x, dtype=np.float64).reshape(-1, pb.n))
+    nq = x.shape[0]
+    ia = lambda v: None if v is None else np.ascontiguousarray(np.broadcast_to(np.asarray(v, dtype=np.int32), (nq,)))
+    da = lambda v, w: None if v is None else np.ascontiguousarray(np.asarray(v, dtype=np.float64).reshape(nq, w))
+    k, problem, u, fx_in = ia(k), ia(problem), da(u, pb.m), da(fx_in, pb.nt)
+    o = dict(fx=np.empty((nq, pb.nt)), J=np.empty((nq, pb.r, pb.n)), diff=np.empty((nq, pb.r)), cost=np.empty(nq), cost_x=np.empty((nq, pb.n)),
+             cost_xx=np.empty((nq, pb.n, pb.n)))
+    _check(load().oracle_eval_point(C.byref(d), nq, cabi.iptr(problem), cabi.iptr(k), cabi.dptr(x), cabi.dptr(u), cabi.dptr(fx_in), cabi.dptr(o["fx"]),
+                                    cabi.dptr(o["J"]), cabi.dptr(o["diff"]), cabi.dptr(o["cost"]), cabi.dptr(o["cost_x"]), cabi.dptr(o["cost_xx"])))
+    return o
+
+
+def sd(op, a, b=None, c=None):
+    """twin of solver.sd"""
+    a = np.ascontiguousarray(np.asarray(a, dtype=np.float64).reshape(-1, 4))
+    nq = a.shape[0]
+    cv = lambda v: None if v is None else np.ascontiguousarray(np.asarray(v, dtype=np.float64).reshape(nq, 4))
+    b, c = cv(b), cv(c)
+    out = np.empty(nq) if op == cabi.SD_DISTANCE else np.empty((nq, 3, 4)) if op == cabi.SD_DQUAT_TO_W_JAC else np.empty((nq, 4))
+    _check(load().oracle_sd(op, nq, cabi.dptr(a), cabi.dptr(b), cabi.dptr(c), cabi.dptr(out)))
+    return out
