@@ -1,0 +1,474 @@
+// fused_time.cuh — fast path of the Recursive iLQR solve for first-order systems WITH the time state
+// (PosOrnTimePlannerSys nb_deriv = 1: x = [q, t], u = [dq, s], dt = s^2; PosOrnTimePlannerSys.cpp:149-177):
+//   A = I,   B = [ dt I_d   2 s dq ]      n = m = dof + 1 <= 8
+//                [  0        2 s   ]
+// Two kernels per iteration (plus k_kp_derivs for l_x / l_xx), one problem per warp:
+//
+//   k_backward_time   Riccati recursion (ILQRRecursive.cpp:69-97).  [P | p] lives in registers as an 8 x 16 pair of DMMA accumulator
+//                     tiles (the vector rides in column 8).  B is a scaled identity plus one column, so its products are scalings
+//                     and one reduction each: B^T [P|p] = dt [P|p] on the joint rows and the column sums c^T [P|p] on the time row
+//                     (3 shuffle rounds), (B^T P) B and P B = a scaling of the columns and one row sum (2 shuffle rounds).  What is
+//                     left per step are the dense products of the reference's update — K = -(Quu + 1e-6 I)^-1 Qux, M = Quu K + Qux,
+//                     K^T M, Qxu K — 16 mma.sync m8n8k4.f64, operands re-laid-out through shared memory, the inverse by the
+//                     in-register Gauss-Jordan of fused1.cuh.
+//
+//   k_forward_time    line search + accept (ILQRRecursive.cpp:101-176).  dt = s^2 makes the rollout bilinear in the controls, so
+//                     the candidates are not affine in alpha (fused1.cuh's trick does not apply): lane c rolls candidate c out in
+//                     registers (x' [8], one 8 x 8 gain product per step), all lanes reading the same K_k, d_k, X_k, U_k from a
+//                     shared-memory ring the bulk-copy engine fills (cp.async.bulk + mbarrier, as in fused1_fwd.cuh); kinematics
+//                     only at the keypoint steps (and where a joint limit is violated).  The reference's sequential choice, then the
+//                     chosen candidate is rolled out once more — same code, same alpha, same numbers — with lane 0 writing X and U.
+//                     Replaces k_linesearch + k_accept, which wrote all 11 candidate control trajectories to global memory
+//                     (285 MB per iteration at B = 4096, T = 100).
+#pragma once
+#include "fused1_fwd.cuh"
+
+namespace ilqrb {
+
+struct BwdTimeSmem {
+    static constexpr int LD = 20, SZ = 8 * LD;
+    // [Qux|Qu], [K|d] (pivot rows of the elimination before that), (Quu + 1e-6 I)^-1 then M = Quu [K|d] + [Qux|Qu], [Quu | Qxu]
+    static constexpr int PER_WARP = 4 * SZ;
+};
+
+// store an 8 x 16 accumulator pair: lane (g, t) owns (g, 8 ct + 2t .. + 1)
+__device__ __forceinline__ void st_c2(double* M, const double (&e)[2][2], int g, int t) {
+    constexpr int LD = BwdTimeSmem::LD;
+#pragma unroll
+    for (int ct = 0; ct < 2; ct++) *reinterpret_cast<double2*>(M + g * LD + 8 * ct + 2 * t) = make_double2(e[ct][0], e[ct][1]);
+}
+
+// DOF > 0: dof at compile time (n = m = DOF + 1); DOF == 0: read from the problem
+template <int DOF>
+__device__ __forceinline__ void backward_time_body(const DevProblem& P, const Work& W, int b, int lane, double* wsmem) {
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr int LD = BwdTimeSmem::LD, SZ = BwdTimeSmem::SZ;
+    const int g = lane >> 2, t = lane & 3;
+    const int d = DOF > 0 ? DOF : P.dof, n = d + 1, m = n, H = P.H;
+    const int ns = (n + 1) & ~1, ms = ns;
+    double* sQux = wsmem;
+    double* sKd = sQux + SZ;
+    double* sM = sKd + SZ;
+    double* sQuu = sM + SZ;  // columns 0..7: Quu, columns 8..15: Qxu
+
+    const double Rrow = (g < m) ? P.r_diag[g] : 0.0;
+    const double* Xb = W.X + (size_t)b * H * ns;
+    const double* Ub = W.U + (size_t)b * (H - 1) * ms;
+    const int S_kp = P.n_kp_steps;
+    const int j0 = 2 * t, j1 = 2 * t + 1;  // this lane's columns inside a tile
+
+    // joint limits of the first limit-carrying task in registers (weight 0 -> +-inf); further tasks: slow loop
+    int l0 = -1, l1 = -1;
+    if (P.any_limits)
+        for (int ti = P.n_tasks - 1; ti >= 0; ti--)
+            if (P.tasks[ti].limits_set) {
+                l1 = l0;
+                l0 = ti;
+            }
+    double lmx = INFINITY, lmn = -INFINITY;
+    if (l0 >= 0 && g < n && P.tasks[l0].limit_weight[g] != 0) {
+        lmx = P.tasks[l0].state_max[g];
+        lmn = P.tasks[l0].state_min[g];
+    }
+    // e += [l_xx | l_x] of keypoint step index s                                        System.cpp:252-260,290-296
+    auto add_kp = [&](double (&e)[2][2], int s) {
+        const double* lx = W.LX + ((size_t)b * S_kp + s) * n;
+        const double* lxx = W.LXX + ((size_t)b * S_kp + s) * n * n;
+        if (g < n) {
+            if (j0 < n) e[0][0] += lxx[g * n + j0];
+            if (j1 < n) e[0][1] += lxx[g * n + j1];
+            if (t == 0) e[1][0] += lx[g];
+        }
+    };
+    // e += [L^T L | -L^T q], L = diag(violated), q = limit - x                          System.cpp:121-142,263-269,299-305
+    auto add_lq = [&](double (&e)[2][2], double q) {
+        if (j0 == g) e[0][0] += 1.0 * 1.0;
+        if (j1 == g) e[0][1] += 1.0 * 1.0;
+        if (t == 0) e[1][0] += -1.0 * q;
+    };
+    auto add_limits = [&](double (&e)[2][2], double xr) {
+        if (xr > lmx) add_lq(e, lmx - xr);
+        else if (xr < lmn) add_lq(e, lmn - xr);
+        if (l1 >= 0)
+            for (int ti = l1; ti < P.n_tasks; ti++) {
+                const DevTask& tk = P.tasks[ti];
+                if (!tk.limits_set || g >= n) continue;
+                bool act;
+                const double q = limit_q(tk, g, xr, act);
+                if (act) add_lq(e, q);
+            }
+    };
+
+    // terminal: P = cost_F_xx, p = cost_F_x   (ILQRRecursive.cpp:69-71)
+    double Pa[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+    int sp = S_kp - 1;
+    int next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
+    if (next_kp == H - 1) {
+        add_kp(Pa, sp);
+        sp--;
+        next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
+    }
+    if (l0 >= 0) add_limits(Pa, g < n ? Xb[(size_t)(H - 1) * ns + g] : 0.0);
+
+    auto load_u = [&](int k, double& uR, double& uC0, double& uC1, double& sq, double& xr) {
+        const double* Uk = Ub + (size_t)k * ms;
+        uR = (g < m) ? Uk[g] : 0.0;
+        uC0 = (j0 < m) ? Uk[j0] : 0.0;
+        uC1 = (j1 < m) ? Uk[j1] : 0.0;
+        sq = Uk[d];
+        xr = (l0 >= 0 && g < n) ? Xb[(size_t)k * ns + g] : 0.0;
+    };
+    double uRn, uC0n, uC1n, sqn, xrn;
+    load_u(H - 2, uRn, uC0n, uC1n, sqn, xrn);
+    bool spd = true;
+    double* Kg = W.K + ((size_t)b * (H - 1) + (H - 2)) * m * ns;  // walks backwards with k
+    double* dg = W.d + ((size_t)b * (H - 1) + (H - 2)) * ms;
+
+    for (int k = H - 2; k >= 0; k--, Kg -= m * ns, dg -= ms) {
+        const double uR = uRn, uC0 = uC0n, uC1 = uC1n, sq = sqn, xr = xrn;
+        if (k > 0) load_u(k - 1, uRn, uC0n, uC1n, sqn, xrn);  // prefetch the next step's rows
+        // dynamics of this step (PosOrnTimePlannerSys.cpp:149-176): dt = s^2, last control column c = [2 s dq ; 2 s]
+        const double dt = sq * sq, s2 = 2 * sq;
+        const double cR = (g < d) ? s2 * uR : (g == d ? s2 : 0.0);
+        const double cC0 = (j0 < d) ? s2 * uC0 : (j0 == d ? s2 : 0.0), cC1 = (j1 < d) ? s2 * uC1 : (j1 == d ? s2 : 0.0);
+
+        // BP = B^T [P|p]: joint rows scaled by dt, the time row = c^T [P|p]                ILQRRecursive.cpp:82-83,86
+        double BP[2][2];
+        {
+            double w00 = cR * Pa[0][0], w01 = cR * Pa[0][1], w10 = cR * Pa[1][0];
+#pragma unroll
+            for (int o = 4; o < 32; o <<= 1) {
+                w00 += __shfl_xor_sync(FULL, w00, o);
+                w01 += __shfl_xor_sync(FULL, w01, o);
+                w10 += __shfl_xor_sync(FULL, w10, o);
+            }
+            BP[0][0] = (g < d) ? dt * Pa[0][0] : (g == d ? w00 : 0.0);
+            BP[0][1] = (g < d) ? dt * Pa[0][1] : (g == d ? w01 : 0.0);
+            BP[1][0] = (g < d) ? dt * Pa[1][0] : (g == d ? w10 : 0.0);
+            BP[1][1] = 0.0;
+        }
+        // [Qux|Qu] = [0 | R u] + BP A_aug (A = I)
+        double Qa[2][2] = {{BP[0][0], BP[0][1]}, {BP[1][0], 0.0}};
+        if (t == 0) Qa[1][0] = Rrow * uR + BP[1][0];
+        // Quu = R + BP B ;  Qxu = (A^T P) B = P B: columns scaled by dt, the s column = row sums against c
+        double Quu[2], Qxu[2], Inv[1][1][2];
+        {
+            double ru = BP[0][0] * cC0 + BP[0][1] * cC1, rx = Pa[0][0] * cC0 + Pa[0][1] * cC1;
+            ru += __shfl_xor_sync(FULL, ru, 1);
+            rx += __shfl_xor_sync(FULL, rx, 1);
+            ru += __shfl_xor_sync(FULL, ru, 2);
+            rx += __shfl_xor_sync(FULL, rx, 2);
+            double q0 = (j0 < d) ? BP[0][0] * dt : (j0 == d ? ru : 0.0), q1 = (j1 < d) ? BP[0][1] * dt : (j1 == d ? ru : 0.0);
+            if (g == j0) q0 = Rrow + q0;
+            if (g == j1) q1 = Rrow + q1;
+            Quu[0] = (g < m) ? q0 : 0.0;
+            Quu[1] = (g < m) ? q1 : 0.0;
+            Qxu[0] = (j0 < d) ? Pa[0][0] * dt : (j0 == d ? rx : 0.0);
+            Qxu[1] = (j1 < d) ? Pa[0][1] * dt : (j1 == d ? rx : 0.0);
+            // Quu + 1e-6 I, identity outside the leading block                            ILQRRecursive.cpp:89
+            Inv[0][0][0] = (g == j0) ? ((g < m) ? Quu[0] + 1e-6 * 1.0 : 1.0) : Quu[0];
+            Inv[0][0][1] = (g == j1) ? ((g < m) ? Quu[1] + 1e-6 * 1.0 : 1.0) : Quu[1];
+        }
+        // [Qxx|Qx] = [l_xx|l_x] + (A^T [P|p]) A_aug
+        double Qx[2][2] = {{Pa[0][0], Pa[0][1]}, {Pa[1][0], 0.0}};
+        if (k == next_kp) {
+            add_kp(Qx, sp);
+            sp--;
+            next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
+        }
+        if (l0 >= 0) add_limits(Qx, xr);
+
+        st_c2(sQux, Qa, g, t);
+        {
+            const double QQ[2][2] = {{Quu[0], Quu[1]}, {Qxu[0], Qxu[1]}};
+            st_c2(sQuu, QQ, g, t);
+        }
+        // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]                                            ILQRRecursive.cpp:89-91
+        spd = gj_inverse_regs<1, (DOF > 0 ? DOF + 1 : 0), LD>(Inv, sKd, m, g, t) && spd;
+        *reinterpret_cast<double2*>(sM + g * LD + 2 * t) = make_double2(Inv[0][0][0], Inv[0][0][1]);
+        __syncwarp();
+        double Kd[2][2];
+#pragma unroll
+        for (int ct = 0; ct < 2; ct++) {
+            double c0 = 0.0, c1 = 0.0;
+#pragma unroll
+            for (int s = 0; s < 2; s++) dmma884(c0, c1, ld_a<LD>(sM, 0, 0, s, g, t), ld_b<LD>(sQux, 0, s, ct, g, t));
+            Kd[ct][0] = -c0;
+            Kd[ct][1] = -c1;
+        }
+        st_c2(sKd, Kd, g, t);
+        // stream K, d to global (time-forward index); pad columns of K carry zeros
+        if (g < m) {
+            if (j0 < ns) *reinterpret_cast<double2*>(Kg + g * ns + j0) = make_double2(Kd[0][0], Kd[0][1]);
+            if (t == 0) dg[g] = Kd[1][0];
+        }
+        __syncwarp();
+        // [P|p] = [Qxx|Qx] + K^T (Quu [K|d] + [Qux|Qu]) + Qxu [K|d], the bracket with the un-regularised Quu (see fused1.cuh on
+        // why the reference's form is kept rather than its collapsed equivalent)       ILQRRecursive.cpp:93-94
+        double kb[2][2], mb[2][2];
+#pragma unroll
+        for (int s = 0; s < 2; s++)
+#pragma unroll
+            for (int ct = 0; ct < 2; ct++) kb[s][ct] = ld_b<LD>(sKd, 0, s, ct, g, t);  // B fragment of [K|d]; kb[s][0] is also the A fragment of K^T
+        {
+            double Mm[2][2];
+#pragma unroll
+            for (int ct = 0; ct < 2; ct++) {
+                double c0 = Qa[ct][0], c1 = Qa[ct][1];
+#pragma unroll
+                for (int s = 0; s < 2; s++) dmma884(c0, c1, ld_a<LD>(sQuu, 0, 0, s, g, t), kb[s][ct]);
+                Mm[ct][0] = c0;
+                Mm[ct][1] = c1;
+            }
+            __syncwarp();  // every lane has read the inverse in sM
+            st_c2(sM, Mm, g, t);
+            __syncwarp();
+        }
+#pragma unroll
+        for (int s = 0; s < 2; s++)
+#pragma unroll
+            for (int ct = 0; ct < 2; ct++) mb[s][ct] = ld_b<LD>(sM, 0, s, ct, g, t);
+#pragma unroll
+        for (int ct = 0; ct < 2; ct++) {
+            double c0 = Qx[ct][0], c1 = Qx[ct][1];
+#pragma unroll
+            for (int s = 0; s < 2; s++) dmma884(c0, c1, kb[s][0], mb[s][ct]);
+#pragma unroll
+            for (int s = 0; s < 2; s++) dmma884(c0, c1, ld_a<LD>(sQuu, 0, 1, s, g, t), kb[s][ct]);
+            const bool v0 = g < n && (ct == 0 ? j0 < n : t == 0), v1 = g < n && ct == 0 && j1 < n;
+            Pa[ct][0] = v0 ? c0 : 0.0;
+            Pa[ct][1] = v1 ? c1 : 0.0;
+        }
+        __syncwarp();  // shared operands are rewritten by the next step
+    }
+    if (!__all_sync(FULL, spd) && lane == 0) atomicOr(W.status + b, ILQRB_ST_QUU_NOT_SPD);
+}
+
+template <int DOF, int WARPS, int MINB>
+__global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_time(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
+    extern __shared__ double smem[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int bl = blockIdx.x * WARPS + wid;
+    if (bl >= nB) return;
+    const int b = b0 + bl;
+    if (W.done[b]) return;
+    backward_time_body<DOF>(*Pp, W, b, lane, smem + (size_t)wid * BwdTimeSmem::PER_WARP);
+}
+
+// ------------------------------------------------------------------------------------------------------------------------------
+// forward pass.  Ring stage = SPS steps of K [m][ns], d [ms], X [ns], U [ms] (doubles)
+template <int SPS>
+__host__ __device__ inline int fwd_time_stage_doubles(int m, int ns) { return SPS * (m * ns + 3 * ns); }
+template <int RING, int SPS>
+__host__ __device__ inline size_t fwd_time_warp_bytes(int m, int ns) {
+    return ((size_t)RING * fwd_time_stage_doubles<SPS>(m, ns) * 8 + RING * 8 + 127) / 128 * 128;
+}
+
+template <int DOF, int RING, int SPS>
+__device__ __forceinline__ void forward_time_body(const DevProblem& P, const Work& W, int b, int lane, double* ring, unsigned long long* bars, const double* s_lim, int it,
+                                                  int nb_iter, int line_search, int early_stop) {
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr int N = 8;
+    const int d = DOF > 0 ? DOF : P.dof, n = d + 1, m = n, H = P.H, S = P.n_kp_steps;
+    const int ns = (n + 1) & ~1, ms = ns;
+    const int stage_d = fwd_time_stage_doubles<SPS>(m, ns);
+    double* Xb = W.X + (size_t)b * H * ns;
+    double* Ub = W.U + (size_t)b * (H - 1) * ms;
+    const double* Kb = W.K + (size_t)b * (H - 1) * m * ns;
+    const double* db = W.d + (size_t)b * (H - 1) * ms;
+    // the accepted trajectory is staged in this problem's slice of the candidate-control scratch: U' [H-1][ms], then X'_1.. [H-1][ns]
+    // (written in place it would race with the bulk copies of the steps ahead, which must still see the old X and U)
+    double* Us = W.Uc + (size_t)b * (H - 1) * NCAND * ms;
+    double* Xs = Us + (size_t)(H - 1) * ms;
+    const bool slow_limits = s_lim == nullptr && P.any_limits;  // several limit-carrying sub-systems: the full cost at every step
+
+    // steps 0 .. H-1: step H-1 is the final cost only (no control, no copies)
+    const int n_stages = (H + SPS - 1) / SPS;
+    int issued = 0, waited = 0;  // stages issued / consumed since the barriers were initialised (both passes share the ring)
+    auto issue = [&](int q) {    // lane 0 only: stage q of the horizon into the next slot
+        const int slot = issued % RING, k0 = q * SPS;
+        const int steps = (H - 1 - k0) < SPS ? (H - 1 - k0) : SPS;
+        double* sK = ring + (size_t)slot * stage_d;
+        double* sd = sK + SPS * m * ns;
+        double* sx = sd + SPS * ms;
+        double* su = sx + SPS * ns;
+        if (steps <= 0) {  // the stage of the final cost alone: the phase completes with this arrival
+            mbar_expect_tx(&bars[slot], 0u);
+            return;
+        }
+        const unsigned bK = (unsigned)(steps * m * ns * 8), bv = (unsigned)(steps * ns * 8);
+        mbar_expect_tx(&bars[slot], bK + 3 * bv);
+        bulk_g2s(sK, Kb + (size_t)k0 * m * ns, bK, &bars[slot]);
+        bulk_g2s(sd, db + (size_t)k0 * ms, bv, &bars[slot]);
+        bulk_g2s(sx, Xb + (size_t)k0 * ns, bv, &bars[slot]);
+        bulk_g2s(su, Ub + (size_t)k0 * ms, bv, &bars[slot]);
+    };
+    if (lane == 0) {
+        for (int s = 0; s < RING; s++) mbar_init(&bars[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+
+    const double cost0 = W.cost0[b];
+    double alpha = alpha_of(lane < NCAND ? lane : 0);
+    bool active = lane < NCAND && (line_search || lane == 0);
+    double newCost = 0.0, dun_sel = 0.0;
+    // pass 0: lane c rolls out the candidate of step length 2^-c (ILQRRecursive.cpp:124-154) ; pass 1: lane 0 rolls the chosen one
+    // out again — same code, same alpha, same numbers — and stores it
+    for (int pass = 0; pass < 2; pass++) {
+        const bool write = pass == 1;
+        double x[N];
+        load_x0<N>(P, b, x);
+        double cost = 0.0, dun = 0.0;
+        int skp = 0;
+        int next_kp = S > 0 ? P.kp_steps[0] : -1;
+        if (lane == 0) {
+            for (int q = 0; q < RING && q < n_stages; q++) {
+                issue(q);
+                issued++;
+            }
+        }
+        issued = __shfl_sync(FULL, issued, 0);
+        for (int q = 0; q < n_stages; q++) {
+            const int slot = waited % RING, k0 = q * SPS;
+            const double* sK = ring + (size_t)slot * stage_d;
+            const double* sd = sK + SPS * m * ns;
+            const double* sx = sd + SPS * ms;
+            const double* su = sx + SPS * ns;
+            mbar_wait(&bars[slot], (unsigned)((waited / RING) & 1));
+            waited++;
+#pragma unroll
+            for (int j = 0; j < SPS; j++) {
+                const int k = k0 + j;
+                const bool last = k == H - 1;
+                if (k < H && active) {
+                    double u[N];
+                    if (!last) {
+                        const double* Kk = sK + (size_t)j * m * ns;
+                        double dx[N];
+#pragma unroll
+                        for (int c = 0; c < N; c++) dx[c] = (c < n) ? __dsub_rn(x[c], sx[j * ns + c]) : 0.0;
+                        double nrm2 = 0.0;
+#pragma unroll
+                        for (int i = 0; i < N; i++) {
+                            u[i] = 0.0;
+                            if (i < m) {
+                                double acc = 0.0;
+#pragma unroll
+                                for (int c = 0; c < N; c += 2) {  // ns is even and the pad column of K holds zeros
+                                    if (c < ns) {
+                                        const double2 kk = *reinterpret_cast<const double2*>(Kk + i * ns + c);
+                                        acc += kk.x * dx[c];
+                                        acc += kk.y * dx[c + 1];
+                                    }
+                                }
+                                const double du = acc + alpha * sd[j * ms + i];
+                                nrm2 += du * du;
+                                u[i] = su[j * ms + i] + du;
+                            }
+                        }
+                        dun += sqrt(nrm2);
+                    }
+                    // cost of (x, u) at step k: task terms at the keypoint steps, limit terms where a limit is violated, the final cost
+                    bool need = (k == next_kp) || slow_limits || last;
+                    if (s_lim) {
+#pragma unroll
+                        for (int c = 0; c < N; c++)
+                            if (c < n) need = need || (x[c] > s_lim[c]) || (x[c] < s_lim[8 + c]);
+                    }
+                    if (need) cost += lean_stage_cost<N>(P, b, x, last ? nullptr : u, k);
+                    if (!last) {
+                        if (write) {
+#pragma unroll
+                            for (int i = 0; i < N; i += 2)
+                                if (i < ms) *reinterpret_cast<double2*>(Us + (size_t)k * ms + i) = make_double2(u[i], u[i + 1]);
+                        }
+                        step_state<N>(P, x, u);
+                        if (write) {
+#pragma unroll
+                            for (int c = 0; c < N; c += 2)
+                                if (c < ns) *reinterpret_cast<double2*>(Xs + (size_t)k * ns + c) = make_double2(x[c], x[c + 1]);
+                        }
+                    }
+                }
+                if (k == next_kp) {
+                    skp++;
+                    next_kp = skp < S ? P.kp_steps[skp] : -1;
+                }
+            }
+            __syncwarp();  // every lane is done with the slot before the copy engine refills it
+            if (lane == 0 && q + RING < n_stages) {
+                issue(q + RING);
+                issued++;
+            }
+            issued = __shfl_sync(FULL, issued, 0);
+        }
+        if (pass == 0) {
+            // the reference's do/while (ILQRRecursive.cpp:107-155): first alpha in 1, 1/2, .. whose cost is not (>= cost0 or NaN);
+            // alpha = 2^-10 is taken unconditionally (Q2)
+            int sel = 0;
+            if (line_search) {
+                const unsigned ok = __ballot_sync(FULL, active && !((cost >= cost0) || isnan(cost)));
+                sel = ok ? __ffs(ok) - 1 : NCAND - 1;
+            }
+            newCost = __shfl_sync(FULL, cost, sel);
+            dun_sel = __shfl_sync(FULL, dun, sel);
+            alpha = alpha_of(sel);
+            active = lane == 0;
+        }
+    }
+    __syncwarp();
+    // the staged trajectory becomes the current one (X_0 is the fixed initial state)
+    for (int e = lane; e < (H - 1) * ms; e += 32) Ub[e] = Us[e];
+    for (int e = lane; e < (H - 1) * ns; e += 32) Xb[ns + e] = Xs[e];
+    if (lane == 0) {
+        W.cost0[b] = newCost;
+        W.cost_hist[(size_t)b * nb_iter + it] = newCost;
+        W.alpha_hist[(size_t)b * nb_iter + it] = alpha;
+        W.alpha_last[b] = alpha;
+        W.iters[b] = it + 1;
+        int st = W.status[b];
+        if (isnan(newCost)) st |= ILQRB_ST_NAN_COST;
+        const bool stop = early_stop && (alpha * sqrt(dun_sel) < 1e-3) && (newCost < 1e-3);
+        if (stop) {
+            st |= ILQRB_ST_EARLY_STOP;
+            W.done[b] = 1;
+        }
+        W.status[b] = st;
+    }
+}
+
+template <int DOF, int RING, int SPS, int WARPS, int MINB>
+__global__ void __launch_bounds__(32 * WARPS, MINB) k_forward_time(const DevProblem* __restrict__ Pp, Work W, int b0, int nB, int it, int nb_iter, int line_search,
+                                                                   int early_stop) {
+    extern __shared__ __align__(128) unsigned char fwd_smem[];
+    const DevProblem& P = *Pp;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int d = DOF > 0 ? DOF : P.dof, n = d + 1, ns = (n + 1) & ~1;
+    // limits of the single limit-carrying sub-system, shared by the block: [0..7] max, [8..15] min (weight 0 -> +-inf)
+    double* s_lim = reinterpret_cast<double*>(fwd_smem);
+    int l0 = -1, nl = 0;
+    if (P.any_limits)
+        for (int ti = 0; ti < P.n_tasks; ti++)
+            if (P.tasks[ti].limits_set) {
+                if (l0 < 0) l0 = ti;
+                nl++;
+            }
+    if (threadIdx.x < 16) {
+        const int c = threadIdx.x & 7;
+        double v = threadIdx.x < 8 ? INFINITY : -INFINITY;
+        if (l0 >= 0 && c < n && P.tasks[l0].limit_weight[c] != 0) v = threadIdx.x < 8 ? P.tasks[l0].state_max[c] : P.tasks[l0].state_min[c];
+        s_lim[threadIdx.x] = v;
+    }
+    __syncthreads();
+    const int bl = blockIdx.x * WARPS + wid;
+    if (bl >= nB) return;
+    const int b = b0 + bl;
+    if (W.done[b]) return;
+    unsigned char* mine = fwd_smem + 128 + (size_t)wid * fwd_time_warp_bytes<RING, SPS>(n, ns);
+    double* ring = reinterpret_cast<double*>(mine);
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(mine + (size_t)RING * fwd_time_stage_doubles<SPS>(n, ns) * 8);
+    forward_time_body<DOF, RING, SPS>(P, W, b, lane, ring, bars, nl == 1 ? s_lim : nullptr, it, nb_iter, line_search, early_stop);
+}
+
+}  // namespace ilqrb

@@ -148,6 +148,10 @@ int launch_rollout_jac(ilqrb_handle h, double* Jout);
 int launch_kinematics(ilqrb_handle h, int robot, int nq, const double* q, const double* dq, double* x, double* quat, double* J, double* dx, double* w);
 bool generic_forced();  // ILQRB_GENERIC set: A/B switch for tests and profiling
 
+// ---- launch_time.cu -------------------------------------------------------------------------------------------------
+bool fast_time_applies(ilqrb_handle h, bool al);
+int launch_backward_time(ilqrb_handle h, int b0, int nB, cudaStream_t st);
+int launch_forward_time(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop);
 // ---- launch_fused1.cu -----------------------------------------------------------------------------------------------
 bool fast_n1_applies(ilqrb_handle h, bool al);
 int fast_n1_wave(ilqrb_handle h);  // problems one full wave of the forward kernel holds

@@ -326,6 +326,17 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
         h->last_solver = 1;
         return 0;
     }
+    if (fast_time_applies(h, al != nullptr)) {
+        // first-order time systems: keypoint derivatives, fused backward pass, fused line search + accept (fused_time.cuh)
+        for (int it = 0; it < opts->nb_iter; it++) {
+            if ((rc = launch_derivs(h))) return rc;
+            if ((rc = launch_backward_time(h, 0, B, h->stream))) return rc;
+            if ((rc = launch_forward_time(h, 0, B, h->stream, it, std::max(opts->nb_iter, 1), opts->line_search, opts->early_stop))) return rc;
+        }
+        h->last_nb_iter = opts->nb_iter;
+        h->last_solver = 1;
+        return 0;
+    }
     for (int it = 0; it < opts->nb_iter; it++) {
         if ((rc = launch_derivs(h))) return rc;
         if ((rc = fast_n2_applies(h, al != nullptr) ? launch_backward_n2(h, al != nullptr, pen_frozen) : launch_backward_generic(h, al != nullptr, pen_frozen))) return rc;

@@ -157,6 +157,31 @@ def config4(batch=8192, horizon=200, offset=0):
     return ProblemBatch(cabi.SYS_POS_ORN_TIME, 1, horizon, 0.0, 7, [RobotSpec(cabi.ROBOT_KDL, 7, segs)], [task], R, q0, np.zeros_like(q0))
 
 
+def config4_short(batch=16, horizon=60, dof=5, offset=0, tight_limits=True, two_tasks=False):
+    """parity-test shape of the time-system fast path: the first `dof` joints of the chain, PosOrnTime nb_deriv=1, soft joint limits
+    tight enough to be violated along the way; two_tasks: a second sub-system (its own keypoint, limits of its own) on the same chain"""
+    segs = _truncated_chain(dof)
+    d = _draws(11, offset, offset + batch, [("q0", -0.4, 0.4, dof), ("t1", -0.6, 0.6, dof), ("t2", -0.6, 0.6, dof), ("t3", -0.5, 0.5, dof)])
+    q0 = PANDA_Q0[:dof] + d["q0"]
+    tg = _posorn_targets(segs, q0, [d["t1"], d["t2"]])
+    tg[:, 0, 14] = 1.5
+    tg[:, 1, 14] = 3.5
+    Q = np.diag([1, 1, 1, .1, .1, .1, .1])
+    R = np.ones(dof + 1) * 1e-5
+    span = 0.3 if tight_limits else 30.0
+    smax = np.concatenate([PANDA_Q0[:dof] + 0.4 + span, [0.0]])
+    smin = np.concatenate([PANDA_Q0[:dof] - 0.4 - span, [0.0]])
+    w = np.array([1] * dof + [0], dtype=np.int32)
+    tasks = [TaskSpec(kp_timestep=[horizon // 2 - 1, horizon - 1], kp_target=tg, kp_precision=np.array([[Q, Q]]), r_diag=R, state_max=smax, state_min=smin,
+                      limit_weight=w)]
+    if two_tasks:
+        tg2 = _posorn_targets(segs, q0, [d["t3"]])
+        tg2[:, 0, 14] = 0.8
+        tasks.append(TaskSpec(kp_timestep=[horizon // 4], kp_target=tg2, kp_precision=np.array([[Q]]), r_diag=R, state_max=smax - 0.3, state_min=smin + 0.3,
+                              limit_weight=w))
+    return ProblemBatch(cabi.SYS_POS_ORN_TIME, 1, horizon, 0.0, dof, [RobotSpec(cabi.ROBOT_KDL, dof, segs)], tasks, R, q0, np.zeros_like(q0))
+
+
 def u0_time(pb):
     """time systems start from s = 0.01 (POS_ORN_TIME_SYS cell 8)"""
     u = np.zeros((pb.batch, pb.horizon - 1, pb.m))

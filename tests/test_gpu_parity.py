@@ -382,6 +382,59 @@ def _check_batch(pb, u0, nb_iter, oracle, psi=None, early_stop=False):
     return out, ref
 
 
+@pytest.mark.parametrize("case", ["full_horizon", "early_stop", "no_line_search", "five_joints_tight_limits", "two_sub_systems"])
+def test_time_system_fast_path_vs_oracle(oracle_lib, case):
+    """fused_time.cuh (k_backward_time / k_forward_time): compile-time and runtime joint counts, joint limits that are violated along
+    the way (limit terms of the line search and of the backward pass), two limit-carrying sub-systems (the slow limit loops)"""
+    from ilqr_planner_b200 import synth
+    if case == "five_joints_tight_limits":
+        pb = synth.config4_short(batch=16)
+    elif case == "two_sub_systems":
+        pb = synth.config4_short(batch=12, dof=6, two_tasks=True)
+    else:
+        pb = synth.config4(batch=24, horizon=100)
+    u0 = synth.u0_time(pb)
+    if case == "early_stop":
+        _check_recursive(pb, u0, 25, oracle_lib, early_stop=True, min_tie_free=0.25)
+    elif case == "no_line_search":
+        from ilqr_planner_b200.solver import Handle
+        from oracle import oracle
+        with Handle(pb) as h:
+            out = h.solve_recursive(u0, 3, False, False)
+        ref = oracle.solve_recursive(pb, u0, 3, False, False, threads=8)
+        assert np.all(out.alpha_hist == 1.0) and np.all(ref.alpha_hist == 1.0)
+        ok = np.isfinite(ref.cost_hist[:, -1])
+        assert rel(out.cost_hist[ok], ref.cost_hist[ok], floor=0.0) < 1e-6 and rel(out.X[ok], ref.X[ok]) < 1e-6
+    else:
+        _check_recursive(pb, u0, 8, oracle_lib, min_tie_free=0.25)
+
+
+def test_time_system_fast_path_equals_generic_path():
+    """the same time-system solve under ILQRB_NO_FAST_TIME=1 (generic k_backward<.., TIME> + k_linesearch + k_accept): both GPU paths
+    must agree with each other as closely as each agrees with the oracle"""
+    code = (
+        "import numpy as np\n"
+        "from ilqr_planner_b200 import synth\n"
+        "from ilqr_planner_b200.solver import Handle\n"
+        "pb = synth.config4(batch=32, horizon=100)\n"
+        "with Handle(pb, device=0) as h:\n"
+        "    out = h.solve_recursive(synth.u0_time(pb), 8, True, False)\n"
+        "    prof = h.launch_count()\n"
+        "np.savez(%r, cost_hist=out.cost_hist, alpha_hist=out.alpha_hist, X=out.X, U=out.U, K=out.K, launches=prof)\n")
+    import os
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        fa, fb = os.path.join(td, "fast.npz"), os.path.join(td, "generic.npz")
+        _subprocess_case(code % fa, {})
+        _subprocess_case(code % fb, {"ILQRB_NO_FAST_TIME": "1"})
+        a, b = np.load(fa), np.load(fb)
+        assert int(a["launches"]) < int(b["launches"]), "the fast path launches 3 kernels per iteration, the generic one 4"
+        same = pt.same_sequence(a["alpha_hist"], b["alpha_hist"])
+        assert same.sum() >= 16, "the two GPU paths choose different steps in %d of 32 problems" % (~same).sum()
+        assert rel(a["cost_hist"][same], b["cost_hist"][same], floor=0.0) < 1e-5
+        assert rel(a["X"][same], b["X"][same]) < 1e-4
+
+
 def test_batch_ilqr_time_system_vs_oracle(oracle_lib):
     """C4 shape at a size the oracle finishes in seconds: PosOrnTime, N = 8 * 39 = 312"""
     from ilqr_planner_b200 import synth
