@@ -381,8 +381,15 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
         // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]                                            ILQRRecursive.cpp:89-91
         double Kd[NT][NT][2];
         if constexpr (NT == 1) {  // explicit inverse, then the product on DMMA
-            spd = gj_inverse_regs<NT, DOF, LD>(Inv, sKd, m, g, t) && spd;
+            const bool okk = __all_sync(0xffffffffu, gj_inverse_regs<NT, DOF, LD>(Inv, sKd, m, g, t));
+            if (!okk) {  // a pivot was not positive: Quu + 1e-6 I again, for the reference's pivoted LU inverse (rare)
+                spd = false;
+                const int j = 2 * t;
+                Inv[0][0][0] = Quu[0][0][0] + ((g == j) ? ((g < m) ? 1e-6 * 1.0 : 1.0) : 0.0);
+                Inv[0][0][1] = Quu[0][0][1] + ((g == j + 1) ? ((g < m) ? 1e-6 * 1.0 : 1.0) : 0.0);
+            }
             st_c<NT, LD>(sM, Inv, g, t);
+            if (!okk) wm_inverse_pivoted(sM, LD, m, sKd, lane);
             __syncwarp();
             double c0 = 0.0, c1 = 0.0;
 #pragma unroll
@@ -397,7 +404,30 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
                     Kd[rt][ct][0] = -Qa[rt][ct][0];
                     Kd[rt][ct][1] = -Qa[rt][ct][1];
                 }
-            spd = gj_solve_regs<NT, DOF>(Inv, Kd, m, g, t) && spd;
+            if (!__all_sync(0xffffffffu, gj_solve_regs<NT, DOF>(Inv, Kd, m, g, t))) {
+                // a pivot was not positive: the reference's pivoted LU inverse of Quu + 1e-6 I, then the product (rare, plain loops)
+                spd = false;
+                __syncwarp();
+                for (int e = lane; e < 8 * NT * 8 * NT; e += 32) {
+                    const int i = e / (8 * NT), j = e % (8 * NT);
+                    double v = sQuu[i * LD + j];
+                    if (i == j) v = (i < m) ? v + 1e-6 * 1.0 : 1.0;
+                    sM[i * LD + j] = v;
+                }
+                wm_inverse_pivoted(sM, LD, m, sKd, lane);
+#pragma unroll
+                for (int rt = 0; rt < NT; rt++)
+#pragma unroll
+                    for (int ct = 0; ct < NT; ct++)
+#pragma unroll
+                        for (int h = 0; h < 2; h++) {
+                            const int i = 8 * rt + g, j = 8 * ct + 2 * t + h;
+                            double acc = 0.0;
+                            for (int l = 0; l < m; l++) acc += sM[i * LD + l] * sQux[l * LD + j];
+                            Kd[rt][ct][h] = (i < m) ? -acc : 0.0;
+                        }
+                __syncwarp();
+            }
         }
         st_c<NT, LD>(sKd, Kd, g, t);
         // stream K, d to global (time-forward index)

@@ -195,9 +195,15 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
         // area), then the product on DMMA                                                ILQRRecursive.cpp:89-91
         st_w(sM, Qa, g, t);
         double Iv[1][1][2] = {{{Lr[0], Lr[1]}}};
-        spd = gj_inverse_regs<1, DOF, S::LDW>(Iv, sKd, m, g, t) && spd;
+        const bool okk = __all_sync(0xffffffffu, gj_inverse_regs<1, DOF, S::LDW>(Iv, sKd, m, g, t));
+        if (!okk) {  // a pivot was not positive: Quu + 1e-6 I again, for the reference's pivoted LU inverse (rare)
+            spd = false;
+            Iv[0][0][0] = Lr[0];
+            Iv[0][0][1] = Lr[1];
+        }
         *reinterpret_cast<double2*>(sInv + g * S::LDQ + 2 * t) = make_double2(Iv[0][0][0], Iv[0][0][1]);
         *reinterpret_cast<double2*>(sQuu + g * S::LDQ + 2 * t) = make_double2(Quu[0], Quu[1]);  // un-regularised, for the P update
+        if (!okk) wm_inverse_pivoted(sInv, S::LDQ, m, sKd, lane);
         __syncwarp();
         double Kd[2][2];
         {

@@ -184,8 +184,14 @@ __device__ __forceinline__ void backward_time_body(const DevProblem& P, const Wo
             st_c2(sQuu, QQ, g, t);
         }
         // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]                                            ILQRRecursive.cpp:89-91
-        spd = gj_inverse_regs<1, (DOF > 0 ? DOF + 1 : 0), LD>(Inv, sKd, m, g, t) && spd;
+        const bool okk = __all_sync(FULL, gj_inverse_regs<1, (DOF > 0 ? DOF + 1 : 0), LD>(Inv, sKd, m, g, t));
+        if (!okk) {  // a pivot was not positive: Quu + 1e-6 I again, for the reference's pivoted LU inverse (rare)
+            spd = false;
+            Inv[0][0][0] = (g == j0) ? ((g < m) ? Quu[0] + 1e-6 * 1.0 : 1.0) : Quu[0];
+            Inv[0][0][1] = (g == j1) ? ((g < m) ? Quu[1] + 1e-6 * 1.0 : 1.0) : Quu[1];
+        }
         *reinterpret_cast<double2*>(sM + g * LD + 2 * t) = make_double2(Inv[0][0][0], Inv[0][0][1]);
+        if (!okk) wm_inverse_pivoted(sM, LD, m, sKd, lane);
         __syncwarp();
         double Kd[2][2];
 #pragma unroll
@@ -263,6 +269,10 @@ template <int RING, int SPS>
 __host__ __device__ inline size_t fwd_time_warp_bytes(int m, int ns) {
     return ((size_t)RING * fwd_time_stage_doubles<SPS>(m, ns) * 8 + RING * 8 + 127) / 128 * 128;
 }
+
+// System::cost at one step, out of line: the kinematics want ~100 registers and index their arguments at run time; as a call they
+// leave the step loop of the rollout its own register allocation (x, u, dx stay in registers there)
+static __device__ __noinline__ double time_stage_cost(const DevProblem& P, int b, const double* x, const double* u, int k) { return lean_stage_cost<8>(P, b, x, u, k); }
 
 template <int DOF, int RING, int SPS>
 __device__ __forceinline__ void forward_time_body(const DevProblem& P, const Work& W, int b, int lane, double* ring, unsigned long long* bars, const double* s_lim, int it,
@@ -343,6 +353,8 @@ __device__ __forceinline__ void forward_time_body(const DevProblem& P, const Wor
                 const bool last = k == H - 1;
                 if (k < H && active) {
                     double u[N];
+#pragma unroll
+                    for (int i = 0; i < N; i++) u[i] = 0.0;
                     if (!last) {
                         const double* Kk = sK + (size_t)j * m * ns;
                         double dx[N];
@@ -370,20 +382,41 @@ __device__ __forceinline__ void forward_time_body(const DevProblem& P, const Wor
                         dun += sqrt(nrm2);
                     }
                     // cost of (x, u) at step k: task terms at the keypoint steps, limit terms where a limit is violated, the final cost
-                    bool need = (k == next_kp) || slow_limits || last;
-                    if (s_lim) {
+                    bool need = !write && ((k == next_kp) || slow_limits || last);  // the accept pass keeps the cost of the candidate pass
+                    if (s_lim && !write) {
 #pragma unroll
                         for (int c = 0; c < N; c++)
                             if (c < n) need = need || (x[c] > s_lim[c]) || (x[c] < s_lim[8 + c]);
                     }
-                    if (need) cost += lean_stage_cost<N>(P, b, x, last ? nullptr : u, k);
+                    if (need) {
+                        // the kinematics index their arguments at run time: they get copies, so that x and u of the step loop stay
+                        // in registers (every index into them is a compile-time constant)
+                        double xc[N], uc[N];
+#pragma unroll
+                        for (int c = 0; c < N; c++) {
+                            xc[c] = x[c];
+                            uc[c] = last ? 0.0 : u[c];
+                        }
+                        cost += time_stage_cost(P, b, xc, last ? nullptr : uc, k);
+                    }
                     if (!last) {
                         if (write) {
 #pragma unroll
                             for (int i = 0; i < N; i += 2)
                                 if (i < ms) *reinterpret_cast<double2*>(Us + (size_t)k * ms + i) = make_double2(u[i], u[i + 1]);
                         }
-                        step_state<N>(P, x, u);
+                        // one integrator step with the reference's operation order and no FMA contraction (step_state, work.cuh):
+                        // dt = s^2 ; q += dt dq + dt^2/2 * 0 ; t += dt                       SimulationInterface.cpp:19-31
+                        double sq = 0.0;
+#pragma unroll
+                        for (int c = 0; c < N; c++)
+                            if (c == d) sq = u[c];
+                        const double dts = __dmul_rn(sq, sq), hdt2 = __dmul_rn(dts, dts) / 2;
+#pragma unroll
+                        for (int c = 0; c < N; c++) {
+                            if (c < d) x[c] = __dadd_rn(x[c], __dadd_rn(__dmul_rn(dts, u[c]), __dmul_rn(hdt2, 0.0)));
+                            else if (c == d) x[c] = __dadd_rn(x[c], dts);
+                        }
                         if (write) {
 #pragma unroll
                             for (int c = 0; c < N; c += 2)

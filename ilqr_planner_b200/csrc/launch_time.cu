@@ -54,8 +54,20 @@ int launch_backward_time(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
 
 int launch_forward_time(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop) {
     h->begin(PS_LINESEARCH);
-    int rc = h->hp.dof == 7 ? launch_forward_time_t<7, 3, 2, 4, 4>(h, b0, nB, st, it, nb_iter, line_search, early_stop)
-                            : launch_forward_time_t<0, 3, 2, 4, 4>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+    // ring shape <RING, SPS>: stages in flight x steps per stage (4 bulk copies per stage); ILQRB_TIME_FWD picks another for sweeps
+    static const int variant = getenv("ILQRB_TIME_FWD") ? atoi(getenv("ILQRB_TIME_FWD")) : 0;
+    int rc;
+#define FWD(RING, SPS, WARPS, MINB)                                                                                             \
+    (h->hp.dof == 7 ? launch_forward_time_t<7, RING, SPS, WARPS, MINB>(h, b0, nB, st, it, nb_iter, line_search, early_stop) \
+                    : launch_forward_time_t<0, RING, SPS, WARPS, MINB>(h, b0, nB, st, it, nb_iter, line_search, early_stop))
+    switch (variant) {
+        case 1: rc = FWD(3, 2, 4, 4); break;
+        case 2: rc = FWD(2, 4, 4, 4); break;
+        case 3: rc = FWD(3, 4, 4, 4); break;
+        case 4: rc = FWD(2, 16, 4, 3); break;
+        default: rc = FWD(2, 8, 4, 4); break;
+    }
+#undef FWD
     h->end();
     if (rc) return rc;
     CU(cudaGetLastError());

@@ -170,7 +170,7 @@ inline py::dict view_dict(const solver::BatchView& v, const std::shared_ptr<void
     d["iters"] = py::array_t<int32_t>(std::vector<ssize_t>{B}, v.iters, base);
     d["status"] = py::array_t<int32_t>(std::vector<ssize_t>{B}, v.status, base);
     if (v.anyQuuNotSpd())
-        PyErr_WarnEx(PyExc_RuntimeWarning, "Quu was not positive definite in some problems (status & ILQRB_ST_QUU_NOT_SPD): those results are not minimisers", 1);
+        PyErr_WarnEx(PyExc_RuntimeWarning, "Quu + 1e-6 I was not positive definite in some problems (status & ILQRB_ST_QUU_NOT_SPD): those steps used the pivoted LU inverse, as the reference does", 1);
     return d;
 }
 
@@ -203,7 +203,7 @@ inline py::dict result_dict(const solver::BatchResult& r, bool batch_solver) {
     d["status"] = status;
     for (int32_t st : r.status)
         if (st & ILQRB_ST_QUU_NOT_SPD) {
-            PyErr_WarnEx(PyExc_RuntimeWarning, "Quu was not positive definite in some problems (status & ILQRB_ST_QUU_NOT_SPD): those results are not minimisers", 1);
+            PyErr_WarnEx(PyExc_RuntimeWarning, "Quu + 1e-6 I was not positive definite in some problems (status & ILQRB_ST_QUU_NOT_SPD): those steps used the pivoted LU inverse, as the reference does", 1);
             break;
         }
     return d;

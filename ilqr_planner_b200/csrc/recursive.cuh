@@ -831,7 +831,16 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward(const DevProblem*
             Inv[e] = v;
         }
         __syncwarp();
-        spd = wm_inverse_spd<NUT>(Inv, LDU, m, lane) && spd;
+        if (!wm_inverse_spd<NUT>(Inv, LDU, m, lane)) {  // a pivot was not positive: the reference's pivoted LU inverse (rare)
+            spd = false;
+            for (int e = lane; e < NU * LDU; e += 32) {
+                const int i = e / LDU, j = e % LDU;
+                double v = Quu[e];
+                if (i == j) v = (i < m) ? v + 1e-6 * 1.0 : 1.0;
+                Inv[e] = v;
+            }
+            wm_inverse_pivoted(Inv, LDU, m, Kd, lane);
+        }
         // [K|d] = -(Inv [Qux|Qu])          ILQRRecursive.cpp:90-91
         wm_gemm<NUT, NXT, NUT, false, false, false, true>(Kd, LDX, Inv, LDU, QuxQu, LDX, lane);
         // stream K, d to global (time-forward index)

@@ -127,4 +127,65 @@ __device__ __forceinline__ bool wm_inverse_spd(double* M, int ld, int m, int lan
     return ok;
 }
 
+// Rare path: in-place inverse of the leading m x m block of a shared-memory matrix WITH partial pivoting — what the reference
+// computes at ILQRRecursive.cpp:89 / AL-ILQR.cpp:136 (Eigen's PartialPivLU(m).inverse()): unblocked right-looking LU, the first
+// maximum of |a_ik| as pivot, then unit-lower forward and upper backward substitution on P I.  Taken when the unpivoted
+// elimination of the fast kernels met a pivot that was not positive (Quu + 1e-6 I indefinite or nearly singular), so that such a
+// step returns the reference's answer instead of an unpivoted one.  Lane 0 works, the warp waits; X: m x ld scratch.
+// Rows / columns >= m are left untouched.
+static __device__ __noinline__ void wm_inverse_pivoted(double* M, int ld, int m, double* X, int lane) {
+    __syncwarp();
+    if (lane == 0) {
+        int perm[16];
+        for (int i = 0; i < m; i++) perm[i] = i;
+        for (int k = 0; k < m; k++) {
+            int piv = k;
+            double best = fabs(M[k * ld + k]);
+            for (int i = k + 1; i < m; i++) {
+                const double v = fabs(M[i * ld + k]);
+                if (v > best) {
+                    best = v;
+                    piv = i;
+                }
+            }
+            if (piv != k) {
+                for (int j = 0; j < m; j++) {
+                    const double tmp = M[k * ld + j];
+                    M[k * ld + j] = M[piv * ld + j];
+                    M[piv * ld + j] = tmp;
+                }
+                const int tp = perm[k];
+                perm[k] = perm[piv];
+                perm[piv] = tp;
+            }
+            const double pk = M[k * ld + k];
+            for (int i = k + 1; i < m; i++) M[i * ld + k] /= pk;
+            for (int i = k + 1; i < m; i++) {
+                const double lik = M[i * ld + k];
+                for (int j = k + 1; j < m; j++) M[i * ld + j] -= lik * M[k * ld + j];
+            }
+        }
+        for (int i = 0; i < m; i++)
+            for (int j = 0; j < m; j++) X[i * ld + j] = (perm[i] == j) ? 1.0 : 0.0;  // P I
+        for (int i = 0; i < m; i++)  // L y = P I (unit diagonal)
+            for (int k = 0; k < i; k++) {
+                const double lik = M[i * ld + k];
+                if (lik == 0.0) continue;
+                for (int j = 0; j < m; j++) X[i * ld + j] -= lik * X[k * ld + j];
+            }
+        for (int i = m - 1; i >= 0; i--) {  // U x = y
+            for (int k = i + 1; k < m; k++) {
+                const double uik = M[i * ld + k];
+                if (uik == 0.0) continue;
+                for (int j = 0; j < m; j++) X[i * ld + j] -= uik * X[k * ld + j];
+            }
+            const double uii = M[i * ld + i];
+            for (int j = 0; j < m; j++) X[i * ld + j] /= uii;
+        }
+        for (int i = 0; i < m; i++)
+            for (int j = 0; j < m; j++) M[i * ld + j] = X[i * ld + j];
+    }
+    __syncwarp();
+}
+
 }  // namespace ilqrb

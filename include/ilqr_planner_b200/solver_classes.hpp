@@ -14,16 +14,15 @@ inline void report(CallBackMessage* cb, const BatchResult& r, bool with_time, do
         detail::emit(cb, line);
     }
 }
-// ILQRB_ST_QUU_NOT_SPD of any problem: the backward pass met a control Hessian that is not positive definite and the result
-// is not a minimiser's; the reference inverts such a Quu silently (ILQRRecursive.cpp:97), here it is said once per solve
-inline void warn_status(CallBackMessage* cb, const int32_t* status, int B) {
+// ILQRB_ST_QUU_NOT_SPD of any problem: the backward pass met a control Hessian that is not positive definite (the step taken then
+// is not a descent step of a convex model); the reference inverts such a Quu silently (ILQRRecursive.cpp:89), here it is said once per solve
+inline void warn_status(const int32_t* status, int B) {
     int bad = 0;
     for (int b = 0; b < B; b++) bad += (status[b] & ILQRB_ST_QUU_NOT_SPD) ? 1 : 0;
-    if (bad) {
-        const std::string line = "[ilqr_planner_b200] warning: Quu was not positive definite in " + std::to_string(bad) + " of " + std::to_string(B) + " problems (ILQRB_ST_QUU_NOT_SPD)";
-        if (cb) cb->notify(line);
-        else std::cerr << line << std::endl;
-    }
+    // to stderr, never through the callback: the callback carries the reference's per-iteration lines and nothing else
+    if (bad)
+        std::cerr << "[ilqr_planner_b200] note: Quu + 1e-6 I was not positive definite in " << bad << " of " << B
+                  << " problems (ILQRB_ST_QUU_NOT_SPD): those steps used the pivoted LU inverse, as the reference does" << std::endl;
 }
 inline double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 }  // namespace detail_solver
@@ -38,7 +37,7 @@ public:
         const double t0 = detail_solver::now();
         BatchResult r = solveBatch({s}, {U0}, nb_iter, line_search, early_stop);
         detail_solver::report(cb, r, true, detail_solver::now() - t0);
-        detail_solver::warn_status(cb, r.status.data(), r.B);
+        detail_solver::warn_status(r.status.data(), r.B);
         const int H = r.H, n = r.n, m = r.m;
         std::vector<MatrixXd> Ks;
         for (int k = 0; k < H - 1; k++) Ks.push_back(detail::from_row_major(r.K.data() + size_t(k) * m * n, m, n));
@@ -100,7 +99,7 @@ public:
         const double t0 = detail_solver::now();
         BatchResult r = solveBatch({s}, {U0}, nb_iter, lag_update_step, penalty, scaling_factor, line_search, early_stop);
         detail_solver::report(cb, r, true, detail_solver::now() - t0);
-        detail_solver::warn_status(cb, r.status.data(), r.B);
+        detail_solver::warn_status(r.status.data(), r.B);
         multipliers = detail_solver::rows(r.lambda, 0, r.H - 1, r.nc);  // the reference keeps the updated multipliers in the solver
         return std::make_tuple(detail_solver::rows(r.X, 0, r.H, r.n), detail_solver::rows(r.fX, 0, r.H, r.nt), detail_solver::rows(r.U, 0, r.H - 1, r.m));
     }

@@ -71,7 +71,7 @@ extern "C" {
 
 /* per-problem status bits in ilqrb_result.status */
 #define ILQRB_ST_NAN_COST 1       /* a candidate or accepted cost was NaN          */
-#define ILQRB_ST_QUU_NOT_SPD 2    /* Cholesky fast path hit a non-positive pivot    */
+#define ILQRB_ST_QUU_NOT_SPD 2    /* Quu + 1e-6 I had a non-positive pivot: that step used the pivoted LU inverse (ILQRRecursive.cpp:89) */
 #define ILQRB_ST_EARLY_STOP 4     /* stopped by the early-stop rule                 */
 
 /* One KDL chain segment = KDL::Segment(joint, f_tip) as built by

@@ -409,6 +409,38 @@ def test_time_system_fast_path_vs_oracle(oracle_lib, case):
         _check_recursive(pb, u0, 8, oracle_lib, min_tie_free=0.25)
 
 
+@pytest.mark.parametrize("case", ["single_integrator", "double_integrator", "time_system"])
+def test_indefinite_quu_takes_the_pivoted_inverse(oracle_lib, case):
+    """a keypoint with a NEGATIVE precision repels: the control Hessian Quu + 1e-6 I turns indefinite, the unpivoted elimination of the
+    backward kernels meets a non-positive pivot, and the step is redone with the partial-pivot LU inverse the reference uses
+    (ILQRRecursive.cpp:89; wmat.cuh wm_inverse_pivoted).  The status word says so, and the result follows the oracle's LU."""
+    from ilqr_planner_b200 import cabi, synth
+    from ilqr_planner_b200.solver import Handle
+    from oracle import oracle
+    if case == "single_integrator":
+        pb, u0 = synth.config2(batch=16), None
+    elif case == "double_integrator":
+        pb, u0 = synth.config3_short(batch=16, tight_limits=False), None
+    else:
+        pb = synth.config4(batch=16, horizon=60)
+        u0 = synth.u0_time(pb)
+    tk = pb.tasks[0]
+    pr = np.array(tk.kp_precision, dtype=np.float64)
+    pr[0, 0] = -0.05 * pr[0, 0]
+    tk.kp_precision = pr
+    nit = 4
+    with Handle(pb) as h:
+        out = h.solve_recursive(u0, nit, True, False)
+    flagged = (out.status & cabi.ST_QUU_NOT_SPD) != 0
+    assert flagged.sum() >= 4, "the crafted case must drive Quu indefinite (flagged %d of %d)" % (flagged.sum(), pb.batch)
+    ref = oracle.solve_recursive(pb, u0, nit, True, False, threads=8)
+    ok = np.isfinite(ref.cost_hist).all(axis=1) & pt.same_sequence(out.alpha_hist, ref.alpha_hist)
+    assert (ok & flagged).sum() >= 2, "no flagged problem with a comparable step sequence"
+    sel = ok & flagged
+    assert rel(out.cost_hist[sel], ref.cost_hist[sel], floor=0.0) < 1e-6, rel(out.cost_hist[sel], ref.cost_hist[sel], floor=0.0)
+    assert rel(out.X[sel], ref.X[sel]) < 1e-5 and rel(out.K[sel], ref.K[sel]) < 1e-4
+
+
 def test_time_system_fast_path_equals_generic_path():
     """the same time-system solve under ILQRB_NO_FAST_TIME=1 (generic k_backward<.., TIME> + k_linesearch + k_accept): both GPU paths
     must agree with each other as closely as each agrees with the oracle"""
