@@ -93,7 +93,7 @@ def iptr(a):
     return a.ctypes.data_as(c_int32_p)
 
 
-# every symbol include/ilqrb.h declares (tests/test_cabi_symbols.py checks the built library exports them all)
+# every symbol include/ilqrb.h declares (tests/test_cabi_cpu.py checks the built library exports them all)
 SYMBOLS = [
     "ilqrb_abi_version", "ilqrb_last_error", "ilqrb_get_dims", "ilqrb_create", "ilqrb_destroy", "ilqrb_set_stream",
     "ilqrb_synchronize", "ilqrb_update_problems", "ilqrb_solve_recursive", "ilqrb_solve_recursive_async", "ilqrb_solve_al", "ilqrb_solve_batch",

@@ -265,43 +265,33 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_time(const DevPro
 // forward pass.  Ring stage = SPS steps of K [m][ns], d [ms], X [ns], U [ms] (doubles)
 template <int SPS>
 __host__ __device__ inline int fwd_time_stage_doubles(int m, int ns) { return SPS * (m * ns + 3 * ns); }
-template <int RING, int SPS>
-__host__ __device__ inline size_t fwd_time_warp_bytes(int m, int ns) {
-    return ((size_t)RING * fwd_time_stage_doubles<SPS>(m, ns) * 8 + RING * 8 + 127) / 128 * 128;
-}
 
-// System::cost at one step, out of line: the kinematics want ~100 registers and index their arguments at run time; as a call they
-// leave the step loop of the rollout its own register allocation (x, u, dx stay in registers there)
+// System::cost at one step, out of line: the kinematics want ~100 registers and index their arguments at run time
 static __device__ __noinline__ double time_stage_cost(const DevProblem& P, int b, const double* x, const double* u, int k) { return lean_stage_cost<8>(P, b, x, u, k); }
 
-template <int DOF, int RING, int SPS>
-__device__ __forceinline__ void forward_time_body(const DevProblem& P, const Work& W, int b, int lane, double* ring, unsigned long long* bars, const double* s_lim, int it,
-                                                  int nb_iter, int line_search, int early_stop) {
-    constexpr unsigned FULL = 0xffffffffu;
-    constexpr int N = 8;
-    const int d = DOF > 0 ? DOF : P.dof, n = d + 1, m = n, H = P.H, S = P.n_kp_steps;
-    const int ns = (n + 1) & ~1, ms = ns;
-    const int stage_d = fwd_time_stage_doubles<SPS>(m, ns);
-    double* Xb = W.X + (size_t)b * H * ns;
-    double* Ub = W.U + (size_t)b * (H - 1) * ms;
-    const double* Kb = W.K + (size_t)b * (H - 1) * m * ns;
-    const double* db = W.d + (size_t)b * (H - 1) * ms;
-    // the accepted trajectory is staged in this problem's slice of the candidate-control scratch: U' [H-1][ms], then X'_1.. [H-1][ns]
-    // (written in place it would race with the bulk copies of the steps ahead, which must still see the old X and U)
-    double* Us = W.Uc + (size_t)b * (H - 1) * NCAND * ms;
-    double* Xs = Us + (size_t)(H - 1) * ms;
-    const bool slow_limits = s_lim == nullptr && P.any_limits;  // several limit-carrying sub-systems: the full cost at every step
+// per-warp shared memory of k_forward_time: the ring, its barriers, and (x, u) of every candidate at the steps that cost something
+// without a limit violation (keypoint steps + the final state): [S + 1][NCAND][16] doubles
+template <int RING, int SPS>
+__host__ __device__ inline size_t fwd_time_warp_bytes(int m, int ns, int S) {
+    return ((size_t)RING * fwd_time_stage_doubles<SPS>(m, ns) * 8 + RING * 8 + (size_t)(S + 1) * NCAND * 16 * 8 + 127) / 128 * 128;
+}
 
-    // steps 0 .. H-1: step H-1 is the final cost only (no control, no copies)
-    const int n_stages = (H + SPS - 1) / SPS;
-    int issued = 0, waited = 0;  // stages issued / consumed since the barriers were initialised (both passes share the ring)
-    auto issue = [&](int q) {    // lane 0 only: stage q of the horizon into the next slot
+// the bulk-copy ring of one warp: stage q = steps [q SPS, (q+1) SPS) of K, d, X, U; both passes of the forward kernel share it
+template <int RING, int SPS>
+struct TimeRing {
+    double* ring;
+    unsigned long long* bars;
+    const double *Kb, *db, *Xb, *Ub;
+    int m, ns, H, n_stages, stage_d;
+    int issued, waited;  // stages issued / consumed since the barriers were initialised (issued: lane 0's copy is the truth)
+    __device__ __forceinline__ void issue(int q) {  // lane 0 only
         const int slot = issued % RING, k0 = q * SPS;
         const int steps = (H - 1 - k0) < SPS ? (H - 1 - k0) : SPS;
         double* sK = ring + (size_t)slot * stage_d;
         double* sd = sK + SPS * m * ns;
-        double* sx = sd + SPS * ms;
+        double* sx = sd + SPS * ns;
         double* su = sx + SPS * ns;
+        issued++;
         if (steps <= 0) {  // the stage of the final cost alone: the phase completes with this arrival
             mbar_expect_tx(&bars[slot], 0u);
             return;
@@ -309,146 +299,208 @@ __device__ __forceinline__ void forward_time_body(const DevProblem& P, const Wor
         const unsigned bK = (unsigned)(steps * m * ns * 8), bv = (unsigned)(steps * ns * 8);
         mbar_expect_tx(&bars[slot], bK + 3 * bv);
         bulk_g2s(sK, Kb + (size_t)k0 * m * ns, bK, &bars[slot]);
-        bulk_g2s(sd, db + (size_t)k0 * ms, bv, &bars[slot]);
+        bulk_g2s(sd, db + (size_t)k0 * ns, bv, &bars[slot]);
         bulk_g2s(sx, Xb + (size_t)k0 * ns, bv, &bars[slot]);
-        bulk_g2s(su, Ub + (size_t)k0 * ms, bv, &bars[slot]);
-    };
+        bulk_g2s(su, Ub + (size_t)k0 * ns, bv, &bars[slot]);
+    }
+    __device__ __forceinline__ const double* wait_next() {  // all lanes: the next stage in order
+        const int slot = waited % RING;
+        mbar_wait(&bars[slot], (unsigned)((waited / RING) & 1));
+        waited++;
+        return ring + (size_t)slot * stage_d;
+    }
+};
+
+// One closed-loop rollout per lane with that lane's step length (ILQRRecursive.cpp:124-154).
+//   MODE 0  candidates, fast: nothing is called inside the step loop (x, u, dx live in registers); (x, u) at the keypoint steps and the
+//           final state go to `slots`, the costs are evaluated after the loop in step order.  Exact as long as no candidate violates a
+//           joint limit anywhere (then every other step adds an exact zero to the reference's running sum); `viol` reports otherwise.
+//   MODE 1  candidates, exact: System::cost inside the loop at every step that needs it, in the reference's order (slow; only for
+//           problems whose fast pass reported a violation, or with several limit-carrying sub-systems).
+//   MODE 2  accept: no cost; the lane stores its controls and states to Us / Xs.
+template <int DOF, int RING, int SPS, int MODE>
+__device__ __forceinline__ void time_rollout(const DevProblem& P, int b, int lane, TimeRing<RING, SPS>& R, const double alpha, const bool active, const double* s_lim,
+                                             const bool slow_limits, double* slots, double* Us, double* Xs, double& cost_out, double& dun_out, bool& viol_out) {
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr int N = 8;
+    const int d = DOF > 0 ? DOF : P.dof, n = d + 1, m = n, H = P.H, S = P.n_kp_steps;
+    const int ns = (n + 1) & ~1, ms = ns;
+    double x[N], u[N];
+    load_x0<N>(P, b, x);
+#pragma unroll
+    for (int i = 0; i < N; i++) u[i] = 0.0;
+    double cost = 0.0, dun = 0.0;
+    bool viol = false;
+    int skp = 0;
+    int next_kp = S > 0 ? P.kp_steps[0] : -1;
+    if (lane == 0)
+        for (int q = 0; q < RING && q < R.n_stages; q++) R.issue(q);
+    const double* sK = R.ring;
+#pragma unroll 1
+    for (int k = 0; k < H; k++) {
+        const int j = k % SPS;
+        if (j == 0) sK = R.wait_next();  // first step of a stage: its copies have landed
+        const bool last = k == H - 1;
+        if (!last && active) {
+            const double* Kk = sK + (size_t)j * m * ns;
+            const double* sd = sK + SPS * m * ns;
+            const double* sx = sd + SPS * ms;
+            const double* su = sx + SPS * ns;
+            double dx[N];
+#pragma unroll
+            for (int c = 0; c < N; c++) dx[c] = (c < n) ? __dsub_rn(x[c], sx[j * ns + c]) : 0.0;
+            double nrm2 = 0.0;
+#pragma unroll
+            for (int i = 0; i < N; i++) {
+                if (i < m) {
+                    double acc = 0.0;
+#pragma unroll
+                    for (int c = 0; c < N; c += 2) {  // ns is even and the pad column of K holds zeros
+                        if (c < ns) {
+                            const double2 kk = *reinterpret_cast<const double2*>(Kk + i * ns + c);
+                            acc += kk.x * dx[c];
+                            acc += kk.y * dx[c + 1];
+                        }
+                    }
+                    const double du = acc + alpha * sd[j * ms + i];
+                    nrm2 += du * du;
+                    u[i] = su[j * ms + i] + du;
+                }
+            }
+            dun += sqrt(nrm2);
+        }
+        if (MODE != 2 && active) {
+            bool out = false;  // this state is beyond a joint limit
+            if (s_lim) {
+#pragma unroll
+                for (int c = 0; c < N; c++)
+                    if (c < n) out = out || (x[c] > s_lim[c]) || (x[c] < s_lim[8 + c]);
+            }
+            if (MODE == 0) {
+                viol = viol || out;
+                if (k == next_kp || last) {  // (x, u) of this candidate at a step that costs something
+                    double* sl = slots + ((size_t)(last ? S : skp) * NCAND + lane) * 16;
+#pragma unroll
+                    for (int c = 0; c < N; c += 2) {
+                        *reinterpret_cast<double2*>(sl + c) = make_double2(x[c], x[c + 1]);
+                        *reinterpret_cast<double2*>(sl + 8 + c) = make_double2(u[c], u[c + 1]);
+                    }
+                }
+            } else if (k == next_kp || last || out || slow_limits) {
+                double xc[N], uc[N];  // the kinematics index their arguments at run time: they get copies
+#pragma unroll
+                for (int c = 0; c < N; c++) {
+                    xc[c] = x[c];
+                    uc[c] = u[c];
+                }
+                cost += time_stage_cost(P, b, xc, last ? nullptr : uc, k);
+            }
+        }
+        if (!last && active) {
+            if (MODE == 2) {
+#pragma unroll
+                for (int i = 0; i < N; i += 2)
+                    if (i < ms) *reinterpret_cast<double2*>(Us + (size_t)k * ms + i) = make_double2(u[i], u[i + 1]);
+            }
+            // one integrator step with the reference's operation order and no FMA contraction (step_state, work.cuh):
+            // dt = s^2 ; q += dt dq + dt^2/2 * 0 ; t += dt                               SimulationInterface.cpp:19-31
+            double sq = 0.0;
+#pragma unroll
+            for (int c = 0; c < N; c++)
+                if (c == d) sq = u[c];
+            const double dts = __dmul_rn(sq, sq), hdt2 = __dmul_rn(dts, dts) / 2;
+#pragma unroll
+            for (int c = 0; c < N; c++) {
+                if (c < d) x[c] = __dadd_rn(x[c], __dadd_rn(__dmul_rn(dts, u[c]), __dmul_rn(hdt2, 0.0)));
+                else if (c == d) x[c] = __dadd_rn(x[c], dts);
+            }
+            if (MODE == 2) {
+#pragma unroll
+                for (int c = 0; c < N; c += 2)
+                    if (c < ns) *reinterpret_cast<double2*>(Xs + (size_t)k * ns + c) = make_double2(x[c], x[c + 1]);
+            }
+        }
+        if (k == next_kp) {
+            skp++;
+            next_kp = skp < S ? P.kp_steps[skp] : -1;
+        }
+        if (j == SPS - 1 || last) {  // last step of a stage: every lane is done with the slot before the copy engine refills it
+            __syncwarp();
+            const int q = k / SPS;
+            if (lane == 0 && q + RING < R.n_stages) R.issue(q + RING);
+        }
+    }
+    if (MODE == 0) {
+        // costs of the stored states, in step order (a keypoint on the last step is part of the final cost, not a slot of its own)
+        __syncwarp();
+        const int nslots = (S > 0 && P.kp_steps[S - 1] == H - 1) ? S - 1 : S;
+        for (int q = 0; q <= nslots; q++) {
+            const bool fin = q == nslots;
+            const double* sl = slots + ((size_t)(fin ? S : q) * NCAND + lane) * 16;
+            if (active) cost += time_stage_cost(P, b, sl, fin ? nullptr : sl + 8, fin ? H - 1 : P.kp_steps[q]);
+        }
+    }
+    cost_out = cost;
+    dun_out = dun;
+    viol_out = viol;
+}
+
+template <int DOF, int RING, int SPS>
+__device__ __forceinline__ void forward_time_body(const DevProblem& P, const Work& W, int b, int lane, double* ring, unsigned long long* bars, double* slots,
+                                                  const double* s_lim, const bool slow_limits, int it, int nb_iter, int line_search, int early_stop) {
+    constexpr unsigned FULL = 0xffffffffu;
+    const int d = DOF > 0 ? DOF : P.dof, n = d + 1, m = n, H = P.H;
+    const int ns = (n + 1) & ~1, ms = ns;
+    double* Xb = W.X + (size_t)b * H * ns;
+    double* Ub = W.U + (size_t)b * (H - 1) * ms;
+    // the accepted trajectory is staged in this problem's slice of the candidate-control scratch: U' [H-1][ms], then X'_1.. [H-1][ns]
+    // (written in place it would race with the bulk copies of the steps ahead, which must still see the old X and U)
+    double* Us = W.Uc + (size_t)b * (H - 1) * NCAND * ms;
+    double* Xs = Us + (size_t)(H - 1) * ms;
+
+    TimeRing<RING, SPS> R;
+    R.ring = ring;
+    R.bars = bars;
+    R.Kb = W.K + (size_t)b * (H - 1) * m * ns;
+    R.db = W.d + (size_t)b * (H - 1) * ms;
+    R.Xb = Xb;
+    R.Ub = Ub;
+    R.m = m, R.ns = ns, R.H = H;
+    R.n_stages = (H + SPS - 1) / SPS;  // steps 0 .. H-1: step H-1 is the final cost only (no control, no copies)
+    R.stage_d = fwd_time_stage_doubles<SPS>(m, ns);
+    R.issued = R.waited = 0;
     if (lane == 0) {
         for (int s = 0; s < RING; s++) mbar_init(&bars[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
 
+    // ---- candidates: lane c = step length 2^-c --------------------------------------------------------------------------------
+    const bool cand = lane < NCAND && (line_search || lane == 0);
+    const double alpha_c = alpha_of(lane < NCAND ? lane : 0);
+    double cost, dun;
+    bool viol = false;
+    if (!slow_limits) {
+        time_rollout<DOF, RING, SPS, 0>(P, b, lane, R, alpha_c, cand, s_lim, false, slots, Us, Xs, cost, dun, viol);
+        viol = __any_sync(FULL, viol);
+    } else {
+        viol = true;  // several limit-carrying sub-systems: the exact pass straight away
+    }
+    if (viol) time_rollout<DOF, RING, SPS, 1>(P, b, lane, R, alpha_c, cand, s_lim, slow_limits, slots, Us, Xs, cost, dun, viol);
+    // the reference's do/while (ILQRRecursive.cpp:107-155): first alpha in 1, 1/2, .. whose cost is not (>= cost0 or NaN);
+    // alpha = 2^-10 is taken unconditionally (Q2)
     const double cost0 = W.cost0[b];
-    double alpha = alpha_of(lane < NCAND ? lane : 0);
-    bool active = lane < NCAND && (line_search || lane == 0);
-    double newCost = 0.0, dun_sel = 0.0;
-    // pass 0: lane c rolls out the candidate of step length 2^-c (ILQRRecursive.cpp:124-154) ; pass 1: lane 0 rolls the chosen one
-    // out again — same code, same alpha, same numbers — and stores it
-    for (int pass = 0; pass < 2; pass++) {
-        const bool write = pass == 1;
-        double x[N];
-        load_x0<N>(P, b, x);
-        double cost = 0.0, dun = 0.0;
-        int skp = 0;
-        int next_kp = S > 0 ? P.kp_steps[0] : -1;
-        if (lane == 0) {
-            for (int q = 0; q < RING && q < n_stages; q++) {
-                issue(q);
-                issued++;
-            }
-        }
-        issued = __shfl_sync(FULL, issued, 0);
-        for (int q = 0; q < n_stages; q++) {
-            const int slot = waited % RING, k0 = q * SPS;
-            const double* sK = ring + (size_t)slot * stage_d;
-            const double* sd = sK + SPS * m * ns;
-            const double* sx = sd + SPS * ms;
-            const double* su = sx + SPS * ns;
-            mbar_wait(&bars[slot], (unsigned)((waited / RING) & 1));
-            waited++;
-#pragma unroll
-            for (int j = 0; j < SPS; j++) {
-                const int k = k0 + j;
-                const bool last = k == H - 1;
-                if (k < H && active) {
-                    double u[N];
-#pragma unroll
-                    for (int i = 0; i < N; i++) u[i] = 0.0;
-                    if (!last) {
-                        const double* Kk = sK + (size_t)j * m * ns;
-                        double dx[N];
-#pragma unroll
-                        for (int c = 0; c < N; c++) dx[c] = (c < n) ? __dsub_rn(x[c], sx[j * ns + c]) : 0.0;
-                        double nrm2 = 0.0;
-#pragma unroll
-                        for (int i = 0; i < N; i++) {
-                            u[i] = 0.0;
-                            if (i < m) {
-                                double acc = 0.0;
-#pragma unroll
-                                for (int c = 0; c < N; c += 2) {  // ns is even and the pad column of K holds zeros
-                                    if (c < ns) {
-                                        const double2 kk = *reinterpret_cast<const double2*>(Kk + i * ns + c);
-                                        acc += kk.x * dx[c];
-                                        acc += kk.y * dx[c + 1];
-                                    }
-                                }
-                                const double du = acc + alpha * sd[j * ms + i];
-                                nrm2 += du * du;
-                                u[i] = su[j * ms + i] + du;
-                            }
-                        }
-                        dun += sqrt(nrm2);
-                    }
-                    // cost of (x, u) at step k: task terms at the keypoint steps, limit terms where a limit is violated, the final cost
-                    bool need = !write && ((k == next_kp) || slow_limits || last);  // the accept pass keeps the cost of the candidate pass
-                    if (s_lim && !write) {
-#pragma unroll
-                        for (int c = 0; c < N; c++)
-                            if (c < n) need = need || (x[c] > s_lim[c]) || (x[c] < s_lim[8 + c]);
-                    }
-                    if (need) {
-                        // the kinematics index their arguments at run time: they get copies, so that x and u of the step loop stay
-                        // in registers (every index into them is a compile-time constant)
-                        double xc[N], uc[N];
-#pragma unroll
-                        for (int c = 0; c < N; c++) {
-                            xc[c] = x[c];
-                            uc[c] = last ? 0.0 : u[c];
-                        }
-                        cost += time_stage_cost(P, b, xc, last ? nullptr : uc, k);
-                    }
-                    if (!last) {
-                        if (write) {
-#pragma unroll
-                            for (int i = 0; i < N; i += 2)
-                                if (i < ms) *reinterpret_cast<double2*>(Us + (size_t)k * ms + i) = make_double2(u[i], u[i + 1]);
-                        }
-                        // one integrator step with the reference's operation order and no FMA contraction (step_state, work.cuh):
-                        // dt = s^2 ; q += dt dq + dt^2/2 * 0 ; t += dt                       SimulationInterface.cpp:19-31
-                        double sq = 0.0;
-#pragma unroll
-                        for (int c = 0; c < N; c++)
-                            if (c == d) sq = u[c];
-                        const double dts = __dmul_rn(sq, sq), hdt2 = __dmul_rn(dts, dts) / 2;
-#pragma unroll
-                        for (int c = 0; c < N; c++) {
-                            if (c < d) x[c] = __dadd_rn(x[c], __dadd_rn(__dmul_rn(dts, u[c]), __dmul_rn(hdt2, 0.0)));
-                            else if (c == d) x[c] = __dadd_rn(x[c], dts);
-                        }
-                        if (write) {
-#pragma unroll
-                            for (int c = 0; c < N; c += 2)
-                                if (c < ns) *reinterpret_cast<double2*>(Xs + (size_t)k * ns + c) = make_double2(x[c], x[c + 1]);
-                        }
-                    }
-                }
-                if (k == next_kp) {
-                    skp++;
-                    next_kp = skp < S ? P.kp_steps[skp] : -1;
-                }
-            }
-            __syncwarp();  // every lane is done with the slot before the copy engine refills it
-            if (lane == 0 && q + RING < n_stages) {
-                issue(q + RING);
-                issued++;
-            }
-            issued = __shfl_sync(FULL, issued, 0);
-        }
-        if (pass == 0) {
-            // the reference's do/while (ILQRRecursive.cpp:107-155): first alpha in 1, 1/2, .. whose cost is not (>= cost0 or NaN);
-            // alpha = 2^-10 is taken unconditionally (Q2)
-            int sel = 0;
-            if (line_search) {
-                const unsigned ok = __ballot_sync(FULL, active && !((cost >= cost0) || isnan(cost)));
-                sel = ok ? __ffs(ok) - 1 : NCAND - 1;
-            }
-            newCost = __shfl_sync(FULL, cost, sel);
-            dun_sel = __shfl_sync(FULL, dun, sel);
-            alpha = alpha_of(sel);
-            active = lane == 0;
-        }
+    int sel = 0;
+    if (line_search) {
+        const unsigned ok = __ballot_sync(FULL, cand && !((cost >= cost0) || isnan(cost)));
+        sel = ok ? __ffs(ok) - 1 : NCAND - 1;
+    }
+    const double newCost = __shfl_sync(FULL, cost, sel), dun_sel = __shfl_sync(FULL, dun, sel), alpha = alpha_of(sel);
+    // ---- accept: lane 0 rolls the chosen candidate out again — same code, same alpha, same numbers — and stores it -----------------
+    {
+        double c2, d2;
+        bool v2;
+        time_rollout<DOF, RING, SPS, 2>(P, b, lane, R, alpha, lane == 0, s_lim, false, slots, Us, Xs, c2, d2, v2);
     }
     __syncwarp();
     // the staged trajectory becomes the current one (X_0 is the fixed initial state)
@@ -498,10 +550,12 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_forward_time(const DevProb
     if (bl >= nB) return;
     const int b = b0 + bl;
     if (W.done[b]) return;
-    unsigned char* mine = fwd_smem + 128 + (size_t)wid * fwd_time_warp_bytes<RING, SPS>(n, ns);
+    unsigned char* mine = fwd_smem + 128 + (size_t)wid * fwd_time_warp_bytes<RING, SPS>(n, ns, P.n_kp_steps);
     double* ring = reinterpret_cast<double*>(mine);
-    unsigned long long* bars = reinterpret_cast<unsigned long long*>(mine + (size_t)RING * fwd_time_stage_doubles<SPS>(n, ns) * 8);
-    forward_time_body<DOF, RING, SPS>(P, W, b, lane, ring, bars, nl == 1 ? s_lim : nullptr, it, nb_iter, line_search, early_stop);
+    const size_t ringb = (size_t)RING * fwd_time_stage_doubles<SPS>(n, ns) * 8;
+    double* slots = reinterpret_cast<double*>(mine + ringb);
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(mine + ringb + (size_t)(P.n_kp_steps + 1) * NCAND * 16 * 8);
+    forward_time_body<DOF, RING, SPS>(P, W, b, lane, ring, bars, slots, nl == 1 ? s_lim : nullptr, nl > 1, it, nb_iter, line_search, early_stop);
 }
 
 }  // namespace ilqrb

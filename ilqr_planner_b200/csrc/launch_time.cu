@@ -32,7 +32,8 @@ int launch_backward_time_t(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
 template <int DOF, int RING, int SPS, int WARPS, int MINB>
 int launch_forward_time_t(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop) {
     const int n = h->hp.n, ns = h->W.ns;
-    const size_t smem = 128 + (size_t)WARPS * fwd_time_warp_bytes<RING, SPS>(n, ns);
+    const size_t smem = 128 + (size_t)WARPS * fwd_time_warp_bytes<RING, SPS>(n, ns, h->hp.n_kp_steps);
+    if (smem > 220 * 1024) return fail(ILQRB_EUNSUPPORTED, "time-system forward pass: too many keypoint steps for the shared-memory candidate slots");
     auto kern = k_forward_time<DOF, RING, SPS, WARPS, MINB>;
     static DynSmem attr;
     int rc = attr.ensure(kern, smem, h->device);

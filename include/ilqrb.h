@@ -5,7 +5,7 @@
  * reference has no C ABI: its boundary is the C++ classes in
  * ilqr_planner/ilqr_planner/include/ilqr_planner/{sim,system,solver}/ and the
  * pybind11 module pylqr_planner/src/bindings.cpp.  The C++ host classes of this
- * repo (ilqr_planner_b200/host/) keep those names and flatten themselves into the POD
+ * repo (include/ilqr_planner_b200/*.hpp, PyLQR/) keep those names and flatten themselves into the POD
  * descriptor below; every entry point cites the reference method it replaces.
  *
  * Conventions
