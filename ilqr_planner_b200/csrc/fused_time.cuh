@@ -269,11 +269,12 @@ __host__ __device__ inline int fwd_time_stage_doubles(int m, int ns) { return SP
 // System::cost at one step, out of line: the kinematics want ~100 registers and index their arguments at run time
 static __device__ __noinline__ double time_stage_cost(const DevProblem& P, int b, const double* x, const double* u, int k) { return lean_stage_cost<8>(P, b, x, u, k); }
 
-// per-warp shared memory of k_forward_time: the ring, its barriers, and (x, u) of every candidate at the steps that cost something
-// without a limit violation (keypoint steps + the final state): [S + 1][NCAND][16] doubles
+// per-warp shared memory of k_forward_time: the ring, its barriers, (x, u) of every candidate at the keypoint steps and at the final
+// state ([S + 1][NCAND][16] doubles), and the 8 x 16 deviation matrix of the current step (row stride 20) + 16 limit-cost totals
+constexpr int FWD_TIME_DX_DOUBLES = 8 * 20 + 16;
 template <int RING, int SPS>
 __host__ __device__ inline size_t fwd_time_warp_bytes(int m, int ns, int S) {
-    return ((size_t)RING * fwd_time_stage_doubles<SPS>(m, ns) * 8 + RING * 8 + (size_t)(S + 1) * NCAND * 16 * 8 + 127) / 128 * 128;
+    return ((size_t)RING * fwd_time_stage_doubles<SPS>(m, ns) * 8 + RING * 8 + (size_t)(S + 1) * NCAND * 16 * 8 + FWD_TIME_DX_DOUBLES * 8 + 127) / 128 * 128;
 }
 
 // the bulk-copy ring of one warp: stage q = steps [q SPS, (q+1) SPS) of K, d, X, U; both passes of the forward kernel share it
@@ -445,9 +446,163 @@ __device__ __forceinline__ void time_rollout(const DevProblem& P, int b, int lan
     viol_out = viol;
 }
 
+// The rollouts of ALL candidates as one matrix product per step on the FP64 tensor pipe: column c of the 8 x 16 deviation matrix DX is
+// candidate c's x' - x (columns >= NCAND ride along with alpha = 0), and  K_k DX  = 4 mma.sync m8n8k4.f64 replaces 11 x 64 FMAs.
+// Lane (g, t) owns row g of candidates 2t, 2t+1, 8+2t, 8+2t+1 (the accumulator layout): their u'_g, x'_g, the limits of state g.
+//   dt of a candidate = (its u'_d)^2 comes from the lane holding row d of the same columns (one shuffle per column);
+//   the next step's B fragments (DX re-laid-out, contraction index 2t+s so that both A fragments of K_k are one 16-byte load) go
+//   through an 8 x 20 shared-memory matrix.
+// MODE 0: candidates (alpha per column); (x, u) at the keypoint steps and at the end go to `slots`, joint-limit penalties of the other
+//         steps are accumulated per lane; the costs are completed after the loop, lane c = candidate c (kinematics out of line).
+//         The sum runs over the same terms as the reference's but not in step order when a limit is violated (then it differs in
+//         the last bits; without violations every skipped term is an exact zero).
+// MODE 2: accept: every column carries the chosen alpha (the same arithmetic as that candidate's column in MODE 0, bit for bit);
+//         the lanes of column 0 store U' and X', and sum |du| for the early-stop test.
+template <int DOF, int RING, int SPS, int MODE>
+__device__ __forceinline__ void time_rollout_mma(const DevProblem& P, int b, int lane, TimeRing<RING, SPS>& R, const double alpha_sel, const int line_search,
+                                                 const double* s_lim, double* slots, double* sDX, double* Us, double* Xs, double& cost_out, double& dun_out) {
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr int LDX = 20;
+    const int g = lane >> 2, t = lane & 3;
+    const int d = DOF > 0 ? DOF : P.dof, n = d + 1, m = n, H = P.H, S = P.n_kp_steps;
+    const int ns = (n + 1) & ~1, ms = ns;
+    double* sLim = sDX + 8 * LDX;  // [16] limit-cost totals per column
+    // this lane's four columns
+    int col[4];
+    double al[4], xs[4], u[4], limc[4];
+    const double x0g = (g < d) ? P.q0[(size_t)b * d + g] : 0.0;  // x0 = [q0, 0]   PosOrnTimePlannerSys.cpp:55-62
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+        col[e] = 8 * (e >> 1) + 2 * t + (e & 1);
+        al[e] = MODE == 2 ? alpha_sel : ((col[e] < NCAND && (line_search || col[e] == 0)) ? alpha_of(col[e]) : 0.0);
+        xs[e] = x0g;
+        u[e] = 0.0;
+        limc[e] = 0.0;
+    }
+    const double lmx = (s_lim && g < n) ? s_lim[g] : INFINITY, lmn = (s_lim && g < n) ? s_lim[8 + g] : -INFINITY;
+    const bool vrow = g < m, vcolk = 2 * t < ns;
+    double dun = 0.0;
+    int skp = 0;
+    int next_kp = S > 0 ? P.kp_steps[0] : -1;
+    if (lane == 0)
+        for (int q = 0; q < RING && q < R.n_stages; q++) R.issue(q);
+    const double* sK = R.ring;
+#pragma unroll 1
+    for (int k = 0; k < H; k++) {
+        const int j = k % SPS;
+        if (j == 0) sK = R.wait_next();  // first step of a stage: its copies have landed
+        const bool last = k == H - 1;
+        const double* sd = sK + SPS * m * ns;
+        const double* sx = sd + SPS * ms;
+        const double* su = sx + SPS * ns;
+        if (!last) {
+            // DX of this step, re-laid-out for the B operand
+            const double xk = (g < n) ? sx[j * ns + g] : 0.0;
+            double dx[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) dx[e] = (g < n) ? __dsub_rn(xs[e], xk) : 0.0;
+            *reinterpret_cast<double2*>(sDX + g * LDX + 2 * t) = make_double2(dx[0], dx[1]);
+            *reinterpret_cast<double2*>(sDX + g * LDX + 8 + 2 * t) = make_double2(dx[2], dx[3]);
+            __syncwarp();
+            double2 a = make_double2(0.0, 0.0);
+            if (vrow && vcolk) a = *reinterpret_cast<const double2*>(sK + (size_t)j * m * ns + g * ns + 2 * t);  // K_k[g][2t], [2t+1]
+            double du[4];
+#pragma unroll
+            for (int ct = 0; ct < 2; ct++) {
+                double c0 = 0.0, c1 = 0.0;
+                dmma884(c0, c1, a.x, sDX[(2 * t) * LDX + 8 * ct + g]);      // contraction index 2t + 0
+                dmma884(c0, c1, a.y, sDX[(2 * t + 1) * LDX + 8 * ct + g]);  // contraction index 2t + 1
+                du[2 * ct] = c0;
+                du[2 * ct + 1] = c1;
+            }
+            __syncwarp();  // sDX is rewritten by the next step
+            const double dk = vrow ? sd[j * ms + g] : 0.0, uk = vrow ? su[j * ms + g] : 0.0;
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                du[e] = du[e] + al[e] * dk;  // du = K dx + alpha d ; u' = u + du        ILQRRecursive.cpp:128-130
+                u[e] = vrow ? uk + du[e] : 0.0;
+            }
+            if (MODE == 2) {  // |du| of column 0 (rows over g)
+                double n2 = du[0] * du[0];
+                n2 += __shfl_xor_sync(FULL, n2, 4);
+                n2 += __shfl_xor_sync(FULL, n2, 8);
+                n2 += __shfl_xor_sync(FULL, n2, 16);
+                dun += sqrt(n2);
+            }
+        }
+        if (MODE == 0) {
+            if (k == next_kp || last) {  // (x, u) of the candidates at a step whose cost needs the kinematics
+                const int q = last ? S : skp;
+#pragma unroll
+                for (int e = 0; e < 4; e++)
+                    if (col[e] < NCAND) {
+                        double* sl = slots + ((size_t)q * NCAND + col[e]) * 16;
+                        sl[g] = xs[e];
+                        sl[8 + g] = last ? 0.0 : u[e];
+                    }
+            } else {  // System::inspectJointLimit terms of a step without a keypoint (System.cpp:121-142, 226-232)
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    if (xs[e] > lmx) {
+                        const double q = lmx - xs[e];
+                        limc[e] += (q * 1.0) * q;
+                    } else if (xs[e] < lmn) {
+                        const double q = lmn - xs[e];
+                        limc[e] += (q * 1.0) * q;
+                    }
+                }
+            }
+        }
+        if (!last) {
+            if (MODE == 2 && t == 0 && g < ms) Us[(size_t)k * ms + g] = u[0];
+            // one integrator step with the reference's operation order and no FMA contraction (step_state, work.cuh):
+            // dt = s^2 ; q += dt dq + dt^2/2 * 0 ; t += dt                               SimulationInterface.cpp:19-31
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const double sq = __shfl_sync(FULL, u[e], 4 * d + t);  // row d of the same columns
+                const double dts = __dmul_rn(sq, sq), hdt2 = __dmul_rn(dts, dts) / 2;
+                if (g < d) xs[e] = __dadd_rn(xs[e], __dadd_rn(__dmul_rn(dts, u[e]), __dmul_rn(hdt2, 0.0)));
+                else if (g == d) xs[e] = __dadd_rn(xs[e], dts);
+            }
+            if (MODE == 2 && t == 0 && g < ns) Xs[(size_t)k * ns + g] = (g < n) ? xs[0] : 0.0;
+        }
+        if (k == next_kp) {
+            skp++;
+            next_kp = skp < S ? P.kp_steps[skp] : -1;
+        }
+        if (j == SPS - 1 || last) {  // last step of a stage: every lane is done with the slot before the copy engine refills it
+            __syncwarp();
+            const int q = k / SPS;
+            if (lane == 0 && q + RING < R.n_stages) R.issue(q + RING);
+        }
+    }
+    double cost = 0.0;
+    if (MODE == 0) {
+        // limit penalties of each column over its rows, then lane c = candidate c completes its cost with the stored states
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            limc[e] += __shfl_xor_sync(FULL, limc[e], 4);
+            limc[e] += __shfl_xor_sync(FULL, limc[e], 8);
+            limc[e] += __shfl_xor_sync(FULL, limc[e], 16);
+            if (g == 0) sLim[col[e]] = limc[e];
+        }
+        __syncwarp();
+        const bool active = lane < NCAND && (line_search || lane == 0);
+        const int nslots = (S > 0 && P.kp_steps[S - 1] == H - 1) ? S - 1 : S;
+        for (int q = 0; q <= nslots; q++) {  // in step order (a keypoint on the last step is part of the final cost)
+            const bool fin = q == nslots;
+            const double* sl = slots + ((size_t)(fin ? S : q) * NCAND + (lane < NCAND ? lane : 0)) * 16;
+            if (active) cost += time_stage_cost(P, b, sl, fin ? nullptr : sl + 8, fin ? H - 1 : P.kp_steps[q]);
+        }
+        if (active) cost += sLim[lane];
+    }
+    cost_out = cost;
+    dun_out = dun;
+}
+
 template <int DOF, int RING, int SPS>
 __device__ __forceinline__ void forward_time_body(const DevProblem& P, const Work& W, int b, int lane, double* ring, unsigned long long* bars, double* slots,
-                                                  const double* s_lim, const bool slow_limits, int it, int nb_iter, int line_search, int early_stop) {
+                                                  double* sDX, const double* s_lim, const bool slow_limits, int it, int nb_iter, int line_search, int early_stop) {
     constexpr unsigned FULL = 0xffffffffu;
     const int d = DOF > 0 ? DOF : P.dof, n = d + 1, m = n, H = P.H;
     const int ns = (n + 1) & ~1, ms = ns;
@@ -475,18 +630,15 @@ __device__ __forceinline__ void forward_time_body(const DevProblem& P, const Wor
     }
     __syncwarp();
 
-    // ---- candidates: lane c = step length 2^-c --------------------------------------------------------------------------------
+    // ---- candidates: column c of the rollout = step length 2^-c ----------------------------------------------------------------
     const bool cand = lane < NCAND && (line_search || lane == 0);
-    const double alpha_c = alpha_of(lane < NCAND ? lane : 0);
     double cost, dun;
-    bool viol = false;
     if (!slow_limits) {
-        time_rollout<DOF, RING, SPS, 0>(P, b, lane, R, alpha_c, cand, s_lim, false, slots, Us, Xs, cost, dun, viol);
-        viol = __any_sync(FULL, viol);
-    } else {
-        viol = true;  // several limit-carrying sub-systems: the exact pass straight away
+        time_rollout_mma<DOF, RING, SPS, 0>(P, b, lane, R, 0.0, line_search, s_lim, slots, sDX, Us, Xs, cost, dun);
+    } else {  // several limit-carrying sub-systems: the scalar pass, System::cost at every step
+        bool viol;
+        time_rollout<DOF, RING, SPS, 1>(P, b, lane, R, alpha_of(lane < NCAND ? lane : 0), cand, s_lim, true, slots, Us, Xs, cost, dun, viol);
     }
-    if (viol) time_rollout<DOF, RING, SPS, 1>(P, b, lane, R, alpha_c, cand, s_lim, slow_limits, slots, Us, Xs, cost, dun, viol);
     // the reference's do/while (ILQRRecursive.cpp:107-155): first alpha in 1, 1/2, .. whose cost is not (>= cost0 or NaN);
     // alpha = 2^-10 is taken unconditionally (Q2)
     const double cost0 = W.cost0[b];
@@ -495,12 +647,18 @@ __device__ __forceinline__ void forward_time_body(const DevProblem& P, const Wor
         const unsigned ok = __ballot_sync(FULL, cand && !((cost >= cost0) || isnan(cost)));
         sel = ok ? __ffs(ok) - 1 : NCAND - 1;
     }
-    const double newCost = __shfl_sync(FULL, cost, sel), dun_sel = __shfl_sync(FULL, dun, sel), alpha = alpha_of(sel);
-    // ---- accept: lane 0 rolls the chosen candidate out again — same code, same alpha, same numbers — and stores it -----------------
-    {
+    const double newCost = __shfl_sync(FULL, cost, sel), alpha = alpha_of(sel);
+    // ---- accept: the chosen candidate rolled out again — same arithmetic, same numbers — and stored --------------------------------
+    double dun_sel;
+    if (!slow_limits) {
+        double c2;
+        time_rollout_mma<DOF, RING, SPS, 2>(P, b, lane, R, alpha, line_search, s_lim, slots, sDX, Us, Xs, c2, dun_sel);
+        dun_sel = __shfl_sync(FULL, dun_sel, 0);
+    } else {
         double c2, d2;
         bool v2;
         time_rollout<DOF, RING, SPS, 2>(P, b, lane, R, alpha, lane == 0, s_lim, false, slots, Us, Xs, c2, d2, v2);
+        dun_sel = __shfl_sync(FULL, d2, 0);
     }
     __syncwarp();
     // the staged trajectory becomes the current one (X_0 is the fixed initial state)
@@ -554,8 +712,9 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_forward_time(const DevProb
     double* ring = reinterpret_cast<double*>(mine);
     const size_t ringb = (size_t)RING * fwd_time_stage_doubles<SPS>(n, ns) * 8;
     double* slots = reinterpret_cast<double*>(mine + ringb);
-    unsigned long long* bars = reinterpret_cast<unsigned long long*>(mine + ringb + (size_t)(P.n_kp_steps + 1) * NCAND * 16 * 8);
-    forward_time_body<DOF, RING, SPS>(P, W, b, lane, ring, bars, slots, nl == 1 ? s_lim : nullptr, nl > 1, it, nb_iter, line_search, early_stop);
+    double* sDX = slots + (size_t)(P.n_kp_steps + 1) * NCAND * 16;
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(sDX + FWD_TIME_DX_DOUBLES);
+    forward_time_body<DOF, RING, SPS>(P, W, b, lane, ring, bars, slots, sDX, nl == 1 ? s_lim : nullptr, nl > 1, it, nb_iter, line_search, early_stop);
 }
 
 }  // namespace ilqrb
