@@ -454,6 +454,7 @@ __device__ __forceinline__ void time_rollout(const DevProblem& P, int b, int lan
 //   through an 8 x 20 shared-memory matrix.
 // MODE 0: candidates (alpha per column); (x, u) at the keypoint steps and at the end go to `slots`, joint-limit penalties of the other
 //         steps are accumulated per lane; the costs are completed after the loop, lane c = candidate c (kinematics out of line).
+//         Every candidate's controls go to the scratch Us = [H-1][NCAND][ms] (W.Uc), from which the accept step takes the chosen ones.
 //         The sum runs over the same terms as the reference's but not in step order when a limit is violated (then it differs in
 //         the last bits; without violations every skipped term is an exact zero).
 // MODE 2: accept: every column carries the chosen alpha (the same arithmetic as that candidate's column in MODE 0, bit for bit);
@@ -555,6 +556,11 @@ __device__ __forceinline__ void time_rollout_mma(const DevProblem& P, int b, int
         }
         if (!last) {
             if (MODE == 2 && t == 0 && g < ms) Us[(size_t)k * ms + g] = u[0];
+            if (MODE == 0 && g < ms) {  // the controls of every candidate: the accept step reads the chosen one's back (L2)
+#pragma unroll
+                for (int e = 0; e < 4; e++)
+                    if (col[e] < NCAND) Us[((size_t)k * NCAND + col[e]) * ms + g] = u[e];
+            }
             // one integrator step with the reference's operation order and no FMA contraction (step_state, work.cuh):
             // dt = s^2 ; q += dt dq + dt^2/2 * 0 ; t += dt                               SimulationInterface.cpp:19-31
 #pragma unroll
@@ -608,8 +614,9 @@ __device__ __forceinline__ void forward_time_body(const DevProblem& P, const Wor
     const int ns = (n + 1) & ~1, ms = ns;
     double* Xb = W.X + (size_t)b * H * ns;
     double* Ub = W.U + (size_t)b * (H - 1) * ms;
-    // the accepted trajectory is staged in this problem's slice of the candidate-control scratch: U' [H-1][ms], then X'_1.. [H-1][ns]
-    // (written in place it would race with the bulk copies of the steps ahead, which must still see the old X and U)
+    // this problem's slice of the candidate-control scratch: the controls of all candidates [H-1][NCAND][ms] (tensor-pipe pass), or, on
+    // the scalar pass, the accepted trajectory staged as U' [H-1][ms], X'_1.. [H-1][ns] (written in place it would race with the bulk
+    // copies of the steps ahead, which must still see the old X and U)
     double* Us = W.Uc + (size_t)b * (H - 1) * NCAND * ms;
     double* Xs = Us + (size_t)(H - 1) * ms;
 
@@ -648,22 +655,54 @@ __device__ __forceinline__ void forward_time_body(const DevProblem& P, const Wor
         sel = ok ? __ffs(ok) - 1 : NCAND - 1;
     }
     const double newCost = __shfl_sync(FULL, cost, sel), alpha = alpha_of(sel);
-    // ---- accept: the chosen candidate rolled out again — same arithmetic, same numbers — and stored --------------------------------
+    // ---- accept ---------------------------------------------------------------------------------------------------------------
     double dun_sel;
     if (!slow_limits) {
-        double c2;
-        time_rollout_mma<DOF, RING, SPS, 2>(P, b, lane, R, alpha, line_search, s_lim, slots, sDX, Us, Xs, c2, dun_sel);
-        dun_sel = __shfl_sync(FULL, dun_sel, 0);
+        // the chosen candidate's controls come back from the scratch; sum |u' - u| for the early-stop test (steps over lanes), then X is
+        // re-integrated from them with the operations of the rollout, in order — the trajectory the candidate's cost was computed on
+        const double* Usel = Us + (size_t)sel * ms;  // row k at + k NCAND ms
+        double ds = 0.0;
+        for (int k = lane; k < H - 1; k += 32) {
+            double n2 = 0.0;
+            for (int i = 0; i < m; i++) {
+                const double dd = Usel[(size_t)k * NCAND * ms + i] - Ub[(size_t)k * ms + i];
+                n2 += dd * dd;
+            }
+            ds += sqrt(n2);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(FULL, ds, o);
+        dun_sel = ds;
+        __syncwarp();
+        double xg = (lane < d) ? P.q0[(size_t)b * d + lane] : 0.0;  // lane g < n owns state g
+        constexpr int PFK = 8;
+        for (int k0 = 0; k0 < H - 1; k0 += PFK) {
+            double ub[PFK];
+#pragma unroll
+            for (int q = 0; q < PFK; q++) ub[q] = (k0 + q < H - 1 && lane < ms) ? Usel[(size_t)(k0 + q) * NCAND * ms + lane] : 0.0;
+#pragma unroll
+            for (int q = 0; q < PFK; q++) {
+                const int k = k0 + q;
+                if (k < H - 1) {  // warp-uniform
+                    const double sq = __shfl_sync(FULL, ub[q], d);
+                    const double dts = __dmul_rn(sq, sq), hdt2 = __dmul_rn(dts, dts) / 2;
+                    if (lane < d) xg = __dadd_rn(xg, __dadd_rn(__dmul_rn(dts, ub[q]), __dmul_rn(hdt2, 0.0)));
+                    else if (lane == d) xg = __dadd_rn(xg, dts);
+                    if (lane < ms) Ub[(size_t)k * ms + lane] = ub[q];
+                    if (lane < ns) Xb[(size_t)(k + 1) * ns + lane] = (lane < n) ? xg : 0.0;
+                }
+            }
+        }
     } else {
         double c2, d2;
         bool v2;
         time_rollout<DOF, RING, SPS, 2>(P, b, lane, R, alpha, lane == 0, s_lim, false, slots, Us, Xs, c2, d2, v2);
         dun_sel = __shfl_sync(FULL, d2, 0);
+        __syncwarp();
+        // the staged trajectory becomes the current one (X_0 is the fixed initial state)
+        for (int e = lane; e < (H - 1) * ms; e += 32) Ub[e] = Us[e];
+        for (int e = lane; e < (H - 1) * ns; e += 32) Xb[ns + e] = Xs[e];
     }
-    __syncwarp();
-    // the staged trajectory becomes the current one (X_0 is the fixed initial state)
-    for (int e = lane; e < (H - 1) * ms; e += 32) Ub[e] = Us[e];
-    for (int e = lane; e < (H - 1) * ns; e += 32) Xb[ns + e] = Xs[e];
     if (lane == 0) {
         W.cost0[b] = newCost;
         W.cost_hist[(size_t)b * nb_iter + it] = newCost;

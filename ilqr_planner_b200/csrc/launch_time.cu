@@ -63,10 +63,12 @@ int launch_forward_time(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it,
                     : launch_forward_time_t<0, RING, SPS, WARPS, MINB>(h, b0, nB, st, it, nb_iter, line_search, early_stop))
     switch (variant) {
         case 1: rc = FWD(3, 2, 4, 4); break;
-        case 2: rc = FWD(2, 4, 4, 4); break;
+        case 2: rc = FWD(2, 8, 4, 4); break;
         case 3: rc = FWD(3, 4, 4, 4); break;
-        case 4: rc = FWD(2, 16, 4, 3); break;
-        default: rc = FWD(2, 8, 4, 4); break;
+        case 4: rc = FWD(2, 4, 4, 5); break;
+        case 5: rc = FWD(2, 2, 4, 6); break;
+        case 6: rc = FWD(2, 4, 2, 10); break;
+        default: rc = FWD(2, 4, 4, 4); break;
     }
 #undef FWD
     h->end();
