@@ -482,6 +482,9 @@ __device__ __forceinline__ void time_rollout_mma(const DevProblem& P, int b, int
     }
     const double lmx = (s_lim && g < n) ? s_lim[g] : INFINITY, lmn = (s_lim && g < n) ? s_lim[8 + g] : -INFINITY;
     const bool vrow = g < m, vcolk = 2 * t < ns;
+    double* up[4];  // where this lane's control of column e goes at the current step
+#pragma unroll
+    for (int e = 0; e < 4; e++) up[e] = Us + (size_t)col[e] * ms + g;
     double dun = 0.0;
     int skp = 0;
     int next_kp = S > 0 ? P.kp_steps[0] : -1;
@@ -542,14 +545,19 @@ __device__ __forceinline__ void time_rollout_mma(const DevProblem& P, int b, int
                         sl[8 + g] = last ? 0.0 : u[e];
                     }
             } else {  // System::inspectJointLimit terms of a step without a keypoint (System.cpp:121-142, 226-232)
+                bool anyv = false;
 #pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    if (xs[e] > lmx) {
-                        const double q = lmx - xs[e];
-                        limc[e] += (q * 1.0) * q;
-                    } else if (xs[e] < lmn) {
-                        const double q = lmn - xs[e];
-                        limc[e] += (q * 1.0) * q;
+                for (int e = 0; e < 4; e++) anyv = anyv || (xs[e] > lmx) || (xs[e] < lmn);
+                if (anyv) {  // rare: one branch per step instead of one per column
+#pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        if (xs[e] > lmx) {
+                            const double q = lmx - xs[e];
+                            limc[e] += (q * 1.0) * q;
+                        } else if (xs[e] < lmn) {
+                            const double q = lmn - xs[e];
+                            limc[e] += (q * 1.0) * q;
+                        }
                     }
                 }
             }
@@ -559,7 +567,11 @@ __device__ __forceinline__ void time_rollout_mma(const DevProblem& P, int b, int
             if (MODE == 0 && g < ms) {  // the controls of every candidate: the accept step reads the chosen one's back (L2)
 #pragma unroll
                 for (int e = 0; e < 4; e++)
-                    if (col[e] < NCAND) Us[((size_t)k * NCAND + col[e]) * ms + g] = u[e];
+                    if (col[e] < NCAND) *up[e] = u[e];
+            }
+            if (MODE == 0) {
+#pragma unroll
+                for (int e = 0; e < 4; e++) up[e] += NCAND * ms;
             }
             // one integrator step with the reference's operation order and no FMA contraction (step_state, work.cuh):
             // dt = s^2 ; q += dt dq + dt^2/2 * 0 ; t += dt                               SimulationInterface.cpp:19-31

@@ -271,8 +271,19 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
     }
     if ((rc = launch_init(h))) return rc;
     if (al && (rc = launch_al_init(h))) return rc;
-    if (fast_n1_applies(h, al != nullptr)) {
-        if (opts->nb_iter > 0 && (rc = launch_derivs(h))) return rc;  // later iterations: phase F of the forward pass
+    const bool fast1 = fast_n1_applies(h, al != nullptr), fastt = !fast1 && fast_time_applies(h, al != nullptr);
+    if (fast1 || fastt) {
+        // one iteration of problems [b0, b0 + nB) on stream st.  Single-integrator path: backward, forward (phase F of the forward pass
+        // leaves l_x / l_xx for the next backward pass; the first ones come from k_kp_derivs below).  Time path: k_kp_derivs, backward, forward.
+        auto iteration = [&](int b0, int nB, cudaStream_t st, int it, cudaEvent_t after_backward) -> int {
+            int r;
+            if (fastt && (r = launch_derivs(h, b0, nB, st))) return r;
+            if ((r = fast1 ? launch_backward_n1(h, b0, nB, st) : launch_backward_time(h, b0, nB, st))) return r;
+            if (after_backward) CU(cudaEventRecord(after_backward, st));
+            return fast1 ? launch_forward_n1(h, b0, nB, st, it, opts->nb_iter, opts->line_search, opts->early_stop)
+                         : launch_forward_time(h, b0, nB, st, it, opts->nb_iter, opts->line_search, opts->early_stop);
+        };
+        if (fast1 && opts->nb_iter > 0 && (rc = launch_derivs(h))) return rc;
         // The batch is split into G groups of problems, each on its own stream, the first backward pass of group g+1
         // held back until group g has finished its own: from then on the FP64-bound backward pass of one group shares
         // the SMs with the latency-bound forward pass of another.  (Profiling mode: one group, per-kernel event pairs.)
@@ -280,17 +291,15 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
         // must hide its own downloads, 5 when the caller streams batches through two handles (the other handle's solve covers the
         // downloads, and fewer, larger groups keep the kernels closer to a full wave)
         // device-resident results: about three groups per two waves of the forward kernel (28 resident warps per SM with one state
-        // tile, 12 with two), at least 3: C2 B = 4096 / 8192 / 16384 -> 3 / 3 / 6, C5 B = 8192 -> 7 (sweeps in DESIGN.md)
-        const int wave = fast_n1_wave(h);
+        // tile, 12 with two; 16 on the time path), at least 3: C2 B = 4096 / 8192 / 16384 -> 3 / 3 / 6, C5 B = 8192 -> 7 (sweeps in DESIGN.md)
+        const int wave = fast1 ? fast_n1_wave(h) : 148 * 16;
         const int g_dev = std::min(8, std::max(3, (3 * B + 2 * wave - 1) / (2 * wave)));
         int G = h->prof ? 1 : (int)env_uint("ILQRB_GROUPS", out_async ? (h->streaming ? 5 : 8) : g_dev);
         if (G > ilqrb_handle_s::MAX_GROUPS) G = ilqrb_handle_s::MAX_GROUPS;
         if (G < 1 || B < 64 * G) G = 1;
         if (G == 1) {
-            for (int it = 0; it < opts->nb_iter; it++) {
-                if ((rc = launch_backward_n1(h, 0, B, h->stream))) return rc;
-                if ((rc = launch_forward_n1(h, 0, B, h->stream, it, opts->nb_iter, opts->line_search, opts->early_stop))) return rc;
-            }
+            for (int it = 0; it < opts->nb_iter; it++)
+                if ((rc = iteration(0, B, h->stream, it, nullptr))) return rc;
         } else if (opts->nb_iter > 0) {
             if ((rc = h->ensure_groups(G))) return rc;
             CU(cudaEventRecord(h->ev_start, h->stream));
@@ -305,9 +314,7 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
                 cudaStream_t st = h->gstream[gi];
                 if (gi > 0) CU(cudaStreamWaitEvent(st, h->ev_stagger[gi - 1], 0));
                 for (int it = 0; it < opts->nb_iter; it++) {
-                    if ((rc = launch_backward_n1(h, b0, b1 - b0, st))) return rc;
-                    if (stag == 0 && it == 0 && gi + 1 < G) CU(cudaEventRecord(h->ev_stagger[gi], st));
-                    if ((rc = launch_forward_n1(h, b0, b1 - b0, st, it, opts->nb_iter, opts->line_search, opts->early_stop))) return rc;
+                    if ((rc = iteration(b0, b1 - b0, st, it, (stag == 0 && it == 0 && gi + 1 < G) ? h->ev_stagger[gi] : nullptr))) return rc;
                     if (stag > 0 && it == stag - 1 && gi + 1 < G) CU(cudaEventRecord(h->ev_stagger[gi], st));
                 }
             }
@@ -321,17 +328,6 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
                 CU(cudaEventRecord(h->ev_done[gi], h->gstream[gi]));
                 CU(cudaStreamWaitEvent(h->stream, h->ev_done[gi], 0));
             }
-        }
-        h->last_nb_iter = opts->nb_iter;
-        h->last_solver = 1;
-        return 0;
-    }
-    if (fast_time_applies(h, al != nullptr)) {
-        // first-order time systems: keypoint derivatives, fused backward pass, fused line search + accept (fused_time.cuh)
-        for (int it = 0; it < opts->nb_iter; it++) {
-            if ((rc = launch_derivs(h))) return rc;
-            if ((rc = launch_backward_time(h, 0, B, h->stream))) return rc;
-            if ((rc = launch_forward_time(h, 0, B, h->stream, it, std::max(opts->nb_iter, 1), opts->line_search, opts->early_stop))) return rc;
         }
         h->last_nb_iter = opts->nb_iter;
         h->last_solver = 1;
