@@ -768,4 +768,97 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_forward_time(const DevProb
     forward_time_body<DOF, RING, SPS>(P, W, b, lane, ring, bars, slots, sDX, nl == 1 ? s_lim : nullptr, nl > 1, it, nb_iter, line_search, early_stop);
 }
 
+// ------------------------------------------------------------------------------------------------------------------------------
+// l_x = sum_tasks ((-J^T) Q) diff, l_xx = sum_tasks (J^T Q) J at the keypoint steps of the current trajectory (System.cpp:252-260,
+// 290-296) for the time systems of this file: one warp per problem, lane (sg, i) = (keypoint step s0 + sg, state column i).  Every
+// lane runs the lean kinematics of its step and forms its own Jacobian column in closed form (the time state's column is the unit
+// vector of the time row, PosOrnTimePlannerSys.cpp:104-110); the columns meet in shared memory.  Replaces k_kp_derivs (one thread
+// per (problem, keypoint step): 8192 threads at B = 4096, 77 us) on this path.
+template <int WARPS>
+__global__ void __launch_bounds__(32 * WARPS) k_kp_derivs_time(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr int NX = 8, RR = 7;  // state columns per keypoint step, residual rows (6 + time)
+    __shared__ double s_Jall[WARPS][32 * RR];
+    const DevProblem& P = *Pp;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int bl = blockIdx.x * WARPS + wid;
+    if (bl >= nB) return;
+    const int b = b0 + bl;
+    if (W.done[b]) return;
+    double* s_J = s_Jall[wid];
+    const int d = P.dof, n = d + 1, H = P.H, S = P.n_kp_steps, ns = (n + 1) & ~1;
+    const double* Xb = W.X + (size_t)b * H * ns;
+    const int sg = lane / NX, i = lane % NX;
+    for (int s0 = 0; s0 < S; s0 += 32 / NX) {
+        const int s = s0 + sg;
+        const bool act = (s < S) && (i < n);
+        const int k = P.kp_steps[s < S ? s : 0];
+        const double* xk = Xb + (size_t)k * ns;
+        double lxi = 0.0, row[NX];
+#pragma unroll
+        for (int j = 0; j < NX; j++) row[j] = 0.0;
+        for (int ti = 0; ti < P.n_tasks; ti++) {
+            const DevTask& tk = P.tasks[ti];
+            const int kp = task_kp_at(tk, k);
+            const bool has = act && kp >= 0;
+            if (!__any_sync(FULL, has)) continue;
+            const int off = tk.joint_offset, r = tk.r_t;  // r = 7
+            const int cj_ = i - off;
+            const int cj = (cj_ >= 0 && cj_ < P.robots[tk.robot].dof && i < d) ? cj_ : -1;
+            double fx[8], Jc[RR], res[RR], jq[RR];
+#pragma unroll
+            for (int a = 0; a < RR; a++) res[a] = 0.0;
+            lean_task_eval(P, tk, [&](int j) { return xk[off + j]; }, cj, fx, Jc);
+            Jc[6] = (i == d) ? 1.0 : 0.0;  // the time row of the task Jacobian
+            fx[7] = xk[n - 1];
+            if (kp >= 0) {
+                const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
+                task_residual(P, tk, fx, tg, res, task_deadzone(tk, kp));
+            }
+            const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + (kp >= 0 ? kp : 0)) * r * r;
+            double gsum = 0.0;
+#pragma unroll
+            for (int c = 0; c < RR; c++) {
+                double a = 0.0, na = 0.0;
+                if (c < r) {
+#pragma unroll
+                    for (int a2 = 0; a2 < RR; a2++)
+                        if (a2 < r) {
+                            const double qv = Q[a2 * r + c];
+                            a += Jc[a2] * qv;
+                            na += (-1.0 * Jc[a2]) * qv;
+                        }
+                }
+                jq[c] = a;
+                gsum += na * res[c];
+            }
+#pragma unroll
+            for (int a = 0; a < RR; a++) s_J[lane * RR + a] = has ? Jc[a] : 0.0;
+            __syncwarp();
+            if (has) {
+                lxi += gsum;
+#pragma unroll
+                for (int j = 0; j < NX; j++) {
+                    if (j < n) {
+                        const double* Jj = s_J + (sg * NX + j) * RR;
+                        double hh = 0.0;
+#pragma unroll
+                        for (int c = 0; c < RR; c++)
+                            if (c < r) hh += jq[c] * Jj[c];
+                        row[j] += hh;
+                    }
+                }
+            }
+            __syncwarp();
+        }
+        if (act) {
+            W.LX[((size_t)b * S + s) * n + i] = lxi;
+            double* out = W.LXX + (((size_t)b * S + s) * n + i) * n;
+#pragma unroll
+            for (int j = 0; j < NX; j++)
+                if (j < n) out[j] = row[j];
+        }
+    }
+}
+
 }  // namespace ilqrb

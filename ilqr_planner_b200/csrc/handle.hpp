@@ -150,6 +150,7 @@ bool generic_forced();  // ILQRB_GENERIC set: A/B switch for tests and profiling
 
 // ---- launch_time.cu -------------------------------------------------------------------------------------------------
 bool fast_time_applies(ilqrb_handle h, bool al);
+int launch_derivs_time(ilqrb_handle h, int b0, int nB, cudaStream_t st);
 int launch_backward_time(ilqrb_handle h, int b0, int nB, cudaStream_t st);
 int launch_forward_time(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop);
 // ---- launch_fused1.cu -----------------------------------------------------------------------------------------------

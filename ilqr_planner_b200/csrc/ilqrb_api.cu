@@ -277,7 +277,7 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
         // leaves l_x / l_xx for the next backward pass; the first ones come from k_kp_derivs below).  Time path: k_kp_derivs, backward, forward.
         auto iteration = [&](int b0, int nB, cudaStream_t st, int it, cudaEvent_t after_backward) -> int {
             int r;
-            if (fastt && (r = launch_derivs(h, b0, nB, st))) return r;
+            if (fastt && (r = launch_derivs_time(h, b0, nB, st))) return r;
             if ((r = fast1 ? launch_backward_n1(h, b0, nB, st) : launch_backward_time(h, b0, nB, st))) return r;
             if (after_backward) CU(cudaEventRecord(after_backward, st));
             return fast1 ? launch_forward_n1(h, b0, nB, st, it, opts->nb_iter, opts->line_search, opts->early_stop)

@@ -44,6 +44,14 @@ int launch_forward_time_t(ilqrb_handle h, int b0, int nB, cudaStream_t st, int i
 
 }  // namespace
 
+int launch_derivs_time(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
+    h->begin(PS_KP_DERIVS);
+    k_kp_derivs_time<4><<<(nB + 3) / 4, 128, 0, st>>>(h->dp, h->W, b0, nB);
+    h->end();
+    CU(cudaGetLastError());
+    return 0;
+}
+
 int launch_backward_time(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
     h->begin(PS_BACKWARD);
     int rc = h->hp.dof == 7 ? launch_backward_time_t<7, 4, 4>(h, b0, nB, st) : launch_backward_time_t<0, 4, 4>(h, b0, nB, st);

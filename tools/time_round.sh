@@ -26,8 +26,8 @@ with Handle(pb) as h:
     h.synchronize()
     print("ms %.3f solves/s %.0f" % (dt * 1e3, pb.batch / dt), h.profile())
 PY
-for v in 0 1 4; do echo "variant $v"; ILQRB_TIME_FWD=$v timeout 300 python /tmp/time_bench.py; done > gpurun_out/${TAG}_sweep.txt 2>&1
-for g in 1 2 3 4 6; do echo "groups $g"; ILQRB_GROUPS=$g timeout 300 python /tmp/time_bench.py; done >> gpurun_out/${TAG}_sweep.txt 2>&1
+for v in 0; do echo "variant $v"; ILQRB_TIME_FWD=$v timeout 300 python /tmp/time_bench.py; done > gpurun_out/${TAG}_sweep.txt 2>&1
+for g in 1 2 3; do echo "groups $g"; ILQRB_GROUPS=$g timeout 300 python /tmp/time_bench.py; done >> gpurun_out/${TAG}_sweep.txt 2>&1
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/${TAG}_launches.csv python tools/profile_run.py 3 time > gpurun_out/${TAG}_ncu_l.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_\(backward_time\|forward_time\) -s 2 -c 2 -o gpurun_out/${TAG}_time -f python tools/profile_run.py 3 time > gpurun_out/${TAG}_ncu_f.log 2>&1
 ncu -i gpurun_out/${TAG}_time.ncu-rep --page raw --csv > gpurun_out/${TAG}_time_raw.csv 2>/dev/null
