@@ -24,6 +24,8 @@
 //   k_batch_select    sequential line-search rule over the 11 candidate costs (accept if cost < cost0 or alpha < 1e-3,
 //                     :135-157), u update, trace (the PRE-step cost is what the reference prints, :160), early stop.
 #pragma once
+#include <cuda.h>  // CUtensorMap (types only: cuTensorMapEncodeTiled is fetched through cudaGetDriverEntryPoint)
+
 #include <algorithm>
 #include <functional>
 #include <string>
@@ -541,6 +543,189 @@ __global__ void __launch_bounds__(256, 2) k_batch_chol_ll(Work W, BatchDev BW, i
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// The same left-looking factorisation with the operand tiles moved by the TMA engine (default).  k_batch_chol_ll above stages every
+// 64 x 64 operand tile global -> registers -> shared memory with two __syncthreads per block product (ncu: 3.8 warps per issue
+// stalled at the barrier, DMMA pipe 56 % active).  Here L(I,k) and L(J,k) arrive by `cp.async.bulk.tensor.3d` (SASS UTMALDG) through
+// a tensor map over the chunk's [problem][row][column] matrices into a two-stage shared-memory ring, completion on one mbarrier
+// per stage: thread 0 issues the tiles of product k+1 before the CTA computes product k, one __syncthreads per product (the ring
+// slot's readers are done before it is refilled).  Tiles land as four [64][16] boxes in the 128-byte swizzle, which makes the
+// DMMA fragment reads (8 rows x 4 column pairs per warp) conflict-free without the 68-double row padding the register path needs.
+// 198 KB of shared memory: one CTA of 8 warps per SM (the register-staged kernel runs two); the copies no longer wait for
+// the warps and the warps no longer wait for the copies.
+constexpr int CHT_TILE = 64 * 64;  // doubles per operand tile (4 boxes of 64 x 16)
+
+__device__ __forceinline__ void tma_load_box(double* dst, const CUtensorMap* tm, int col, int row, int prob, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"((unsigned)__cvta_generic_to_shared(dst)),
+                 "l"(tm), "r"(col), "r"(row), "r"(prob), "r"((unsigned)__cvta_generic_to_shared(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void cht_mbar_init(unsigned long long* bar) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)));
+}
+__device__ __forceinline__ void cht_expect(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+// bounded wait: a copy that never lands (bad tensor map) traps instead of hanging the device
+__device__ __forceinline__ void cht_wait(unsigned long long* bar, unsigned parity) {
+    unsigned done = 0;
+    for (long long spin = 0; !done; spin++) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"((unsigned)__cvta_generic_to_shared(bar)), "r"(parity)
+            : "memory");
+        if (spin > (1ll << 26)) __trap();
+    }
+}
+
+__global__ void __launch_bounds__(256, 1) k_batch_chol_tma(const __grid_constant__ CUtensorMap tmA, Work W, BatchDev BW, int b0) {
+    extern __shared__ __align__(1024) unsigned char cht_smem[];
+    double* ring = reinterpret_cast<double*>(cht_smem);  // [2 stages][X tile, Y tile]
+    double* sD = ring + 4 * CHT_TILE;                    // diagonal block, its factor, then the factor's inverse (row stride CH_LD)
+    double* sC = sD + 64 * CH_LD;                        // the updated block C ; Linv while the diagonal block is inverted
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(sC + 64 * CH_LD);
+    const int bl = blockIdx.x, b = b0 + bl;
+    if (W.done[b]) return;
+    const int Np = BW.Np, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, t = lane & 3;
+    double* A = BW.A + (size_t)bl * Np * Np;
+    __shared__ int s_bad;
+    if (tid == 0) {
+        s_bad = 0;
+        cht_mbar_init(&bars[0]);
+        cht_mbar_init(&bars[1]);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    // element (row, col) of a tile: box col/16, 128-byte rows, 16-byte chunks XOR-ed with row % 8 (CU_TENSOR_MAP_SWIZZLE_128B).
+    // Every fragment row of this lane has row % 8 == g, so the in-row offset depends on (ks % 4, g, t) only:
+    int sw[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) sw[q] = (((2 * q + (t >> 1)) ^ g) << 1) + (t & 1);
+    const int arow = (8 * warp + g) * 16;
+    auto issue = [&](int stage, int I0, int J0, int k0, bool diag) {  // thread 0
+        double* sX = ring + (size_t)stage * 2 * CHT_TILE;
+        double* sY = sX + CHT_TILE;
+        cht_expect(&bars[stage], (diag ? 1u : 2u) * CHT_TILE * 8u);
+#pragma unroll
+        for (int bx = 0; bx < 4; bx++) tma_load_box(sX + bx * 1024, &tmA, k0 + 16 * bx, I0, bl, &bars[stage]);
+        if (!diag) {
+#pragma unroll
+            for (int bx = 0; bx < 4; bx++) tma_load_box(sY + bx * 1024, &tmA, k0 + 16 * bx, J0, bl, &bars[stage]);
+        }
+    };
+    unsigned cnt = 0;  // block products so far: stage = cnt % 2, phase parity = (cnt / 2) % 2
+    for (int J0 = 0; J0 < Np; J0 += CH_NB) {
+        // the blocks of column J0 - 64 were written with ordinary stores: order them before the copy engine's reads
+        asm volatile("fence.proxy.async;" ::: "memory");
+        __syncthreads();
+        for (int I0 = J0; I0 < Np; I0 += 64) {
+            const bool diag = (I0 == J0);
+            double c[8][2];
+#pragma unroll
+            for (int ct = 0; ct < 8; ct++) c[ct][0] = c[ct][1] = 0.0;
+            const int nk = J0 / CH_NB;
+            if (nk > 0 && tid == 0) issue(cnt & 1, I0, J0, 0, diag);
+            for (int kk = 0; kk < nk; kk++, cnt++) {
+                if (tid == 0 && kk + 1 < nk) issue((cnt + 1) & 1, I0, J0, (kk + 1) * CH_NB, diag);
+                const double* sX = ring + (size_t)(cnt & 1) * 2 * CHT_TILE;
+                const double* sB = diag ? sX : sX + CHT_TILE;
+                cht_wait(&bars[cnt & 1], (cnt >> 1) & 1);
+                double a[16];
+#pragma unroll
+                for (int ks = 0; ks < 16; ks++) a[ks] = sX[(ks >> 2) * 1024 + arow + sw[ks & 3]];
+#pragma unroll
+                for (int ct = 0; ct < 8; ct++) {
+                    if (diag && ct > warp) continue;  // lower triangle only
+#pragma unroll
+                    for (int ks = 0; ks < 16; ks++) dmma884(c[ct][0], c[ct][1], a[ks], sB[(ks >> 2) * 1024 + (8 * ct + g) * 16 + sw[ks & 3]]);
+                }
+                __syncthreads();  // the slot's readers are done: it is refilled by the issue of the next iteration
+            }
+            // C = A(I,J) - sum, into shared memory (the diagonal block into sD, the others into sC)
+            double* sCC = diag ? sD : sC;
+#pragma unroll
+            for (int ct = 0; ct < 8; ct++) {
+                const double2 o = *reinterpret_cast<const double2*>(A + (size_t)(I0 + 8 * warp + g) * Np + J0 + 8 * ct + 2 * t);
+                sCC[(8 * warp + g) * CH_LD + 8 * ct + 2 * t] = o.x - c[ct][0];
+                sCC[(8 * warp + g) * CH_LD + 8 * ct + 2 * t + 1] = o.y - c[ct][1];
+            }
+            __syncthreads();
+            if (diag) {
+                // factor the diagonal block (lower part)
+                for (int j = 0; j < 64; j++) {
+                    __syncthreads();  // rank-1 update of step j-1 complete
+                    const double djj = sD[j * CH_LD + j];
+                    __syncthreads();  // everybody holds the pivot before it is overwritten
+                    const double d = sqrt(djj);
+                    if (tid == 0) {
+                        if (!(djj > 0.0)) s_bad = 1;
+                        sD[j * CH_LD + j] = d;
+                    }
+                    if (tid > j && tid < 64) sD[tid * CH_LD + j] /= d;
+                    __syncthreads();
+                    for (int e = tid; e < 64 * 64; e += 256) {
+                        const int i = e >> 6, k = e & 63;
+                        if (k > j && k <= i) sD[i * CH_LD + k] -= sD[i * CH_LD + j] * sD[k * CH_LD + j];
+                    }
+                }
+                __syncthreads();
+                // write the factor back (upper part of the block zeroed) ; Linv into sC by forward substitution, one column per thread
+                for (int e = tid; e < 64 * 64; e += 256) {
+                    const int i = e >> 6, k = e & 63;
+                    const double v = (k <= i) ? sD[i * CH_LD + k] : 0.0;
+                    sD[i * CH_LD + k] = v;
+                    A[(size_t)(J0 + i) * Np + J0 + k] = v;
+                }
+                __syncthreads();
+                if (tid < 64) {
+                    const int j = tid;  // column j of the inverse: L x = e_j
+                    for (int i = 0; i < 64; i++) {
+                        double acc = (i == j) ? 1.0 : 0.0;
+                        for (int k = j; k < i; k++) acc -= sD[i * CH_LD + k] * sC[k * CH_LD + j];
+                        sC[i * CH_LD + j] = (i < j) ? 0.0 : acc / sD[i * CH_LD + i];
+                    }
+                }
+                __syncthreads();
+                for (int e = tid; e < 64 * 64; e += 256) sD[(e >> 6) * CH_LD + (e & 63)] = sC[(e >> 6) * CH_LD + (e & 63)];
+                __syncthreads();
+            } else {
+                // L(I,J) = C Linv^T
+                ch_xyT<false>(A + (size_t)I0 * Np + J0, Np, sC, sD, 1.0, false, warp, lane);
+                __syncthreads();  // sC is rewritten by the next block
+            }
+        }
+    }
+    __syncthreads();
+    if (tid == 0 && s_bad) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
+}
+
+// tensor map over the chunk's matrices A [nB][Np][Np] (FP64): box = 16 columns x 64 rows x 1 problem, 128-byte swizzle.
+// cuTensorMapEncodeTiled comes from the driver through the runtime (no link against libcuda); false = not available.
+inline bool cht_make_tensor_map(CUtensorMap* out, const double* A, int nB, int Np) {
+    typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) == cudaSuccess && qr == cudaDriverEntryPointSuccess) fn = (encode_fn)p;
+    }
+    if (!fn) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)Np, (cuuint64_t)Np, (cuuint64_t)nB};
+    const cuuint64_t strides[2] = {(cuuint64_t)Np * 8, (cuuint64_t)Np * Np * 8};
+    const cuuint32_t box[3] = {16, 64, 1}, estr[3] = {1, 1, 1};
+    return fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double*>(A), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // du = (L L^T)^-1 rhs : forward then backward substitution, one CTA (256 threads) per problem, 64-wide blocks.
 __global__ void __launch_bounds__(256) k_batch_trsv(Work W, BatchDev BW, int b0) {
     extern __shared__ double sm[];
@@ -842,10 +1027,14 @@ inline int batch_run(cudaStream_t st, int device, const DevProblem& P, const Dev
         BCU(cudaMemsetAsync(W.cost0, 0, B * sizeof(double), st));
     }
     const size_t smem_chol = 3 * 64 * CH_LD * sizeof(double), smem_trsv = (64 * CH_LD + Np) * sizeof(double);
+    const size_t smem_tma = (4 * (size_t)CHT_TILE + 2 * 64 * CH_LD) * sizeof(double) + 16;
     const size_t smem_asm = ((size_t)Sn * Sr + (size_t)Sn * Sn + Sn + H) * sizeof(double), smem_cp = (2 * (size_t)Sn * std::max(nw, 1) + (size_t)nw * (nw + 1)) * sizeof(double);
     static const bool chol_right_looking = getenv("ILQRB_CHOL_RL") != nullptr;  // A/B switch: the first (right-looking) kernel
+    static const bool chol_no_tma = getenv("ILQRB_CHOL_NO_TMA") != nullptr;     // A/B switch: the register-staged left-looking kernel
+    CUtensorMap tmA;
+    const bool use_tma = !cp && !chol_right_looking && !chol_no_tma && cht_make_tensor_map(&tmA, BW.A, BW.chunk, Np);
     {
-        static DynSmem a_chol, a_chol_ll, a_trsv, a_asm, a_cp;  // per-device "raised to" values
+        static DynSmem a_chol, a_chol_ll, a_trsv, a_asm, a_cp, a_tma;  // per-device "raised to" values
         auto ens = [&](DynSmem& a, auto kern, size_t smem) -> int {
             if (smem <= 48 * 1024) return 0;
             const bool tracked = device >= 0 && device < MAX_DEVICES;
@@ -856,7 +1045,7 @@ inline int batch_run(cudaStream_t st, int device, const DevProblem& P, const Dev
             return 0;
         };
         if ((rc = ens(a_chol, k_batch_chol, smem_chol)) || (rc = ens(a_chol_ll, k_batch_chol_ll, smem_chol)) || (rc = ens(a_trsv, k_batch_trsv, smem_trsv)) ||
-            (rc = ens(a_asm, k_batch_assemble, smem_asm)) || (rc = ens(a_cp, k_batch_cp, smem_cp)))
+            (rc = ens(a_asm, k_batch_assemble, smem_asm)) || (rc = ens(a_cp, k_batch_cp, smem_cp)) || (use_tma && (rc = ens(a_tma, k_batch_chol_tma, smem_tma))))
             return rc;
     }
     for (int b0 = 0; b0 < B; b0 += BW.chunk) {
@@ -874,7 +1063,8 @@ inline int batch_run(cudaStream_t st, int device, const DevProblem& P, const Dev
                 k_batch_syrk<<<dim3((unsigned)((Np / 8) * (Np / 64) + 3) / 4, nB), 128, 0, st>>>(dp, W, K, b0);
                 end();
                 begin(3);
-                if (chol_right_looking) k_batch_chol<<<nB, 256, smem_chol, st>>>(W, K, b0);
+                if (use_tma) k_batch_chol_tma<<<nB, 256, smem_tma, st>>>(tmA, W, K, b0);
+                else if (chol_right_looking) k_batch_chol<<<nB, 256, smem_chol, st>>>(W, K, b0);
                 else k_batch_chol_ll<<<nB, 256, smem_chol, st>>>(W, K, b0);
                 end();
                 begin(3);
