@@ -602,11 +602,16 @@ __global__ void __launch_bounds__(256, 1) k_batch_chol_tma(const __grid_constant
     }
     __syncthreads();
     // element (row, col) of a tile: box col/16, 128-byte rows, 16-byte chunks XOR-ed with row % 8 (CU_TENSOR_MAP_SWIZZLE_128B).
-    // Every fragment row of this lane has row % 8 == g, so the in-row offset depends on (ks % 4, g, t) only:
+    // A 64-bit shared-memory load is served per half-warp (lanes g = 0..3 and g = 4..7): with fragment row g = tile row g the four
+    // rows of a half differ in two bits only and the XOR maps both column pairs of a lane quad onto the same four chunks (ncu: 46 %
+    // of the wavefronts were conflicts).  Fragment row g therefore stands for tile row pg = 2 (g % 4) + g / 4 — rows 0, 2, 4, 6 in
+    // one half, 1, 3, 5, 7 in the other — for the A rows, the B rows (= output columns) and the output alike.
+    const int pg = 2 * (g & 3) + (g >> 2);
     int sw[4];
 #pragma unroll
-    for (int q = 0; q < 4; q++) sw[q] = (((2 * q + (t >> 1)) ^ g) << 1) + (t & 1);
-    const int arow = (8 * warp + g) * 16;
+    for (int q = 0; q < 4; q++) sw[q] = (((2 * q + (t >> 1)) ^ pg) << 1) + (t & 1);
+    const int arow = (8 * warp + pg) * 16;
+    const int pc0 = 2 * ((2 * t) & 3) + ((2 * t) >> 2), pc1 = 2 * ((2 * t + 1) & 3) + ((2 * t + 1) >> 2);  // output columns of slots 0, 1
     auto issue = [&](int stage, int I0, int J0, int k0, bool diag) {  // thread 0
         double* sX = ring + (size_t)stage * 2 * CHT_TILE;
         double* sY = sX + CHT_TILE;
@@ -642,17 +647,20 @@ __global__ void __launch_bounds__(256, 1) k_batch_chol_tma(const __grid_constant
                 for (int ct = 0; ct < 8; ct++) {
                     if (diag && ct > warp) continue;  // lower triangle only
 #pragma unroll
-                    for (int ks = 0; ks < 16; ks++) dmma884(c[ct][0], c[ct][1], a[ks], sB[(ks >> 2) * 1024 + (8 * ct + g) * 16 + sw[ks & 3]]);
+                    for (int ks = 0; ks < 16; ks++) dmma884(c[ct][0], c[ct][1], a[ks], sB[(ks >> 2) * 1024 + (8 * ct + pg) * 16 + sw[ks & 3]]);
                 }
                 __syncthreads();  // the slot's readers are done: it is refilled by the issue of the next iteration
             }
             // C = A(I,J) - sum, into shared memory (the diagonal block into sD, the others into sC)
             double* sCC = diag ? sD : sC;
+            {
+                const double* Arow = A + (size_t)(I0 + 8 * warp + pg) * Np + J0;
+                double* Crow = sCC + (8 * warp + pg) * CH_LD;
 #pragma unroll
-            for (int ct = 0; ct < 8; ct++) {
-                const double2 o = *reinterpret_cast<const double2*>(A + (size_t)(I0 + 8 * warp + g) * Np + J0 + 8 * ct + 2 * t);
-                sCC[(8 * warp + g) * CH_LD + 8 * ct + 2 * t] = o.x - c[ct][0];
-                sCC[(8 * warp + g) * CH_LD + 8 * ct + 2 * t + 1] = o.y - c[ct][1];
+                for (int ct = 0; ct < 8; ct++) {
+                    Crow[8 * ct + pc0] = Arow[8 * ct + pc0] - c[ct][0];
+                    Crow[8 * ct + pc1] = Arow[8 * ct + pc1] - c[ct][1];
+                }
             }
             __syncthreads();
             if (diag) {
