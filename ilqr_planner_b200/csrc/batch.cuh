@@ -340,14 +340,15 @@ constexpr int CH_NB = 64, CH_LD = 68;
 
 // C(64x64 at Cg, leading dim ldc) = beta_old * C + sign * X Y^T with X, Y 64 x 64 in shared memory (leading dim CH_LD).
 // 8 warps: warp w owns rows 8w..8w+7, all eight column tiles.  lower_only: skip tiles strictly above the diagonal.
-template <bool ACCUM>
-__device__ __forceinline__ void ch_xyT(double* Cg, int ldc, const double* sX, const double* sY, double sign, bool lower_only, int warp, int lane) {
+template <bool ACCUM, int NCT = 8>
+__device__ __forceinline__ void ch_xyT(double* Cg, int ldc, const double* sX, const double* sY, double sign, bool lower_only, int warp, int lane, int ct0 = 0) {
     const int g = lane >> 2, t = lane & 3;
     double a[16];
 #pragma unroll
     for (int ks = 0; ks < 16; ks++) a[ks] = sX[(8 * warp + g) * CH_LD + 4 * ks + t];
 #pragma unroll
-    for (int ct = 0; ct < 8; ct++) {
+    for (int cti = 0; cti < NCT; cti++) {
+        const int ct = ct0 + cti;
         if (lower_only && ct > warp) continue;
         double c0 = 0.0, c1 = 0.0;
 #pragma unroll
@@ -582,7 +583,10 @@ __device__ __forceinline__ void cht_wait(unsigned long long* bar, unsigned parit
     }
 }
 
-__global__ void __launch_bounds__(256, 1) k_batch_chol_tma(const __grid_constant__ CUtensorMap tmA, Work W, BatchDev BW, int b0) {
+// NW = 8: warp w owns tile rows 8w..8w+7 and all eight column groups; NW = 16: warps w and w + 8 share the rows and split the
+// column groups (twice the warps to cover the DMMA and shared-memory latencies at one CTA per SM; the A fragments are read twice).
+template <int NW>
+__global__ void __launch_bounds__(32 * NW, 1) k_batch_chol_tma(const __grid_constant__ CUtensorMap tmA, Work W, BatchDev BW, int b0) {
     extern __shared__ __align__(1024) unsigned char cht_smem[];
     double* ring = reinterpret_cast<double*>(cht_smem);  // [2 stages][X tile, Y tile]
     double* sD = ring + 4 * CHT_TILE;                    // diagonal block, its factor, then the factor's inverse (row stride CH_LD)
@@ -590,7 +594,9 @@ __global__ void __launch_bounds__(256, 1) k_batch_chol_tma(const __grid_constant
     unsigned long long* bars = reinterpret_cast<unsigned long long*>(sC + 64 * CH_LD);
     const int bl = blockIdx.x, b = b0 + bl;
     if (W.done[b]) return;
-    const int Np = BW.Np, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    constexpr int NT = 32 * NW, NCT = 64 / NW;  // threads; column groups per warp (8 or 4)
+    const int Np = BW.Np, tid = threadIdx.x, lane = tid & 31;
+    const int warp = (tid >> 5) & 7, ct0 = ((tid >> 5) >> 3) * NCT;  // row group ; first column group
     const int g = lane >> 2, t = lane & 3;
     double* A = BW.A + (size_t)bl * Np * Np;
     __shared__ int s_bad;
@@ -630,9 +636,9 @@ __global__ void __launch_bounds__(256, 1) k_batch_chol_tma(const __grid_constant
         __syncthreads();
         for (int I0 = J0; I0 < Np; I0 += 64) {
             const bool diag = (I0 == J0);
-            double c[8][2];
+            double c[NCT][2];
 #pragma unroll
-            for (int ct = 0; ct < 8; ct++) c[ct][0] = c[ct][1] = 0.0;
+            for (int ct = 0; ct < NCT; ct++) c[ct][0] = c[ct][1] = 0.0;
             const int nk = J0 / CH_NB;
             if (nk > 0 && tid == 0) issue(cnt & 1, I0, J0, 0, diag);
             for (int kk = 0; kk < nk; kk++, cnt++) {
@@ -644,10 +650,10 @@ __global__ void __launch_bounds__(256, 1) k_batch_chol_tma(const __grid_constant
 #pragma unroll
                 for (int ks = 0; ks < 16; ks++) a[ks] = sX[(ks >> 2) * 1024 + arow + sw[ks & 3]];
 #pragma unroll
-                for (int ct = 0; ct < 8; ct++) {
-                    if (diag && ct > warp) continue;  // lower triangle only
+                for (int ct = 0; ct < NCT; ct++) {
+                    if (diag && ct0 + ct > warp) continue;  // lower triangle only
 #pragma unroll
-                    for (int ks = 0; ks < 16; ks++) dmma884(c[ct][0], c[ct][1], a[ks], sB[(ks >> 2) * 1024 + (8 * ct + pg) * 16 + sw[ks & 3]]);
+                    for (int ks = 0; ks < 16; ks++) dmma884(c[ct][0], c[ct][1], a[ks], sB[(ks >> 2) * 1024 + (8 * (ct0 + ct) + pg) * 16 + sw[ks & 3]]);
                 }
                 __syncthreads();  // the slot's readers are done: it is refilled by the issue of the next iteration
             }
@@ -657,9 +663,9 @@ __global__ void __launch_bounds__(256, 1) k_batch_chol_tma(const __grid_constant
                 const double* Arow = A + (size_t)(I0 + 8 * warp + pg) * Np + J0;
                 double* Crow = sCC + (8 * warp + pg) * CH_LD;
 #pragma unroll
-                for (int ct = 0; ct < 8; ct++) {
-                    Crow[8 * ct + pc0] = Arow[8 * ct + pc0] - c[ct][0];
-                    Crow[8 * ct + pc1] = Arow[8 * ct + pc1] - c[ct][1];
+                for (int ct = 0; ct < NCT; ct++) {
+                    Crow[8 * (ct0 + ct) + pc0] = Arow[8 * (ct0 + ct) + pc0] - c[ct][0];
+                    Crow[8 * (ct0 + ct) + pc1] = Arow[8 * (ct0 + ct) + pc1] - c[ct][1];
                 }
             }
             __syncthreads();
@@ -676,14 +682,14 @@ __global__ void __launch_bounds__(256, 1) k_batch_chol_tma(const __grid_constant
                     }
                     if (tid > j && tid < 64) sD[tid * CH_LD + j] /= d;
                     __syncthreads();
-                    for (int e = tid; e < 64 * 64; e += 256) {
+                    for (int e = tid; e < 64 * 64; e += NT) {
                         const int i = e >> 6, k = e & 63;
                         if (k > j && k <= i) sD[i * CH_LD + k] -= sD[i * CH_LD + j] * sD[k * CH_LD + j];
                     }
                 }
                 __syncthreads();
                 // write the factor back (upper part of the block zeroed) ; Linv into sC by forward substitution, one column per thread
-                for (int e = tid; e < 64 * 64; e += 256) {
+                for (int e = tid; e < 64 * 64; e += NT) {
                     const int i = e >> 6, k = e & 63;
                     const double v = (k <= i) ? sD[i * CH_LD + k] : 0.0;
                     sD[i * CH_LD + k] = v;
@@ -699,11 +705,11 @@ __global__ void __launch_bounds__(256, 1) k_batch_chol_tma(const __grid_constant
                     }
                 }
                 __syncthreads();
-                for (int e = tid; e < 64 * 64; e += 256) sD[(e >> 6) * CH_LD + (e & 63)] = sC[(e >> 6) * CH_LD + (e & 63)];
+                for (int e = tid; e < 64 * 64; e += NT) sD[(e >> 6) * CH_LD + (e & 63)] = sC[(e >> 6) * CH_LD + (e & 63)];
                 __syncthreads();
             } else {
                 // L(I,J) = C Linv^T
-                ch_xyT<false>(A + (size_t)I0 * Np + J0, Np, sC, sD, 1.0, false, warp, lane);
+                ch_xyT<false, NCT>(A + (size_t)I0 * Np + J0, Np, sC, sD, 1.0, false, warp, lane, ct0);
                 __syncthreads();  // sC is rewritten by the next block
             }
         }
@@ -1039,10 +1045,11 @@ inline int batch_run(cudaStream_t st, int device, const DevProblem& P, const Dev
     const size_t smem_asm = ((size_t)Sn * Sr + (size_t)Sn * Sn + Sn + H) * sizeof(double), smem_cp = (2 * (size_t)Sn * std::max(nw, 1) + (size_t)nw * (nw + 1)) * sizeof(double);
     static const bool chol_right_looking = getenv("ILQRB_CHOL_RL") != nullptr;  // A/B switch: the first (right-looking) kernel
     static const bool chol_no_tma = getenv("ILQRB_CHOL_NO_TMA") != nullptr;     // A/B switch: the register-staged left-looking kernel
+    static const int chol_tma_warps = getenv("ILQRB_CHOL_TMA_WARPS") ? atoi(getenv("ILQRB_CHOL_TMA_WARPS")) : 16;  // 8 | 16 warps per CTA
     CUtensorMap tmA;
     const bool use_tma = !cp && !chol_right_looking && !chol_no_tma && cht_make_tensor_map(&tmA, BW.A, BW.chunk, Np);
     {
-        static DynSmem a_chol, a_chol_ll, a_trsv, a_asm, a_cp, a_tma;  // per-device "raised to" values
+        static DynSmem a_chol, a_chol_ll, a_trsv, a_asm, a_cp, a_tma, a_tma16;  // per-device "raised to" values
         auto ens = [&](DynSmem& a, auto kern, size_t smem) -> int {
             if (smem <= 48 * 1024) return 0;
             const bool tracked = device >= 0 && device < MAX_DEVICES;
@@ -1053,7 +1060,7 @@ inline int batch_run(cudaStream_t st, int device, const DevProblem& P, const Dev
             return 0;
         };
         if ((rc = ens(a_chol, k_batch_chol, smem_chol)) || (rc = ens(a_chol_ll, k_batch_chol_ll, smem_chol)) || (rc = ens(a_trsv, k_batch_trsv, smem_trsv)) ||
-            (rc = ens(a_asm, k_batch_assemble, smem_asm)) || (rc = ens(a_cp, k_batch_cp, smem_cp)) || (use_tma && (rc = ens(a_tma, k_batch_chol_tma, smem_tma))))
+            (rc = ens(a_asm, k_batch_assemble, smem_asm)) || (rc = ens(a_cp, k_batch_cp, smem_cp)) || (use_tma && ((rc = ens(a_tma, k_batch_chol_tma<8>, smem_tma)) || (rc = ens(a_tma16, k_batch_chol_tma<16>, smem_tma)))))
             return rc;
     }
     for (int b0 = 0; b0 < B; b0 += BW.chunk) {
@@ -1071,7 +1078,8 @@ inline int batch_run(cudaStream_t st, int device, const DevProblem& P, const Dev
                 k_batch_syrk<<<dim3((unsigned)((Np / 8) * (Np / 64) + 3) / 4, nB), 128, 0, st>>>(dp, W, K, b0);
                 end();
                 begin(3);
-                if (use_tma) k_batch_chol_tma<<<nB, 256, smem_tma, st>>>(tmA, W, K, b0);
+                if (use_tma && chol_tma_warps == 8) k_batch_chol_tma<8><<<nB, 256, smem_tma, st>>>(tmA, W, K, b0);
+                else if (use_tma) k_batch_chol_tma<16><<<nB, 512, smem_tma, st>>>(tmA, W, K, b0);
                 else if (chol_right_looking) k_batch_chol<<<nB, 256, smem_chol, st>>>(W, K, b0);
                 else k_batch_chol_ll<<<nB, 256, smem_chol, st>>>(W, K, b0);
                 end();

@@ -21,7 +21,7 @@ with Handle(pb) as h:
     dt = time.perf_counter() - t0
     print("B %d ms/iter %.2f" % (B, dt * 1e3 / 3), {k: round(v[0], 2) for k, v in h.profile().items()}, "cost", float(out.cost.mean()), float(np.abs(out.U).sum()))
 PY
-for e in "" "ILQRB_CHOL_NO_TMA=1"; do echo "env $e"; env $e timeout 600 python /tmp/chol_bench.py 592; env $e timeout 600 python /tmp/chol_bench.py 1024; done > gpurun_out/${TAG}_sweep.txt 2>&1
+for e in "ILQRB_CHOL_TMA_WARPS=16" "ILQRB_CHOL_TMA_WARPS=8" "ILQRB_CHOL_NO_TMA=1"; do echo "env $e"; env $e timeout 600 python /tmp/chol_bench.py 592; env $e timeout 600 python /tmp/chol_bench.py 1024; done > gpurun_out/${TAG}_sweep.txt 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_batch_chol -c 1 -o gpurun_out/${TAG}_chol -f python /tmp/chol_bench.py 148 > gpurun_out/${TAG}_ncu_f.log 2>&1
 ncu -i gpurun_out/${TAG}_chol.ncu-rep --page raw --csv > gpurun_out/${TAG}_chol_raw.csv 2>/dev/null
 tail -4 gpurun_out/${TAG}_pytest.log; cat gpurun_out/${TAG}_sweep.txt
