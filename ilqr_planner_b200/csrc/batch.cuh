@@ -586,7 +586,7 @@ __device__ __forceinline__ void cht_wait(unsigned long long* bar, unsigned parit
 // NW = 8: warp w owns tile rows 8w..8w+7 and all eight column groups; NW = 16: warps w and w + 8 share the rows and split the
 // column groups (twice the warps to cover the DMMA and shared-memory latencies at one CTA per SM; the A fragments are read twice).
 template <int NW>
-__global__ void __launch_bounds__(32 * NW, 1) k_batch_chol_tma(const __grid_constant__ CUtensorMap tmA, Work W, BatchDev BW, int b0) {
+__global__ void __launch_bounds__(32 * NW, 1) k_batch_chol_tma(const __grid_constant__ CUtensorMap tmA, const DevProblem* __restrict__ Pp, Work W, BatchDev BW, int b0) {
     extern __shared__ __align__(1024) unsigned char cht_smem[];
     double* ring = reinterpret_cast<double*>(cht_smem);  // [2 stages][X tile, Y tile]
     double* sD = ring + 4 * CHT_TILE;                    // diagonal block, its factor, then the factor's inverse (row stride CH_LD)
@@ -630,6 +630,7 @@ __global__ void __launch_bounds__(32 * NW, 1) k_batch_chol_tma(const __grid_cons
         }
     };
     unsigned cnt = 0;  // block products so far: stage = cnt % 2, phase parity = (cnt / 2) % 2
+    bool prefetched = false;  // the first tiles of the coming block are already on their way
     for (int J0 = 0; J0 < Np; J0 += CH_NB) {
         // the blocks of column J0 - 64 were written with ordinary stores: order them before the copy engine's reads
         asm volatile("fence.proxy.async;" ::: "memory");
@@ -640,7 +641,8 @@ __global__ void __launch_bounds__(32 * NW, 1) k_batch_chol_tma(const __grid_cons
 #pragma unroll
             for (int ct = 0; ct < NCT; ct++) c[ct][0] = c[ct][1] = 0.0;
             const int nk = J0 / CH_NB;
-            if (nk > 0 && tid == 0) issue(cnt & 1, I0, J0, 0, diag);
+            if (nk > 0 && tid == 0 && !prefetched) issue(cnt & 1, I0, J0, 0, diag);
+            prefetched = false;
             for (int kk = 0; kk < nk; kk++, cnt++) {
                 if (tid == 0 && kk + 1 < nk) issue((cnt + 1) & 1, I0, J0, (kk + 1) * CH_NB, diag);
                 const double* sX = ring + (size_t)(cnt & 1) * 2 * CHT_TILE;
@@ -657,15 +659,38 @@ __global__ void __launch_bounds__(32 * NW, 1) k_batch_chol_tma(const __grid_cons
                 }
                 __syncthreads();  // the slot's readers are done: it is refilled by the issue of the next iteration
             }
+            // the first operand tiles of the next block of this column travel while this block is finished (its slot's readers passed
+            // the barrier of product cnt - 2; a column's first block is not prefetched: it reads blocks this column is still writing)
+            if (nk > 0 && I0 + 64 < Np) {
+                if (tid == 0) issue(cnt & 1, I0 + 64, J0, 0, false);
+                prefetched = true;
+            }
             // C = A(I,J) - sum, into shared memory (the diagonal block into sD, the others into sC)
+            // lstq_A(I,J) = Su(:,I)^T T(:,J) + R (BatchILQR.cpp:130; identity on the padding) is formed here, from the rank-SnP factors,
+            // instead of being written by k_batch_syrk and read back (2 x 20 MB per problem and iteration at C4)
             double* sCC = diag ? sD : sC;
             {
-                const double* Arow = A + (size_t)(I0 + 8 * warp + pg) * Np + J0;
+                const int SnP = BW.SnP, N = BW.N, m = Pp->m;
+                const double* Su = BW.Su + (size_t)bl * SnP * Np + I0 + 8 * warp + pg;
+                const double* Tm = BW.T + (size_t)bl * SnP * Np + J0 + pg;
+                double e[NCT][2];
+#pragma unroll
+                for (int ct = 0; ct < NCT; ct++) e[ct][0] = e[ct][1] = 0.0;
+                for (int ks = 0; ks < SnP / 4; ks++) {
+                    const double av = Su[(size_t)(4 * ks + t) * Np];
+#pragma unroll
+                    for (int ct = 0; ct < NCT; ct++) dmma884(e[ct][0], e[ct][1], av, Tm[(size_t)(4 * ks + t) * Np + 8 * (ct0 + ct)]);
+                }
+                const int gi = I0 + 8 * warp + pg;
                 double* Crow = sCC + (8 * warp + pg) * CH_LD;
 #pragma unroll
                 for (int ct = 0; ct < NCT; ct++) {
-                    Crow[8 * (ct0 + ct) + pc0] = Arow[8 * (ct0 + ct) + pc0] - c[ct][0];
-                    Crow[8 * (ct0 + ct) + pc1] = Arow[8 * (ct0 + ct) + pc1] - c[ct][1];
+                    const int j0 = 8 * (ct0 + ct) + pc0, j1 = 8 * (ct0 + ct) + pc1;
+                    double v0 = e[ct][0], v1 = e[ct][1];
+                    if (gi == J0 + j0) v0 += (gi < N) ? Pp->r_diag[gi % m] : 1.0;
+                    if (gi == J0 + j1) v1 += (gi < N) ? Pp->r_diag[gi % m] : 1.0;
+                    Crow[j0] = v0 - c[ct][0];
+                    Crow[j1] = v1 - c[ct][1];
                 }
             }
             __syncthreads();
@@ -1074,12 +1099,14 @@ inline int batch_run(cudaStream_t st, int device, const DevProblem& P, const Dev
             k_batch_assemble<<<nB, 256, smem_asm, st>>>(dp, W, K, b0);
             end();
             if (!cp) {
-                begin(2);
-                k_batch_syrk<<<dim3((unsigned)((Np / 8) * (Np / 64) + 3) / 4, nB), 128, 0, st>>>(dp, W, K, b0);
-                end();
+                if (!use_tma) {  // the TMA factorisation forms the blocks of lstq_A itself
+                    begin(2);
+                    k_batch_syrk<<<dim3((unsigned)((Np / 8) * (Np / 64) + 3) / 4, nB), 128, 0, st>>>(dp, W, K, b0);
+                    end();
+                }
                 begin(3);
-                if (use_tma && chol_tma_warps == 8) k_batch_chol_tma<8><<<nB, 256, smem_tma, st>>>(tmA, W, K, b0);
-                else if (use_tma) k_batch_chol_tma<16><<<nB, 512, smem_tma, st>>>(tmA, W, K, b0);
+                if (use_tma && chol_tma_warps == 8) k_batch_chol_tma<8><<<nB, 256, smem_tma, st>>>(tmA, dp, W, K, b0);
+                else if (use_tma) k_batch_chol_tma<16><<<nB, 512, smem_tma, st>>>(tmA, dp, W, K, b0);
                 else if (chol_right_looking) k_batch_chol<<<nB, 256, smem_chol, st>>>(W, K, b0);
                 else k_batch_chol_ll<<<nB, 256, smem_chol, st>>>(W, K, b0);
                 end();
