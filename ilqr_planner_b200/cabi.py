@@ -16,6 +16,7 @@ JOINT_FIXED, JOINT_ROT, JOINT_TRANS = 0, 1, 2
 KP_STRIDE = 15
 N_ALPHA = 11
 MAX_SEGMENTS = 24
+BATCH_WOODBURY = 1
 SD_LOGMAP, SD_EXPMAP, SD_DISTANCE, SD_TRANSPORT, SD_DQUAT_TO_W_JAC = range(5)
 KIN_STATIC_MAX_NQ = 4096
 ST_NAN_COST, ST_QUU_NOT_SPD, ST_EARLY_STOP = 1, 2, 4
@@ -61,7 +62,7 @@ class ALDesc(C.Structure):
 
 
 class BatchDesc(C.Structure):
-    _fields_ = [("Q", c_double_p), ("psi", c_double_p), ("nw", C.c_int32), ("pad_", C.c_int32)]
+    _fields_ = [("Q", c_double_p), ("psi", c_double_p), ("nw", C.c_int32), ("flags", C.c_int32)]
 
 
 class SolveOpts(C.Structure):

@@ -908,6 +908,83 @@ __global__ void __launch_bounds__(128) k_batch_cp(const DevProblem* __restrict__
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// OPTIONAL fast mode of BatchILQR (ILQRB_BATCH_WOODBURY).  Not the reference's algorithm: lstq_A = R + Su^T W Su is a
+// rank-Sn update (Sn = keypoint steps x n, 16 at C4) of the diagonal R, so  du = lstq_A^-1 rhs  follows from the Woodbury identity
+//   du = R^-1 (rhs - Su^T y),   (I + W G) y = W z,   G = Su R^-1 Su^T,   z = Su R^-1 rhs
+// with one Sn x Sn system instead of the N x N factorisation (N = 1592: 10^4 times fewer flops).  The answer differs from the dense
+// path's in its rounding (cond(lstq_A) eps either way); it is parity-checked on its own (tests) and never the reported number.
+__global__ void __launch_bounds__(128) k_batch_woodbury(const DevProblem* __restrict__ Pp, Work W, BatchDev BW, int b0) {
+    extern __shared__ double sm[];
+    const DevProblem& P = *Pp;
+    const int bl = blockIdx.x, b = b0 + bl;
+    if (W.done[b]) return;
+    const int Sn = BW.Sn, N = BW.N, Np = BW.Np, m = P.m, tid = threadIdx.x, ld = Sn + 1;
+    double* sG = sm;             // [Sn][Sn]   G, then W G
+    double* sM = sG + Sn * Sn;   // [Sn][Sn+1] augmented system (I + W G | W z)
+    double* sz = sM + Sn * ld;   // [Sn]
+    const double* Su = BW.Su + (size_t)bl * BW.SnP * Np;
+    const double* Wm = BW.Wm + (size_t)bl * Sn * Sn;
+    const double* rhs = BW.rhs + (size_t)bl * Np;
+    for (int idx = tid; idx < Sn * (Sn + 1); idx += blockDim.x) {
+        const int k = idx / (Sn + 1), k2 = idx % (Sn + 1);
+        double v = 0.0;
+        if (k2 < Sn) {
+            for (int col = 0; col < N; col++) v += (Su[(size_t)k * Np + col] / P.r_diag[col % m]) * Su[(size_t)k2 * Np + col];
+            sG[k * Sn + k2] = v;
+        } else {
+            for (int col = 0; col < N; col++) v += (Su[(size_t)k * Np + col] / P.r_diag[col % m]) * rhs[col];
+            sz[k] = v;
+        }
+    }
+    __syncthreads();
+    for (int idx = tid; idx < Sn * ld; idx += blockDim.x) {
+        const int k = idx / ld, k2 = idx % ld;
+        double v = 0.0;
+        if (k2 < Sn) {
+            for (int q = 0; q < Sn; q++) v += Wm[k * Sn + q] * sG[q * Sn + k2];
+            if (k == k2) v += 1.0;
+        } else {
+            for (int q = 0; q < Sn; q++) v += Wm[k * Sn + q] * sz[q];
+        }
+        sM[idx] = v;
+    }
+    __syncthreads();
+    if (tid == 0) {  // Sn is small: Gaussian elimination with partial pivoting
+        for (int k = 0; k < Sn; k++) {
+            int piv = k;
+            double best = fabs(sM[k * ld + k]);
+            for (int i = k + 1; i < Sn; i++)
+                if (fabs(sM[i * ld + k]) > best) {
+                    best = fabs(sM[i * ld + k]);
+                    piv = i;
+                }
+            if (piv != k)
+                for (int j = 0; j < ld; j++) {
+                    const double tmp = sM[k * ld + j];
+                    sM[k * ld + j] = sM[piv * ld + j];
+                    sM[piv * ld + j] = tmp;
+                }
+            const double d = sM[k * ld + k];
+            for (int i = k + 1; i < Sn; i++) {
+                const double f = sM[i * ld + k] / d;
+                for (int j = k; j < ld; j++) sM[i * ld + j] -= f * sM[k * ld + j];
+            }
+        }
+        for (int k = Sn - 1; k >= 0; k--) {
+            double acc = sM[k * ld + Sn];
+            for (int j = k + 1; j < Sn; j++) acc -= sM[k * ld + j] * sM[j * ld + Sn];
+            sM[k * ld + Sn] = acc / sM[k * ld + k];
+        }
+    }
+    __syncthreads();
+    for (int col = tid; col < N; col += blockDim.x) {
+        double v = rhs[col];
+        for (int k = 0; k < Sn; k++) v -= Su[(size_t)k * Np + col] * sM[k * ld + Sn];
+        BW.du[(size_t)b * N + col] = v / P.r_diag[col % m];
+    }
+}
+
 // Su-only variant of the assemble kernel is not needed: k_batch_assemble also serves the CP path (T and rhs unused there).
 
 // ------------------------------------------------------------------------------------------------------------
@@ -1002,6 +1079,7 @@ inline int batch_run(cudaStream_t st, int device, const DevProblem& P, const Dev
     const int B = P.B, H = P.H, n = P.n, m = P.m, r = P.r, S = P.n_kp_steps;
     const int N = (H - 1) * m, Np = (N + 63) / 64 * 64, Sn = S * n, SnP = (Sn + 3) / 4 * 4, Sr = nk * r;
     const int nw = (bd && bd->psi) ? bd->nw : 0, cp = nw > 0;
+    const bool woodbury = bd && (bd->flags & ILQRB_BATCH_WOODBURY) && !cp;
     if (cp && nw > 128) {
         err = "BatchILQRCP: more than 128 primitive weights";
         return ILQRB_EUNSUPPORTED;
@@ -1072,9 +1150,14 @@ inline int batch_run(cudaStream_t st, int device, const DevProblem& P, const Dev
     static const bool chol_no_tma = getenv("ILQRB_CHOL_NO_TMA") != nullptr;     // A/B switch: the register-staged left-looking kernel
     static const int chol_tma_warps = getenv("ILQRB_CHOL_TMA_WARPS") ? atoi(getenv("ILQRB_CHOL_TMA_WARPS")) : 16;  // 8 | 16 warps per CTA
     CUtensorMap tmA;
-    const bool use_tma = !cp && !chol_right_looking && !chol_no_tma && cht_make_tensor_map(&tmA, BW.A, BW.chunk, Np);
+    const bool use_tma = !cp && !woodbury && !chol_right_looking && !chol_no_tma && cht_make_tensor_map(&tmA, BW.A, BW.chunk, Np);
+    const size_t smem_wb = ((size_t)Sn * Sn + (size_t)Sn * (Sn + 1) + Sn) * sizeof(double);
+    if (woodbury && smem_wb > 200 * 1024) {
+        err = "BatchILQR Woodbury mode: too many keypoint rows for the shared-memory reduced system";
+        return ILQRB_EUNSUPPORTED;
+    }
     {
-        static DynSmem a_chol, a_chol_ll, a_trsv, a_asm, a_cp, a_tma, a_tma16;  // per-device "raised to" values
+        static DynSmem a_chol, a_chol_ll, a_trsv, a_asm, a_cp, a_tma, a_tma16, a_wb;  // per-device "raised to" values
         auto ens = [&](DynSmem& a, auto kern, size_t smem) -> int {
             if (smem <= 48 * 1024) return 0;
             const bool tracked = device >= 0 && device < MAX_DEVICES;
@@ -1085,7 +1168,8 @@ inline int batch_run(cudaStream_t st, int device, const DevProblem& P, const Dev
             return 0;
         };
         if ((rc = ens(a_chol, k_batch_chol, smem_chol)) || (rc = ens(a_chol_ll, k_batch_chol_ll, smem_chol)) || (rc = ens(a_trsv, k_batch_trsv, smem_trsv)) ||
-            (rc = ens(a_asm, k_batch_assemble, smem_asm)) || (rc = ens(a_cp, k_batch_cp, smem_cp)) || (use_tma && ((rc = ens(a_tma, k_batch_chol_tma<8>, smem_tma)) || (rc = ens(a_tma16, k_batch_chol_tma<16>, smem_tma)))))
+            (rc = ens(a_asm, k_batch_assemble, smem_asm)) || (rc = ens(a_cp, k_batch_cp, smem_cp)) || (use_tma && ((rc = ens(a_tma, k_batch_chol_tma<8>, smem_tma)) || (rc = ens(a_tma16, k_batch_chol_tma<16>, smem_tma)))) ||
+            (woodbury && (rc = ens(a_wb, k_batch_woodbury, smem_wb))))
             return rc;
     }
     for (int b0 = 0; b0 < B; b0 += BW.chunk) {
@@ -1098,7 +1182,11 @@ inline int batch_run(cudaStream_t st, int device, const DevProblem& P, const Dev
             begin(1);
             k_batch_assemble<<<nB, 256, smem_asm, st>>>(dp, W, K, b0);
             end();
-            if (!cp) {
+            if (woodbury) {
+                begin(3);
+                k_batch_woodbury<<<nB, 128, smem_wb, st>>>(dp, W, K, b0);
+                end();
+            } else if (!cp) {
                 if (!use_tma) {  // the TMA factorisation forms the blocks of lstq_A itself
                     begin(2);
                     k_batch_syrk<<<dim3((unsigned)((Np / 8) * (Np / 64) + 3) / 4, nB), 128, 0, st>>>(dp, W, K, b0);

@@ -211,8 +211,12 @@ struct BwdN1Smem {
 // (composite robots, C5): l_xx, R and the dynamics are block diagonal there, so P, Quu and K are — in the reference's dense
 // arithmetic too, where the off-diagonal blocks are sums and products of exact zeros — and the pass splits into
 // independent passes per block; strides stay those of the full state.
-template <int NT, int DOF>
-__device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work& W, int b, int lane, double* wsmem, const int off = 0, const int nsub = 0) {
+// PIVOT = false (the kernels' first pass): the unpivoted eliminations only; returns false (warp-uniform) if some pivot was not positive.
+// PIVOT = true  (the out-of-line second pass of such a problem, rare): a step whose elimination meets a non-positive pivot is
+// redone with the reference's partial-pivot LU inverse (wmat.cuh wm_inverse_pivoted).  The fallback code lives in the second pass
+// only: inside the first it cost registers in the step loop (72-register cap: spills, 251 -> 276 us per launch at C2).
+template <int NT, int DOF, bool PIVOT = false>
+__device__ __forceinline__ bool backward_n1_body(const DevProblem& P, const Work& W, int b, int lane, double* wsmem, const int off = 0, const int nsub = 0) {
     using S = BwdN1Smem<NT>;
     constexpr int LD = S::LD, SZ = S::SZ;
     const int g = lane >> 2, t = lane & 3;
@@ -381,15 +385,20 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
         // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]                                            ILQRRecursive.cpp:89-91
         double Kd[NT][NT][2];
         if constexpr (NT == 1) {  // explicit inverse, then the product on DMMA
-            const bool okk = __all_sync(0xffffffffu, gj_inverse_regs<NT, DOF, LD>(Inv, sKd, m, g, t));
-            if (!okk) {  // a pivot was not positive: Quu + 1e-6 I again, for the reference's pivoted LU inverse (rare)
-                spd = false;
-                const int j = 2 * t;
-                Inv[0][0][0] = Quu[0][0][0] + ((g == j) ? ((g < m) ? 1e-6 * 1.0 : 1.0) : 0.0);
-                Inv[0][0][1] = Quu[0][0][1] + ((g == j + 1) ? ((g < m) ? 1e-6 * 1.0 : 1.0) : 0.0);
+            if constexpr (PIVOT) {
+                const bool okk = __all_sync(0xffffffffu, gj_inverse_regs<NT, DOF, LD>(Inv, sKd, m, g, t));
+                if (!okk) {  // a pivot was not positive: Quu + 1e-6 I again, for the reference's pivoted LU inverse
+                    spd = false;
+                    const int j = 2 * t;
+                    Inv[0][0][0] = Quu[0][0][0] + ((g == j) ? ((g < m) ? 1e-6 * 1.0 : 1.0) : 0.0);
+                    Inv[0][0][1] = Quu[0][0][1] + ((g == j + 1) ? ((g < m) ? 1e-6 * 1.0 : 1.0) : 0.0);
+                }
+                st_c<NT, LD>(sM, Inv, g, t);
+                if (!okk) wm_inverse_pivoted(sM, LD, m, sKd, lane);
+            } else {
+                spd = gj_inverse_regs<NT, DOF, LD>(Inv, sKd, m, g, t) && spd;
+                st_c<NT, LD>(sM, Inv, g, t);
             }
-            st_c<NT, LD>(sM, Inv, g, t);
-            if (!okk) wm_inverse_pivoted(sM, LD, m, sKd, lane);
             __syncwarp();
             double c0 = 0.0, c1 = 0.0;
 #pragma unroll
@@ -404,7 +413,9 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
                     Kd[rt][ct][0] = -Qa[rt][ct][0];
                     Kd[rt][ct][1] = -Qa[rt][ct][1];
                 }
-            if (!__all_sync(0xffffffffu, gj_solve_regs<NT, DOF>(Inv, Kd, m, g, t))) {
+            const bool oks = gj_solve_regs<NT, DOF>(Inv, Kd, m, g, t);
+            if constexpr (!PIVOT) spd = oks && spd;
+            if (PIVOT && !__all_sync(0xffffffffu, oks)) {
                 // a pivot was not positive: the reference's pivoted LU inverse of Quu + 1e-6 I, then the product (rare, plain loops)
                 spd = false;
                 __syncwarp();
@@ -506,7 +517,19 @@ __device__ __forceinline__ void backward_n1_body(const DevProblem& P, const Work
             }
         __syncwarp();  // shared operands are rewritten by the next step
     }
-    if (!__all_sync(0xffffffffu, spd) && lane == 0) atomicOr(W.status + b, ILQRB_ST_QUU_NOT_SPD);
+    return __all_sync(0xffffffffu, spd);
+}
+// second pass of a problem whose first pass met a non-positive pivot: the same recursion with the pivoted fallback, out of line
+template <int NT, int DOF>
+__device__ __noinline__ void backward_n1_redo(const DevProblem& P, const Work& W, int b, int lane, double* wsmem, int off, int nsub) {
+    backward_n1_body<NT, DOF, true>(P, W, b, lane, wsmem, off, nsub);
+}
+template <int NT, int DOF>
+__device__ __forceinline__ void backward_n1_run(const DevProblem& P, const Work& W, int b, int lane, double* wsmem, const int off = 0, const int nsub = 0) {
+    if (!backward_n1_body<NT, DOF, false>(P, W, b, lane, wsmem, off, nsub)) {
+        if (lane == 0) atomicOr(W.status + b, ILQRB_ST_QUU_NOT_SPD);
+        backward_n1_redo<NT, DOF>(P, W, b, lane, wsmem, off, nsub);
+    }
 }
 
 // diagonal blocks of the state that no task couples (ilqrb_api.cu: find_state_blocks)
@@ -524,7 +547,7 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1_blocks(const D
     if (bl >= nB) return;
     const int b = b0 + bl;
     if (W.done[b]) return;
-    backward_n1_body<1, DOF>(*Pp, W, b, lane, smem + (size_t)wid * BwdN1Smem<1>::PER_WARP, sb.off[blk], sb.size[blk]);
+    backward_n1_run<1, DOF>(*Pp, W, b, lane, smem + (size_t)wid * BwdN1Smem<1>::PER_WARP, sb.off[blk], sb.size[blk]);
 }
 
 template <int NT, int DOF, int WARPS, int MINB>
@@ -535,7 +558,7 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n1(const DevProbl
     if (bl >= nB) return;
     const int b = b0 + bl;
     if (W.done[b]) return;
-    backward_n1_body<NT, DOF>(*Pp, W, b, lane, smem + (size_t)wid * BwdN1Smem<NT>::PER_WARP);
+    backward_n1_run<NT, DOF>(*Pp, W, b, lane, smem + (size_t)wid * BwdN1Smem<NT>::PER_WARP);
 }
 
 // ------------------------------------------------------------------------------------------------------------

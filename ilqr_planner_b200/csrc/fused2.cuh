@@ -29,8 +29,10 @@ __device__ __forceinline__ void st_w(double* M, const double (&e)[2][2], int g, 
     for (int c = 0; c < 2; c++) *reinterpret_cast<double2*>(M + g * BwdN2Smem::LDW + 8 * c + 2 * t) = make_double2(e[c][0], e[c][1]);
 }
 
-template <int DOF, bool AL>
-__device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work& W, int b, int lane, double* wsmem, double penalty_frozen) {
+// PIVOT: see backward_n1_body (fused1.cuh) — false = first pass, unpivoted only, returns whether every pivot was positive;
+// true = the out-of-line second pass with the pivoted fallback.
+template <int DOF, bool AL, bool PIVOT = false>
+__device__ __forceinline__ bool backward_n2_body(const DevProblem& P, const Work& W, int b, int lane, double* wsmem, double penalty_frozen) {
     using S = BwdN2Smem;
     const int g = lane >> 2, t = lane & 3;
     const int dof = DOF > 0 ? DOF : P.dof, n = 2 * dof, m = dof, H = P.H;
@@ -195,15 +197,20 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
         // area), then the product on DMMA                                                ILQRRecursive.cpp:89-91
         st_w(sM, Qa, g, t);
         double Iv[1][1][2] = {{{Lr[0], Lr[1]}}};
-        const bool okk = __all_sync(0xffffffffu, gj_inverse_regs<1, DOF, S::LDW>(Iv, sKd, m, g, t));
-        if (!okk) {  // a pivot was not positive: Quu + 1e-6 I again, for the reference's pivoted LU inverse (rare)
-            spd = false;
-            Iv[0][0][0] = Lr[0];
-            Iv[0][0][1] = Lr[1];
+        bool okk = true;
+        if constexpr (PIVOT) {
+            okk = __all_sync(0xffffffffu, gj_inverse_regs<1, DOF, S::LDW>(Iv, sKd, m, g, t));
+            if (!okk) {  // a pivot was not positive: Quu + 1e-6 I again, for the reference's pivoted LU inverse
+                spd = false;
+                Iv[0][0][0] = Lr[0];
+                Iv[0][0][1] = Lr[1];
+            }
+        } else {
+            spd = gj_inverse_regs<1, DOF, S::LDW>(Iv, sKd, m, g, t) && spd;
         }
         *reinterpret_cast<double2*>(sInv + g * S::LDQ + 2 * t) = make_double2(Iv[0][0][0], Iv[0][0][1]);
         *reinterpret_cast<double2*>(sQuu + g * S::LDQ + 2 * t) = make_double2(Quu[0], Quu[1]);  // un-regularised, for the P update
-        if (!okk) wm_inverse_pivoted(sInv, S::LDQ, m, sKd, lane);
+        if (PIVOT && !okk) wm_inverse_pivoted(sInv, S::LDQ, m, sKd, lane);
         __syncwarp();
         double Kd[2][2];
         {
@@ -281,7 +288,11 @@ __device__ __forceinline__ void backward_n2_body(const DevProblem& P, const Work
             }
         __syncwarp();
     }
-    if (!__all_sync(0xffffffffu, spd) && lane == 0) W.status[b] |= ILQRB_ST_QUU_NOT_SPD;
+    return __all_sync(0xffffffffu, spd);
+}
+template <int DOF, bool AL>
+__device__ __noinline__ void backward_n2_redo(const DevProblem& P, const Work& W, int b, int lane, double* wsmem, double penalty_frozen) {
+    backward_n2_body<DOF, AL, true>(P, W, b, lane, wsmem, penalty_frozen);
 }
 
 template <int DOF, bool AL, int WARPS, int MINB>
@@ -292,7 +303,11 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_n2(const DevProbl
     if (bl >= nB) return;
     const int b = b0 + bl;
     if (W.done[b]) return;
-    backward_n2_body<DOF, AL>(*Pp, W, b, lane, smem + (size_t)wid * BwdN2Smem::PER_WARP, penalty_frozen);
+    double* ws = smem + (size_t)wid * BwdN2Smem::PER_WARP;
+    if (!backward_n2_body<DOF, AL, false>(*Pp, W, b, lane, ws, penalty_frozen)) {
+        if (lane == 0) atomicOr(W.status + b, ILQRB_ST_QUU_NOT_SPD);
+        backward_n2_redo<DOF, AL>(*Pp, W, b, lane, ws, penalty_frozen);
+    }
 }
 
 }  // namespace ilqrb

@@ -39,8 +39,9 @@ __device__ __forceinline__ void st_c2(double* M, const double (&e)[2][2], int g,
 }
 
 // DOF > 0: dof at compile time (n = m = DOF + 1); DOF == 0: read from the problem
-template <int DOF>
-__device__ __forceinline__ void backward_time_body(const DevProblem& P, const Work& W, int b, int lane, double* wsmem) {
+// PIVOT: see backward_n1_body (fused1.cuh)
+template <int DOF, bool PIVOT = false>
+__device__ __forceinline__ bool backward_time_body(const DevProblem& P, const Work& W, int b, int lane, double* wsmem) {
     constexpr unsigned FULL = 0xffffffffu;
     constexpr int LD = BwdTimeSmem::LD, SZ = BwdTimeSmem::SZ;
     const int g = lane >> 2, t = lane & 3;
@@ -184,14 +185,19 @@ __device__ __forceinline__ void backward_time_body(const DevProblem& P, const Wo
             st_c2(sQuu, QQ, g, t);
         }
         // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]                                            ILQRRecursive.cpp:89-91
-        const bool okk = __all_sync(FULL, gj_inverse_regs<1, (DOF > 0 ? DOF + 1 : 0), LD>(Inv, sKd, m, g, t));
-        if (!okk) {  // a pivot was not positive: Quu + 1e-6 I again, for the reference's pivoted LU inverse (rare)
-            spd = false;
-            Inv[0][0][0] = (g == j0) ? ((g < m) ? Quu[0] + 1e-6 * 1.0 : 1.0) : Quu[0];
-            Inv[0][0][1] = (g == j1) ? ((g < m) ? Quu[1] + 1e-6 * 1.0 : 1.0) : Quu[1];
+        bool okk = true;
+        if constexpr (PIVOT) {
+            okk = __all_sync(FULL, gj_inverse_regs<1, (DOF > 0 ? DOF + 1 : 0), LD>(Inv, sKd, m, g, t));
+            if (!okk) {  // a pivot was not positive: Quu + 1e-6 I again, for the reference's pivoted LU inverse
+                spd = false;
+                Inv[0][0][0] = (g == j0) ? ((g < m) ? Quu[0] + 1e-6 * 1.0 : 1.0) : Quu[0];
+                Inv[0][0][1] = (g == j1) ? ((g < m) ? Quu[1] + 1e-6 * 1.0 : 1.0) : Quu[1];
+            }
+        } else {
+            spd = gj_inverse_regs<1, (DOF > 0 ? DOF + 1 : 0), LD>(Inv, sKd, m, g, t) && spd;
         }
         *reinterpret_cast<double2*>(sM + g * LD + 2 * t) = make_double2(Inv[0][0][0], Inv[0][0][1]);
-        if (!okk) wm_inverse_pivoted(sM, LD, m, sKd, lane);
+        if (PIVOT && !okk) wm_inverse_pivoted(sM, LD, m, sKd, lane);
         __syncwarp();
         double Kd[2][2];
 #pragma unroll
@@ -247,7 +253,11 @@ __device__ __forceinline__ void backward_time_body(const DevProblem& P, const Wo
         }
         __syncwarp();  // shared operands are rewritten by the next step
     }
-    if (!__all_sync(FULL, spd) && lane == 0) atomicOr(W.status + b, ILQRB_ST_QUU_NOT_SPD);
+    return __all_sync(FULL, spd);
+}
+template <int DOF>
+__device__ __noinline__ void backward_time_redo(const DevProblem& P, const Work& W, int b, int lane, double* wsmem) {
+    backward_time_body<DOF, true>(P, W, b, lane, wsmem);
 }
 
 template <int DOF, int WARPS, int MINB>
@@ -258,7 +268,11 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_backward_time(const DevPro
     if (bl >= nB) return;
     const int b = b0 + bl;
     if (W.done[b]) return;
-    backward_time_body<DOF>(*Pp, W, b, lane, smem + (size_t)wid * BwdTimeSmem::PER_WARP);
+    double* ws = smem + (size_t)wid * BwdTimeSmem::PER_WARP;
+    if (!backward_time_body<DOF, false>(*Pp, W, b, lane, ws)) {
+        if (lane == 0) atomicOr(W.status + b, ILQRB_ST_QUU_NOT_SPD);
+        backward_time_redo<DOF>(*Pp, W, b, lane, ws);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------------------------------------

@@ -17,10 +17,10 @@ def make_al_desc(A, b, lambda0, lag_update_step, penalty, scaling_factor):
     return al
 
 
-def make_batch_desc(Q=None, psi=None):
+def make_batch_desc(Q=None, psi=None, woodbury=False):
     Q = None if Q is None else np.ascontiguousarray(np.asarray(Q, dtype=np.float64))
     psi = None if psi is None else np.ascontiguousarray(np.asarray(psi, dtype=np.float64))
-    bd = cabi.BatchDesc(cabi.dptr(Q), cabi.dptr(psi), 0 if psi is None else psi.shape[1], 0)
+    bd = cabi.BatchDesc(cabi.dptr(Q), cabi.dptr(psi), 0 if psi is None else psi.shape[1], cabi.BATCH_WOODBURY if woodbury else 0)
     bd._keep = (Q, psi)
     return bd
 
@@ -86,8 +86,9 @@ class Handle:
         cabi.check(self.lib.ilqrb_solve_al(self.h, cabi.dptr(U0), C.byref(al), C.byref(o), C.byref(out.res)))
         return out
 
-    def solve_batch(self, u0, nb_iter, early_stop=False, Q=None, psi=None, out=None):
-        bd = make_batch_desc(Q, psi)
+    def solve_batch(self, u0, nb_iter, early_stop=False, Q=None, psi=None, out=None, woodbury=False):
+        """woodbury=True: the optional reduced solve of ilqrb.h ILQRB_BATCH_WOODBURY (BatchILQR only; not the reference's algorithm)"""
+        bd = make_batch_desc(Q, psi, woodbury)
         out = out or ResultBuffers(self.pb, nb_iter, "batch")
         u0 = self._u(u0)
         o = opts(nb_iter, True, early_stop)

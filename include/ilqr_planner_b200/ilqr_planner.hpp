@@ -4,6 +4,7 @@
 #include "dense.hpp"
 #include "keypoint.hpp"
 #include "sd.hpp"
+#include "serialize.hpp"
 #include "sim.hpp"
 #include "solver.hpp"
 #include "system.hpp"

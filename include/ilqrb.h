@@ -5,7 +5,7 @@
  * reference has no C ABI: its boundary is the C++ classes in
  * ilqr_planner/ilqr_planner/include/ilqr_planner/{sim,system,solver}/ and the
  * pybind11 module pylqr_planner/src/bindings.cpp.  The C++ host classes of this
- * repo (include/ilqr_planner_b200/*.hpp, PyLQR/) keep those names and flatten themselves into the POD
+ * repo (include/ilqr_planner_b200/, PyLQR/) keep those names and flatten themselves into the POD
  * descriptor below; every entry point cites the reference method it replaces.
  *
  * Conventions
@@ -165,8 +165,12 @@ typedef struct ilqrb_batch_desc {
     const double* Q;   /* optional [(Kp r)][(Kp r)] precision override shared by the batch; NULL = block-diag of keypoints */
     const double* psi; /* CP only: [N][nw] control primitives, N = m (H-1); NULL for BatchILQR */
     int32_t nw;
-    int32_t pad_;
+    int32_t flags;     /* 0, or ILQRB_BATCH_WOODBURY (was padding, must be 0, before ABI 2) */
 } ilqrb_batch_desc;
+/* BatchILQR only, OPTIONAL and not the reference's algorithm: du = lstq_A^-1 rhs through the Woodbury identity on the rank
+ * (keypoint steps x n) update of the diagonal R instead of the dense N x N factorisation (BatchILQR.cpp:132).  Same answer up to
+ * rounding (cond(lstq_A) eps); parity-checked on its own, never the benchmarked path.                                        */
+#define ILQRB_BATCH_WOODBURY 1
 
 typedef struct ilqrb_solve_opts {
     int32_t nb_iter;

@@ -467,6 +467,31 @@ def test_time_system_fast_path_equals_generic_path():
         assert rel(a["X"][same], b["X"][same]) < 1e-4
 
 
+@pytest.mark.parametrize("case", ["posorn", "time"])
+def test_batch_ilqr_woodbury_option(oracle_lib, case):
+    """the optional Woodbury solve (ILQRB_BATCH_WOODBURY: one (keypoint steps x n)^2 system instead of the N x N factorisation; not the
+    reference's algorithm) gives the dense path's answer to the accuracy either has, and the oracle's within the batch tolerances"""
+    from ilqr_planner_b200 import synth
+    from ilqr_planner_b200.solver import Handle
+    from oracle import oracle
+    if case == "posorn":
+        pb, u0, nit = synth.config2(batch=6, horizon=60), None, 4
+    else:
+        pb = synth.config4(batch=6, horizon=40)
+        u0, nit = synth.u0_time(pb), 5
+    uu = None if u0 is None else u0.reshape(pb.batch, -1)
+    with Handle(pb) as h:
+        dense = h.solve_batch(uu, nit)
+        dU, dC, dA = dense.U.copy(), dense.cost_hist.copy(), dense.alpha_hist.copy()
+        wb = h.solve_batch(uu, nit, woodbury=True)
+    ref = oracle.solve_batch(pb, uu, nit, False, threads=8)
+    same = pt.same_sequence(wb.alpha_hist, dA) & pt.same_sequence(wb.alpha_hist, ref.alpha_hist)
+    assert same.sum() >= pb.batch // 2
+    tol_c, tol_u = (1e-8, 1e-6) if case == "posorn" else (1e-5, 1e-3)
+    assert rel(wb.cost_hist[same], dC[same], floor=0.0) < tol_c and rel(wb.U[same], dU[same]) < tol_u
+    assert rel(wb.cost_hist[same], ref.cost_hist[same], floor=0.0) < tol_c and rel(wb.U[same], ref.U[same]) < tol_u
+
+
 def test_batch_ilqr_time_system_vs_oracle(oracle_lib):
     """C4 shape at a size the oracle finishes in seconds: PosOrnTime, N = 8 * 39 = 312"""
     from ilqr_planner_b200 import synth

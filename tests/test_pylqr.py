@@ -82,6 +82,37 @@ def test_headers_compile_standalone(tmp_path):
     assert r.returncode == 0, r.stderr[-3000:]
 
 
+def test_csv_helpers_round_trip(tmp_path):
+    """EigenSerialize::save / load of utils.cpp:20-60 (4 significant digits, one vector per line, matrices row by row)"""
+    src = tmp_path / "t.cpp"
+    src.write_text('''#include <ilqr_planner_b200/serialize.hpp>
+#include <cstdio>
+using namespace ilqr_planner;
+int main(int, char** argv) {
+    std::string d = argv[1];
+    std::vector<VectorXd> xs = {VectorXd({1.0, -2.5, 3.14159265}), VectorXd({1e-7, 12345.678, 0.0})};
+    EigenSerialize::save(xs, d + "/v.csv");
+    auto back = EigenSerialize::load<3>(d + "/v.csv");
+    if (back.size() != 2 || back[0](1) != -2.5 || back[1](0) != 1e-7) return 1;
+    MatrixXd A(2, 3);
+    for (int i = 0; i < 2; i++) for (int j = 0; j < 3; j++) A(i, j) = i * 3 + j + 0.125;
+    EigenSerialize::save(A, d + "/m.csv");
+    EigenSerialize::save(std::vector<MatrixXd>{A, A}, d + "/ms.csv");
+    EigenSerialize::save(xs[0], d + "/b.csv");
+    auto v = eigenMatrixToStdVector(A);
+    return (v.size() == 6 && v[1] == 3.125) ? 0 : 2;  // column-major like Eigen
+}
+''')
+    exe = tmp_path / "t"
+    r = subprocess.run(["g++", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    assert subprocess.run([str(exe), str(tmp_path)]).returncode == 0
+    assert (tmp_path / "v.csv").read_text() == "1,-2.5,3.142\n1e-07,1.235e+04,0\n"
+    assert (tmp_path / "m.csv").read_text() == "0.125,1.125,2.125\n3.125,4.125,5.125\n"
+    assert (tmp_path / "b.csv").read_text() == "1,-2.5,3.142\n"
+    assert (tmp_path / "ms.csv").read_text().count("=================================== \n") == 2
+
+
 def test_pylqr_module_surface():
     P = _pylqr()
     for mod, names in (("sim", ["SimulationInterface", "KDLRobot", "Robot2D", "TransformedSimulationInterface"]),

@@ -13,6 +13,8 @@ if [ "$2" != "noncu" ]; then
   ILQRB_GROUPS=1 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/${TAG}_launches.csv python tools/profile_run.py 3 c2 > gpurun_out/${TAG}_ncu_l.log 2>&1
   ILQRB_GROUPS=1 timeout 900 ncu --set full --metrics $M --clock-control none --import-source on -k regex:k_\(backward_n1\|forward_ring_n1\) -s 3 -c 3 -o gpurun_out/${TAG}_c2 -f python tools/profile_run.py 3 c2 > gpurun_out/${TAG}_ncu_f.log 2>&1
   ncu -i gpurun_out/${TAG}_c2.ncu-rep --page raw --csv > gpurun_out/${TAG}_c2_raw.csv 2>/dev/null
+  ILQRB_GROUPS=1 timeout 900 ncu --set full --metrics $M --clock-control none --import-source on -k regex:k_\(backward_time\|forward_time\|kp_derivs_time\) -s 3 -c 3 -o gpurun_out/${TAG}_time -f python tools/profile_run.py 3 time > gpurun_out/${TAG}_ncu_t.log 2>&1
+  ncu -i gpurun_out/${TAG}_time.ncu-rep --page raw --csv > gpurun_out/${TAG}_time_raw.csv 2>/dev/null
   python tools/ncu_kernels_json.py gpurun_out/${TAG}_c2_raw.csv 4096 "gpurun_out/${TAG}_c2_raw.csv: ncu --set full --clock-control none, ILQRB_GROUPS=1 python tools/profile_run.py 3 c2 (B=4096, one launch = whole batch)" gpurun_out/${TAG}_ncu_kernels.json > /dev/null 2>&1
 fi
 tail -5 gpurun_out/${TAG}_pytest.log
