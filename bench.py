@@ -189,8 +189,15 @@ def other_configs(torch, device, fp64_peak, hbm_peak):
             ald = make_al_desc(**al) if al else None
             bd = make_batch_desc(None, psi) if kind == "batch" else None
 
+            # the initial controls are reset inside the timed region from a device-resident copy (a host array would put a 26 MB
+            # pageable H2D copy of U0 into the device-resident number of the time-system configs)
+            u0d = None if u0 is None else torch.from_numpy(np.ascontiguousarray(u0)).to("cuda")
+
             def go():
-                h.upload_u0(u0)
+                if u0d is None:
+                    h.upload_u0(None)
+                else:
+                    h.upload_u0_device(u0d.data_ptr())
                 if kind == "al":
                     h.run_al(ald, nit, True, False)
                 elif kind == "batch":

@@ -604,7 +604,7 @@ int ilqrb_upload_u0(ilqrb_handle h, const double* U0) {
     }
     int rc = ensure_pack(h, rows * m);
     if (rc) return rc;
-    CU(cudaMemcpyAsync(h->d_pack, U0, rows * m * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->d_pack, U0, rows * m * sizeof(double), cudaMemcpyDefault, h->stream));  // host or device memory
     const size_t tot = rows * ms;
     k_unpack<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(h->W.U, h->d_pack, rows, m, ms);
     CU(cudaGetLastError());

@@ -100,6 +100,10 @@ class Handle:
         self._u0_keep = self._u(U0)
         cabi.check(self.lib.ilqrb_upload_u0(self.h, cabi.dptr(self._u0_keep)))
 
+    def upload_u0_device(self, ptr):
+        """U0 [B][H-1][m] already on a GPU: `ptr` = its device address (e.g. torch_tensor.data_ptr())"""
+        cabi.check(self.lib.ilqrb_upload_u0(self.h, C.cast(C.c_void_p(int(ptr)), cabi.c_double_p)))
+
     def run_recursive(self, nb_iter, line_search=True, early_stop=False):
         o = opts(nb_iter, line_search, early_stop)
         cabi.check(self.lib.ilqrb_run_recursive(self.h, C.byref(o)))

@@ -232,7 +232,7 @@ int ilqrb_solve_al(ilqrb_handle h, const double* U0, const ilqrb_al_desc* al, co
 int ilqrb_solve_batch(ilqrb_handle h, const double* u0, const ilqrb_batch_desc* bd, const ilqrb_solve_opts* opts, ilqrb_result* out);
 
 /* ---- split entry points (device-resident timing: upload once, run many, download once) ---- */
-int ilqrb_upload_u0(ilqrb_handle h, const double* U0); /* NULL = zeros */
+int ilqrb_upload_u0(ilqrb_handle h, const double* U0); /* NULL = zeros; host memory, or device memory of any GPU (a warm start that is already resident) */
 int ilqrb_run_recursive(ilqrb_handle h, const ilqrb_solve_opts* opts); /* async on the stream */
 int ilqrb_run_al(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solve_opts* opts);
 int ilqrb_run_batch(ilqrb_handle h, const ilqrb_batch_desc* bd, const ilqrb_solve_opts* opts);
