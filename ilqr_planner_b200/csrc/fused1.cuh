@@ -571,7 +571,7 @@ __device__ __forceinline__ double warp_sum(double v) {
 // per-warp shared memory of k_forward_n1 (doubles): deviation controls of the whole horizon, deviation states at the
 // keypoint steps, candidate x keypoint costs, one Jacobian column per lane
 __host__ __device__ inline int fwd_n1_smem_doubles(int H, int ns, int S) {
-    const int du = (H - 1) * ns > 32 * 6 ? (H - 1) * ns : 32 * 6;  // the Jacobian columns of phase F reuse the sDU area
+    const int du = (H - 1) * ns > 32 * 7 ? (H - 1) * ns : 32 * 7;  // the Jacobian columns of phase F reuse the sDU area
     return du + S * ns + NCAND * S;
 }
 
@@ -579,7 +579,9 @@ __host__ __device__ inline int fwd_n1_smem_doubles(int H, int ns, int S) {
 // returns true when the early-stop rule fired for this problem
 // SPLIT: phase A has run in its own kernel (k_fwd_rollout_n1, fused1_fwd.cuh) and left du, dx at the keypoint steps and the limit
 // flag in global memory; this body then does phases B-F only, with `smem` = [32][6] Jacobian columns + [NCAND][S] costs.
-template <int NT, int DOF, bool SPLIT = false>
+// RR: residual rows of a task the FK phases provide for: 6 (end-effector tasks), 7 when the system has a joint-space task
+// (JointSpacePlannerSys sub-systems, f(x) = x, J = I: 7 joints = 7 rows).
+template <int NT, int DOF, bool SPLIT = false, int RR = 6>
 __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work& W, int b, int lane, double* smem, int it, int nb_iter, int line_search, int early_stop,
                                                 double* s_cc_split = nullptr) {
     constexpr int NX = 8 * NT;
@@ -794,7 +796,7 @@ __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work&
             const int kp = task_kp_at(tk, k);
             if (kp < 0) continue;
             const int off = tk.joint_offset;
-            double fx[7], Jc[6], res[6];
+            double fx[7], Jc[RR], res[RR];
             lean_task_eval(P, tk, [&](int j) { return xk[off + j] + alpha * dxk[off + j]; }, -1, fx, Jc);
             double cst = lean_task_cost(P, tk, b, kp, fx, res);
             if (k < H - 1) {
@@ -878,9 +880,12 @@ __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work&
                 const int off = tk.joint_offset, r = tk.r_t;
                 const int cj_ = i - off;
                 const int cj = (cj_ >= 0 && cj_ < P.robots[tk.robot].dof) ? cj_ : -1;
-                double fx[7], Jc[6], res[6], jq[6];
+                double fx[7], Jc[RR], res[RR], jq[RR];
 #pragma unroll
-                for (int a = 0; a < 6; a++) res[a] = 0.0;
+                for (int a = 0; a < RR; a++) {
+                    res[a] = 0.0;
+                    Jc[a] = 0.0;
+                }
                 lean_task_eval(P, tk, [&](int j) { return xk[off + j]; }, cj, fx, Jc);
                 if (kp >= 0) {
                     const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
@@ -889,11 +894,11 @@ __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work&
                 const double* Q = tk.kp_precision + ((size_t)(tk.precision_per_problem ? b : 0) * tk.n_keypoints + (kp >= 0 ? kp : 0)) * r * r;
                 double gsum = 0.0;
 #pragma unroll
-                for (int c = 0; c < 6; c++) {
+                for (int c = 0; c < RR; c++) {
                     double a = 0.0, na = 0.0;
                     if (c < r) {
 #pragma unroll
-                        for (int a2 = 0; a2 < 6; a2++)
+                        for (int a2 = 0; a2 < RR; a2++)
                             if (a2 < r) {
                                 const double qv = Q[a2 * r + c];
                                 a += Jc[a2] * qv;
@@ -904,17 +909,17 @@ __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work&
                     gsum += na * res[c];
                 }
 #pragma unroll
-                for (int a = 0; a < 6; a++) s_J[lane * 6 + a] = has ? Jc[a] : 0.0;
+                for (int a = 0; a < RR; a++) s_J[lane * RR + a] = has ? Jc[a] : 0.0;
                 __syncwarp();
                 if (has) {
                     lxi += gsum;
 #pragma unroll
                     for (int j = 0; j < NX; j++) {
                         if (j < n) {
-                            const double* Jj = s_J + (sg * NX + j) * 6;
+                            const double* Jj = s_J + (sg * NX + j) * RR;
                             double h = 0.0;
 #pragma unroll
-                            for (int c = 0; c < 6; c++)
+                            for (int c = 0; c < RR; c++)
                                 if (c < r) h += jq[c] * Jj[c];
                             row[j] += h;
                         }

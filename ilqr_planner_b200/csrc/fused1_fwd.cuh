@@ -217,10 +217,10 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_fwd_rollout_n1(const DevPr
 template <int RING, int SPS>
 __host__ __device__ inline size_t fwd_fused_warp_bytes(int m, int ns, int S) {
     size_t ringb = (size_t)RING * fwd_ring_stage_doubles<SPS>(m, ns) * 8;
-    if (ringb < 32 * 6 * 8) ringb = 32 * 6 * 8;
+    if (ringb < 32 * 7 * 8) ringb = 32 * 7 * 8;
     return (ringb + (size_t)NCAND * S * 8 + RING * 8 + 127) / 128 * 128;  // bulk copies need 16-byte aligned destinations
 }
-template <int NT, int DOF, int RING, int SPS, int WARPS, int MINB>
+template <int NT, int DOF, int RING, int SPS, int WARPS, int MINB, int RR = 6>
 __global__ void __launch_bounds__(32 * WARPS, MINB) k_forward_ring_n1(const DevProblem* __restrict__ Pp, Work W, int b0, int nB, int it, int nb_iter, int line_search,
                                                                       int early_stop) {
     extern __shared__ __align__(128) unsigned char fwd_smem[];
@@ -234,16 +234,16 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) k_forward_ring_n1(const DevP
     unsigned char* mine = fwd_smem + (size_t)wid * fwd_fused_warp_bytes<RING, SPS>(n, ns, S);
     double* ring = reinterpret_cast<double*>(mine);
     size_t ringb = (size_t)RING * fwd_ring_stage_doubles<SPS>(n, ns) * 8;
-    if (ringb < 32 * 6 * 8) ringb = 32 * 6 * 8;
+    if (ringb < 32 * 7 * 8) ringb = 32 * 7 * 8;
     double* s_cc = reinterpret_cast<double*>(mine + ringb);
     unsigned long long* bars = reinterpret_cast<unsigned long long*>(mine + ringb + (size_t)NCAND * S * 8);
     fwd_rollout_ring<NT, DOF, RING, SPS>(P, W, b, lane, ring, bars);
     __syncwarp();  // the deviation and the limit flag written by some lanes are read by others
-    forward_n1_body<NT, DOF, true>(P, W, b, lane, ring, it, nb_iter, line_search, early_stop, s_cc);
+    forward_n1_body<NT, DOF, true, RR>(P, W, b, lane, ring, it, nb_iter, line_search, early_stop, s_cc);
 }
 
 // phases B-F: one warp per block (the FK sweeps of phases C and F get the registers they need)
-__host__ __device__ inline int fwd_select_smem_doubles(int S) { return 32 * 6 + NCAND * S; }
+__host__ __device__ inline int fwd_select_smem_doubles(int S) { return 32 * 7 + NCAND * S; }
 
 template <int NT, int DOF, int MINB>
 __global__ void __launch_bounds__(32, MINB) k_fwd_select_n1(const DevProblem* __restrict__ Pp, Work W, int b0, int it, int nb_iter, int line_search, int early_stop) {

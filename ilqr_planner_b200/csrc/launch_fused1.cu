@@ -8,8 +8,8 @@ namespace ilqrb {
 
 bool fast_n1_applies(ilqrb_handle h, bool al) {
     const DevProblem& P = h->hp;
-    for (int t = 0; t < P.n_tasks; t++)
-        if (P.tasks[t].kind != ILQRB_TASK_POSE) return false;  // joint-space tasks: generic kernels
+    for (int t = 0; t < P.n_tasks; t++)  // the forward kernel holds 7 residual rows for a joint-space task
+        if (P.tasks[t].kind == ILQRB_TASK_JOINT && P.robots[P.tasks[t].robot].dof > 7) return false;
     return !generic_forced() && !al && P.nb_deriv == 1 && !P.time && P.n == P.m && P.n + 1 <= 16 &&
            (size_t)fwd_n1_smem_doubles(P.H, h->W.ns, P.n_kp_steps) * sizeof(double) <= 200 * 1024;
 }
@@ -124,15 +124,20 @@ int launch_fwd_select_t(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it,
     k_fwd_select_n1<NT, DOF, MINB><<<nB, 32, smem, st>>>(h->dp, h->W, b0, it, nb_iter, line_search, early_stop);
     return 0;
 }
-template <int NT, int DOF, int RING, int SPS, int WARPS, int MINB>
+template <int NT, int DOF, int RING, int SPS, int WARPS, int MINB, int RR = 6>
 int launch_forward_ring_t(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop) {
     const size_t smem = (size_t)WARPS * fwd_fused_warp_bytes<RING, SPS>(h->hp.m, h->W.ns, h->hp.n_kp_steps);
-    auto kern = k_forward_ring_n1<NT, DOF, RING, SPS, WARPS, MINB>;
+    auto kern = k_forward_ring_n1<NT, DOF, RING, SPS, WARPS, MINB, RR>;
     static DynSmem attr;
     int rc = attr.ensure(kern, smem, h->device);
     if (rc) return rc;
     kern<<<(nB + WARPS - 1) / WARPS, 32 * WARPS, smem, st>>>(h->dp, h->W, b0, nB, it, nb_iter, line_search, early_stop);
     return 0;
+}
+bool has_joint_task(const DevProblem& P) {
+    for (int t = 0; t < P.n_tasks; t++)
+        if (P.tasks[t].kind == ILQRB_TASK_JOINT) return true;
+    return false;
 }
 // A/B switches: ILQRB_FWD_V1 = the single-kernel forward pass of round 1 (gains through a register ring), ILQRB_FWD_SPLIT = the
 // bulk-copy rollout and phases B-F as two launches; default = both in one kernel (k_forward_ring_n1)
@@ -164,6 +169,14 @@ int launch_backward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
 int launch_forward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop) {
     const int n = h->hp.n;
     int rc;
+    if (has_joint_task(h->hp)) {  // joint-space sub-systems (f(x) = x, J = I; joint tasks have at most 7 joints): 7 residual rows
+        h->begin(PS_LINESEARCH);
+        rc = launch_forward_ring_t<1, 0, 2, 4, 1, 24, 7>(h, b0, nB, st, it, nb_iter, line_search, early_stop);
+        h->end();
+        if (rc) return rc;
+        CU(cudaGetLastError());
+        return 0;
+    }
     if (fwd_mode() == 0) {
         h->begin(PS_LINESEARCH);
         // (RING, SPS, WARPS per block, blocks per SM) measured on B200 at C2 (tools/sweep_fwd.sh, profiles/r2_sweep_forward.txt), us per
