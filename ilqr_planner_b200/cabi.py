@@ -65,6 +65,11 @@ class BatchDesc(C.Structure):
     _fields_ = [("Q", c_double_p), ("psi", c_double_p), ("nw", C.c_int32), ("flags", C.c_int32)]
 
 
+class LqtDesc(C.Structure):
+    _fields_ = [("nq", C.c_int32), ("n", C.c_int32), ("m", C.c_int32), ("T", C.c_int32), ("ab_per_problem", C.c_int32), ("pad_", C.c_int32),
+                ("A", c_double_p), ("B", c_double_p), ("Qs", c_double_p), ("mu", c_double_p), ("r", C.c_double)]
+
+
 class SolveOpts(C.Structure):
     _fields_ = [("nb_iter", C.c_int32), ("line_search", C.c_int32), ("early_stop", C.c_int32), ("pad_", C.c_int32)]
 
@@ -100,7 +105,7 @@ SYMBOLS = [
     "ilqrb_synchronize", "ilqrb_update_problems", "ilqrb_solve_recursive", "ilqrb_solve_recursive_async", "ilqrb_solve_al", "ilqrb_solve_batch",
     "ilqrb_upload_u0", "ilqrb_run_recursive", "ilqrb_run_al", "ilqrb_run_batch", "ilqrb_download", "ilqrb_rollout",
     "ilqrb_kinematics", "ilqrb_set_profiling", "ilqrb_get_profile", "ilqrb_reset_profile", "ilqrb_launch_count",
-    "ilqrb_chain_from_urdf", "ilqrb_build_psi", "ilqrb_fp64_peaks", "ilqrb_kinematics_static", "ilqrb_eval_point", "ilqrb_keypoint_diff", "ilqrb_sd", "ilqrb_host_alloc", "ilqrb_host_free",
+    "ilqrb_chain_from_urdf", "ilqrb_build_psi", "ilqrb_fp64_peaks", "ilqrb_kinematics_static", "ilqrb_eval_point", "ilqrb_keypoint_diff", "ilqrb_sd", "ilqrb_host_alloc", "ilqrb_host_free", "ilqrb_lqt_solve", "ilqrb_lqt_command",
     "ilqrb_multi_plan", "ilqrb_create_multi", "ilqrb_multi_destroy", "ilqrb_multi_count", "ilqrb_multi_slice", "ilqrb_multi_solve_recursive",
     "ilqrb_multi_solve_al", "ilqrb_multi_solve_batch", "ilqrb_multi_upload_u0", "ilqrb_multi_run_recursive", "ilqrb_multi_synchronize", "ilqrb_multi_download",
 ]
@@ -145,6 +150,8 @@ def load():
     lib.ilqrb_keypoint_diff.argtypes = [C.c_int] * 5 + [c_double_p, c_double_p, C.c_int, c_double_p, c_double_p]
     lib.ilqrb_sd.argtypes = [C.c_int, C.c_int, C.c_int] + [c_double_p] * 4
     lib.ilqrb_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
+    lib.ilqrb_lqt_solve.argtypes = [C.c_int, C.POINTER(LqtDesc)] + [c_double_p] * 6 + [c_int32_p]
+    lib.ilqrb_lqt_command.argtypes = [C.c_int] * 5 + [c_double_p] * 3 + [C.c_int, c_int32_p, c_int32_p, c_double_p, c_double_p]
     lib.ilqrb_host_free.argtypes = [C.c_void_p]
     lib.ilqrb_multi_plan.argtypes = [C.c_int, C.c_int, IP, IP]
     lib.ilqrb_create_multi.argtypes = [C.POINTER(ProblemDesc), C.c_int, IP, C.POINTER(H)]

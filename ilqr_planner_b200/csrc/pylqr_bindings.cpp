@@ -478,4 +478,44 @@ PYBIND11_MODULE(_pylqr, m) {
              py::arg("systems"), py::arg("U0") = py::none(), py::arg("nb_iter") = 10, py::arg("line_search") = true, py::arg("early_stop") = false, py::arg("devices") = Devs{0},
              "Batched solve of a list of system objects of one structure (they may differ in robot state, keypoint targets and precisions); results are copies.")
         .def("cache_stats", &solver::ILQRRecursive::cacheStats);
+    // bindings.cpp:862-869
+    py::class_<solver::LQT>(m_sol, "LQT")
+        .def(py::init<const MatrixXd&, const MatrixXd&, const std::vector<MatrixXd>&, const VectorXd&, float, int>(), py::arg("A"), py::arg("B"), py::arg("Qs"), py::arg("states"),
+             py::arg("rfactor") = 0.1f, py::arg("nb_deriv") = 2)
+        .def("solve_DP", &solver::LQT::solveDP, py::call_guard<py::gil_scoped_release>())
+        .def("solve_lin_al", &solver::LQT::solveLinAl, py::call_guard<py::gil_scoped_release>())
+        .def("get_nb_states", &solver::LQT::getNbStates)
+        .def("get_predicted_states", &solver::LQT::getPredictedStates)
+        .def("get_command", static_cast<VectorXd (solver::LQT::*)(int)>(&solver::LQT::getCommand))
+        .def("get_command", static_cast<VectorXd (solver::LQT::*)(int, const VectorXd&)>(&solver::LQT::getCommand))
+        .def("get_Ps", &solver::LQT::getPs, "solve_DP's matrices in time order (private in the reference)")
+        .def("get_ds", &solver::LQT::getds)
+        .def_static(
+            "solve_batch",
+            [](const MatrixXd& A, const MatrixXd& B, DArr Qs, DArr mu, float rfactor, int nb_deriv, int device) {
+                if (Qs.ndim() != 4 || mu.ndim() != 2 || Qs.shape(0) != mu.shape(0)) throw std::invalid_argument("LQT.solve_batch: Qs [nq, T, n, n] and mu [nq, T*n] expected");
+                const int nq = int(Qs.shape(0)), T = int(Qs.shape(1));
+                const std::vector<double> q(Qs.data(), Qs.data() + Qs.size()), muv(mu.data(), mu.data() + mu.size());
+                solver::LQT::BatchOut o;
+                {
+                    py::gil_scoped_release rel;
+                    o = solver::LQT::solveBatch(A, B, nq, T, q, muv, rfactor, nb_deriv, device);
+                }
+                const ssize_t n = A.cols(), m = B.cols();
+                auto arr = [](const std::vector<double>& v, std::vector<ssize_t> shape) {
+                    py::array_t<double> a(shape);
+                    std::copy(v.begin(), v.end(), a.mutable_data());
+                    return a;
+                };
+                py::dict d;
+                d["u"] = arr(o.u, {nq, (T - 1) * m});
+                d["xhat"] = arr(o.xhat, {nq, T * n});
+                d["Ps"] = arr(o.Ps, {nq, T, n, n});
+                d["ds"] = arr(o.ds, {nq, T, n});
+                d["K"] = arr(o.K, {nq, T - 1, m, n});
+                d["f"] = arr(o.f, {nq, T - 1, m});
+                return d;
+            },
+            py::arg("A"), py::arg("B"), py::arg("Qs"), py::arg("mu"), py::arg("rfactor") = 0.1f, py::arg("nb_deriv") = 2, py::arg("device") = 0,
+            "Many tracking problems of one shape in one device call: Qs [nq, T, n, n], mu [nq, T*n].");
 }

@@ -320,3 +320,42 @@ def sd(op, a, b=None, c=None, device=0):
     out = np.empty(nq) if op == cabi.SD_DISTANCE else np.empty((nq, 3, 4)) if op == cabi.SD_DQUAT_TO_W_JAC else np.empty((nq, 4))
     cabi.check(lib.ilqrb_sd(device, op, nq, cabi.dptr(a), cabi.dptr(b), cabi.dptr(c), cabi.dptr(out)))
     return out
+
+
+def lqt_solve(A, B, Qs, mu, r, device=0):
+    """solver::LQT for a batch (ilqrb_lqt_solve; lqt.cpp:16-126).  A [n,n] / B [n,m] shared by the problems, or [nq,n,n] / [nq,n,m]; Qs [nq,T,n,n];
+    mu [nq,T*n]; r = pow(rfactor, nb_deriv).  Returns Ps, ds (solveDP, time order), K, f (getCommand(timestep, state)), u, xhat (solveLinAl), status."""
+    lib = cabi.load()
+    Qs = np.ascontiguousarray(Qs, dtype=np.float64)
+    if Qs.ndim != 4 or Qs.shape[2] != Qs.shape[3]:
+        raise ValueError("Qs: [nq, T, n, n] expected")
+    nq, T, n = Qs.shape[0], Qs.shape[1], Qs.shape[2]
+    A = np.ascontiguousarray(A, dtype=np.float64)
+    B = np.ascontiguousarray(B, dtype=np.float64)
+    m = B.shape[-1]
+    per = int(A.ndim == 3)
+    if A.shape != ((nq, n, n) if per else (n, n)) or B.shape != ((nq, n, m) if per else (n, m)):
+        raise ValueError("A / B: [n, n] and [n, m] (or one pair per problem) expected")
+    mu = np.ascontiguousarray(np.asarray(mu, dtype=np.float64).reshape(nq, T * n))
+    d = cabi.LqtDesc(nq, n, m, T, per, 0, cabi.dptr(A), cabi.dptr(B), cabi.dptr(Qs), cabi.dptr(mu), float(r))
+    o = {"Ps": np.empty((nq, T, n, n)), "ds": np.empty((nq, T, n)), "K": np.empty((nq, T - 1, m, n)), "f": np.empty((nq, T - 1, m)),
+         "u": np.empty((nq, (T - 1) * m)), "xhat": np.empty((nq, T * n)), "status": np.zeros(nq, dtype=np.int32)}
+    cabi.check(lib.ilqrb_lqt_solve(device, C.byref(d), cabi.dptr(o["Ps"]), cabi.dptr(o["ds"]), cabi.dptr(o["K"]), cabi.dptr(o["f"]), cabi.dptr(o["u"]),
+                                   cabi.dptr(o["xhat"]), cabi.iptr(o["status"])))
+    return o
+
+
+def lqt_command(K, f, mu, timestep, state, problem=None, device=0):
+    """LQT::getCommand(timestep, curr_state) for a set of queries (ilqrb_lqt_command; lqt.cpp:105-124)"""
+    lib = cabi.load()
+    K = np.ascontiguousarray(K, dtype=np.float64)
+    nq, Tm1, m, n = K.shape
+    f = np.ascontiguousarray(f, dtype=np.float64)
+    mu = np.ascontiguousarray(np.asarray(mu, dtype=np.float64).reshape(nq, (Tm1 + 1) * n))
+    ts = np.ascontiguousarray(np.atleast_1d(timestep), dtype=np.int32)
+    nc = ts.shape[0]
+    st = np.ascontiguousarray(np.asarray(state, dtype=np.float64).reshape(nc, n))
+    pr = None if problem is None else np.ascontiguousarray(np.atleast_1d(problem), dtype=np.int32)
+    u = np.empty((nc, m))
+    cabi.check(lib.ilqrb_lqt_command(device, nq, n, m, Tm1 + 1, cabi.dptr(K), cabi.dptr(f), cabi.dptr(mu), nc, cabi.iptr(pr), cabi.iptr(ts), cabi.dptr(st), cabi.dptr(u)))
+    return u

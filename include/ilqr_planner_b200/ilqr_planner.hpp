@@ -3,6 +3,7 @@
 #pragma once
 #include "dense.hpp"
 #include "keypoint.hpp"
+#include "lqt.hpp"
 #include "sd.hpp"
 #include "serialize.hpp"
 #include "sim.hpp"

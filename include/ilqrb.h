@@ -319,6 +319,37 @@ int ilqrb_keypoint_diff(int device, int sys_kind, int task_kind, int nb_deriv, i
 #define ILQRB_SD_DQUAT_TO_W_JAC 4
 int ilqrb_sd(int device, int op, int nq, const double* a, const double* b, const double* c, double* out);
 
+/* ---- solver::LQT (lqt.h:24-88, lqt.cpp:16-126) ---------------------------------- */
+/* nq independent linear quadratic tracking problems of one shape, one warp each:  x' = A x + B u,
+ * cost sum_t (x_t - mu_t)^T Q_t (x_t - mu_t) + sum_t u_t^T (r I) u_t,  x_0 = mu_0.  n, m <= 16; T >= 2.
+ *   A [n][n], B [n][m]   row-major, shared by the problems; ab_per_problem != 0: [nq][n][n], [nq][n][m]
+ *   Qs [nq][T][n][n]     LQT(A, B, Qs, states, rfactor, nb_deriv) (lqt.cpp:16-26)
+ *   mu [nq][T*n]         the stacked desired states
+ *   r                    pow(rfactor, nb_deriv) as the constructor forms it (lqt.cpp:17; rfactor is a float there)
+ * Outputs, host memory, in TIME order, any may be NULL:
+ *   Ps [nq][T][n][n], ds [nq][T][n]      LQT::solveDP (lqt.cpp:29-53; the reference stores them last timestep first)
+ *   K [nq][T-1][m][n], f [nq][T-1][m]    the gain and feed-forward of LQT::getCommand(timestep, state) (lqt.cpp:105-124),
+ *                                        i.e. formed from P, d and mu of timestep + 1 as written there
+ *   u [nq][(T-1)m], xhat [nq][T*n]       LQT::solveLinAl's controls (lqt.cpp:84-96) and getPredictedStates (lqt.cpp:119-125).
+ *                                        The reference inverts the dense (T-1)m x (T-1)m matrix Su^T Q Su + R; the same minimiser
+ *                                        is computed here by the Riccati sweep that solveDP already runs (exact for this
+ *                                        objective), checked against the dense form in the oracle.
+ *   status [nq]          ILQRB_ST_QUU_NOT_SPD when B^T P B + r I needed the pivoted inverse                                */
+typedef struct ilqrb_lqt_desc {
+    int32_t nq, n, m, T;
+    int32_t ab_per_problem, pad_;
+    const double* A;
+    const double* B;
+    const double* Qs;
+    const double* mu;
+    double r;
+} ilqrb_lqt_desc;
+int ilqrb_lqt_solve(int device, const ilqrb_lqt_desc* d, double* Ps, double* ds, double* K, double* f, double* u, double* xhat, int32_t* status);
+/* LQT::getCommand(timestep, curr_state) (lqt.cpp:105-124) for nc queries: u = K (mu_{timestep+1} - state) + f with K, f of
+ * ilqrb_lqt_solve.  problem [nc] (NULL = problem 0), timestep [nc] in [0, T-2], state [nc][n] -> u [nc][m].                */
+int ilqrb_lqt_command(int device, int nq, int n, int m, int T, const double* K, const double* f, const double* mu, int nc, const int32_t* problem,
+                      const int32_t* timestep, const double* state, double* u);
+
 /* ---- host-side builders (run once per robot / solver; no GPU work) -------------------------- */
 /* URDF -> chain descriptor.  Replaces tup::TinyURDFParser (TinyURDFParser.cpp:35-160) + the chain part of the
  * sim::KDLRobot constructor (KDLRobot.cpp:17-70), including the trailing "robot_custom_tip" segment built from

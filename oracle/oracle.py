@@ -45,6 +45,7 @@ def load(variant=None):
     lib.oracle_set_margin_out.argtypes = [cabi.c_double_p]
     lib.oracle_eval_point.argtypes = [P(cabi.ProblemDesc), C.c_int, cabi.c_int32_p, cabi.c_int32_p] + [cabi.c_double_p] * 9
     lib.oracle_sd.argtypes = [C.c_int, C.c_int] + [cabi.c_double_p] * 4
+    lib.oracle_lqt.argtypes = [C.c_int] * 5 + [cabi.c_double_p] * 4 + [C.c_double] + [cabi.c_double_p] * 6 + [C.c_int]
     lib.oracle_set_margin_out.restype = None
     _libs[variant] = lib
     return lib
@@ -186,3 +187,20 @@ def sd(op, a, b=None, c=None):
     out = np.empty(nq) if op == cabi.SD_DISTANCE else np.empty((nq, 3, 4)) if op == cabi.SD_DQUAT_TO_W_JAC else np.empty((nq, 4))
     _check(load().oracle_sd(op, nq, cabi.dptr(a), cabi.dptr(b), cabi.dptr(c), cabi.dptr(out)))
     return out
+
+
+def lqt(A, B, Qs, mu, r, dense=True, variant=None):
+    """twin of solver.lqt_solve: solver::LQT restated (lqt.cpp:16-126).  A [n,n] / B [n,m] shared or [nq,n,n] / [nq,n,m]; Qs [nq,T,n,n]; mu [nq,T*n];
+    r = pow(rfactor, nb_deriv).  dense=False skips solveLinAl's (T-1)m-sized inverse (u, xhat stay NaN)."""
+    Qs = np.ascontiguousarray(Qs, dtype=np.float64)
+    nq, T, n = Qs.shape[0], Qs.shape[1], Qs.shape[2]
+    A = np.ascontiguousarray(A, dtype=np.float64)
+    B = np.ascontiguousarray(B, dtype=np.float64)
+    m = B.shape[-1]
+    per = int(A.ndim == 3)
+    mu = np.ascontiguousarray(np.asarray(mu, dtype=np.float64).reshape(nq, T * n))
+    o = {"Ps": np.empty((nq, T, n, n)), "ds": np.empty((nq, T, n)), "K": np.empty((nq, T - 1, m, n)), "f": np.empty((nq, T - 1, m)),
+         "u": np.full((nq, (T - 1) * m), np.nan), "xhat": np.full((nq, T * n), np.nan)}
+    _check(load(variant).oracle_lqt(nq, n, m, T, per, cabi.dptr(A), cabi.dptr(B), cabi.dptr(Qs), cabi.dptr(mu), float(r), cabi.dptr(o["Ps"]), cabi.dptr(o["ds"]),
+                                    cabi.dptr(o["K"]), cabi.dptr(o["f"]), cabi.dptr(o["u"]), cabi.dptr(o["xhat"]), int(dense)))
+    return o
