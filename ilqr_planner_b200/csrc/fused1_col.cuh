@@ -1,0 +1,255 @@
+// fused1_col.cuh — backward Riccati pass of the single-integrator fast path with FOUR problems per warp (n = m = 7).
+//
+// k_backward_n1 (fused1.cuh) gives a whole warp to one problem: the 8x8 augmented matrices sit in the DMMA accumulator layout, two
+// elements per lane, and the in-register Gauss-Jordan spends ~37 instructions per stage on lane-role bookkeeping for 4 useful FP64
+// operations per lane (ncu: 397 instructions per problem and step, 100 of them FP64, issue-bound).  Here 8 lanes own one problem and
+// lane j owns COLUMN j of every augmented matrix ([P|p], [Qux|Qu], [Qxx|Qx], [K|d]; column 7 is the vector), eight rows in
+// registers with compile-time indices:
+//   * the elimination of [Quu + 1e-6 I | -Qux -Qu] needs one broadcast per stage — the multiplier column l_ik / l_kk, 8 doubles,
+//     written by the pivot column's owner and read back as four 16-byte shared-memory loads — and then updates its two columns with
+//     14 independent FMAs; no selects, no shuffles, and it is a solve (no explicit inverse, no product with it);
+//   * products C = A B take column k of A as a shared-memory broadcast and B[k][j] from the lane's own registers: 8 FMAs per 16-byte
+//     pair of loads.  Quu [K|d] is formed as dt^2 (P [K|d]) + R o [K|d], so one product P [K|d] serves both the bracket
+//     M = Quu [K|d] + [Qux|Qu] and Qxu [K|d] = dt P [K|d]; the second product is K^T M.            ILQRRecursive.cpp:82-94
+// ~150 instructions per problem and step, the same FP64 work.  Plain FMA chains in the reference's summation order; no tensor pipe
+// (DMMA and DFMA peak at the same rate on B200: 37.0 against 36.1 TFLOP/s measured, bench.py `peaks_measured_here_tflops`).
+// A problem whose elimination meets a non-positive pivot is redone by the warp-per-problem pass with the pivoted inverse
+// (backward_n1_redo), like there.
+#pragma once
+#include "fused1.cuh"
+
+namespace ilqrb {
+
+struct BwdColSmem {
+    // per problem: 8 multiplier columns (one per stage), [K|d] row-major, P column-major, the limit residuals; the stride keeps the
+    // four problems of a warp on distinct 16-byte bank groups for the broadcast loads (212 * 8 B = 32 mod 128)
+    static constexpr int F = 0, KS = 64, PC = 128, LQ = 192, BLK = 212;
+    static constexpr int PER_WARP = 4 * BLK > BwdN1Smem<1>::PER_WARP ? 4 * BLK : BwdN1Smem<1>::PER_WARP;
+};
+
+__device__ __forceinline__ void ld8(const double* p, double (&o)[8]) {
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const double2 v = *reinterpret_cast<const double2*>(p + 2 * q);
+        o[2 * q] = v.x;
+        o[2 * q + 1] = v.y;
+    }
+}
+__device__ __forceinline__ void st8(double* p, const double (&o)[8]) {
+#pragma unroll
+    for (int q = 0; q < 4; q++) *reinterpret_cast<double2*>(p + 2 * q) = make_double2(o[2 * q], o[2 * q + 1]);
+}
+
+// returns the ballot of lanes whose problem met a non-positive pivot.  bfirst: first problem of this warp; bend: one past the last
+// problem of the launch.  N = 7: the state rows are 8 doubles wide (ns = 8), which the 16-byte loads of u rely on.
+template <int N>
+__device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const Work& W, int bfirst, int bend, int lane, double* wsmem) {
+    static_assert(N == 7, "row stride of 8 doubles assumed");
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr int ns = 8, ms = 8, nf = N;
+    const int sub = lane >> 3, j = lane & 7;
+    const int bq = bfirst + sub;
+    const bool live = bq < bend && !W.done[bq < bend ? bq : bfirst];
+    const int b = live ? bq : bfirst;  // idle groups shadow the warp's first problem and store nothing
+    const int H = P.H;
+    const double dt = 1.0 * P.dt;  // B = Identity * dt
+    double* sm = wsmem + sub * BwdColSmem::BLK;
+    double* sF = sm + BwdColSmem::F;
+    double* sK = sm + BwdColSmem::KS;
+    double* sP = sm + BwdColSmem::PC;
+    double* sQ = sm + BwdColSmem::LQ;
+
+    double R[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) R[i] = i < N ? P.r_diag[i] : 0.0;
+    const double* Xb = W.X + (size_t)b * H * ns;
+    const double* Ub = W.U + (size_t)b * (H - 1) * ms;
+    const int S_kp = P.n_kp_steps;
+
+    // joint limits of the (single) limit-carrying task: lane j checks state j   System.cpp:121-142
+    int l0 = -1;
+    if (P.any_limits)
+        for (int ti = P.n_tasks - 1; ti >= 0; ti--)
+            if (P.tasks[ti].limits_set) l0 = ti;
+    double lmx = INFINITY, lmn = -INFINITY;
+    if (l0 >= 0 && j < N && P.tasks[l0].limit_weight[j] != 0) {
+        lmx = P.tasks[l0].state_max[j];
+        lmn = P.tasks[l0].state_min[j];
+    }
+    // e += [L^T L | -L^T q] with L = diag(violated), q = limit - x                      System.cpp:263-269,299-305
+    auto add_limits = [&](double (&e)[8], double x) {
+        double q = 0.0;
+        bool act = false;
+        if (x > lmx) {
+            q = lmx - x;
+            act = true;
+        } else if (x < lmn) {
+            q = lmn - x;
+            act = true;
+        }
+        sQ[j] = act ? -1.0 * q : 0.0;
+        __syncwarp();
+        double qv[8];
+        ld8(sQ, qv);
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+            if (i == j && act) e[i] += 1.0 * 1.0;
+            if (j == N) e[i] += qv[i];
+        }
+        __syncwarp();
+    };
+    // e += [l_xx | l_x] of keypoint step index s                                         System.cpp:252-260,290-296
+    auto add_kp = [&](double (&e)[8], int s) {
+        const double* lx = W.LX + ((size_t)b * S_kp + s) * nf;
+        const double* lxx = W.LXX + ((size_t)b * S_kp + s) * nf * nf;
+#pragma unroll
+        for (int i = 0; i < N; i++) e[i] += (j < N) ? lxx[i * nf + j] : lx[i];
+    };
+
+    // terminal: P = cost_F_xx, p = cost_F_x   (ILQRRecursive.cpp:69-71)
+    double Pc[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) Pc[i] = 0.0;
+    int sp = S_kp - 1;
+    int next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
+    if (next_kp == H - 1) {
+        add_kp(Pc, sp);
+        sp--;
+        next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
+    }
+    if (l0 >= 0) add_limits(Pc, Xb[(size_t)(H - 1) * ns + j]);
+    st8(sP + j * 8, Pc);
+    double un[8], xn = 0.0;
+    ld8(Ub + (size_t)(H - 2) * ms, un);
+    if (l0 >= 0) xn = Xb[(size_t)(H - 2) * ns + j];
+    bool ok = true;
+    double* Kg = W.K + ((size_t)b * (H - 1) + (H - 2)) * nf * ns;  // walks backwards with k
+    double* dg = W.d + ((size_t)b * (H - 1) + (H - 2)) * ms;
+    __syncwarp();
+
+    for (int k = H - 2; k >= 0; k--, Kg -= nf * ns, dg -= ms) {
+        double u[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) u[i] = un[i];
+        const double x = xn;
+        if (k > 0) {  // prefetch the next step's controls / state
+            ld8(Ub + (size_t)(k - 1) * ms, un);
+            if (l0 >= 0) xn = Xb[(size_t)(k - 1) * ns + j];
+        }
+        // [Qux|Qu] = [0 | R u] + (B^T [P|p]) A_aug ;  Quu = R + (B^T P) B ;  [Qxx|Qx] = [l_xx|l_x] + (A^T [P|p]) A_aug   ILQRRecursive.cpp:82-87
+        double Qa[8], L[8], Rh[8], Qx[8];
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+            const double bp = dt * Pc[i];
+            Qa[i] = (j == N) ? R[i] * u[i] + bp : bp;
+            double quu = bp * dt;
+            if (i == j) quu = (R[i] + quu) + 1e-6 * 1.0;  // Quu + 1e-6 I                     ILQRRecursive.cpp:89
+            L[i] = (j < N) ? quu : 0.0;                 // lane 7 carries the vector column: no matrix column of its own
+            Rh[i] = -Qa[i];
+            Qx[i] = Pc[i];
+        }
+        if (k == next_kp) {
+            add_kp(Qx, sp);
+            sp--;
+            next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
+        }
+        if (l0 >= 0) add_limits(Qx, x);
+
+        // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]: Gauss-Jordan without pivoting on the columns, one multiplier broadcast per stage
+#pragma unroll
+        for (int s = 0; s < N; s++) {
+            {
+                const double inv = fast_rcp(L[s]);
+                double f[8];
+#pragma unroll
+                for (int i = 0; i < 8; i++) f[i] = (i == s) ? inv : (i < N ? L[i] * inv : 0.0);
+                if (j == s) st8(sF + s * 8, f);
+            }
+            __syncwarp();
+            double f[8];
+            ld8(sF + s * 8, f);
+            const int hi = __double2hiint(f[s]);  // 1 / pivot: positive and finite iff the pivot was
+            ok = ok && (hi > 0) && (hi < 0x7ff00000);
+            const double lk = L[s], rk = Rh[s];
+#pragma unroll
+            for (int i = 0; i < N; i++) {
+                if (i == s) {
+                    L[i] = lk * f[s];
+                    Rh[i] = rk * f[s];
+                } else {
+                    L[i] = fma(-f[i], lk, L[i]);
+                    Rh[i] = fma(-f[i], rk, Rh[i]);
+                }
+            }
+        }
+        // Rh = column j of [K|d].  Publish the rows for K^T M, stream K and d to global (time-forward index)
+#pragma unroll
+        for (int i = 0; i < N; i++) sK[i * 8 + j] = Rh[i];
+        if (live) {
+#pragma unroll
+            for (int i = 0; i < N; i++) Kg[i * ns + j] = (j < N) ? Rh[i] : 0.0;
+            if (j == N) {
+                double dv[8];
+#pragma unroll
+                for (int i = 0; i < 8; i++) dv[i] = i < N ? Rh[i] : 0.0;
+                st8(dg, dv);
+            }
+        }
+        __syncwarp();
+        // PK = P [K|d]
+        double PK[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) PK[i] = 0.0;
+#pragma unroll
+        for (int c = 0; c < N; c++) {
+            double pc[8];
+            ld8(sP + c * 8, pc);
+#pragma unroll
+            for (int i = 0; i < N; i++) PK[i] = fma(pc[i], Rh[c], PK[i]);
+        }
+        // M = Quu [K|d] + [Qux|Qu], un-regularised Quu = R + dt^2 P                        ILQRRecursive.cpp:93
+        double M[8];
+#pragma unroll
+        for (int i = 0; i < N; i++) M[i] = fma(R[i], Rh[i], (dt * PK[i]) * dt) + Qa[i];
+        // [P|p] = [Qxx|Qx] + K^T M + Qxu [K|d]                                             ILQRRecursive.cpp:93-94
+        double acc[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) acc[i] = 0.0;
+#pragma unroll
+        for (int c = 0; c < N; c++) {
+            double kr[8];
+            ld8(sK + c * 8, kr);
+#pragma unroll
+            for (int i = 0; i < N; i++) acc[i] = fma(kr[i], M[c], acc[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < N; i++) Pc[i] = (Qx[i] + acc[i]) + dt * PK[i];
+        __syncwarp();  // every lane has read sP and sK
+        st8(sP + j * 8, Pc);
+        __syncwarp();
+    }
+    return __ballot_sync(FULL, !ok);
+}
+
+template <int N, int WARPS>
+__global__ void __launch_bounds__(32 * WARPS) k_backward_n1_col(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
+    extern __shared__ __align__(16) double smem_col[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int bfirst = b0 + 4 * (blockIdx.x * WARPS + wid), bend = b0 + nB;
+    if (bfirst >= bend) return;
+    double* ws = smem_col + (size_t)wid * BwdColSmem::PER_WARP;
+    bool any = false;
+    for (int s = 0; s < 4; s++) any = any || (bfirst + s < bend && !W.done[bfirst + s]);
+    if (!any) return;
+    const unsigned bad = backward_n1_col<N>(*Pp, W, bfirst, bend, lane, ws);
+    if (bad == 0) return;
+    for (int s = 0; s < 4; s++) {  // rare: the reference's pivoted inverse for the problems that need it, a warp each
+        const int b = bfirst + s;
+        if (((bad >> (8 * s)) & 0xffu) == 0 || b >= bend || W.done[b]) continue;
+        if (lane == 0) atomicOr(W.status + b, ILQRB_ST_QUU_NOT_SPD);
+        __syncwarp();
+        backward_n1_redo<1, N>(*Pp, W, b, lane, ws, 0, 0);
+    }
+}
+
+}  // namespace ilqrb

@@ -1,6 +1,7 @@
 // launch_fused1.cu — launchers of the single-integrator fast path (fused1.cuh): k_backward_n1 / k_backward_n1_blocks / k_forward_n1.
 #include <cstdlib>
 
+#include "fused1_col.cuh"
 #include "fused1_fwd.cuh"
 #include "handle.hpp"
 
@@ -27,6 +28,25 @@ int launch_backward_n1_t(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
     if (rc) return rc;
     kern<<<(nB + WARPS - 1) / WARPS, 32 * WARPS, smem, st>>>(h->dp, h->W, b0, nB);
     return 0;
+}
+// four problems per warp, a column of the augmented matrices per lane (fused1_col.cuh); n = m = 7, at most one limit-carrying task
+template <int WARPS>
+int launch_backward_n1_col_t(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
+    const size_t smem = (size_t)WARPS * BwdColSmem::PER_WARP * sizeof(double);
+    auto kern = k_backward_n1_col<7, WARPS>;
+    static DynSmem attr;
+    int rc = attr.ensure(kern, smem, h->device);
+    if (rc) return rc;
+    const int warps = (nB + 3) / 4;
+    kern<<<(warps + WARPS - 1) / WARPS, 32 * WARPS, smem, st>>>(h->dp, h->W, b0, nB);
+    return 0;
+}
+bool col_backward_applies(const DevProblem& P) {
+    static const bool off_switch = getenv("ILQRB_BWD_WARP") != nullptr;  // A/B switch: the warp-per-problem kernel
+    if (off_switch || P.n != 7 || P.m != 7) return false;
+    int nlim = 0;
+    for (int t = 0; t < P.n_tasks; t++) nlim += P.tasks[t].limits_set ? 1 : 0;
+    return nlim <= 1;
 }
 // Diagonal blocks of the state that no task couples: every task reads the joints [joint_offset, joint_offset + dof of its
 // robot) only, so l_x / l_xx (and with R diagonal, A = I, B = dt I the whole Riccati recursion) are block diagonal over
@@ -157,7 +177,8 @@ int launch_backward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
         bool all7 = true;
         for (int i = 0; i < sb.nblk; i++) all7 = all7 && sb.size[i] == 7;
         rc = all7 ? launch_backward_n1_blocks_t<7, 4, 7>(h, b0, nB, st, sb) : launch_backward_n1_blocks_t<0, 4, 7>(h, b0, nB, st, sb);
-    } else if (n == 7) rc = launch_backward_n1_t<1, 7, 4, 7>(h, b0, nB, st);
+    } else if (col_backward_applies(h->hp)) rc = launch_backward_n1_col_t<1>(h, b0, nB, st);
+    else if (n == 7) rc = launch_backward_n1_t<1, 7, 4, 7>(h, b0, nB, st);
     else if (n == 14) rc = launch_backward_n1_t<2, 14, 4, 2>(h, b0, nB, st);
     else if (n + 1 <= 8) rc = launch_backward_n1_t<1, 0, 4, 7>(h, b0, nB, st);
     else rc = launch_backward_n1_t<2, 0, 4, 2>(h, b0, nB, st);
