@@ -543,7 +543,7 @@ def main():
         from ilqr_planner_b200.solver import fp64_peaks
         dfma_peak, dmma_peak = fp64_peaks(local_rank)  # micro-benchmarks of the library itself (csrc/ubench.cu)
         figs = ncu_figures()
-        nb, nf = ncu_kernel(figs, "k_backward_n1", B), (ncu_kernel(figs, "k_forward_ring_n1", B) or ncu_kernel(figs, "k_forward_n1", B))
+        nb, nf = (ncu_kernel(figs, "k_backward_n1_col", B) or ncu_kernel(figs, "k_backward_n1", B)), (ncu_kernel(figs, "k_forward_ring_n1", B) or ncu_kernel(figs, "k_forward_n1", B))
         tot_ms = sum(v[0] for v in prof.values())
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
                 "ms_per_iteration": ms_max / args.steps / NB_ITER, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -561,8 +561,9 @@ def main():
                         "d2h_ceiling_note": "aggregate D2H rate of this box with all %d GPUs copying 256 MB blocks into pinned host memory at once" % world},
                 "north_star_target": north_star,
                 "gpu_launches": int(launches),
-                # dominant kernel = the backward Riccati pass; SURVEY 8d: it is bound by the FP64 (tensor/DMMA + DFMA) pipe
-                "roofline": {"kernel": "riccati_backward (k_backward_n1: DMMA m8n8k4.f64 + DFMA)", "bound": "tensor",
+                # dominant kernel = the backward Riccati pass; SURVEY 8d: a compute roofline on the FP64 pipe.  k_backward_n1_col issues DFMA
+                # (four problems per warp); DFMA, DMMA m8n8k4 and cuBLAS DGEMM peak at the same rate on B200 (peaks_measured_here_tflops)
+                "roofline": {"kernel": "riccati_backward (k_backward_n1_col: FP64 FMA, four problems per warp)", "bound": "tensor",
                              "achieved": alg_flops / bw_avg_s / 1e12 if bw_avg_s > 0 else None, "peak": fp64_peak, "unit": "TFLOP/s",
                              "frac": (alg_flops / bw_avg_s / 1e12 / fp64_peak) if (bw_avg_s > 0 and fp64_peak) else None,
                              "traffic": nb.get("dram_bytes"),

@@ -5,9 +5,9 @@
 // operations per lane (ncu: 397 instructions per problem and step, 100 of them FP64, issue-bound).  Here 8 lanes own one problem and
 // lane j owns COLUMN j of every augmented matrix ([P|p], [Qux|Qu], [Qxx|Qx], [K|d]; column 7 is the vector), eight rows in
 // registers with compile-time indices:
-//   * the elimination of [Quu + 1e-6 I | -Qux -Qu] needs one broadcast per stage — the multiplier column l_ik / l_kk, 8 doubles,
-//     written by the pivot column's owner and read back as four 16-byte shared-memory loads — and then updates its two columns with
-//     14 independent FMAs; no selects, no shuffles, and it is a solve (no explicit inverse, no product with it);
+//   * the elimination of [Quu + 1e-6 I | -Qux -Qu] needs one broadcast per stage — the multiplier column l_ik / l_kk, 7 doubles
+//     shuffled from the pivot column's owner — and then updates its two columns with 14 independent FMAs; it is a solve (no
+//     explicit inverse, no product with it);
 //   * products C = A B take column k of A as a shared-memory broadcast and B[k][j] from the lane's own registers: 8 FMAs per 16-byte
 //     pair of loads.  Quu [K|d] is formed as dt^2 (P [K|d]) + R o [K|d], so one product P [K|d] serves both the bracket
 //     M = Quu [K|d] + [Qux|Qu] and Qxu [K|d] = dt P [K|d]; the second product is K^T M.            ILQRRecursive.cpp:82-94
@@ -21,9 +21,11 @@
 namespace ilqrb {
 
 struct BwdColSmem {
-    // per problem: 8 multiplier columns (one per stage), [K|d] row-major, P column-major, the limit residuals; the stride keeps the
-    // four problems of a warp on distinct 16-byte bank groups for the broadcast loads (212 * 8 B = 32 mod 128)
-    static constexpr int F = 0, KS = 64, PC = 128, LQ = 192, BLK = 212;
+    // per problem: [K|d] row-major (odd problems shifted by 32 bytes so that the 64-byte row stores of two problems fall on disjoint
+    // banks), P column-major with a column stride of 10 doubles (the 16-byte column stores of 8 lanes hit 8 different bank groups),
+    // the limit residuals.  The block stride keeps the problems of a half-warp on distinct 16-byte bank groups for the broadcast
+    // loads (164 * 8 B = 32 mod 128).
+    static constexpr int KS = 0, PC = 68, PCS = 10, LQ = 148, BLK = 164;
     static constexpr int PER_WARP = 4 * BLK > BwdN1Smem<1>::PER_WARP ? 4 * BLK : BwdN1Smem<1>::PER_WARP;
 };
 
@@ -54,14 +56,21 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
     const int H = P.H;
     const double dt = 1.0 * P.dt;  // B = Identity * dt
     double* sm = wsmem + sub * BwdColSmem::BLK;
-    double* sF = sm + BwdColSmem::F;
-    double* sK = sm + BwdColSmem::KS;
+    double* sK = sm + BwdColSmem::KS + 4 * (sub & 1);
+    const int gsrc = lane & ~7;  // first lane of this problem's group
     double* sP = sm + BwdColSmem::PC;
     double* sQ = sm + BwdColSmem::LQ;
 
-    double R[8];
+    // R, and per-lane constants that stand in for selects on the lane's column index: the diagonal terms of Quu + 1e-6 I are added
+    // as x + 0 everywhere else (exact), R u enters the vector column only
+    double R[N], Rd[N], Ed[N], Rv[N];
 #pragma unroll
-    for (int i = 0; i < 8; i++) R[i] = i < N ? P.r_diag[i] : 0.0;
+    for (int i = 0; i < N; i++) {
+        R[i] = P.r_diag[i];
+        Rd[i] = (i == j) ? R[i] : 0.0;
+        Ed[i] = (i == j) ? 1e-6 * 1.0 : 0.0;
+        Rv[i] = (j == N) ? R[i] : 0.0;
+    }
     const double* Xb = W.X + (size_t)b * H * ns;
     const double* Ub = W.U + (size_t)b * (H - 1) * ms;
     const int S_kp = P.n_kp_steps;
@@ -118,7 +127,7 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
         next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
     }
     if (l0 >= 0) add_limits(Pc, Xb[(size_t)(H - 1) * ns + j]);
-    st8(sP + j * 8, Pc);
+    st8(sP + j * BwdColSmem::PCS, Pc);
     double un[8], xn = 0.0;
     ld8(Ub + (size_t)(H - 2) * ms, un);
     if (l0 >= 0) xn = Xb[(size_t)(H - 2) * ns + j];
@@ -141,10 +150,8 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
 #pragma unroll
         for (int i = 0; i < N; i++) {
             const double bp = dt * Pc[i];
-            Qa[i] = (j == N) ? R[i] * u[i] + bp : bp;
-            double quu = bp * dt;
-            if (i == j) quu = (R[i] + quu) + 1e-6 * 1.0;  // Quu + 1e-6 I                     ILQRRecursive.cpp:89
-            L[i] = (j < N) ? quu : 0.0;                 // lane 7 carries the vector column: no matrix column of its own
+            Qa[i] = fma(Rv[i], u[i], bp);
+            L[i] = ((bp * dt) + Rd[i]) + Ed[i];  // Quu + 1e-6 I (ILQRRecursive.cpp:89); lane 7 carries the vector column: its L is never a pivot column
             Rh[i] = -Qa[i];
             Qx[i] = Pc[i];
         }
@@ -155,27 +162,22 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
         }
         if (l0 >= 0) add_limits(Qx, x);
 
-        // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]: Gauss-Jordan without pivoting on the columns, one multiplier broadcast per stage
+        // [K|d] = -(Quu + 1e-6 I)^-1 [Qux|Qu]: Gauss-Jordan without pivoting on the columns; per stage every lane takes column s
+        // from its owner by shuffle (raw, so the shuffles do not wait for the reciprocal) and scales its own pivot-row entries
 #pragma unroll
         for (int s = 0; s < N; s++) {
-            {
-                const double inv = fast_rcp(L[s]);
-                double f[8];
+            double f[N];
 #pragma unroll
-                for (int i = 0; i < 8; i++) f[i] = (i == s) ? inv : (i < N ? L[i] * inv : 0.0);
-                if (j == s) st8(sF + s * 8, f);
-            }
-            __syncwarp();
-            double f[8];
-            ld8(sF + s * 8, f);
-            const int hi = __double2hiint(f[s]);  // 1 / pivot: positive and finite iff the pivot was
+            for (int i = 0; i < N; i++) f[i] = __shfl_sync(FULL, L[i], gsrc + s);
+            const double inv = fast_rcp(f[s]);
+            const int hi = __double2hiint(inv);  // 1 / pivot: positive and finite iff the pivot was
             ok = ok && (hi > 0) && (hi < 0x7ff00000);
-            const double lk = L[s], rk = Rh[s];
+            const double lk = L[s] * inv, rk = Rh[s] * inv;
 #pragma unroll
             for (int i = 0; i < N; i++) {
                 if (i == s) {
-                    L[i] = lk * f[s];
-                    Rh[i] = rk * f[s];
+                    L[i] = lk;
+                    Rh[i] = rk;
                 } else {
                     L[i] = fma(-f[i], lk, L[i]);
                     Rh[i] = fma(-f[i], rk, Rh[i]);
@@ -187,7 +189,8 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
         for (int i = 0; i < N; i++) sK[i * 8 + j] = Rh[i];
         if (live) {
 #pragma unroll
-            for (int i = 0; i < N; i++) Kg[i * ns + j] = (j < N) ? Rh[i] : 0.0;
+            for (int i = 0; i < N; i++)
+                if (j < N) Kg[i * ns + j] = Rh[i];  // the pad column stays as the solve's memset left it
             if (j == N) {
                 double dv[8];
 #pragma unroll
@@ -203,7 +206,7 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
 #pragma unroll
         for (int c = 0; c < N; c++) {
             double pc[8];
-            ld8(sP + c * 8, pc);
+            ld8(sP + c * BwdColSmem::PCS, pc);
 #pragma unroll
             for (int i = 0; i < N; i++) PK[i] = fma(pc[i], Rh[c], PK[i]);
         }
@@ -225,7 +228,7 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
 #pragma unroll
         for (int i = 0; i < N; i++) Pc[i] = (Qx[i] + acc[i]) + dt * PK[i];
         __syncwarp();  // every lane has read sP and sK
-        st8(sP + j * 8, Pc);
+        st8(sP + j * BwdColSmem::PCS, Pc);
         __syncwarp();
     }
     return __ballot_sync(FULL, !ok);

@@ -290,10 +290,9 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
         // measured on B200 (C2, B = 4096; ILQRB_GROUPS sweeps in DESIGN.md): 3 groups for device-resident results, 8 when one blocking call
         // must hide its own downloads, 5 when the caller streams batches through two handles (the other handle's solve covers the
         // downloads, and fewer, larger groups keep the kernels closer to a full wave)
-        // device-resident results: about three groups per two waves of the forward kernel (28 resident warps per SM with one state
-        // tile, 12 with two; 16 on the time path), at least 3: C2 B = 4096 / 8192 / 16384 -> 3 / 3 / 6, C5 B = 8192 -> 7 (sweeps in DESIGN.md)
-        const int wave = fast1 ? fast_n1_wave(h) : 148 * 16;
-        const int g_dev = std::min(8, std::max(3, (3 * B + 2 * wave - 1) / (2 * wave)));
+        // device-resident results: fast_n1_default_groups (launch_fused1.cu); time path: about three groups per two waves of 16 warps per SM
+        const int wave = 148 * 16;
+        const int g_dev = fast1 ? fast_n1_default_groups(h, B) : std::min(8, std::max(3, (3 * B + 2 * wave - 1) / (2 * wave)));
         int G = h->prof ? 1 : (int)env_uint("ILQRB_GROUPS", out_async ? (h->streaming ? 5 : 8) : g_dev);
         if (G > ilqrb_handle_s::MAX_GROUPS) G = ilqrb_handle_s::MAX_GROUPS;
         if (G < 1 || B < 64 * G) G = 1;

@@ -1,5 +1,6 @@
 // launch_fused1.cu — launchers of the single-integrator fast path (fused1.cuh): k_backward_n1 / k_backward_n1_blocks / k_forward_n1.
 #include <cstdlib>
+#include <cstring>
 
 #include "fused1_col.cuh"
 #include "fused1_fwd.cuh"
@@ -41,9 +42,15 @@ int launch_backward_n1_col_t(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
     kern<<<(warps + WARPS - 1) / WARPS, 32 * WARPS, smem, st>>>(h->dp, h->W, b0, nB);
     return 0;
 }
+int backward_form() {  // A/B switch: ILQRB_BWD = warp (one problem per warp, fused1.cuh) | col (four per warp, fused1_col.cuh; default)
+    static const int form = [] {
+        const char* e = getenv("ILQRB_BWD");
+        return (e && !strcmp(e, "warp")) ? 0 : 1;
+    }();
+    return form;
+}
 bool col_backward_applies(const DevProblem& P) {
-    static const bool off_switch = getenv("ILQRB_BWD_WARP") != nullptr;  // A/B switch: the warp-per-problem kernel
-    if (off_switch || P.n != 7 || P.m != 7) return false;
+    if (backward_form() == 0 || P.n != 7 || P.m != 7) return false;
     int nlim = 0;
     for (int t = 0; t < P.n_tasks; t++) nlim += P.tasks[t].limits_set ? 1 : 0;
     return nlim <= 1;
@@ -168,6 +175,17 @@ int fwd_mode() {
 
 }  // namespace
 
+// Problem groups (streams) for device-resident results.  The warp-per-problem backward kernel fills the SMs' warp slots and gains
+// from sharing them with another group's forward pass: about three groups per two waves of the forward kernel, at least 3 (C2
+// B = 4096 / 8192 / 16384 -> 3 / 3 / 6, C5 B = 8192 -> 7).  The column-per-lane kernel holds 4 problems per warp and is bound by latency
+// below ~8 warps per SM: it wants the whole batch in one launch (profiles/r2f_backward_col_groups.txt: B = 4096: 636 / 620 / 589 / 572 k
+// solves/s with 1 / 2 / 3 / 4 groups; 8192: flat; 16384: 768 / 778 / 750 / 744 k).
+int fast_n1_default_groups(ilqrb_handle h, int B) {
+    if (col_backward_applies(h->hp) && find_state_blocks(h->hp).nblk < 2) return std::max(1, B / 8192);
+    const int wave = fast_n1_wave(h);
+    return std::min(8, std::max(3, (3 * B + 2 * wave - 1) / (2 * wave)));
+}
+
 int launch_backward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
     h->begin(PS_BACKWARD);
     const int n = h->hp.n;
@@ -177,7 +195,10 @@ int launch_backward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
         bool all7 = true;
         for (int i = 0; i < sb.nblk; i++) all7 = all7 && sb.size[i] == 7;
         rc = all7 ? launch_backward_n1_blocks_t<7, 4, 7>(h, b0, nB, st, sb) : launch_backward_n1_blocks_t<0, 4, 7>(h, b0, nB, st, sb);
-    } else if (col_backward_applies(h->hp)) rc = launch_backward_n1_col_t<1>(h, b0, nB, st);
+    } else if (col_backward_applies(h->hp)) {
+        static const int cw = getenv("ILQRB_COL_WARPS") ? atoi(getenv("ILQRB_COL_WARPS")) : 1;  // warps per block (sweep in DESIGN.md)
+        rc = cw == 4 ? launch_backward_n1_col_t<4>(h, b0, nB, st) : cw == 2 ? launch_backward_n1_col_t<2>(h, b0, nB, st) : launch_backward_n1_col_t<1>(h, b0, nB, st);
+    }
     else if (n == 7) rc = launch_backward_n1_t<1, 7, 4, 7>(h, b0, nB, st);
     else if (n == 14) rc = launch_backward_n1_t<2, 14, 4, 2>(h, b0, nB, st);
     else if (n + 1 <= 8) rc = launch_backward_n1_t<1, 0, 4, 7>(h, b0, nB, st);

@@ -2,7 +2,7 @@
 # Column-per-lane backward kernel (fused1_col.cuh) on the GPU box: parity tests, A/B timing against the warp-per-problem kernel.
 mkdir -p gpurun_out
 TAG=${1:-r2c}
-timeout 1500 python -m pytest tests/test_gpu_parity.py tests/test_gpu_n3.py tests/test_gpu_multi.py -m gpu -q -x > gpurun_out/${TAG}_pytest.log 2>&1
+[ "$2" == "notest" ] || timeout 1500 python -m pytest tests/test_gpu_parity.py tests/test_gpu_n3.py tests/test_gpu_multi.py -m gpu -q -x > gpurun_out/${TAG}_pytest.log 2>&1
 echo "pytest rc=$?" >> gpurun_out/${TAG}_pytest.log
 tail -5 gpurun_out/${TAG}_pytest.log
 cat > /tmp/c2_bench.py <<'PY'
@@ -29,9 +29,8 @@ with Handle(pb) as h:
     print("B %d ms %.3f solves/s %.0f backward %.3f forward %.3f" % (B, dt * 1e3, pb.batch / dt, pr["riccati_backward"][0], pr["linesearch_rollout"][0]))
 PY
 for B in 4096 8192; do
-  echo "col"; timeout 300 python /tmp/c2_bench.py $B
-  echo "warp"; ILQRB_BWD_WARP=1 timeout 300 python /tmp/c2_bench.py $B
-  echo "col groups=1"; ILQRB_GROUPS=1 timeout 300 python /tmp/c2_bench.py $B
-  echo "warp groups=1"; ILQRB_GROUPS=1 ILQRB_BWD_WARP=1 timeout 300 python /tmp/c2_bench.py $B
+  for CW in 1 2 4; do
+    echo "col warps/block=$CW"; ILQRB_COL_WARPS=$CW ILQRB_GROUPS=1 timeout 300 python /tmp/c2_bench.py $B
+  done
 done > gpurun_out/${TAG}_ab.txt 2>&1
 cat gpurun_out/${TAG}_ab.txt
