@@ -42,17 +42,16 @@ __device__ __forceinline__ void st8(double* p, const double (&o)[8]) {
     for (int q = 0; q < 4; q++) *reinterpret_cast<double2*>(p + 2 * q) = make_double2(o[2 * q], o[2 * q + 1]);
 }
 
-// returns the ballot of lanes whose problem met a non-positive pivot.  bfirst: first problem of this warp; bend: one past the last
-// problem of the launch.  N = 7: the state rows are 8 doubles wide (ns = 8), which the 16-byte loads of u rely on.
-template <int N>
-__device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const Work& W, int bfirst, int bend, int lane, double* wsmem) {
-    static_assert(N == 7, "row stride of 8 doubles assumed");
+// returns the ballot of lanes whose problem met a non-positive pivot.  The 8 lanes of a group work on problem b (idle groups shadow
+// a live problem and store nothing).  BLK = false: the problem's state is the 7 joints (row stride 8 doubles: 16-byte accesses).
+// BLK = true: the group handles the diagonal block [off, off + 7) of a problem whose tasks touch disjoint joint ranges (composite
+// robots, C5; see backward_n1_body): strides are those of the full state.
+template <int N, bool BLK>
+__device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const Work& W, int b, bool live, int off, int lane, double* wsmem) {
+    static_assert(N == 7, "8 x 8 augmented matrices");
     constexpr unsigned FULL = 0xffffffffu;
-    constexpr int ns = 8, ms = 8, nf = N;
+    const int nf = BLK ? P.n : N, ns = BLK ? ((nf + 1) & ~1) : 8, ms = ns;
     const int sub = lane >> 3, j = lane & 7;
-    const int bq = bfirst + sub;
-    const bool live = bq < bend && !W.done[bq < bend ? bq : bfirst];
-    const int b = live ? bq : bfirst;  // idle groups shadow the warp's first problem and store nothing
     const int H = P.H;
     const double dt = 1.0 * P.dt;  // B = Identity * dt
     double* sm = wsmem + sub * BwdColSmem::BLK;
@@ -66,25 +65,28 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
     double R[N], Rd[N], Ed[N], Rv[N];
 #pragma unroll
     for (int i = 0; i < N; i++) {
-        R[i] = P.r_diag[i];
+        R[i] = P.r_diag[off + i];
         Rd[i] = (i == j) ? R[i] : 0.0;
         Ed[i] = (i == j) ? 1e-6 * 1.0 : 0.0;
         Rv[i] = (j == N) ? R[i] : 0.0;
     }
-    const double* Xb = W.X + (size_t)b * H * ns;
-    const double* Ub = W.U + (size_t)b * (H - 1) * ms;
+    const double* Xb = W.X + (size_t)b * H * ns + off;
+    const double* Ub = W.U + (size_t)b * (H - 1) * ms + off;
     const int S_kp = P.n_kp_steps;
 
-    // joint limits of the (single) limit-carrying task: lane j checks state j   System.cpp:121-142
+    // joint limits: lane j checks state off + j against the one sub-system that limits it (the launcher sends systems where two
+    // sub-systems limit the same state to the warp-per-problem kernel)   System.cpp:121-142, SequentialSystem.cpp:119-165
     int l0 = -1;
-    if (P.any_limits)
-        for (int ti = P.n_tasks - 1; ti >= 0; ti--)
-            if (P.tasks[ti].limits_set) l0 = ti;
     double lmx = INFINITY, lmn = -INFINITY;
-    if (l0 >= 0 && j < N && P.tasks[l0].limit_weight[j] != 0) {
-        lmx = P.tasks[l0].state_max[j];
-        lmn = P.tasks[l0].state_min[j];
-    }
+    if (P.any_limits)
+        for (int ti = 0; ti < P.n_tasks; ti++)
+            if (P.tasks[ti].limits_set) {
+                l0 = ti;
+                if (j < N && P.tasks[ti].limit_weight[off + j] != 0) {
+                    lmx = P.tasks[ti].state_max[off + j];
+                    lmn = P.tasks[ti].state_min[off + j];
+                }
+            }
     // e += [L^T L | -L^T q] with L = diag(violated), q = limit - x                      System.cpp:263-269,299-305
     auto add_limits = [&](double (&e)[8], double x) {
         double q = 0.0;
@@ -109,8 +111,8 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
     };
     // e += [l_xx | l_x] of keypoint step index s                                         System.cpp:252-260,290-296
     auto add_kp = [&](double (&e)[8], int s) {
-        const double* lx = W.LX + ((size_t)b * S_kp + s) * nf;
-        const double* lxx = W.LXX + ((size_t)b * S_kp + s) * nf * nf;
+        const double* lx = W.LX + ((size_t)b * S_kp + s) * nf + off;
+        const double* lxx = W.LXX + ((size_t)b * S_kp + s) * nf * nf + (size_t)off * nf + off;
 #pragma unroll
         for (int i = 0; i < N; i++) e[i] += (j < N) ? lxx[i * nf + j] : lx[i];
     };
@@ -128,12 +130,18 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
     }
     if (l0 >= 0) add_limits(Pc, Xb[(size_t)(H - 1) * ns + j]);
     st8(sP + j * BwdColSmem::PCS, Pc);
+    auto load_u = [&](int k, double (&o)[8]) {  // the controls enter the vector column only
+        if constexpr (BLK) {
+#pragma unroll
+            for (int i = 0; i < N; i++) o[i] = (j == N) ? Ub[(size_t)k * ms + i] : 0.0;
+        } else ld8(Ub + (size_t)k * ms, o);
+    };
     double un[8], xn = 0.0;
-    ld8(Ub + (size_t)(H - 2) * ms, un);
+    load_u(H - 2, un);
     if (l0 >= 0) xn = Xb[(size_t)(H - 2) * ns + j];
     bool ok = true;
-    double* Kg = W.K + ((size_t)b * (H - 1) + (H - 2)) * nf * ns;  // walks backwards with k
-    double* dg = W.d + ((size_t)b * (H - 1) + (H - 2)) * ms;
+    double* Kg = W.K + ((size_t)b * (H - 1) + (H - 2)) * nf * ns + (size_t)off * ns + off;  // walks backwards with k
+    double* dg = W.d + ((size_t)b * (H - 1) + (H - 2)) * ms + off;
     __syncwarp();
 
     for (int k = H - 2; k >= 0; k--, Kg -= nf * ns, dg -= ms) {
@@ -142,7 +150,7 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
         for (int i = 0; i < 8; i++) u[i] = un[i];
         const double x = xn;
         if (k > 0) {  // prefetch the next step's controls / state
-            ld8(Ub + (size_t)(k - 1) * ms, un);
+            load_u(k - 1, un);
             if (l0 >= 0) xn = Xb[(size_t)(k - 1) * ns + j];
         }
         // [Qux|Qu] = [0 | R u] + (B^T [P|p]) A_aug ;  Quu = R + (B^T P) B ;  [Qxx|Qx] = [l_xx|l_x] + (A^T [P|p]) A_aug   ILQRRecursive.cpp:82-87
@@ -192,10 +200,15 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
             for (int i = 0; i < N; i++)
                 if (j < N) Kg[i * ns + j] = Rh[i];  // the pad column stays as the solve's memset left it
             if (j == N) {
-                double dv[8];
+                if constexpr (BLK) {
 #pragma unroll
-                for (int i = 0; i < 8; i++) dv[i] = i < N ? Rh[i] : 0.0;
-                st8(dg, dv);
+                    for (int i = 0; i < N; i++) dg[i] = Rh[i];
+                } else {
+                    double dv[8];
+#pragma unroll
+                    for (int i = 0; i < 8; i++) dv[i] = i < N ? Rh[i] : 0.0;
+                    st8(dg, dv);
+                }
             }
         }
         __syncwarp();
@@ -235,16 +248,19 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
 }
 
 template <int N, int WARPS>
-__global__ void __launch_bounds__(32 * WARPS) k_backward_n1_col(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
+__global__ void __maxnreg__(200) k_backward_n1_col(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
     extern __shared__ __align__(16) double smem_col[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int bfirst = b0 + 4 * (blockIdx.x * WARPS + wid), bend = b0 + nB;
     if (bfirst >= bend) return;
     double* ws = smem_col + (size_t)wid * BwdColSmem::PER_WARP;
-    bool any = false;
-    for (int s = 0; s < 4; s++) any = any || (bfirst + s < bend && !W.done[bfirst + s]);
-    if (!any) return;
-    const unsigned bad = backward_n1_col<N>(*Pp, W, bfirst, bend, lane, ws);
+    int shadow = -1;
+    for (int s = 3; s >= 0; s--)
+        if (bfirst + s < bend && !W.done[bfirst + s]) shadow = bfirst + s;
+    if (shadow < 0) return;
+    const int bq = bfirst + (lane >> 3);
+    const bool live = bq < bend && !W.done[bq < bend ? bq : shadow];
+    const unsigned bad = backward_n1_col<N, false>(*Pp, W, live ? bq : shadow, live, 0, lane, ws);
     if (bad == 0) return;
     for (int s = 0; s < 4; s++) {  // rare: the reference's pivoted inverse for the problems that need it, a warp each
         const int b = bfirst + s;
@@ -252,6 +268,41 @@ __global__ void __launch_bounds__(32 * WARPS) k_backward_n1_col(const DevProblem
         if (lane == 0) atomicOr(W.status + b, ILQRB_ST_QUU_NOT_SPD);
         __syncwarp();
         backward_n1_redo<1, N>(*Pp, W, b, lane, ws, 0, 0);
+    }
+}
+
+// composite robots: one group of 8 lanes per (problem, diagonal block of 7 joints)
+template <int N, int WARPS>
+__global__ void __maxnreg__(200) k_backward_n1_col_blocks(const DevProblem* __restrict__ Pp, Work W, int b0, int nB, StateBlocks sb) {
+    extern __shared__ __align__(16) double smem_col[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int ufirst = 4 * (blockIdx.x * WARPS + wid), uend = nB * sb.nblk;
+    if (ufirst >= uend) return;
+    double* ws = smem_col + (size_t)wid * BwdColSmem::PER_WARP;
+    int shadow = -1;
+    for (int s = 3; s >= 0; s--)
+        if (ufirst + s < uend && !W.done[b0 + (ufirst + s) / sb.nblk]) shadow = ufirst + s;
+    if (shadow < 0) return;
+    const int uq = ufirst + (lane >> 3);
+    const bool live = uq < uend && !W.done[b0 + (uq < uend ? uq : shadow) / sb.nblk];
+    const int u = live ? uq : shadow;
+    const int bl = u / sb.nblk, blk = u - bl * sb.nblk;
+    int off = 0;
+    for (int q = 0; q < 4; q++)
+        if (q == blk) off = sb.off[q];
+    const unsigned bad = backward_n1_col<N, true>(*Pp, W, b0 + bl, live, off, lane, ws);
+    if (bad == 0) return;
+    for (int s = 0; s < 4; s++) {
+        const int us = ufirst + s;
+        if (((bad >> (8 * s)) & 0xffu) == 0 || us >= uend) continue;
+        const int b = b0 + us / sb.nblk, bk = us % sb.nblk;
+        if (W.done[b]) continue;
+        if (lane == 0) atomicOr(W.status + b, ILQRB_ST_QUU_NOT_SPD);
+        __syncwarp();
+        int o = 0;
+        for (int q = 0; q < 4; q++)
+            if (q == bk) o = sb.off[q];
+        backward_n1_redo<1, N>(*Pp, W, b, lane, ws, o, N);
     }
 }
 

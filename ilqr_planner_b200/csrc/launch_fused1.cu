@@ -49,11 +49,26 @@ int backward_form() {  // A/B switch: ILQRB_BWD = warp (one problem per warp, fu
     }();
     return form;
 }
-bool col_backward_applies(const DevProblem& P) {
-    if (backward_form() == 0 || P.n != 7 || P.m != 7) return false;
-    int nlim = 0;
-    for (int t = 0; t < P.n_tasks; t++) nlim += P.tasks[t].limits_set ? 1 : 0;
-    return nlim <= 1;
+// blocks: the state splits into diagonal blocks of 7 joints each (find_state_blocks), one group of lanes per block
+bool col_backward_applies(const DevProblem& P, bool blocks) {
+    if (backward_form() == 0 || P.n != P.m || (!blocks && P.n != 7)) return false;
+    for (int i = 0; i < P.n; i++) {  // a lane checks its state against ONE sub-system's limits
+        int nlim = 0;
+        for (int t = 0; t < P.n_tasks; t++) nlim += (P.tasks[t].limits_set && P.tasks[t].limit_weight[i] != 0) ? 1 : 0;
+        if (nlim > 1) return false;
+    }
+    return true;
+}
+template <int WARPS>
+int launch_backward_n1_col_blocks_t(ilqrb_handle h, int b0, int nB, cudaStream_t st, const StateBlocks& sb) {
+    const size_t smem = (size_t)WARPS * BwdColSmem::PER_WARP * sizeof(double);
+    auto kern = k_backward_n1_col_blocks<7, WARPS>;
+    static DynSmem attr;
+    int rc = attr.ensure(kern, smem, h->device);
+    if (rc) return rc;
+    const int warps = (nB * sb.nblk + 3) / 4;
+    kern<<<(warps + WARPS - 1) / WARPS, 32 * WARPS, smem, st>>>(h->dp, h->W, b0, nB, sb);
+    return 0;
 }
 // Diagonal blocks of the state that no task couples: every task reads the joints [joint_offset, joint_offset + dof of its
 // robot) only, so l_x / l_xx (and with R diagonal, A = I, B = dt I the whole Riccati recursion) are block diagonal over
@@ -181,7 +196,7 @@ int fwd_mode() {
 // below ~8 warps per SM: it wants the whole batch in one launch (profiles/r2f_backward_col_groups.txt: B = 4096: 636 / 620 / 589 / 572 k
 // solves/s with 1 / 2 / 3 / 4 groups; 8192: flat; 16384: 768 / 778 / 750 / 744 k).
 int fast_n1_default_groups(ilqrb_handle h, int B) {
-    if (col_backward_applies(h->hp) && find_state_blocks(h->hp).nblk < 2) return std::max(1, B / 8192);
+    if (col_backward_applies(h->hp, false) && find_state_blocks(h->hp).nblk < 2) return std::max(1, B / 8192);
     const int wave = fast_n1_wave(h);
     return std::min(8, std::max(3, (3 * B + 2 * wave - 1) / (2 * wave)));
 }
@@ -194,11 +209,9 @@ int launch_backward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
     if (sb.nblk >= 2) {
         bool all7 = true;
         for (int i = 0; i < sb.nblk; i++) all7 = all7 && sb.size[i] == 7;
-        rc = all7 ? launch_backward_n1_blocks_t<7, 4, 7>(h, b0, nB, st, sb) : launch_backward_n1_blocks_t<0, 4, 7>(h, b0, nB, st, sb);
-    } else if (col_backward_applies(h->hp)) {
-        static const int cw = getenv("ILQRB_COL_WARPS") ? atoi(getenv("ILQRB_COL_WARPS")) : 1;  // warps per block (sweep in DESIGN.md)
-        rc = cw == 4 ? launch_backward_n1_col_t<4>(h, b0, nB, st) : cw == 2 ? launch_backward_n1_col_t<2>(h, b0, nB, st) : launch_backward_n1_col_t<1>(h, b0, nB, st);
-    }
+        if (all7 && col_backward_applies(h->hp, true)) rc = launch_backward_n1_col_blocks_t<1>(h, b0, nB, st, sb);
+        else rc = all7 ? launch_backward_n1_blocks_t<7, 4, 7>(h, b0, nB, st, sb) : launch_backward_n1_blocks_t<0, 4, 7>(h, b0, nB, st, sb);
+    } else if (col_backward_applies(h->hp, false)) rc = launch_backward_n1_col_t<1>(h, b0, nB, st);  // 1 / 2 / 4 warps per block measured alike
     else if (n == 7) rc = launch_backward_n1_t<1, 7, 4, 7>(h, b0, nB, st);
     else if (n == 14) rc = launch_backward_n1_t<2, 14, 4, 2>(h, b0, nB, st);
     else if (n + 1 <= 8) rc = launch_backward_n1_t<1, 0, 4, 7>(h, b0, nB, st);
