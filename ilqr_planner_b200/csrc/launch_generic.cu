@@ -130,9 +130,17 @@ int launch_init(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
     if (nB < 0) nB = h->hp.B;
     if (!st) st = h->stream;
     h->begin(PS_ROLLOUT_INIT);
-#define CALL(N, M) k_rollout_init<N, M><<<(nB + 127) / 128, 128, 0, st>>>(h->dp, h->W, b0, nB)
+    const int tot = nB * h->hp.H;
+    {  // threads per problem: joints + time state
+        const int need = h->hp.dof + (h->hp.time ? 1 : 0);
+        if (need <= 8) k_rollout_x<8><<<(nB * 8 + 127) / 128, 128, 0, st>>>(h->dp, h->W, b0, nB);
+        else if (need <= 16) k_rollout_x<16><<<(nB * 16 + 127) / 128, 128, 0, st>>>(h->dp, h->W, b0, nB);
+        else k_rollout_x<32><<<(nB * 32 + 127) / 128, 128, 0, st>>>(h->dp, h->W, b0, nB);
+    }
+#define CALL(N, M) k_stage_costs<N, M><<<(tot + 127) / 128, 128, 0, st>>>(h->dp, h->W, b0, nB)
     DISPATCH_NM(size_class(h->hp.n, h->hp.m), CALL)
 #undef CALL
+    k_sum_costs<<<(nB + 31) / 32, 32, 0, st>>>(h->dp, h->W, b0, nB);
     h->end();
     CU(cudaGetLastError());
     return 0;

@@ -1,6 +1,6 @@
 // recursive.cuh — kernels of the Recursive / AL iLQR solve path (ILQRRecursive.cpp:21-181, AL-ILQR.cpp:50-232).
 //
-//   k_rollout_init   initial rollout + cost                         ILQRRecursive.cpp:41-56
+//   k_rollout_x, k_stage_costs, k_sum_costs   initial rollout + cost   ILQRRecursive.cpp:41-56
 //   k_kp_derivs      l_x, l_xx of the task cost at keypoint steps    System.cpp:248-272,286-308
 //   k_backward       Riccati recursion, one problem per warp (DMMA)  ILQRRecursive.cpp:69-97 (+ AL terms AL-ILQR.cpp:110-145)
 //   k_linesearch     all 11 alpha candidates rolled out in parallel  ILQRRecursive.cpp:101-155
@@ -14,35 +14,94 @@
 namespace ilqrb {
 
 // ------------------------------------------------------------------------------------------------------------
-// initial rollout: one thread per problem
-template <int N, int M>
-__global__ void __launch_bounds__(128) k_rollout_init(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
+// initial rollout + cost (ILQRRecursive.cpp:41-56) as three launches: the states by one thread per problem (the only serial part:
+// step_state), the stage costs by one thread per (problem, timestep) into a scratch (the first B*H doubles of W.Uc, which the line
+// search fills later), their sum by one thread per problem in timestep order — the same values added in the same order as a single
+// serial pass, which took 370 us per solve at C2 (one thread per problem walking 99 x [stage cost, step] on 32 SMs).
+// states: the integrator is independent per joint (SimulationInterface.cpp:19-31: q_i += dt dq_i + dt^2/2 ddq_i ; dq_i += dt ddq_i ;
+// t += dt), so one thread per (problem, joint) — plus one for the time state — walks the horizon with step_state's operations;
+// TP threads per problem (a power of two >= dof + 1), loads of the controls four steps ahead of the serial chain
+template <int TP>
+__global__ void __launch_bounds__(128) k_rollout_x(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
     const DevProblem& P = *Pp;
-    const int bl = blockIdx.x * blockDim.x + threadIdx.x;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int bl = idx / TP, c = idx % TP;
     if (bl >= nB) return;
     const int b = b0 + bl;
-    const int H = P.H;
-    double x[N], u[M];
-    load_x0<N>(P, b, x);
-    double cost = 0.0;
-    for (int k = 0; k < H; k++) {
-        double* Xk = W.X + ((size_t)b * H + k) * W.ns;
+    const int H = P.H, dof = P.dof, n = P.n, ns = W.ns, ms = W.ms;
+    const bool second = P.nb_deriv == 2, joint = c < dof, tim = P.time && c == dof;
+    if (c == 0) {
+        W.done[b] = 0;
+        W.iters[b] = 0;
+        W.alpha_last[b] = 1.0;
+    }
+    double q = joint ? P.q0[(size_t)b * dof + c] : 0.0;
+    double v = (joint && second) ? P.dq0[(size_t)b * dof + c] : 0.0;
+    double* Xb = W.X + (size_t)b * H * ns;
+    const double* Ub = W.U + (size_t)b * (H - 1) * ms;
+    auto put = [&](int k) {
+        double* Xk = Xb + (size_t)k * ns;
+        if (joint) {
+            Xk[c] = q;
+            if (second) Xk[dof + c] = v;
+        } else if (tim) Xk[n - 1] = q;
+        if (c == 0)
+            for (int pad = n; pad < ns; pad++) Xk[pad] = 0.0;  // the padding entries of the row
+    };
+    put(0);
+    constexpr int PF = 4;
+    for (int k0 = 0; k0 < H - 1; k0 += PF) {
+        double uu[PF], ss[PF];
 #pragma unroll
-        for (int i = 0; i < N; i++)
-            if (i < W.ns) Xk[i] = (i < P.n) ? x[i] : 0.0;
-        if (k == H - 1) break;
+        for (int p = 0; p < PF; p++) {
+            const int k = k0 + p < H - 1 ? k0 + p : H - 2;
+            uu[p] = joint ? Ub[(size_t)k * ms + c] : 0.0;
+            ss[p] = P.time ? Ub[(size_t)k * ms + P.m - 1] : 0.0;
+        }
+#pragma unroll
+        for (int p = 0; p < PF; p++) {
+            if (k0 + p >= H - 1) break;
+            double dt = P.dt;
+            if (P.time) dt = __dmul_rn(ss[p], ss[p]);
+            const double hdt2 = __dmul_rn(dt, dt) / 2;
+            if (joint) {
+                if (!second) q = __dadd_rn(q, __dadd_rn(__dmul_rn(dt, uu[p]), __dmul_rn(hdt2, 0.0)));
+                else {
+                    q = __dadd_rn(q, __dadd_rn(__dmul_rn(dt, v), __dmul_rn(hdt2, uu[p])));
+                    v = __dadd_rn(v, __dmul_rn(dt, uu[p]));
+                }
+            } else if (tim) q = __dadd_rn(q, dt);
+            put(k0 + p + 1);
+        }
+    }
+}
+template <int N, int M>
+__global__ void __launch_bounds__(128) k_stage_costs(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
+    const DevProblem& P = *Pp;
+    const int H = P.H;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= nB * H) return;
+    const int k = idx / nB, bl = idx - k * nB, b = b0 + bl;  // a warp holds one timestep of 32 problems: the keypoint branch is uniform
+    double x[N], u[M];
+    const double* Xk = W.X + ((size_t)b * H + k) * W.ns;
+#pragma unroll
+    for (int i = 0; i < N; i++) x[i] = (i < P.n) ? Xk[i] : 0.0;
+    if (k < H - 1) {
         const double* Uk = W.U + ((size_t)b * (H - 1) + k) * W.ms;
 #pragma unroll
         for (int i = 0; i < M; i++) u[i] = (i < P.m) ? Uk[i] : 0.0;
-        cost += stage_cost<N>(P, b, x, u, k);
-        step_state<N>(P, x, u);
     }
-    cost += stage_cost<N>(P, b, x, nullptr, H - 1);
+    W.Uc[(size_t)b * H + k] = stage_cost<N>(P, b, x, k < H - 1 ? u : nullptr, k);
+}
+__global__ void __launch_bounds__(128) k_sum_costs(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
+    const int bl = blockIdx.x * blockDim.x + threadIdx.x;
+    if (bl >= nB) return;
+    const int b = b0 + bl, H = Pp->H;
+    const double* c = W.Uc + (size_t)b * H;
+    double cost = 0.0;
+    for (int k = 0; k < H; k++) cost += c[k];
     W.cost0[b] = cost;
-    W.done[b] = 0;
-    W.iters[b] = 0;
     W.status[b] = isnan(cost) ? ILQRB_ST_NAN_COST : 0;
-    W.alpha_last[b] = 1.0;
 }
 
 // ------------------------------------------------------------------------------------------------------------
