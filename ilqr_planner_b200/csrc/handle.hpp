@@ -156,6 +156,7 @@ int launch_forward_time(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it,
 // ---- launch_fused1.cu -----------------------------------------------------------------------------------------------
 bool fast_n1_applies(ilqrb_handle h, bool al);
 int fast_n1_wave(ilqrb_handle h);  // problems one full wave of the forward kernel holds
+bool fast_n1_col_path(ilqrb_handle h);            // the backward pass runs on the column-per-lane kernels (fused1_col.cuh)
 int fast_n1_default_groups(ilqrb_handle h, int B);  // problem groups for device-resident results
 int launch_backward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st);
 int launch_forward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st, int it, int nb_iter, int line_search, int early_stop);

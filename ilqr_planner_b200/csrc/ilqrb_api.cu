@@ -293,12 +293,21 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
         // device-resident results: fast_n1_default_groups (launch_fused1.cu); time path: about three groups per two waves of 16 warps per SM
         const int wave = 148 * 16;
         const int g_dev = fast1 ? fast_n1_default_groups(h, B) : std::min(8, std::max(3, (3 * B + 2 * wave - 1) / (2 * wave)));
-        int G = h->prof ? 1 : (int)env_uint("ILQRB_GROUPS", out_async ? (h->streaming ? 5 : 8) : g_dev);
+        // host outputs on the column-per-lane backward path (C2; profiles/r2o_e2e_groups.txt): a blocking call 360 / 354-377 / 353 / 330 k
+        // solves/s with 1 / 2 / 3 / 5 groups; the streaming form with gains 504 / 433 / 542 / 552 k with 1 / 2 / 3 / 5, without gains 650 / 638-665 / 636 / 627 k
+        const bool col = fast1 && fast_n1_col_path(h);
+        const int g_host = h->streaming ? ((col && out_async && !out_async->K) ? 2 : 5) : (col ? 2 : 8);
+        int G = h->prof ? 1 : (int)env_uint("ILQRB_GROUPS", out_async ? g_host : g_dev);
         if (G > ilqrb_handle_s::MAX_GROUPS) G = ilqrb_handle_s::MAX_GROUPS;
         if (G < 1 || B < 64 * G) G = 1;
         if (G == 1) {
             for (int it = 0; it < opts->nb_iter; it++)
                 if ((rc = iteration(0, B, h->stream, it, nullptr))) return rc;
+            if (out_async && opts->nb_iter > 0) {  // the copies are queued behind the solve: the streaming entry point returns without waiting
+                h->last_nb_iter = opts->nb_iter;
+                if ((rc = enqueue_download_range(h, out_async, 0, B, std::max(opts->nb_iter, 1), h->stream))) return rc;
+                h->downloaded = true;
+            }
         } else if (opts->nb_iter > 0) {
             if ((rc = h->ensure_groups(G))) return rc;
             CU(cudaEventRecord(h->ev_start, h->stream));

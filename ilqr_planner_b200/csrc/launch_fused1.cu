@@ -195,6 +195,15 @@ int fwd_mode() {
 // B = 4096 / 8192 / 16384 -> 3 / 3 / 6, C5 B = 8192 -> 7).  The column-per-lane kernel holds 4 problems per warp and is bound by latency
 // below ~8 warps per SM: it wants the whole batch in one launch (profiles/r2f_backward_col_groups.txt: B = 4096: 636 / 620 / 589 / 572 k
 // solves/s with 1 / 2 / 3 / 4 groups; 8192: flat; 16384: 768 / 778 / 750 / 744 k).
+bool fast_n1_col_path(ilqrb_handle h) {
+    const StateBlocks sb = find_state_blocks(h->hp);
+    if (sb.nblk >= 2) {
+        for (int i = 0; i < sb.nblk; i++)
+            if (sb.size[i] != 7) return false;
+        return col_backward_applies(h->hp, true);
+    }
+    return col_backward_applies(h->hp, false);
+}
 int fast_n1_default_groups(ilqrb_handle h, int B) {
     if (col_backward_applies(h->hp, false) && find_state_blocks(h->hp).nblk < 2) return std::max(1, B / 8192);
     const int wave = fast_n1_wave(h);
