@@ -285,9 +285,12 @@ def stream_e2e(torch, hs, outs, u0s, steps, nb_iter, streams, barrier):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(streams[0])
     streams[1].wait_event(e0)
+    chain = os.environ.get("ILQRB_BENCH_CHAIN", "once")  # once | always | never
     for i in range(steps):
         k = i % 2
         hs[k].synchronize()
+        if (chain == "once" and i == 1) or chain == "always":
+            hs[k].chain_after_compute(hs[1 - k])
         hs[k].solve_recursive_async(u0s[k], nb_iter, True, False, out=outs[k])
     streams[0].wait_stream(streams[1])
     e1.record(streams[0])
@@ -449,10 +452,19 @@ def main():
     t0 = time.perf_counter()
     e0.record(stream)
     stream2.wait_event(e0)
+    stagger_s = float(os.environ.get("ILQRB_BENCH_STAGGER_MS", "0")) * 1e-3
+    chain = os.environ.get("ILQRB_BENCH_CHAIN", "once")  # once | always | never (A/B switch)
     for i in range(args.steps):
         k = i % 2
         hs[k].synchronize()  # batch i-2 is on the host (a consumer would read outs[k] here) before its buffers are reused
+        if (chain == "once" and i == 1) or chain == "always":
+            # The second handle's first solve starts when the first handle's kernels have finished (ilqrb_chain_after_compute): that puts
+            # the handles half a cycle apart — one computes while the other copies — instead of in phase (compute together, then copy
+            # together).  From then on each handle reissues as soon as its previous batch is on the host.
+            hs[k].chain_after_compute(hs[1 - k])
         hs[k].solve_recursive_async(u0s[k], NB_ITER, True, False, out=outs[k])
+        if i == 0 and stagger_s > 0:
+            time.sleep(stagger_s)  # A/B switch: the second handle starts late instead of being chained
     stream.wait_stream(stream2)
     e1.record(stream)
     barrier()
@@ -550,7 +562,7 @@ def main():
                 "config": workload_config(world, B), "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps,
                         "host_wall_ms_per_step": wall_ms / args.steps,
-                        "mode": "ilqrb_solve_recursive_async on two handles used alternately: batch i's D2H overlaps batch i+1's solve; every batch's "
+                        "mode": "ilqrb_solve_recursive_async on two handles used alternately, the second handle's first solve chained behind the first one's kernels (ilqrb_chain_after_compute) so that one handle computes while the other copies; every batch's "
                                 "U0 H2D and full result D2H (pinned host memory) inside the timed region, which ends with the last batch on the host",
                         "sync_call": {"value": e2e_sync_value, "unit": UNIT, "ms_per_step": ms_sync / args.steps,
                                       "mode": "one blocking ilqrb_solve_recursive per batch (H2D -> solve -> D2H, no overlap across batches)"},

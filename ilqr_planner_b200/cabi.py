@@ -105,7 +105,7 @@ SYMBOLS = [
     "ilqrb_synchronize", "ilqrb_update_problems", "ilqrb_solve_recursive", "ilqrb_solve_recursive_async", "ilqrb_solve_al", "ilqrb_solve_batch",
     "ilqrb_upload_u0", "ilqrb_run_recursive", "ilqrb_run_al", "ilqrb_run_batch", "ilqrb_download", "ilqrb_rollout",
     "ilqrb_kinematics", "ilqrb_set_profiling", "ilqrb_get_profile", "ilqrb_reset_profile", "ilqrb_launch_count",
-    "ilqrb_chain_from_urdf", "ilqrb_build_psi", "ilqrb_fp64_peaks", "ilqrb_kinematics_static", "ilqrb_eval_point", "ilqrb_keypoint_diff", "ilqrb_sd", "ilqrb_host_alloc", "ilqrb_host_free", "ilqrb_lqt_solve", "ilqrb_lqt_command",
+    "ilqrb_chain_from_urdf", "ilqrb_build_psi", "ilqrb_fp64_peaks", "ilqrb_kinematics_static", "ilqrb_eval_point", "ilqrb_keypoint_diff", "ilqrb_sd", "ilqrb_host_alloc", "ilqrb_host_free", "ilqrb_lqt_solve", "ilqrb_lqt_command", "ilqrb_chain_after_compute",
     "ilqrb_multi_plan", "ilqrb_create_multi", "ilqrb_multi_destroy", "ilqrb_multi_count", "ilqrb_multi_slice", "ilqrb_multi_solve_recursive",
     "ilqrb_multi_solve_al", "ilqrb_multi_solve_batch", "ilqrb_multi_upload_u0", "ilqrb_multi_run_recursive", "ilqrb_multi_synchronize", "ilqrb_multi_download",
 ]
@@ -132,6 +132,7 @@ def load():
     lib.ilqrb_destroy.argtypes = [H]
     lib.ilqrb_set_stream.argtypes = [H, C.c_void_p]
     lib.ilqrb_synchronize.argtypes = [H]
+    lib.ilqrb_chain_after_compute.argtypes = [H, H]
     lib.ilqrb_update_problems.argtypes = [H, c_double_p, c_double_p, C.c_int, c_double_p]
     lib.ilqrb_solve_recursive.argtypes = [H, c_double_p, C.POINTER(SolveOpts), C.POINTER(Result)]
     lib.ilqrb_solve_recursive_async.argtypes = [H, c_double_p, C.POINTER(SolveOpts), C.POINTER(Result)]

@@ -91,6 +91,9 @@ struct ilqrb_handle_s {
     cudaStream_t gstream[MAX_GROUPS] = {nullptr};
     cudaEvent_t ev_start = nullptr, ev_stagger[MAX_GROUPS] = {nullptr}, ev_done[MAX_GROUPS] = {nullptr};
     int ensure_groups(int G);
+    // recorded when the last solve's kernels are queued, before its device-to-host copies (ilqrb_chain_after_compute)
+    cudaEvent_t ev_compute[MAX_GROUPS + 1] = {nullptr};
+    int n_ev_compute = 0;
 
     template <class T>
     int alloc(T** p, size_t count) {

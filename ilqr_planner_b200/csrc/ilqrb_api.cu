@@ -218,6 +218,14 @@ int enqueue_download_range(ilqrb_handle h, const ilqrb_result* out, int b0, int 
 
 // out_async != nullptr: the caller wants the results in host buffers; the fast path then sends each problem group's
 // results as soon as that group has finished (sets h->downloaded).
+// marks "the solve's kernels are queued on st" for ilqrb_chain_after_compute (slot i of the handle's compute events)
+static int record_compute_done(ilqrb_handle h, int i, cudaStream_t st) {
+    if (!h->ev_compute[i]) CU(cudaEventCreateWithFlags(&h->ev_compute[i], cudaEventDisableTiming));
+    CU(cudaEventRecord(h->ev_compute[i], st));
+    if (h->n_ev_compute < i + 1) h->n_ev_compute = i + 1;
+    return 0;
+}
+
 int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solve_opts* opts, const ilqrb_result* out_async = nullptr) {
     if (!opts) return fail(ILQRB_EINVAL, "null opts");
     if (opts->nb_iter < 0) return fail(ILQRB_EINVAL, "nb_iter < 0");
@@ -293,16 +301,19 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
         // device-resident results: fast_n1_default_groups (launch_fused1.cu); time path: about three groups per two waves of 16 warps per SM
         const int wave = 148 * 16;
         const int g_dev = fast1 ? fast_n1_default_groups(h, B) : std::min(8, std::max(3, (3 * B + 2 * wave - 1) / (2 * wave)));
-        // host outputs on the column-per-lane backward path (C2; profiles/r2o_e2e_groups.txt): a blocking call 360 / 354-377 / 353 / 330 k
-        // solves/s with 1 / 2 / 3 / 5 groups; the streaming form with gains 504 / 433 / 542 / 552 k with 1 / 2 / 3 / 5, without gains 650 / 638-665 / 636 / 627 k
+        // host outputs on the column-per-lane backward path (C2; profiles/r2o_e2e_groups.txt, r2p_e2e_chain.txt): a blocking call 352 / 371 /
+        // 360 / 349 k solves/s with 1 / 2 / 3 / 5 groups; two streaming handles half a cycle apart 593 / 611 / 602 / 576 k with gains,
+        // 660 / 666 / 632 / 636 k without
         const bool col = fast1 && fast_n1_col_path(h);
-        const int g_host = h->streaming ? ((col && out_async && !out_async->K) ? 2 : 5) : (col ? 2 : 8);
+        const int g_host = col ? 2 : (h->streaming ? 5 : 8);
         int G = h->prof ? 1 : (int)env_uint("ILQRB_GROUPS", out_async ? g_host : g_dev);
         if (G > ilqrb_handle_s::MAX_GROUPS) G = ilqrb_handle_s::MAX_GROUPS;
         if (G < 1 || B < 64 * G) G = 1;
         if (G == 1) {
             for (int it = 0; it < opts->nb_iter; it++)
                 if ((rc = iteration(0, B, h->stream, it, nullptr))) return rc;
+            h->n_ev_compute = 0;
+            if ((rc = record_compute_done(h, 0, h->stream))) return rc;
             if (out_async && opts->nb_iter > 0) {  // the copies are queued behind the solve: the streaming entry point returns without waiting
                 h->last_nb_iter = opts->nb_iter;
                 if ((rc = enqueue_download_range(h, out_async, 0, B, std::max(opts->nb_iter, 1), h->stream))) return rc;
@@ -327,7 +338,9 @@ int run_recursive_like(ilqrb_handle h, const ilqrb_al_desc* al, const ilqrb_solv
                 }
             }
             h->last_nb_iter = opts->nb_iter;
+            h->n_ev_compute = 0;
             for (int gi = 0; gi < G; gi++) {
+                if ((rc = record_compute_done(h, gi, h->gstream[gi]))) return rc;
                 if (out_async) {
                     const int b0 = (int)((long long)B * gi / G), b1 = (int)((long long)B * (gi + 1) / G);
                     if ((rc = enqueue_download_range(h, out_async, b0, b1 - b0, std::max(opts->nb_iter, 1), h->gstream[gi]))) return rc;
@@ -566,6 +579,8 @@ int ilqrb_destroy(ilqrb_handle h) {
         cudaEventDestroy(h->ev_done[gi]);
     }
     if (h->ev_start) cudaEventDestroy(h->ev_start);
+    for (auto e : h->ev_compute)
+        if (e) cudaEventDestroy(e);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return 0;
@@ -577,6 +592,19 @@ int ilqrb_set_stream(ilqrb_handle h, void* s) {
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     h->stream = (cudaStream_t)s;
     h->own_stream = false;
+    return 0;
+}
+
+int ilqrb_chain_after_compute(ilqrb_handle next, ilqrb_handle prev) {
+    if (!next || !prev) return fail(ILQRB_EINVAL, "null handle");
+    CU(cudaSetDevice(next->device));
+    if (prev->n_ev_compute == 0) {  // no solve on the fast paths yet: order behind everything prev has queued
+        if (!prev->ev_compute[0]) CU(cudaEventCreateWithFlags(&prev->ev_compute[0], cudaEventDisableTiming));
+        CU(cudaEventRecord(prev->ev_compute[0], prev->stream));
+        CU(cudaStreamWaitEvent(next->stream, prev->ev_compute[0], 0));
+        return 0;
+    }
+    for (int i = 0; i < prev->n_ev_compute; i++) CU(cudaStreamWaitEvent(next->stream, prev->ev_compute[i], 0));
     return 0;
 }
 

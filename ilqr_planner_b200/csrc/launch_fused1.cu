@@ -193,8 +193,9 @@ int fwd_mode() {
 // Problem groups (streams) for device-resident results.  The warp-per-problem backward kernel fills the SMs' warp slots and gains
 // from sharing them with another group's forward pass: about three groups per two waves of the forward kernel, at least 3 (C2
 // B = 4096 / 8192 / 16384 -> 3 / 3 / 6, C5 B = 8192 -> 7).  The column-per-lane kernel holds 4 problems per warp and is bound by latency
-// below ~8 warps per SM: it wants the whole batch in one launch (profiles/r2f_backward_col_groups.txt: B = 4096: 636 / 620 / 589 / 572 k
-// solves/s with 1 / 2 / 3 / 4 groups; 8192: flat; 16384: 768 / 778 / 750 / 744 k).
+// below ~8 warps per SM: it wants large launches (B = 4096: 636 / 620 / 589 / 572 k solves/s with 1 / 2 / 3 / 4 groups in
+// profiles/r2f_backward_col_groups.txt, 673 / 686 / 625 / 581 k with 1 / 2 / 3 / 5 in r2p_e2e_chain.txt on another box; 8192: flat; 16384: 768 /
+// 778 / 750 / 744 k): two groups from 4096 problems, one per 8192 beyond.
 bool fast_n1_col_path(ilqrb_handle h) {
     const StateBlocks sb = find_state_blocks(h->hp);
     if (sb.nblk >= 2) {
@@ -205,7 +206,7 @@ bool fast_n1_col_path(ilqrb_handle h) {
     return col_backward_applies(h->hp, false);
 }
 int fast_n1_default_groups(ilqrb_handle h, int B) {
-    if (col_backward_applies(h->hp, false) && find_state_blocks(h->hp).nblk < 2) return std::max(1, B / 8192);
+    if (col_backward_applies(h->hp, false) && find_state_blocks(h->hp).nblk < 2) return B < 4096 ? 1 : std::max(2, B / 8192);
     const int wave = fast_n1_wave(h);
     return std::min(8, std::max(3, (3 * B + 2 * wave - 1) / (2 * wave)));
 }

@@ -123,6 +123,10 @@ class Handle:
     def synchronize(self):
         cabi.check(self.lib.ilqrb_synchronize(self.h))
 
+    def chain_after_compute(self, prev):
+        """whatever this handle queues next starts when `prev`'s last solve has left the SMs (its result copies may still run): ilqrb_chain_after_compute"""
+        cabi.check(self.lib.ilqrb_chain_after_compute(self.h, prev.h))
+
     # ---- test hooks
     def rollout(self, U):
         pb = self.pb

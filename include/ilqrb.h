@@ -226,6 +226,12 @@ int ilqrb_solve_recursive(ilqrb_handle h, const double* U0, const ilqrb_solve_op
  * batches through two handles alternately overlaps one batch's result transfer (PCIe) with the next batch's solve.
  * Systems on the generic path (time state, AL) complete synchronously. */
 int ilqrb_solve_recursive_async(ilqrb_handle h, const double* U0, const ilqrb_solve_opts* opts, ilqrb_result* out);
+/* Pipelining two (or more) handles: whatever is queued on `next` after this call starts once the KERNELS of prev's last solve
+ * have finished — prev's device-to-host copies may still be in flight.  Called before each ilqrb_solve_recursive_async(next, ...)
+ * it keeps the solves back to back on the SMs while every batch's result transfer overlaps the following batch's solve
+ * (without it two handles started together stay in phase: they compute together, then copy together).  No reference
+ * counterpart (the reference has no device). */
+int ilqrb_chain_after_compute(ilqrb_handle next, ilqrb_handle prev);
 /* AL_ILQR::solve (AL-ILQR.cpp:50-232). */
 int ilqrb_solve_al(ilqrb_handle h, const double* U0, const ilqrb_al_desc* al, const ilqrb_solve_opts* opts, ilqrb_result* out);
 /* BatchILQR::solve (BatchILQR.cpp:110-173) and BatchILQRCP::solve (BatchILQRCP.cpp:109-174): u0 [B][N]. */

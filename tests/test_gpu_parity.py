@@ -570,6 +570,16 @@ def test_async_solve_on_two_handles_matches_blocking_call():
         for k in range(2):
             hs[k].synchronize()
             assert np.array_equal(outs[k].K, want[k].K) and np.array_equal(outs[k].cost_hist, want[k].cost_hist)
+        # ilqrb_chain_after_compute: each handle's solve ordered behind the other's kernels (its copies still in flight)
+        for r in range(3):
+            for k in range(2):
+                hs[k].synchronize()
+                outs[k].K[:] = np.nan
+                hs[k].chain_after_compute(hs[1 - k])
+                hs[k].solve_recursive_async(u0, 5, True, False, out=outs[k])
+        for k in range(2):
+            hs[k].synchronize()
+            assert np.array_equal(outs[k].K, want[k].K) and np.array_equal(outs[k].X, want[k].X) and np.array_equal(outs[k].cost, want[k].cost)
     finally:
         for h in hs:
             h.close()
