@@ -797,7 +797,7 @@ __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work&
             if (kp < 0) continue;
             const int off = tk.joint_offset;
             double fx[7], Jc[RR], res[RR];
-            lean_task_eval(P, tk, [&](int j) { return xk[off + j] + alpha * dxk[off + j]; }, -1, fx, Jc);
+            lean_task_eval<RR>(P, tk, [&](int j) { return xk[off + j] + alpha * dxk[off + j]; }, -1, fx, Jc);
             double cst = lean_task_cost(P, tk, b, kp, fx, res);
             if (k < H - 1) {
                 double uRu = 0.0, uo[NX], ud[NX];  // compile-time bounds: the loads of a row are in flight together
@@ -886,7 +886,7 @@ __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work&
                     res[a] = 0.0;
                     Jc[a] = 0.0;
                 }
-                lean_task_eval(P, tk, [&](int j) { return xk[off + j]; }, cj, fx, Jc);
+                lean_task_eval<RR>(P, tk, [&](int j) { return xk[off + j]; }, cj, fx, Jc);
                 if (kp >= 0) {
                     const double* tg = tk.kp_target + ((size_t)b * tk.n_keypoints + kp) * ILQRB_KP_STRIDE;
                     task_residual(P, tk, fx, tg, res, task_deadzone(tk, kp));

@@ -102,16 +102,19 @@ __device__ __forceinline__ void lean_kdl_fk(const ilqrb_segment* __restrict__ se
 // Task vector fx = [p, quat] (POSITION: [p]) of task tk and, if cj >= 0, column cj (robot-local joint index) of its
 // 6 x dof geometric Jacobian (rows v then w; POSITION uses the v rows).  nb_deriv == 1 only (no velocity part).
 // Joint-space tasks (ILQRB_TASK_JOINT, first order): fx = q and column cj of the identity — the caller then provides 7 rows for Jc.
-template <class QF>
+// RR: rows of Jc the caller provides; the joint-space branch exists in the RR = 7 instantiations only (systems with a joint-space task).
+template <int RR = 6, class QF>
 __device__ __forceinline__ void lean_task_eval(const DevProblem& P, const DevTask& tk, QF q, int cj, double* fx, double* Jc) {
     const DevRobot& rb = P.robots[tk.robot];
-    if (tk.kind == ILQRB_TASK_JOINT) {  // JointSpacePlannerSys.cpp:77-81
+    if constexpr (RR >= 7) {
+        if (tk.kind == ILQRB_TASK_JOINT) {  // JointSpacePlannerSys.cpp:77-81
 #pragma unroll
-        for (int a = 0; a < 7; a++) {
-            fx[a] = (a < rb.dof) ? q(a) : 0.0;
-            Jc[a] = (a == cj) ? 1.0 : 0.0;
+            for (int a = 0; a < 7; a++) {
+                fx[a] = (a < rb.dof) ? q(a) : 0.0;
+                Jc[a] = (a == cj) ? 1.0 : 0.0;
+            }
+            return;
         }
-        return;
     }
 #pragma unroll
     for (int a = 0; a < 6; a++) Jc[a] = 0.0;
