@@ -835,25 +835,44 @@ __device__ __forceinline__ bool forward_n1_body(const DevProblem& P, const Work&
     const double alpha = alpha_of(sel);
 
     // ---- phase E: accept.  u += alpha du ; x re-integrated from u with the reference's operation order
-    //      (SimulationInterface.cpp:19-31).  Lane i < dof walks the horizon for joint i, loads batched eight steps deep.
-    if (lane < dof) {
-        double xq = P.q0[(size_t)b * dof + lane];
+    //      (SimulationInterface.cpp:19-31).  E1, all lanes: the new controls of every (step, joint) pair, coalesced, and the increment
+    //      dt u' + dt^2/2 * 0 left in the deviation's slot.  E2, lane i < dof: joint i walks the horizon, one load and one add per step.
+    {
         const double hdt2 = __dmul_rn(dt, dt) / 2;
-        for (int k0 = 0; k0 < H - 1; k0 += 8) {
-            double uu[8], dd[8];  // both operand streams loaded ahead of the serial chain (SPLIT: the deviation lives in global memory)
+        const double zterm = __dmul_rn(hdt2, 0.0);
+        const int tot = (H - 1) * ms;
+        for (int e0 = 0; e0 < tot; e0 += 128) {
+            double uu[4], dd[4];
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
-                uu[j] = (k0 + j < H - 1) ? Ub[(size_t)(k0 + j) * ms + lane] : 0.0;
-                dd[j] = (k0 + j < H - 1) ? sDU[(k0 + j) * ms + lane] : 0.0;
+            for (int r = 0; r < 4; r++) {
+                const int idx = e0 + 32 * r + lane;
+                uu[r] = idx < tot ? Ub[idx] : 0.0;
+                dd[r] = idx < tot ? sDU[idx] : 0.0;
             }
 #pragma unroll
-            for (int j = 0; j < 8; j++)
-                if (k0 + j < H - 1) {
-                    const double un = uu[j] + alpha * dd[j];
-                    Ub[(size_t)(k0 + j) * ms + lane] = un;
-                    xq = __dadd_rn(xq, __dadd_rn(__dmul_rn(dt, un), __dmul_rn(hdt2, 0.0)));
-                    Xb[(size_t)(k0 + j + 1) * ns + lane] = xq;
+            for (int r = 0; r < 4; r++) {
+                const int idx = e0 + 32 * r + lane;
+                if (idx < tot) {
+                    const double un = uu[r] + alpha * dd[r];
+                    Ub[idx] = un;
+                    sDU[idx] = __dadd_rn(__dmul_rn(dt, un), zterm);
                 }
+            }
+        }
+        __syncwarp();
+        if (lane < dof) {
+            double xq = P.q0[(size_t)b * dof + lane];
+            for (int k0 = 0; k0 < H - 1; k0 += 8) {
+                double inc[8];
+#pragma unroll
+                for (int j = 0; j < 8; j++) inc[j] = (k0 + j < H - 1) ? sDU[(k0 + j) * ms + lane] : 0.0;
+#pragma unroll
+                for (int j = 0; j < 8; j++)
+                    if (k0 + j < H - 1) {
+                        xq = __dadd_rn(xq, inc[j]);
+                        Xb[(size_t)(k0 + j + 1) * ns + lane] = xq;
+                    }
+            }
         }
     }
     __syncwarp();

@@ -28,15 +28,7 @@ with Handle(pb) as h:
     pr = h.profile()
     print("B %d ms %.3f solves/s %.0f backward %.3f forward %.3f" % (B, dt * 1e3, pb.batch / dt, pr["riccati_backward"][0], pr["linesearch_rollout"][0]))
 PY
-sed -e 's/synth.config2(batch=B, horizon=100)/synth.config5(batch=B)/' /tmp/c2_bench.py > /tmp/c5_bench.py
 for B in 4096 8192; do
-  echo "c2 col"; timeout 300 python /tmp/c2_bench.py $B
+  echo "c2"; timeout 300 python /tmp/c2_bench.py $B
 done > gpurun_out/${TAG}_ab.txt 2>&1
-for B in 8192; do
-  echo "c5 col groups=default"; timeout 300 python /tmp/c5_bench.py $B
-  for G in 1 2 3 5 7; do
-    echo "c5 col groups=$G"; ILQRB_GROUPS=$G timeout 300 python /tmp/c5_bench.py $B
-  done
-  echo "c5 warp"; ILQRB_BWD=warp timeout 300 python /tmp/c5_bench.py $B
-done >> gpurun_out/${TAG}_ab.txt 2>&1
 cat gpurun_out/${TAG}_ab.txt
