@@ -46,11 +46,14 @@ __device__ __forceinline__ void st8(double* p, const double (&o)[8]) {
 // a live problem and store nothing).  BLK = false: the problem's state is the 7 joints (row stride 8 doubles: 16-byte accesses).
 // BLK = true: the group handles the diagonal block [off, off + 7) of a problem whose tasks touch disjoint joint ranges (composite
 // robots, C5; see backward_n1_body): strides are those of the full state.
+// N < 7 (BLK = false): the same lane groups of 8 with lanes N + 1 .. 7 idle (their columns stay zero); global rows are then narrower than
+// 8 doubles and take the scalar accesses of the block form.
 template <int N, bool BLK>
 __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const Work& W, int b, bool live, int off, int lane, double* wsmem) {
-    static_assert(N == 7, "8 x 8 augmented matrices");
+    static_assert(N >= 1 && N <= 7, "8 x 8 augmented matrices");
     constexpr unsigned FULL = 0xffffffffu;
-    const int nf = BLK ? P.n : N, ns = BLK ? ((nf + 1) & ~1) : 8, ms = ns;
+    constexpr bool VEC = !BLK && N == 7;  // 16-byte accesses to the rows of U and d
+    const int nf = BLK ? P.n : N, ns = (nf + 1) & ~1, ms = ns;
     const int sub = lane >> 3, j = lane & 7;
     const int H = P.H;
     const double dt = 1.0 * P.dt;  // B = Identity * dt
@@ -114,7 +117,7 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
         const double* lx = W.LX + ((size_t)b * S_kp + s) * nf + off;
         const double* lxx = W.LXX + ((size_t)b * S_kp + s) * nf * nf + (size_t)off * nf + off;
 #pragma unroll
-        for (int i = 0; i < N; i++) e[i] += (j < N) ? lxx[i * nf + j] : lx[i];
+        for (int i = 0; i < N; i++) e[i] += (j < N) ? lxx[i * nf + j] : (j == N ? lx[i] : 0.0);
     };
 
     // terminal: P = cost_F_xx, p = cost_F_x   (ILQRRecursive.cpp:69-71)
@@ -128,17 +131,17 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
         sp--;
         next_kp = sp >= 0 ? P.kp_steps[sp] : -1;
     }
-    if (l0 >= 0) add_limits(Pc, Xb[(size_t)(H - 1) * ns + j]);
+    if (l0 >= 0) add_limits(Pc, j < N ? Xb[(size_t)(H - 1) * ns + j] : 0.0);
     st8(sP + j * BwdColSmem::PCS, Pc);
     auto load_u = [&](int k, double (&o)[8]) {  // the controls enter the vector column only
-        if constexpr (BLK) {
+        if constexpr (!VEC) {
 #pragma unroll
             for (int i = 0; i < N; i++) o[i] = (j == N) ? Ub[(size_t)k * ms + i] : 0.0;
         } else ld8(Ub + (size_t)k * ms, o);
     };
-    double un[8], xn = 0.0;
+    double un[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, xn = 0.0;
     load_u(H - 2, un);
-    if (l0 >= 0) xn = Xb[(size_t)(H - 2) * ns + j];
+    if (l0 >= 0 && j < N) xn = Xb[(size_t)(H - 2) * ns + j];
     bool ok = true;
     double* Kg = W.K + ((size_t)b * (H - 1) + (H - 2)) * nf * ns + (size_t)off * ns + off;  // walks backwards with k
     double* dg = W.d + ((size_t)b * (H - 1) + (H - 2)) * ms + off;
@@ -151,7 +154,7 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
         const double x = xn;
         if (k > 0) {  // prefetch the next step's controls / state
             load_u(k - 1, un);
-            if (l0 >= 0) xn = Xb[(size_t)(k - 1) * ns + j];
+            if (l0 >= 0 && j < N) xn = Xb[(size_t)(k - 1) * ns + j];
         }
         // [Qux|Qu] = [0 | R u] + (B^T [P|p]) A_aug ;  Quu = R + (B^T P) B ;  [Qxx|Qx] = [l_xx|l_x] + (A^T [P|p]) A_aug   ILQRRecursive.cpp:82-87
         double Qa[8], L[8], Rh[8], Qx[8];
@@ -200,7 +203,7 @@ __device__ __forceinline__ unsigned backward_n1_col(const DevProblem& P, const W
             for (int i = 0; i < N; i++)
                 if (j < N) Kg[i * ns + j] = Rh[i];  // the pad column stays as the solve's memset left it
             if (j == N) {
-                if constexpr (BLK) {
+                if constexpr (!VEC) {
 #pragma unroll
                     for (int i = 0; i < N; i++) dg[i] = Rh[i];
                 } else {
@@ -267,7 +270,7 @@ __global__ void __maxnreg__(200) k_backward_n1_col(const DevProblem* __restrict_
         if (((bad >> (8 * s)) & 0xffu) == 0 || b >= bend || W.done[b]) continue;
         if (lane == 0) atomicOr(W.status + b, ILQRB_ST_QUU_NOT_SPD);
         __syncwarp();
-        backward_n1_redo<1, N>(*Pp, W, b, lane, ws, 0, 0);
+        backward_n1_redo<1, (N == 7 ? 7 : 0)>(*Pp, W, b, lane, ws, 0, 0);
     }
 }
 

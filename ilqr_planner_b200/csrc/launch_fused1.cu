@@ -31,15 +31,14 @@ int launch_backward_n1_t(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
     return 0;
 }
 // four problems per warp, a column of the augmented matrices per lane (fused1_col.cuh); n = m = 7, at most one limit-carrying task
-template <int WARPS>
+template <int N>
 int launch_backward_n1_col_t(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
-    const size_t smem = (size_t)WARPS * BwdColSmem::PER_WARP * sizeof(double);
-    auto kern = k_backward_n1_col<7, WARPS>;
+    const size_t smem = (size_t)BwdColSmem::PER_WARP * sizeof(double);
+    auto kern = k_backward_n1_col<N, 1>;  // 1 / 2 / 4 warps per block measured alike
     static DynSmem attr;
     int rc = attr.ensure(kern, smem, h->device);
     if (rc) return rc;
-    const int warps = (nB + 3) / 4;
-    kern<<<(warps + WARPS - 1) / WARPS, 32 * WARPS, smem, st>>>(h->dp, h->W, b0, nB);
+    kern<<<(nB + 3) / 4, 32, smem, st>>>(h->dp, h->W, b0, nB);
     return 0;
 }
 int backward_form() {  // A/B switch: ILQRB_BWD = warp (one problem per warp, fused1.cuh) | col (four per warp, fused1_col.cuh; default)
@@ -51,7 +50,7 @@ int backward_form() {  // A/B switch: ILQRB_BWD = warp (one problem per warp, fu
 }
 // blocks: the state splits into diagonal blocks of 7 joints each (find_state_blocks), one group of lanes per block
 bool col_backward_applies(const DevProblem& P, bool blocks) {
-    if (backward_form() == 0 || P.n != P.m || (!blocks && P.n != 7)) return false;
+    if (backward_form() == 0 || P.n != P.m || (!blocks && (P.n < 2 || P.n > 7))) return false;
     for (int i = 0; i < P.n; i++) {  // a lane checks its state against ONE sub-system's limits
         int nlim = 0;
         for (int t = 0; t < P.n_tasks; t++) nlim += (P.tasks[t].limits_set && P.tasks[t].limit_weight[i] != 0) ? 1 : 0;
@@ -221,7 +220,16 @@ int launch_backward_n1(ilqrb_handle h, int b0, int nB, cudaStream_t st) {
         for (int i = 0; i < sb.nblk; i++) all7 = all7 && sb.size[i] == 7;
         if (all7 && col_backward_applies(h->hp, true)) rc = launch_backward_n1_col_blocks_t<1>(h, b0, nB, st, sb);
         else rc = all7 ? launch_backward_n1_blocks_t<7, 4, 7>(h, b0, nB, st, sb) : launch_backward_n1_blocks_t<0, 4, 7>(h, b0, nB, st, sb);
-    } else if (col_backward_applies(h->hp, false)) rc = launch_backward_n1_col_t<1>(h, b0, nB, st);  // 1 / 2 / 4 warps per block measured alike
+    } else if (col_backward_applies(h->hp, false)) {
+        switch (n) {
+            case 2: rc = launch_backward_n1_col_t<2>(h, b0, nB, st); break;
+            case 3: rc = launch_backward_n1_col_t<3>(h, b0, nB, st); break;
+            case 4: rc = launch_backward_n1_col_t<4>(h, b0, nB, st); break;
+            case 5: rc = launch_backward_n1_col_t<5>(h, b0, nB, st); break;
+            case 6: rc = launch_backward_n1_col_t<6>(h, b0, nB, st); break;
+            default: rc = launch_backward_n1_col_t<7>(h, b0, nB, st); break;
+        }
+    }
     else if (n == 7) rc = launch_backward_n1_t<1, 7, 4, 7>(h, b0, nB, st);
     else if (n == 14) rc = launch_backward_n1_t<2, 14, 4, 2>(h, b0, nB, st);
     else if (n + 1 <= 8) rc = launch_backward_n1_t<1, 0, 4, 7>(h, b0, nB, st);
