@@ -136,6 +136,49 @@ def test_config5_dual_arm(oracle_lib):
     _check_recursive(synth.config5(batch=16), None, 6, oracle_lib)
 
 
+@pytest.mark.parametrize("dof,batch", [(2, 9), (3, 16), (4, 5), (5, 11), (6, 16), (7, 13)])
+def test_column_per_lane_backward_pass_sizes_and_ragged_batches(oracle_lib, dof, batch):
+    """k_backward_n1_col<N> (four problems per warp, one column of the augmented matrices per lane) for every state size it is
+    instantiated for, on batches that do not fill the last warp (idle lane groups shadow a live problem and must store nothing),
+    without limits and with soft joint limits that the initial controls violate"""
+    from ilqr_planner_b200 import synth
+    _check_recursive(synth.config5_uneven(batch=batch, dofs=(dof,), limits=False), None, 5, oracle_lib)
+    pb = synth.config5_uneven(batch=batch, dofs=(dof,), limits=True)
+    u0 = np.full((pb.batch, pb.horizon - 1, pb.m), 0.3)
+    u0[:, :, ::2] *= -1
+    _check_recursive(pb, u0, 2, oracle_lib)
+
+
+def test_column_per_lane_and_warp_per_problem_backward_kernels_agree():
+    """ILQRB_BWD=warp (read once per process, hence the subprocess) selects the warp-per-problem kernel: the two forms of the backward
+    pass return the same solve up to rounding, on a batch that is not a multiple of 4"""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r)\n"
+        "from ilqr_planner_b200 import synth\n"
+        "from ilqr_planner_b200.solver import Handle\n"
+        "pb = synth.config2(batch=70, horizon=60)\n"
+        "with Handle(pb) as h:\n"
+        "    o = h.solve_recursive(None, 4, True, False)\n"
+        "np.savez(sys.argv[1], X=o.X, U=o.U, K=o.K, cost=o.cost, alpha=o.alpha_hist)\n" % root)
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        outs = {}
+        for form in ("col", "warp"):
+            f = os.path.join(td, form + ".npz")
+            env = dict(os.environ, ILQRB_BWD=form)
+            subprocess.run([sys.executable, "-c", code, f], check=True, env=env, timeout=600)
+            outs[form] = dict(np.load(f))
+    a, b = outs["col"], outs["warp"]
+    same = np.all((a["alpha"] == b["alpha"]) | (np.isnan(a["alpha"]) & np.isnan(b["alpha"])), axis=1)  # a numerical tie may part two sequences
+    assert same.sum() >= 0.9 * same.size
+    for k in ("X", "U", "K", "cost"):
+        assert rel(a[k][same], b[k][same]) < 1e-8, (k, rel(a[k][same], b[k][same]))
+
+
 def test_composite_uneven_blocks(oracle_lib):
     """block-diagonal backward pass (one warp per problem and per group of joints no task couples) with runtime block
     sizes and an odd block offset; then with soft joint limits that the initial controls violate over most of the horizon.
