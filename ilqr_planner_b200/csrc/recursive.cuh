@@ -669,6 +669,17 @@ __global__ void __launch_bounds__(128) k_final_fx(const DevProblem* __restrict__
     double* out = fX + (size_t)idx * P.nt;
     for (int t = 0; t < P.n_tasks; t++) {
         const DevTask& tk = P.tasks[t];
+        if (P.nb_deriv == 1 && P.sys_kind != ILQRB_SYS_POSITION && tk.kind == ILQRB_TASK_POSE && P.robots[tk.robot].kind == ILQRB_ROBOT_KDL) {
+            // first-order end-effector tasks: pose only (the sweep of the forward kernels' cost evaluation, no Jacobian)
+            double fx[7], Jc[6];
+            const double* qb = xs + tk.joint_offset;
+            lean_task_eval(P, tk, [&](int j) { return qb[j]; }, -1, fx, Jc);
+            double* o = out + tk.fx_off;
+#pragma unroll
+            for (int i = 0; i < 7; i++) o[i] = fx[i];
+            if (P.time) o[7] = xs[n - 1];
+            continue;
+        }
         EEState e;
         task_ee(P, tk, xs, dqs, e);
         task_fx(P, tk, e, P.time ? xs[n - 1] : 0.0, out + tk.fx_off);
