@@ -1,4 +1,5 @@
-// fused1_col.cuh — backward Riccati pass of the single-integrator fast path with FOUR problems per warp (n = m = 7).
+// fused1_col.cuh — backward Riccati pass of the single-integrator fast path with FOUR problems per warp (n = m <= 7, and per 7-joint
+// block of composite robots).
 //
 // k_backward_n1 (fused1.cuh) gives a whole warp to one problem: the 8x8 augmented matrices sit in the DMMA accumulator layout, two
 // elements per lane, and the in-register Gauss-Jordan spends ~37 instructions per stage on lane-role bookkeeping for 4 useful FP64
@@ -11,7 +12,7 @@
 //   * products C = A B take column k of A as a shared-memory broadcast and B[k][j] from the lane's own registers: 8 FMAs per 16-byte
 //     pair of loads.  Quu [K|d] is formed as dt^2 (P [K|d]) + R o [K|d], so one product P [K|d] serves both the bracket
 //     M = Quu [K|d] + [Qux|Qu] and Qxu [K|d] = dt P [K|d]; the second product is K^T M.            ILQRRecursive.cpp:82-94
-// ~150 instructions per problem and step, the same FP64 work.  Plain FMA chains in the reference's summation order; no tensor pipe
+// ~175 instructions per problem and step (ncu), the same FP64 work.  Plain FMA chains in the reference's summation order; no tensor pipe
 // (DMMA and DFMA peak at the same rate on B200: 37.0 against 36.1 TFLOP/s measured, bench.py `peaks_measured_here_tflops`).
 // A problem whose elimination meets a non-positive pivot is redone by the warp-per-problem pass with the pivoted inverse
 // (backward_n1_redo), like there.
