@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(128) k_stage_costs(const DevProblem* __restric
 #pragma unroll
         for (int i = 0; i < M; i++) u[i] = (i < P.m) ? Uk[i] : 0.0;
     }
-    W.Uc[(size_t)b * H + k] = stage_cost<N>(P, b, x, k < H - 1 ? u : nullptr, k);
+    W.Uc[(size_t)b * H + k] = lean_stage_cost<N>(P, b, x, k < H - 1 ? u : nullptr, k);  // the FK sweep the line search's candidate costs use
 }
 __global__ void __launch_bounds__(128) k_sum_costs(const DevProblem* __restrict__ Pp, Work W, int b0, int nB) {
     const int bl = blockIdx.x * blockDim.x + threadIdx.x;
